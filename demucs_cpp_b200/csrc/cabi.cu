@@ -1,0 +1,552 @@
+// extern "C" surface of libdemucs_b200.so (declared in include/demucs_b200.h).
+#include "model.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <cuda_fp16.h>
+
+namespace dmx
+{
+static thread_local std::string g_err;
+void set_error(const std::string &msg) { g_err = msg; }
+int num_segments(int64_t L, int shift);
+
+static float half_bits_to_float(uint16_t h)
+{
+    // IEEE binary16 -> binary32, exact (src/model_load.cpp:1092-1300 widens with Eigen::half)
+    const uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+    uint32_t exp = (h >> 10) & 0x1fu, man = h & 0x3ffu;
+    uint32_t bits;
+    if (exp == 0)
+    {
+        if (man == 0)
+            bits = sign;
+        else
+        {
+            int e = -1;
+            do
+            {
+                ++e;
+                man <<= 1;
+            } while (!(man & 0x400u));
+            man &= 0x3ffu;
+            bits = sign | ((uint32_t)(127 - 15 - e) << 23) | (man << 13);
+        }
+    }
+    else if (exp == 31)
+        bits = sign | 0x7f800000u | (man << 13);
+    else
+        bits = sign | ((exp + 127 - 15) << 23) | (man << 13);
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+}
+} // namespace dmx
+
+using namespace dmx;
+
+extern "C"
+{
+
+int dmx_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+        return 0;
+    return n;
+}
+
+const char *dmx_last_error(void) { return g_err.c_str(); }
+
+dmx_model *dmx_model_create(int arch, int device, int max_batch)
+{
+    if (arch != DMX_ARCH_HTDEMUCS_4S && arch != DMX_ARCH_HTDEMUCS_6S && arch != DMX_ARCH_HDEMUCS_V3)
+    {
+        set_error("dmx_model_create: unknown architecture");
+        return nullptr;
+    }
+    if (max_batch < 1)
+    {
+        set_error("dmx_model_create: max_batch must be >= 1");
+        return nullptr;
+    }
+    int n = dmx_device_count();
+    if (n <= 0)
+    {
+        set_error("dmx_model_create: no CUDA device (this library has no CPU fallback)");
+        return nullptr;
+    }
+    if (device < 0 || device >= n)
+    {
+        set_error("dmx_model_create: bad device index");
+        return nullptr;
+    }
+    dmx_model *m = new dmx_model();
+    m->arch = arch;
+    m->device = device;
+    m->maxB = max_batch;
+    return m;
+}
+
+int dmx_model_set_tensor(dmx_model *m, const char *name, const uint16_t *f16, const int32_t *ne, int n_dims)
+{
+    if (!m || !name || !f16 || n_dims < 0 || n_dims > 4)
+    {
+        set_error("dmx_model_set_tensor: bad argument");
+        return -1;
+    }
+    if (m->finalized)
+    {
+        set_error("dmx_model_set_tensor: model already finalized");
+        return -1;
+    }
+    HostTensor t;
+    size_t n = 1;
+    for (int i = 0; i < n_dims; ++i)
+    {
+        if (ne[i] <= 0)
+        {
+            set_error("dmx_model_set_tensor: bad shape");
+            return -1;
+        }
+        t.shape.push_back(ne[i]);
+        n *= (size_t)ne[i];
+    }
+    t.data.resize(n);
+    for (size_t i = 0; i < n; ++i)
+        t.data[i] = half_bits_to_float(f16[i]);
+    m->host[name] = std::move(t);
+    return 0;
+}
+
+int dmx_model_finalize(dmx_model *m)
+{
+    if (!m)
+    {
+        set_error("dmx_model_finalize: null model");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    return model_finalize(m);
+}
+
+dmx_model *dmx_model_load_file(const char *path, int device, int max_batch)
+{
+    FILE *f = fopen(path, "rb");
+    if (!f)
+    {
+        set_error(std::string("dmx_model_load_file: cannot open ") + path);
+        return nullptr;
+    }
+    uint32_t magic = 0;
+    if (fread(&magic, 4, 1, f) != 1)
+    {
+        fclose(f);
+        set_error("dmx_model_load_file: short file");
+        return nullptr;
+    }
+    int arch = 0;
+    if (magic == 0x646d6334u)
+        arch = DMX_ARCH_HTDEMUCS_4S;
+    else if (magic == 0x646d6336u)
+        arch = DMX_ARCH_HTDEMUCS_6S;
+    else if (magic == 0x646d6333u)
+        arch = DMX_ARCH_HDEMUCS_V3;
+    else
+    {
+        fclose(f);
+        set_error("dmx_model_load_file: invalid model data (bad magic)");
+        return nullptr;
+    }
+    dmx_model *m = dmx_model_create(arch, device, max_batch);
+    if (!m)
+    {
+        fclose(f);
+        return nullptr;
+    }
+    std::vector<uint16_t> buf;
+    std::vector<char> name;
+    for (;;)
+    {
+        int32_t hdr[2];
+        if (fread(hdr, 4, 2, f) != 2)
+            break; // EOF (src/model_load.cpp:144-147)
+        const int n_dims = hdr[0], name_len = hdr[1];
+        if (n_dims < 0 || n_dims > 4 || name_len <= 0 || name_len > 4096)
+        {
+            set_error("dmx_model_load_file: corrupt tensor header");
+            goto fail;
+        }
+        int32_t ne[4] = {1, 1, 1, 1};
+        if (n_dims && fread(ne, 4, n_dims, f) != (size_t)n_dims)
+        {
+            set_error("dmx_model_load_file: truncated tensor header");
+            goto fail;
+        }
+        name.assign(name_len + 1, 0);
+        if (fread(name.data(), 1, name_len, f) != (size_t)name_len)
+        {
+            set_error("dmx_model_load_file: truncated tensor name");
+            goto fail;
+        }
+        size_t n = 1;
+        for (int i = 0; i < n_dims; ++i)
+            n *= (size_t)(ne[i] > 0 ? ne[i] : 0);
+        buf.resize(n);
+        if (n == 0 || fread(buf.data(), 2, n, f) != n)
+        {
+            set_error(std::string("dmx_model_load_file: truncated tensor data for ") + name.data());
+            goto fail;
+        }
+        if (dmx_model_set_tensor(m, name.data(), buf.data(), ne, n_dims))
+            goto fail;
+    }
+    fclose(f);
+    f = nullptr;
+    if (dmx_model_finalize(m))
+    {
+        dmx_model_free(m);
+        return nullptr;
+    }
+    return m;
+fail:
+    if (f)
+        fclose(f);
+    dmx_model_free(m);
+    return nullptr;
+}
+
+void dmx_model_free(dmx_model *m)
+{
+    if (!m)
+        return;
+    if (m->finalized || !m->allocs.empty())
+    {
+        cudaSetDevice(m->device);
+        if (m->stream)
+            cudaStreamSynchronize(m->stream);
+        for (void *p : m->allocs)
+            cudaFree(p);
+        if (m->d_audio)
+            cudaFree(m->d_audio);
+        if (m->d_y)
+            cudaFree(m->d_y);
+        if (m->d_out)
+            cudaFree(m->d_out);
+        if (m->stream)
+            cudaStreamDestroy(m->stream);
+    }
+    delete m;
+}
+
+int dmx_model_arch(const dmx_model *m) { return m ? m->arch : -1; }
+int dmx_model_sources(const dmx_model *m) { return m ? (m->arch == DMX_ARCH_HTDEMUCS_6S ? 6 : 4) : -1; }
+int dmx_model_max_batch(const dmx_model *m) { return m ? m->maxB : -1; }
+int64_t dmx_launch_count(const dmx_model *m) { return m ? m->launches : -1; }
+
+static const char *const kProfNames[PC_COUNT] = {"stft",      "istft",      "istft_ola",        "pointwise", "gemm_conv",
+                                                 "gemm_dconv", "gemm_transformer", "attention", "track"};
+
+int dmx_profile_classes(void) { return PC_COUNT; }
+
+const char *dmx_profile_class_name(int cls) { return (cls >= 0 && cls < PC_COUNT) ? kProfNames[cls] : ""; }
+
+int dmx_profile_begin(dmx_model *m)
+{
+    if (!m)
+    {
+        set_error("dmx_profile_begin: null model");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    m->prof.on = true;
+    m->prof.used = 0;
+    m->prof.recs.clear();
+    for (int i = 0; i < PC_COUNT; ++i)
+        m->prof.flops[i] = m->prof.bytes[i] = 0.0;
+    return 0;
+}
+
+int dmx_profile_end(dmx_model *m, double *ms, int64_t *launches, double *flops, double *bytes)
+{
+    if (!m)
+    {
+        set_error("dmx_profile_end: null model");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    m->prof.on = false;
+    DMX_CUDA(cudaSetDevice(m->device));
+    DMX_CUDA(cudaStreamSynchronize(m->stream));
+    for (int i = 0; i < PC_COUNT; ++i)
+    {
+        if (ms)
+            ms[i] = 0.0;
+        if (launches)
+            launches[i] = 0;
+        if (flops)
+            flops[i] = m->prof.flops[i];
+        if (bytes)
+            bytes[i] = m->prof.bytes[i];
+    }
+    for (const ProfRec &r : m->prof.recs)
+    {
+        float t = 0.f;
+        DMX_CUDA(cudaEventElapsedTime(&t, r.e0, r.e1));
+        if (ms)
+            ms[r.cls] += (double)t;
+        if (launches)
+            launches[r.cls] += 1;
+    }
+    m->prof.recs.clear();
+    m->prof.used = 0;
+    return 0;
+}
+
+int dmx_model_set_precision(dmx_model *m, int precision)
+{
+    if (!m || (precision != DMX_PRECISION_FP32 && precision != DMX_PRECISION_BF16))
+    {
+        set_error("dmx_model_set_precision: bad argument");
+        return -1;
+    }
+    m->precision = precision;
+    return 0;
+}
+
+int dmx_num_segments(int64_t n_frames, int shift_offset) { return num_segments(n_frames, shift_offset); }
+
+static int grow(float **p, size_t *cap, size_t n)
+{
+    if (*cap >= n)
+        return 0;
+    if (*p)
+        DMX_CUDA(cudaFree(*p));
+    *p = nullptr;
+    *cap = 0;
+    DMX_CUDA(cudaMalloc(reinterpret_cast<void **>(p), n * sizeof(float)));
+    *cap = n;
+    return 0;
+}
+
+int dmx_separate_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset, float *d_out)
+{
+    if (!m || !d_audio_lr || !d_out)
+    {
+        set_error("dmx_separate_device: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_separate_device: model not finalized");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    return track_separate(m, d_audio_lr, n_frames, shift_offset, d_out, nullptr, nullptr);
+}
+
+int dmx_forward_shard_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset, int rank,
+                             int world, float *d_y)
+{
+    if (!m || !d_audio_lr || !d_y)
+    {
+        set_error("dmx_forward_shard_device: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_forward_shard_device: model not finalized");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    return track_forward_shard(m, d_audio_lr, n_frames, shift_offset, rank, world, d_y, nullptr, nullptr);
+}
+
+int dmx_overlap_add_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset,
+                           const float *d_y_all, int world, float *d_out)
+{
+    if (!m || !d_audio_lr || !d_y_all || !d_out)
+    {
+        set_error("dmx_overlap_add_device: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_overlap_add_device: model not finalized");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    return track_overlap_add(m, d_audio_lr, n_frames, shift_offset, d_y_all, world, d_out);
+}
+
+double dmx_last_device_ms(dmx_model *m)
+{
+    if (!m || !m->ev0 || !m->ev1)
+        return -1.0;
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, m->ev0, m->ev1) != cudaSuccess)
+        return -1.0;
+    return (double)t;
+}
+
+int dmx_separate(dmx_model *m, const float *audio_lr, int64_t n_frames, int shift_offset, float *out,
+                 dmx_progress_fn cb, void *user)
+{
+    if (!m || !audio_lr || !out)
+    {
+        set_error("dmx_separate: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_separate: model not finalized");
+        return -1;
+    }
+    if (n_frames < 2)
+    {
+        set_error("dmx_separate: track too short");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    const size_t S = (size_t)m->S;
+    if (grow(&m->d_audio, &m->cap_audio, (size_t)n_frames * 2) || grow(&m->d_out, &m->cap_out, S * 2 * (size_t)n_frames))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(m->d_audio, audio_lr, (size_t)n_frames * 2 * sizeof(float), cudaMemcpyHostToDevice,
+                             m->stream));
+    if (track_separate(m, m->d_audio, n_frames, shift_offset, m->d_out, cb, user))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(out, m->d_out, S * 2 * (size_t)n_frames * sizeof(float), cudaMemcpyDeviceToHost,
+                             m->stream));
+    DMX_CUDA(cudaStreamSynchronize(m->stream));
+    return 0;
+}
+
+int dmx_forward_segments(dmx_model *m, const float *segs, int n_segments, float *out)
+{
+    if (!m || !segs || !out)
+    {
+        set_error("dmx_forward_segments: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_forward_segments: model not finalized");
+        return -1;
+    }
+    if (n_segments < 1 || n_segments > m->maxB)
+    {
+        set_error("dmx_forward_segments: n_segments must be in [1, max_batch]");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    const size_t S = (size_t)m->S;
+    if (grow(&m->d_y, &m->cap_y, (size_t)n_segments * S * SEG * 2))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(m->mix, segs, (size_t)n_segments * SEG * 2 * sizeof(float), cudaMemcpyHostToDevice,
+                             m->stream));
+    if (model_forward(m, m->mix, n_segments, m->d_y))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(out, m->d_y, (size_t)n_segments * S * SEG * 2 * sizeof(float), cudaMemcpyDeviceToHost,
+                             m->stream));
+    DMX_CUDA(cudaStreamSynchronize(m->stream));
+    return 0;
+}
+
+int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capacity, int64_t dims[4])
+{
+    if (!m || !name)
+    {
+        set_error("dmx_debug_tap: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    auto it = m->taps.find(name);
+    if (it == m->taps.end())
+    {
+        set_error(std::string("dmx_debug_tap: unknown tap ") + name);
+        return -1;
+    }
+    const Tap &t = it->second;
+    const int64_t n = (int64_t)m->lastB * t.d1 * t.d2 * t.C;
+    if (dims)
+    {
+        dims[0] = m->lastB;
+        dims[1] = t.d1;
+        dims[2] = t.d2;
+        dims[3] = t.C;
+    }
+    if (!dst)
+        return n;
+    if (capacity < n)
+    {
+        set_error("dmx_debug_tap: destination too small");
+        return -1;
+    }
+    if (cudaSetDevice(m->device) != cudaSuccess ||
+        cudaMemcpy(dst, t.ptr, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+    {
+        set_error("dmx_debug_tap: copy failed");
+        return -1;
+    }
+    return n;
+}
+
+int dmx_stft_segment(dmx_model *m, const float *seg_lr, float *spec)
+{
+    if (!m || !seg_lr || !spec)
+    {
+        set_error("dmx_stft_segment: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_stft_segment: model not finalized");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    DMX_CUDA(cudaMemcpyAsync(m->mix, seg_lr, (size_t)SEG * 2 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    DMX_CUDA(cudaMemsetAsync(m->stats, 0, 2 * sizeof(double), m->stream));
+    if (launch_stft(m->mix, 1, m->window, m->tw, m->spec, m->stats, m->stream))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(spec, m->spec, (size_t)NBINS * LE * 4 * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    DMX_CUDA(cudaStreamSynchronize(m->stream));
+    return 0;
+}
+
+// Inverse of dmx_stft_segment: spec (2048, 336, 4) -> segment (343980, 2); identity mean/std, zero
+// time branch, one "source" whose four channels are the CaC planes.
+int dmx_istft_segment(dmx_model *m, const float *spec, float *seg_lr)
+{
+    if (!m || !spec || !seg_lr)
+    {
+        set_error("dmx_istft_segment: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    if (!m->finalized)
+    {
+        set_error("dmx_istft_segment: model not finalized");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    DMX_CUDA(cudaMemcpyAsync(m->spec, spec, (size_t)NBINS * LE * 4 * sizeof(float), cudaMemcpyHostToDevice, st));
+    const float ident[2] = {0.f, 1.f};
+    DMX_CUDA(cudaMemcpyAsync(m->meanstd_x, ident, sizeof ident, cudaMemcpyHostToDevice, st));
+    DMX_CUDA(cudaMemcpyAsync(m->meanstd_t, ident, sizeof ident, cudaMemcpyHostToDevice, st));
+    DMX_CUDA(cudaMemsetAsync(m->xt_in, 0, (size_t)SEG * 2 * sizeof(float), st));
+    if (launch_istft(m->spec, 1, 1, m->meanstd_x, m->window, m->tw, m->wss, m->xt_in, m->meanstd_t, m->frames,
+                     m->seg_out, st))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(seg_lr, m->seg_out, (size_t)SEG * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    DMX_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+} // extern "C"

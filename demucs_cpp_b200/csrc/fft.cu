@@ -1,0 +1,255 @@
+// STFT / iSTFT for the 7.8 s segment forward, as shared-memory radix-4 Stockham FFTs.
+//
+// Reference semantics reproduced here (see oracle/demucs_oracle.py for the CPU restatement):
+//   * reflect_padding 1536/1620 with the edge sample included  (src/model_inference.cpp:22-46)
+//   * demucscpp::stft: hop 1024, periodic Hann, rFFT-4096, 1/sqrt(4096); frames 2..337 and
+//     bins 0..2047 kept, complex-as-channels packing            (src/dsp.cpp:51-86,119-149;
+//                                                                src/model_inference.cpp:75-99)
+//   * demucscpp::istft: sqrt(4096) * unscaled inverse, window / 4096 / (wss + 1e-8) overlap-add
+//                                                               (src/dsp.cpp:88-117,151-185)
+//   * per-source reassembly: x*std+mean, zero Nyquist bin, two zero frames each side, crop 1536,
+//     plus de-normalised time branch                            (src/model_inference.cpp:380-474)
+//
+// Both stereo channels ride one complex FFT (z = L + iR); the two real spectra are separated by
+// Hermitian symmetry.  Layouts: mix [B][SEG][2]; spectrogram activations [B][F=2048][T=336][C].
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace dmx
+{
+
+constexpr int FFT_THREADS = 256;
+constexpr int FFT_SMEM = 2 * NFFT * (int)sizeof(float2); // ping-pong, 64 KB
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b)
+{
+    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+
+// In-place (ping-pong) 4096-point complex FFT over shared memory, 6 radix-4 Stockham passes.
+// tw[k] = exp(-2*pi*i*k/4096).  INV conjugates the twiddles and the +-i rotation (unscaled inverse).
+// Result ends in `x` (6 passes = even number of swaps).  Caller syncs before and after.
+template <bool INV>
+__device__ __forceinline__ void fft4096(float2 *x, float2 *y, const float2 *__restrict__ tw)
+{
+    int s = 1;
+#pragma unroll 1
+    for (int n = NFFT; n > 1; n >>= 2, s <<= 2)
+    {
+        const int n1 = n >> 2;
+        for (int t = threadIdx.x; t < NFFT / 4; t += FFT_THREADS)
+        {
+            const int p = t / s, q = t - p * s;
+            float2 w1 = __ldg(&tw[p * s]), w2 = __ldg(&tw[2 * p * s]), w3 = __ldg(&tw[3 * p * s]);
+            if (INV)
+            {
+                w1.y = -w1.y;
+                w2.y = -w2.y;
+                w3.y = -w3.y;
+            }
+            const float2 a = x[q + s * p], b = x[q + s * (p + n1)], c = x[q + s * (p + 2 * n1)],
+                         d = x[q + s * (p + 3 * n1)];
+            const float2 apc = make_float2(a.x + c.x, a.y + c.y), amc = make_float2(a.x - c.x, a.y - c.y);
+            const float2 bpd = make_float2(b.x + d.x, b.y + d.y), bmd = make_float2(b.x - d.x, b.y - d.y);
+            // j*(b-d): forward j = +i -> (-im, re); inverse j = -i -> (im, -re)
+            const float2 jb = INV ? make_float2(bmd.y, -bmd.x) : make_float2(-bmd.y, bmd.x);
+            y[q + s * (4 * p + 0)] = make_float2(apc.x + bpd.x, apc.y + bpd.y);
+            y[q + s * (4 * p + 1)] = cmul(w1, make_float2(amc.x - jb.x, amc.y - jb.y));
+            y[q + s * (4 * p + 2)] = cmul(w2, make_float2(apc.x - bpd.x, apc.y - bpd.y));
+            y[q + s * (4 * p + 3)] = cmul(w3, make_float2(amc.x + jb.x, amc.y + jb.y));
+        }
+        __syncthreads();
+        float2 *tmp = x;
+        x = y;
+        y = tmp;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// STFT: grid (336 frames, B).  Writes raw CaC spectrogram spec[b][f][t][4] = (ReL, ImL, ReR, ImR)
+// and accumulates sum / sum-of-squares per batch item into stats[b][2] (double) for the global
+// normalisation that follows (src/model_inference.cpp:115-124).
+__global__ void __launch_bounds__(FFT_THREADS) stft_kernel(const float2 *__restrict__ mix, // [B][SEG]
+                                                           const float *__restrict__ window, // [4096]
+                                                           const float2 *__restrict__ tw,    // [4096]
+                                                           float4 *__restrict__ spec,        // [B][2048][336]
+                                                           double *__restrict__ stats)       // [B][2]
+{
+    extern __shared__ float2 sm[];
+    float2 *x = sm, *y = sm + NFFT;
+    const int t = blockIdx.x, b = blockIdx.y;
+    const float2 *src = mix + (size_t)b * SEG;
+    // kept frame t is STFT frame j = t + 2; its first sample sits at index j*1024 - 2048 of the
+    // 1536/1620-padded segment, i.e. at (t*1024 - 1536) of the segment before mirroring.
+    const int base = t * HOP - PAD;
+    for (int n = threadIdx.x; n < NFFT; n += FFT_THREADS)
+    {
+        int i = base + n;
+        if (i < 0)
+            i = -1 - i; // edge-including mirror
+        else if (i >= SEG)
+            i = 2 * SEG - 1 - i;
+        const float2 v = __ldg(&src[i]);
+        const float w = __ldg(&window[n]);
+        x[n] = make_float2(v.x * w, v.y * w);
+    }
+    __syncthreads();
+    fft4096<false>(x, y, tw);
+    const float sc = 1.0f / 64.0f; // 1/sqrt(4096)
+    float s1 = 0.f, s2 = 0.f;
+    for (int k = threadIdx.x; k < NBINS; k += FFT_THREADS)
+    {
+        const float2 zk = x[k];
+        const float2 zm = x[(NFFT - k) & (NFFT - 1)];
+        // XL = (Z[k] + conj(Z[N-k]))/2 ; XR = (Z[k] - conj(Z[N-k]))/(2i)
+        float4 o;
+        o.x = 0.5f * (zk.x + zm.x) * sc;
+        o.y = 0.5f * (zk.y - zm.y) * sc;
+        o.z = 0.5f * (zk.y + zm.y) * sc;
+        o.w = -0.5f * (zk.x - zm.x) * sc;
+        spec[((size_t)b * NBINS + k) * LE + t] = o;
+        s1 += o.x + o.y + o.z + o.w;
+        s2 += o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
+    }
+    // block reduce -> one double atomic pair per CTA
+    __shared__ double red[2][FFT_THREADS / 32];
+    double d1 = s1, d2 = s2;
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        d1 += __shfl_xor_sync(0xffffffffu, d1, o);
+        d2 += __shfl_xor_sync(0xffffffffu, d2, o);
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        red[0][threadIdx.x >> 5] = d1;
+        red[1][threadIdx.x >> 5] = d2;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double a = 0, c = 0;
+        for (int i = 0; i < FFT_THREADS / 32; ++i)
+        {
+            a += red[0][i];
+            c += red[1][i];
+        }
+        atomicAdd(&stats[2 * b + 0], a);
+        atomicAdd(&stats[2 * b + 1], c);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// iSTFT stage 1: grid (336 frames, S sources, B).  Reads the freq-branch output
+// xout[b][f][t][4*S] (channels s*4 + {ReL,ImL,ReR,ImR}), de-normalises with the per-item
+// (mean, std) of the input spectrogram, runs the inverse FFT and writes the windowed frame
+// (scaled by 64/4096, not yet divided by the window-sum-square) to frames[b][s][t][4096] (L,R).
+__global__ void __launch_bounds__(FFT_THREADS) istft_frames_kernel(const float *__restrict__ xout, int S,
+                                                                   const float2 *__restrict__ meanstd, // [B] (mean,std)
+                                                                   const float *__restrict__ window,
+                                                                   const float2 *__restrict__ tw,
+                                                                   float2 *__restrict__ frames)
+{
+    extern __shared__ float2 sm[];
+    float2 *x = sm, *y = sm + NFFT;
+    const int t = blockIdx.x, s = blockIdx.y, b = blockIdx.z;
+    const float2 ms = meanstd[b];
+    const int C = 4 * S;
+    for (int k = threadIdx.x; k < NBINS; k += FFT_THREADS)
+    {
+        const float4 v = *reinterpret_cast<const float4 *>(xout + (((size_t)b * NBINS + k) * LE + t) * C + 4 * s);
+        const float lr = v.x * ms.y + ms.x, li = v.y * ms.y + ms.x;
+        const float rr = v.z * ms.y + ms.x, ri = v.w * ms.y + ms.x;
+        if (k == 0)
+        {
+            // real inverse ignores the imaginary part of DC; Nyquist bin is zero-padded
+            x[0] = make_float2(lr, rr);
+            x[NFFT / 2] = make_float2(0.f, 0.f);
+        }
+        else
+        {
+            // Z[k] = XL + i XR ; Z[N-k] = conj(XL) + i conj(XR)
+            x[k] = make_float2(lr - ri, li + rr);
+            x[NFFT - k] = make_float2(lr + ri, rr - li);
+        }
+    }
+    __syncthreads();
+    fft4096<true>(x, y, tw);
+    float2 *dst = frames + (((size_t)b * S + s) * LE + t) * NFFT;
+    const float sc = 64.0f / 4096.0f; // sqrt(4096) / 4096
+    for (int n = threadIdx.x; n < NFFT; n += FFT_THREADS)
+    {
+        const float w = __ldg(&window[n]) * sc;
+        const float2 v = x[n];
+        dst[n] = make_float2(v.x * w, v.y * w);
+    }
+}
+
+// iSTFT stage 2: overlap-add the four frames covering each sample, each divided by (wss + 1e-8)
+// in increasing frame order like the reference's accumulation loop, crop, and add the
+// de-normalised time branch.  out[b][s][n] (L,R).  xt_out: [B][SEG][2*S] channel s*2 + ch.
+__global__ void __launch_bounds__(256) istft_ola_kernel(const float2 *__restrict__ frames, int S,
+                                                        const float *__restrict__ wss,       // [OLA_LEN]
+                                                        const float *__restrict__ xt_out,
+                                                        const float2 *__restrict__ meanstd_t, // [B]
+                                                        float2 *__restrict__ out)
+{
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y, b = blockIdx.z;
+    if (n >= SEG)
+        return;
+    const int q = n + PAD + NFFT / 2; // index in the 351232-long OLA buffer
+    const float inv = 1.0f / (__ldg(&wss[q]) + 1e-8f);
+    const int jhi = q / HOP;
+    float2 acc = make_float2(0.f, 0.f);
+    const float2 *fb = frames + ((size_t)b * S + s) * LE * (size_t)NFFT;
+#pragma unroll
+    for (int d = 3; d >= 0; --d)
+    {
+        const int j = jhi - d;  // STFT frame number, nonzero frames are 2..337
+        const int t = j - 2;
+        if (t >= 0 && t < LE)
+        {
+            const float2 v = __ldg(&fb[(size_t)t * NFFT + (q - j * HOP)]);
+            acc.x += v.x * inv;
+            acc.y += v.y * inv;
+        }
+    }
+    const float2 ms = meanstd_t[b];
+    const float2 xt = *reinterpret_cast<const float2 *>(xt_out + ((size_t)b * SEG + n) * (2 * S) + 2 * s);
+    acc.x += xt.x * ms.y + ms.x;
+    acc.y += xt.y * ms.y + ms.x;
+    out[((size_t)b * S + s) * SEG + n] = acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Opts the FFT kernels into 64 KB of dynamic shared memory; call once per device with it current.
+int fft_init_device()
+{
+    DMX_CUDA(cudaFuncSetAttribute(stft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FFT_SMEM));
+    DMX_CUDA(cudaFuncSetAttribute(istft_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FFT_SMEM));
+    return 0;
+}
+
+int launch_stft(const float *mix, int B, const float *window, const float *tw, float *spec, double *stats,
+                cudaStream_t st)
+{
+    stft_kernel<<<dim3(LE, B), FFT_THREADS, FFT_SMEM, st>>>((const float2 *)mix, window, (const float2 *)tw,
+                                                            (float4 *)spec, stats);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_istft(const float *xout, int B, int S, const float *meanstd, const float *window, const float *tw,
+                 const float *wss, const float *xt_out, const float *meanstd_t, float *frames_scratch,
+                 float *out, cudaStream_t st)
+{
+    istft_frames_kernel<<<dim3(LE, S, B), FFT_THREADS, FFT_SMEM, st>>>(
+        xout, S, (const float2 *)meanstd, window, (const float2 *)tw, (float2 *)frames_scratch);
+    DMX_LAUNCH_CHECK();
+    istft_ola_kernel<<<dim3((SEG + 255) / 256, S, B), 256, 0, st>>>(
+        (const float2 *)frames_scratch, S, wss, xt_out, (const float2 *)meanstd_t, (float2 *)out);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+} // namespace dmx

@@ -1,0 +1,89 @@
+// Launcher declarations for the demucs_b200 kernels (implemented in fft.cu, gemm.cu, pointwise.cu,
+// attention.cu).  All launchers return 0 on success, -1 after set_error().
+#pragma once
+#include "common.cuh"
+
+namespace dmx
+{
+
+// ---------------------------------------------------------------------------------------------
+// "tap-GEMM": every convolution / transposed convolution / linear layer of the model expressed as
+//   C[m, n] = epilogue( sum_{tap, c} prologue(A[row(m, tap), c]) * W[tap*Cin + c, n] + bias[n] )
+// over channels-last activations.  An output row m decodes to (b, u_o, v_o) on a per-item grid
+// Uo x Vo (time branch: U = 1, V = samples; freq branch: U = frequency bins, V = frames); tap j
+// reads input row (u_o*su + du[j], v_o*sv + dv[j]) of the Ui x Vi input grid, zero outside it.
+// Output column n = r*Nco + co is stored at grid position (u_o*ous + r*our + ouo, v_o*ovs + r*ovr + ovo)
+// of the Uout x Vout output grid, channel co, dropped outside it -- which lets ConvTranspose
+// k=8,s=4 run as ONE GEMM with two taps and N = 4*Cout, the crop folded into (ouo/ovo).
+//   reference ops covered: conv1d/conv2d(+_fused_gelu) src/conv.hpp:13-262, conv*_tr src/conv.hpp:264-524,
+//   linear layers of common_encoder_layer src/layers.cpp:426-514.
+struct GemmParams
+{
+    // A operand
+    const float *A = nullptr;
+    const float *A2 = nullptr; // optional second tensor added element-wise (decoder skip, src/encdec.cpp:172)
+    int lda = 0, Cin = 0, K = 0;
+    int ntaps = 1;
+    int du[9] = {0}, dv[9] = {0};
+    int Ui = 1, Vi = 1, Uo = 1, Vo = 1, su = 1, sv = 1;
+    int M = 0;
+    // A prologue: GroupNorm(1 group) + GELU of the producer's raw output (src/layers.cpp:51-94)
+    int pro = 0;
+    const double *pro_stats = nullptr; // [items][2] (sum, sumsq)
+    double pro_count = 1.0;
+    const float *pro_w = nullptr, *pro_b = nullptr;
+    int pro_per_u = 0; // item = b*Ui + u_i (freq rows) or b (time)
+    // B operand: packed fp32 [Kpad][ldw], zero padded
+    const float *W = nullptr;
+    int ldw = 0;
+    const float *bias = nullptr;
+    int N = 0;
+    // epilogue
+    int act = 0;                   // 1 = exact-erf GELU
+    int glu = 0;                   // 1 = columns packed as (a, gate) pairs -> a*sigmoid(gate)
+    const float *rowadd = nullptr; // out += rowadd[u_o*rowadd_ld + co]   (frequency embedding)
+    int rowadd_ld = 0;
+    const float *gamma = nullptr;  // out = C_old + gamma[n]*val           (LayerScale residual)
+    double *stats = nullptr;       // accumulate (sum, sumsq) of the stored values per item
+    int stat_per_u = 0;
+    // output mapping
+    float *C = nullptr;
+    int ldc = 0, Nco = 0;
+    int Uout = 1, Vout = 1, ous = 1, our = 0, ouo = 0, ovs = 1, ovr = 0, ovo = 0;
+};
+
+int launch_gemm(const GemmParams &p, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// fft.cu
+int fft_init_device();
+int launch_stft(const float *mix, int B, const float *window, const float *tw, float *spec, double *stats,
+                cudaStream_t st);
+int launch_istft(const float *xout, int B, int S, const float *meanstd, const float *window, const float *tw,
+                 const float *wss, const float *xt_out, const float *meanstd_t, float *frames_scratch, float *out,
+                 cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// pointwise.cu
+// sum / sumsq of n_per_item floats per batch item -> stats[b][2] (double, must be zeroed)
+int launch_sum_stats(const float *x, int B, size_t n_per_item, double *stats, cudaStream_t st);
+// x = (x - mean)/(std + 1e-5) with unbiased std; writes (mean, std) per item  (src/model_inference.cpp:115-144)
+int launch_normalize_input(float *x, int B, size_t n_per_item, const double *stats, float *meanstd,
+                           cudaStream_t st);
+// DConv tail: x[r][c] += scale[c] * GN(y)[r][c] * sigmoid(GN(y)[r][c+C])  (src/layers.cpp:240-253)
+int launch_gn_glu_residual(const float *y, float *x, int B, int U, int V, int C, const double *stats,
+                           int per_u, const float *gw, const float *gb, const float *scale, cudaStream_t st);
+// LayerNorm over the last dim (unbiased var), optional additive table add[row % add_rows][c]
+int launch_layer_norm(const float *x, float *y, int rows, int C, const float *w, const float *b,
+                      const float *add, int add_rows, cudaStream_t st);
+// MyGroupNorm apply: x = (x-mean)*rstd*w[c]+b[c] per batch item over (rows_per_item, C)
+int launch_group_norm_apply(float *x, int B, int rows_per_item, int C, const double *stats, const float *w,
+                            const float *b, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// attention.cu: softmax(Q K^T / sqrt(dh)) V per head, heads = contiguous dh-wide column blocks
+// (src/layers.cpp:442-482).  Q: [B*T][ldq], K/V: [B*S][ldk|ldv]; O: [B*T][ldo].
+int launch_attention(const float *Q, int ldq, const float *K, int ldk, const float *V, int ldv, float *O, int ldo,
+                     int B, int T, int S, int heads, int dh, cudaStream_t st);
+
+} // namespace dmx

@@ -1,0 +1,871 @@
+// htdemucs (4s / 6s / ft member) on device: weight repacking, workspace and the per-segment forward
+// (reference: demucscpp::model_inference, src/model_inference.cpp:48-475) over a batch of segments.
+//
+// Device layout: channels-last fp32.  Time branch [B][L][C]; frequency branch [B][F][T=336][C]
+// (C fastest, then frames, then bins).  With it every conv of the model is a tap-GEMM on strided
+// views (kernels.cuh) and no transpose/shuffle of the reference is ever
+// materialised; transformer tokens are simply the rows of the [8][336][C] bottleneck (row f*336+t),
+// with the 2-D positional table built in that order.
+#include "model.cuh"
+
+#include <cmath>
+#include <cstring>
+
+namespace dmx
+{
+
+static const int FREQS[5] = {2048, 512, 128, 32, 8};
+static const int TLENS[5] = {SEG, TLEN0, TLEN1, TLEN2, TLEN3};
+static const int CH[5] = {0, 48, 96, 192, 384}; // CH[i+1] = channels after encoder i
+static const int T = LE;
+
+// ------------------------------------------------------------------------------------------------
+// profiling
+cudaEvent_t Profiler::get()
+{
+    if (used == pool.size())
+    {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        pool.push_back(e);
+    }
+    return pool[used++];
+}
+
+ProfScope::ProfScope(dmx_model *m_, int cls, double flops, double bytes) : m(m_)
+{
+    m->launches++;
+    if (!m->prof.on)
+        return;
+    ProfRec r;
+    r.cls = cls;
+    r.e0 = m->prof.get();
+    r.e1 = m->prof.get();
+    e1 = r.e1;
+    m->prof.recs.push_back(r);
+    m->prof.flops[cls] += flops;
+    m->prof.bytes[cls] += bytes;
+    cudaEventRecord(r.e0, m->stream);
+}
+
+ProfScope::~ProfScope()
+{
+    if (e1)
+        cudaEventRecord(e1, m->stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// allocation helpers
+static int dev_alloc(dmx_model *m, void **p, size_t bytes)
+{
+    DMX_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+    m->allocs.push_back(*p);
+    return 0;
+}
+
+template <typename Tp> static int dev_alloc_t(dmx_model *m, Tp **p, size_t n)
+{
+    return dev_alloc(m, reinterpret_cast<void **>(p), n * sizeof(Tp));
+}
+
+static int upload(dmx_model *m, float **dst, const std::vector<float> &v)
+{
+    if (dev_alloc_t(m, dst, v.size()))
+        return -1;
+    DMX_CUDA(cudaMemcpy(*dst, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+static const HostTensor *get(dmx_model *m, const std::string &name, size_t numel)
+{
+    auto it = m->host.find(name);
+    if (it == m->host.end())
+    {
+        set_error("model: missing tensor " + name);
+        return nullptr;
+    }
+    if (it->second.numel() != numel)
+    {
+        set_error("model: tensor " + name + " has " + std::to_string(it->second.numel()) + " elements, expected " +
+                  std::to_string(numel));
+        return nullptr;
+    }
+    return &it->second;
+}
+
+static int upload_vec(dmx_model *m, float **dst, const std::string &name, size_t n)
+{
+    const HostTensor *t = get(m, name, n);
+    if (!t)
+        return -1;
+    return upload(m, dst, t->data);
+}
+
+static inline int round_up(int x, int k) { return (x + k - 1) / k * k; }
+
+// Generic packer: element (k, n) of the GEMM B operand given by f(k, n); bias by fb(n).
+// If glu: output columns are interleaved so that packed 2j = original j, packed 2j+1 = original j + N/2.
+template <typename FW, typename FB>
+static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb)
+{
+    p.K = K;
+    p.N = N;
+    p.ldw = round_up(N, 128);
+    const int Kpad = round_up(K, 16);
+    std::vector<float> w((size_t)Kpad * p.ldw, 0.f), b(p.ldw, 0.f);
+    for (int n = 0; n < N; ++n)
+    {
+        const int src = glu ? ((n & 1) ? (n >> 1) + N / 2 : (n >> 1)) : n;
+        for (int k = 0; k < K; ++k)
+            w[(size_t)k * p.ldw + n] = fw(k, src);
+        b[n] = fb(src);
+    }
+    if (upload(m, &p.W, w) || upload(m, &p.bias, b))
+        return -1;
+    return 0;
+}
+
+// Conv weight (Cout, Cin, ntaps) row-major -> B[tap*Cin + c][cout]   (src/conv.hpp:97-110 equivalent)
+static int pack_conv(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cout, int Cin,
+                     int ntaps, bool glu)
+{
+    const HostTensor *w = get(m, wname, (size_t)Cout * Cin * ntaps);
+    const HostTensor *b = get(m, bname, Cout);
+    if (!w || !b)
+        return -1;
+    const float *wd = w->data.data();
+    const float *bd = b->data.data();
+    return pack(
+        m, p, Cin * ntaps, Cout, glu,
+        [=](int k, int n) {
+            const int tap = k / Cin, c = k % Cin;
+            return wd[((size_t)n * Cin + c) * ntaps + tap];
+        },
+        [=](int n) { return bd[n]; });
+}
+
+// ConvTranspose k=8, s=4 weight (Cin, Cout, 8) -> two taps (x[i-1] with k=r+4, x[i] with k=r),
+// N = 4*Cout columns n = r*Cout + co   (src/conv.hpp:264-474 equivalent)
+static int pack_convtr(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cin, int Cout)
+{
+    const HostTensor *w = get(m, wname, (size_t)Cin * Cout * 8);
+    const HostTensor *b = get(m, bname, Cout);
+    if (!w || !b)
+        return -1;
+    const float *wd = w->data.data();
+    const float *bd = b->data.data();
+    return pack(
+        m, p, 2 * Cin, 4 * Cout, false,
+        [=](int k, int n) {
+            const int tap = k / Cin, c = k % Cin;
+            const int r = n / Cout, co = n % Cout;
+            const int kk = tap == 0 ? r + 4 : r;
+            return wd[((size_t)c * Cout + co) * 8 + kk];
+        },
+        [=](int n) { return bd[n % Cout]; });
+}
+
+// Linear weight rows [row0, row0+N) of an (out, in) matrix -> B[in][n]
+static int pack_linear(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int out_total,
+                       int in, int row0, int N)
+{
+    const HostTensor *w = get(m, wname, (size_t)out_total * in);
+    const HostTensor *b = get(m, bname, out_total);
+    if (!w || !b)
+        return -1;
+    const float *wd = w->data.data();
+    const float *bd = b->data.data();
+    return pack(
+        m, p, in, N, false, [=](int k, int n) { return wd[(size_t)(row0 + n) * in + k]; },
+        [=](int n) { return bd[row0 + n]; });
+}
+
+static int pack_dconv(dmx_model *m, DConvW &d, const std::string &prefix, int C)
+{
+    d.C = C;
+    d.hid = C / 8;
+    for (int j = 0; j < 2; ++j)
+    {
+        const std::string p = prefix + ".dconv.layers." + std::to_string(j) + ".";
+        if (pack_conv(m, d.c1[j], p + "0.weight", p + "0.bias", d.hid, C, 3, false))
+            return -1;
+        if (pack_conv(m, d.c2[j], p + "3.weight", p + "3.bias", 2 * C, d.hid, 1, false))
+            return -1;
+        if (upload_vec(m, &d.g1w[j], p + "1.weight", d.hid) || upload_vec(m, &d.g1b[j], p + "1.bias", d.hid) ||
+            upload_vec(m, &d.g2w[j], p + "4.weight", 2 * C) || upload_vec(m, &d.g2b[j], p + "4.bias", 2 * C) ||
+            upload_vec(m, &d.scale[j], p + "6.scale", C))
+            return -1;
+    }
+    return 0;
+}
+
+static int pack_tlayer(dmx_model *m, TLayerW &L, const std::string &p, bool cross, int d)
+{
+    L.cross = cross;
+    const std::string attn = p + (cross ? "cross_attn." : "self_attn.");
+    if (cross)
+    {
+        if (pack_linear(m, L.q, attn + "in_proj_weight", attn + "in_proj_bias", 3 * d, d, 0, d) ||
+            pack_linear(m, L.kv, attn + "in_proj_weight", attn + "in_proj_bias", 3 * d, d, d, 2 * d))
+            return -1;
+    }
+    else if (pack_linear(m, L.qkv, attn + "in_proj_weight", attn + "in_proj_bias", 3 * d, d, 0, 3 * d))
+        return -1;
+    if (pack_linear(m, L.out, attn + "out_proj.weight", attn + "out_proj.bias", d, d, 0, d) ||
+        pack_linear(m, L.ff1, p + "linear1.weight", p + "linear1.bias", 4 * d, d, 0, 4 * d) ||
+        pack_linear(m, L.ff2, p + "linear2.weight", p + "linear2.bias", d, 4 * d, 0, d))
+        return -1;
+    if (upload_vec(m, &L.n1w, p + "norm1.weight", d) || upload_vec(m, &L.n1b, p + "norm1.bias", d) ||
+        upload_vec(m, &L.n2w, p + "norm2.weight", d) || upload_vec(m, &L.n2b, p + "norm2.bias", d) ||
+        upload_vec(m, &L.now_, p + "norm_out.weight", d) || upload_vec(m, &L.nob, p + "norm_out.bias", d) ||
+        upload_vec(m, &L.g1, p + "gamma_1.scale", d) || upload_vec(m, &L.g2, p + "gamma_2.scale", d))
+        return -1;
+    L.n3w = L.n3b = nullptr;
+    if (cross && (upload_vec(m, &L.n3w, p + "norm3.weight", d) || upload_vec(m, &L.n3b, p + "norm3.bias", d)))
+        return -1;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// constant tables, computed exactly like the reference does (float libm calls)
+static std::vector<float> make_window()
+{
+    // src/dsp.hpp:59-75
+    const float PI = 3.14159265359F;
+    std::vector<float> w(NFFT);
+    const float floatN = (float)(NFFT + 1);
+    for (int n = 0; n < NFFT; ++n)
+        w[n] = 0.5F * (1.0F - cosf(2.0F * PI * (float)n / (floatN - 1)));
+    return w;
+}
+
+static std::vector<float> make_wss(const std::vector<float> &w)
+{
+    // src/dsp.hpp:77-100 with nb_frames = 340
+    const int nb_frames = PADDED / HOP + 1;
+    std::vector<float> out(OLA_LEN, 0.f);
+    for (int i = 0; i < nb_frames; ++i)
+        for (int j = 0; j < NFFT; ++j)
+            out[i * HOP + j] += w[j] * w[j];
+    return out;
+}
+
+static std::vector<float> make_twiddles()
+{
+    std::vector<float> t(2 * NFFT);
+    for (int k = 0; k < NFFT; ++k)
+    {
+        const double a = -2.0 * M_PI * (double)k / (double)NFFT;
+        t[2 * k] = (float)cos(a);
+        t[2 * k + 1] = (float)sin(a);
+    }
+    return t;
+}
+
+// 2-D sinusoidal embedding (src/crosstransformer.cpp:7-53) in token order row = f*T + t.
+static std::vector<float> make_pe2d(int d, int height, int width)
+{
+    std::vector<float> pe((size_t)height * width * d);
+    const int half = d / 2;
+    std::vector<float> div(half / 2);
+    for (int j = 0; j < half / 2; ++j)
+        div[j] = expf((float)(2 * j) * (-logf(10000.0f) / (float)half));
+    for (int f = 0; f < height; ++f)
+        for (int t = 0; t < width; ++t)
+        {
+            float *row = &pe[((size_t)f * width + t) * d];
+            for (int j = 0; j < half / 2; ++j)
+            {
+                const float vw = (float)t * div[j], vh = (float)f * div[j];
+                row[2 * j] = sinf(vw);
+                row[2 * j + 1] = cosf(vw);
+                row[half + 2 * j] = sinf(vh);
+                row[half + 2 * j + 1] = cosf(vh);
+            }
+        }
+    return pe;
+}
+
+// 1-D sinusoidal embedding (src/crosstransformer.cpp:55-77): cos first half, sin second half.
+static std::vector<float> make_pe1d(int length, int d)
+{
+    std::vector<float> pe((size_t)length * d);
+    const int half = d / 2;
+    for (int t = 0; t < length; ++t)
+        for (int i = 0; i < half; ++i)
+        {
+            const float div = (float)i / (float)(half - 1);
+            const float phase = (float)t / powf(10000.0f, div);
+            pe[(size_t)t * d + i] = cosf(phase);
+            pe[(size_t)t * d + half + i] = sinf(phase);
+        }
+    return pe;
+}
+
+// ------------------------------------------------------------------------------------------------
+int model_finalize(dmx_model *m)
+{
+    if (m->finalized)
+        return 0;
+    if (m->arch != DMX_ARCH_HTDEMUCS_4S && m->arch != DMX_ARCH_HTDEMUCS_6S)
+    {
+        set_error("model_finalize: architecture not implemented on the CUDA path (hdemucs_mmi v3 is a later round)");
+        return -1;
+    }
+    DMX_CUDA(cudaSetDevice(m->device));
+    DMX_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+    DMX_CUDA(cudaEventCreate(&m->ev0));
+    DMX_CUDA(cudaEventCreate(&m->ev1));
+    DMX_CUDA(cudaEventCreate(&m->ev2));
+    if (fft_init_device())
+        return -1;
+    const bool is4 = m->arch == DMX_ARCH_HTDEMUCS_4S;
+    m->S = is4 ? 4 : 6;
+    m->d_model = is4 ? 512 : 384;
+    const int S = m->S, d = m->d_model;
+
+    for (int i = 0; i < 4; ++i)
+    {
+        const int cin_f = i == 0 ? 4 : CH[i], cin_t = i == 0 ? 2 : CH[i], C = CH[i + 1];
+        const std::string e = "encoder." + std::to_string(i), te = "tencoder." + std::to_string(i);
+        m->enc[i].Cin = cin_f;
+        m->enc[i].C = C;
+        m->tenc[i].Cin = cin_t;
+        m->tenc[i].C = C;
+        if (pack_conv(m, m->enc[i].conv, e + ".conv.weight", e + ".conv.bias", C, cin_f, 8, false) ||
+            pack_conv(m, m->enc[i].rewrite, e + ".rewrite.weight", e + ".rewrite.bias", 2 * C, C, 1, true) ||
+            pack_dconv(m, m->enc[i].dc, e, C) ||
+            pack_conv(m, m->tenc[i].conv, te + ".conv.weight", te + ".conv.bias", C, cin_t, 8, false) ||
+            pack_conv(m, m->tenc[i].rewrite, te + ".rewrite.weight", te + ".rewrite.bias", 2 * C, C, 1, true) ||
+            pack_dconv(m, m->tenc[i].dc, te, C))
+            return -1;
+    }
+    for (int i = 0; i < 4; ++i)
+    {
+        const int C = CH[4 - i];
+        const int cout_f = i == 3 ? 4 * S : CH[3 - i], cout_t = i == 3 ? 2 * S : CH[3 - i];
+        const std::string dn = "decoder." + std::to_string(i), tn = "tdecoder." + std::to_string(i);
+        m->dec[i].C = C;
+        m->dec[i].Cout = cout_f;
+        m->tdec[i].C = C;
+        m->tdec[i].Cout = cout_t;
+        // 3x3 rewrite weight (2C, C, 3, 3): tap = kh*3 + kw with kh along frequency, kw along frames
+        if (pack_conv(m, m->dec[i].rewrite, dn + ".rewrite.weight", dn + ".rewrite.bias", 2 * C, C, 9, true) ||
+            pack_dconv(m, m->dec[i].dc, dn, C) ||
+            pack_convtr(m, m->dec[i].convtr, dn + ".conv_tr.weight", dn + ".conv_tr.bias", C, cout_f) ||
+            pack_conv(m, m->tdec[i].rewrite, tn + ".rewrite.weight", tn + ".rewrite.bias", 2 * C, C, 3, true) ||
+            pack_dconv(m, m->tdec[i].dc, tn, C) ||
+            pack_convtr(m, m->tdec[i].convtr, tn + ".conv_tr.weight", tn + ".conv_tr.bias", C, cout_t))
+            return -1;
+    }
+    {
+        // x_0(c, f, t) += 2.0 * emb(f, c)   (src/model_inference.cpp:163-179; 10 * 0.2 folded)
+        const HostTensor *t = get(m, "freq_emb.embedding.weight", 512 * 48);
+        if (!t)
+            return -1;
+        std::vector<float> e2(t->data);
+        for (auto &v : e2)
+            v *= 2.0f;
+        if (upload(m, &m->freq_emb2, e2))
+            return -1;
+    }
+    if (is4)
+    {
+        if (pack_conv(m, m->up, "channel_upsampler.weight", "channel_upsampler.bias", 512, 384, 1, false) ||
+            pack_conv(m, m->up_t, "channel_upsampler_t.weight", "channel_upsampler_t.bias", 512, 384, 1, false) ||
+            pack_conv(m, m->down, "channel_downsampler.weight", "channel_downsampler.bias", 384, 512, 1, false) ||
+            pack_conv(m, m->down_t, "channel_downsampler_t.weight", "channel_downsampler_t.bias", 384, 512, 1, false))
+            return -1;
+    }
+    if (upload_vec(m, &m->nin_w, "crosstransformer.norm_in.weight", d) ||
+        upload_vec(m, &m->nin_b, "crosstransformer.norm_in.bias", d) ||
+        upload_vec(m, &m->nint_w, "crosstransformer.norm_in_t.weight", d) ||
+        upload_vec(m, &m->nint_b, "crosstransformer.norm_in_t.bias", d))
+        return -1;
+    for (int i = 0; i < 5; ++i)
+    {
+        if (pack_tlayer(m, m->lay[i], "crosstransformer.layers." + std::to_string(i) + ".", i % 2 == 1, d) ||
+            pack_tlayer(m, m->lay_t[i], "crosstransformer.layers_t." + std::to_string(i) + ".", i % 2 == 1, d))
+            return -1;
+    }
+    // the reference rejects files with unknown tensors (src/model_load.cpp:1065-1070): so do we
+    {
+        const size_t expect = is4 ? 533 : 525;
+        if (m->host.size() != expect)
+        {
+            set_error("model_finalize: expected " + std::to_string(expect) + " tensors, got " +
+                      std::to_string(m->host.size()));
+            return -1;
+        }
+    }
+    {
+        const std::vector<float> w = make_window();
+        if (upload(m, &m->window, w) || upload(m, &m->wss, make_wss(w)) || upload(m, &m->tw, make_twiddles()) ||
+            upload(m, &m->pe2d, make_pe2d(d, 8, T)) || upload(m, &m->pe1d, make_pe1d(TLEN3, d)))
+            return -1;
+    }
+    m->host.clear(); // host fp32 copies are no longer needed
+
+    // ---------------- workspace ----------------
+    const size_t B = (size_t)m->maxB;
+    auto A = [&](float **p, size_t n) { return dev_alloc_t(m, p, B * n); };
+    int rc = 0;
+    rc |= A(&m->mix, (size_t)SEG * 2);
+    rc |= A(&m->spec, (size_t)NBINS * T * 4);
+    rc |= A(&m->xt_in, (size_t)SEG * 2);
+    rc |= A(&m->cA_f, (size_t)512 * T * 48);
+    rc |= A(&m->cA_t, (size_t)TLEN0 * 48);
+    for (int i = 0; i < 4; ++i)
+    {
+        rc |= A(&m->e[i], (size_t)FREQS[i + 1] * T * CH[i + 1]);
+        rc |= A(&m->te[i], (size_t)TLENS[i + 1] * CH[i + 1]);
+        rc |= A(&m->dx[i], (size_t)FREQS[3 - i] * T * m->dec[i].Cout);
+        rc |= A(&m->dxt[i], (size_t)TLENS[3 - i] * m->tdec[i].Cout);
+    }
+    rc |= A(&m->h_f, (size_t)512 * T * 6);
+    rc |= A(&m->y2_f, (size_t)512 * T * 96);
+    rc |= A(&m->h_t, (size_t)TLEN0 * 6);
+    rc |= A(&m->y2_t, (size_t)TLEN0 * 96);
+    const size_t TF = 8 * T, TT = TLEN3;
+    rc |= A(&m->up_f, TF * d);
+    rc |= A(&m->up_tt, TT * d);
+    rc |= A(&m->xq, TF * d);
+    rc |= A(&m->tq, TT * d);
+    rc |= A(&m->ln_f, TF * d);
+    rc |= A(&m->ln_t, TT * d);
+    rc |= A(&m->kn_f, TT * d);
+    rc |= A(&m->kn_t, TF * d);
+    rc |= A(&m->qkv_f, TF * 3 * d);
+    rc |= A(&m->qkv_t, TT * 3 * d);
+    rc |= A(&m->kv_f, TT * 2 * d);
+    rc |= A(&m->kv_t, TF * 2 * d);
+    rc |= A(&m->ao_f, TF * d);
+    rc |= A(&m->ao_t, TT * d);
+    rc |= A(&m->ff_f, TF * 4 * d);
+    rc |= A(&m->ff_t, TT * 4 * d);
+    rc |= A(&m->x3d, TF * 384);
+    rc |= A(&m->xt3d, TT * 384);
+    rc |= A(&m->frames, (size_t)S * T * NFFT * 2);
+    rc |= A(&m->seg_out, (size_t)S * SEG * 2);
+    rc |= A(&m->meanstd_x, 2);
+    rc |= A(&m->meanstd_t, 2);
+    if (rc)
+        return -1;
+    // statistics arena: (sum, sumsq) doubles; DConv needs up to 512 items per batch element and layer
+    m->stats_cap = B * 2 * (size_t)(2 * 2 * 2 * (512 + 128 + 32 + 8) * 2 + 16 * 2 * 2 + 64);
+    if (dev_alloc_t(m, &m->stats, m->stats_cap) || dev_alloc_t(m, &m->track_stats, 2))
+        return -1;
+    m->finalized = true;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward helpers
+struct Fwd
+{
+    dmx_model *m;
+    int B;
+    cudaStream_t st;
+    int rc = 0;
+
+    double *stat_slots(size_t items)
+    {
+        double *p = m->stats + m->stats_used;
+        m->stats_used += 2 * items;
+        if (m->stats_used > m->stats_cap)
+        {
+            set_error("statistics arena overflow");
+            rc = -1;
+            return m->stats;
+        }
+        return p;
+    }
+    void gemm(const GemmParams &p, int cls)
+    {
+        if (rc)
+            return;
+        ProfScope ps(m, cls, 2.0 * (double)p.M * (double)p.N * (double)p.K);
+        rc = launch_gemm(p, st);
+    }
+    // common fields: single batch grid (U, V) in and out, plain output mapping
+    GemmParams base(const float *Ain, int lda, int Cin, const Packed &w, float *C, int ldc, int Ui, int Vi, int Uo,
+                    int Vo)
+    {
+        GemmParams p;
+        p.A = Ain;
+        p.lda = lda;
+        p.Cin = Cin;
+        p.K = w.K;
+        p.W = w.W;
+        p.ldw = w.ldw;
+        p.bias = w.bias;
+        p.N = w.N;
+        p.Ui = Ui;
+        p.Vi = Vi;
+        p.Uo = Uo;
+        p.Vo = Vo;
+        p.M = B * Uo * Vo;
+        p.C = C;
+        p.ldc = ldc;
+        p.Nco = w.N;
+        p.Uout = Uo;
+        p.Vout = Vo;
+        return p;
+    }
+
+    // DConv residual branch (src/layers.cpp:152-375) in place on x [B][U][V][C]; GroupNorm items are
+    // frequency rows (per_u = 1) or whole batch elements (time branch, U = 1).
+    void dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u)
+    {
+        const int C = w.C, hid = w.hid;
+        const size_t items = (size_t)B * (per_u ? U : 1);
+        for (int j = 0; j < 2; ++j)
+        {
+            const int dil = 1 << j;
+            double *s1 = stat_slots(items), *s2 = stat_slots(items);
+            GemmParams p = base(x, C, C, w.c1[j], h, hid, U, V, U, V);
+            p.ntaps = 3;
+            for (int t = 0; t < 3; ++t)
+            {
+                p.du[t] = 0;
+                p.dv[t] = (t - 1) * dil;
+            }
+            p.stats = s1;
+            p.stat_per_u = per_u;
+            gemm(p, PC_GEMM_DCONV);
+            GemmParams q = base(h, hid, hid, w.c2[j], y2, 2 * C, U, V, U, V);
+            q.pro = 1;
+            q.pro_stats = s1;
+            q.pro_count = per_u ? (double)V * hid : (double)U * V * hid;
+            q.pro_w = w.g1w[j];
+            q.pro_b = w.g1b[j];
+            q.pro_per_u = per_u;
+            q.stats = s2;
+            q.stat_per_u = per_u;
+            gemm(q, PC_GEMM_DCONV);
+            if (!rc)
+            {
+                ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * U * V * C * 4.0 * 4.0);
+                rc = launch_gn_glu_residual(y2, x, B, U, V, C, s2, per_u, w.g2w[j], w.g2b[j], w.scale[j], st);
+            }
+        }
+    }
+
+    void layer_norm(const float *x, float *y, int rows, int C, const float *w, const float *b, const float *add = nullptr,
+                    int add_rows = 0)
+    {
+        if (rc)
+            return;
+        ProfScope ps(m, PC_POINTWISE, 0.0, (double)rows * C * 8.0);
+        rc = launch_layer_norm(x, y, rows, C, w, b, add, add_rows, st);
+    }
+
+    // tokens-as-rows linear layer: [B*Tn][Cin] x W -> [B*Tn][N]
+    GemmParams linear(const float *x, int Cin, const Packed &w, float *y, int ldc, int Tn)
+    {
+        return base(x, Cin, Cin, w, y, ldc, 1, Tn, 1, Tn);
+    }
+
+    // one transformer layer (src/layers.cpp:377-531) on q [B*Tq][d]; kn = already-normalised key source
+    // for cross layers (nullptr for self attention).
+    void tlayer(const TLayerW &L, float *q, int Tq, const float *kn, int Tk, float *ln, float *qkv, float *kv, float *ao,
+                float *ff)
+    {
+        const int d = m->d_model, dh = d / 8;
+        layer_norm(q, ln, B * Tq, d, L.n1w, L.n1b);
+        if (!L.cross)
+        {
+            gemm(linear(ln, d, L.qkv, qkv, 3 * d, Tq), PC_GEMM_XFMR);
+            if (!rc)
+            {
+                ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tq * d);
+                rc = launch_attention(qkv, 3 * d, qkv + d, 3 * d, qkv + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
+            }
+        }
+        else
+        {
+            gemm(linear(ln, d, L.q, qkv, d, Tq), PC_GEMM_XFMR);
+            gemm(linear(kn, d, L.kv, kv, 2 * d, Tk), PC_GEMM_XFMR);
+            if (!rc)
+            {
+                ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tk * d);
+                rc = launch_attention(qkv, d, kv, 2 * d, kv + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
+            }
+        }
+        GemmParams po = linear(ao, d, L.out, q, d, Tq);
+        po.gamma = L.g1;
+        gemm(po, PC_GEMM_XFMR);
+        // pre-FFN norm: norm3 for cross layers, norm2 for self layers (src/crosstransformer.cpp:111-113)
+        layer_norm(q, ln, B * Tq, d, L.cross ? L.n3w : L.n2w, L.cross ? L.n3b : L.n2b);
+        GemmParams p1 = linear(ln, d, L.ff1, ff, 4 * d, Tq);
+        p1.act = 1;
+        gemm(p1, PC_GEMM_XFMR);
+        GemmParams p2 = linear(ff, 4 * d, L.ff2, q, d, Tq);
+        p2.gamma = L.g2;
+        double *s = stat_slots(B);
+        p2.stats = s;
+        p2.stat_per_u = 0;
+        gemm(p2, PC_GEMM_XFMR);
+        if (!rc)
+        {
+            ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * Tq * d * 8.0);
+            rc = launch_group_norm_apply(q, B, Tq, d, s, L.now_, L.nob, st);
+        }
+    }
+};
+
+static void set_tap(dmx_model *m, const char *name, float *p, int64_t d1, int64_t d2, int64_t C)
+{
+    Tap t;
+    t.ptr = p;
+    t.d1 = d1;
+    t.d2 = d2;
+    t.C = C;
+    m->taps[name] = t;
+}
+
+int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
+{
+    if (!m->finalized)
+    {
+        set_error("model_forward: model not finalized");
+        return -1;
+    }
+    if (B < 1 || B > m->maxB)
+    {
+        set_error("model_forward: batch exceeds max_batch");
+        return -1;
+    }
+    if (m->precision != DMX_PRECISION_FP32)
+    {
+        set_error("model_forward: precision mode not available in this build");
+        return -1;
+    }
+    cudaStream_t st = m->stream;
+    Fwd f{m, B, st};
+    const int S = m->S, d = m->d_model;
+    m->stats_used = 0;
+    m->lastB = B;
+    DMX_CUDA(cudaMemsetAsync(m->stats, 0, m->stats_cap * sizeof(double), st));
+
+    // ---- STFT, CaC packing and the two input normalisations (src/model_inference.cpp:64-144) ----
+    double *sx = f.stat_slots(B), *sxt = f.stat_slots(B);
+    {
+        // algorithmic bytes: read the segment, write the CaC spectrogram (13.8 MB / segment)
+        ProfScope ps(m, PC_STFT, 0.0, (double)B * ((double)PADDED * 2 * 4 + (double)NBINS * T * 4 * 4));
+        if (launch_stft(d_mix, B, m->window, m->tw, m->spec, sx, st))
+            return -1;
+    }
+    {
+        ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * NBINS * T * 4 * 8.0);
+        if (launch_normalize_input(m->spec, B, (size_t)NBINS * T * 4, sx, m->meanstd_x, st))
+            return -1;
+    }
+    DMX_CUDA(cudaMemcpyAsync(m->xt_in, d_mix, (size_t)B * SEG * 2 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    {
+        ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * SEG * 2 * 4.0);
+        if (launch_sum_stats(m->xt_in, B, (size_t)SEG * 2, sxt, st))
+            return -1;
+    }
+    {
+        ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * SEG * 2 * 8.0);
+        if (launch_normalize_input(m->xt_in, B, (size_t)SEG * 2, sxt, m->meanstd_t, st))
+            return -1;
+    }
+
+    // ---- encoders (src/model_inference.cpp:155-212, src/encdec.cpp:8-164) ----
+    const float *xin_f = m->spec, *xin_t = m->xt_in;
+    for (int i = 0; i < 4; ++i)
+    {
+        const EncW &te = m->tenc[i];
+        const EncW &fe = m->enc[i];
+        const int C = fe.C;
+        // time: conv k8 s4 p2 (+GELU), ceil-mode length
+        {
+            GemmParams p = f.base(xin_t, te.Cin, te.Cin, te.conv, m->cA_t, C, 1, TLENS[i], 1, TLENS[i + 1]);
+            p.ntaps = 8;
+            p.sv = 4;
+            for (int t = 0; t < 8; ++t)
+            {
+                p.du[t] = 0;
+                p.dv[t] = t - 2;
+            }
+            p.act = 1;
+            f.gemm(p, PC_GEMM_CONV);
+            f.dconv(m->cA_t, 1, TLENS[i + 1], te.dc, m->h_t, m->y2_t, 0);
+            GemmParams r = f.base(m->cA_t, C, C, te.rewrite, m->te[i], C, 1, TLENS[i + 1], 1, TLENS[i + 1]);
+            r.glu = 1;
+            r.Nco = C;
+            f.gemm(r, PC_GEMM_CONV);
+        }
+        // freq: conv k8 s4 p2 along frequency (+GELU), frames are independent
+        {
+            GemmParams p = f.base(xin_f, fe.Cin, fe.Cin, fe.conv, m->cA_f, C, FREQS[i], T, FREQS[i + 1], T);
+            p.ntaps = 8;
+            p.su = 4;
+            for (int t = 0; t < 8; ++t)
+            {
+                p.du[t] = t - 2;
+                p.dv[t] = 0;
+            }
+            p.act = 1;
+            f.gemm(p, PC_GEMM_CONV);
+            f.dconv(m->cA_f, FREQS[i + 1], T, fe.dc, m->h_f, m->y2_f, 1);
+            GemmParams r = f.base(m->cA_f, C, C, fe.rewrite, m->e[i], C, FREQS[i + 1], T, FREQS[i + 1], T);
+            r.glu = 1;
+            r.Nco = C;
+            if (i == 0)
+            {
+                r.rowadd = m->freq_emb2;
+                r.rowadd_ld = 48;
+            }
+            f.gemm(r, PC_GEMM_CONV);
+        }
+        xin_t = m->te[i];
+        xin_f = m->e[i];
+    }
+
+    // ---- cross-transformer (src/model_inference.cpp:214-309, src/crosstransformer.cpp:205-339) ----
+    const int TF = 8 * T, TT = TLEN3;
+    const float *tok_f = m->e[3], *tok_t = m->te[3];
+    if (m->arch == DMX_ARCH_HTDEMUCS_4S)
+    {
+        f.gemm(f.linear(m->e[3], 384, m->up, m->up_f, d, TF), PC_GEMM_XFMR);
+        f.gemm(f.linear(m->te[3], 384, m->up_t, m->up_tt, d, TT), PC_GEMM_XFMR);
+        tok_f = m->up_f;
+        tok_t = m->up_tt;
+    }
+    f.layer_norm(tok_f, m->xq, B * TF, d, m->nin_w, m->nin_b, m->pe2d, TF);
+    f.layer_norm(tok_t, m->tq, B * TT, d, m->nint_w, m->nint_b, m->pe1d, TT);
+    for (int i = 0; i < 5; ++i)
+    {
+        if (i % 2 == 0)
+        {
+            f.tlayer(m->lay[i], m->xq, TF, nullptr, 0, m->ln_f, m->qkv_f, m->kv_f, m->ao_f, m->ff_f);
+            f.tlayer(m->lay_t[i], m->tq, TT, nullptr, 0, m->ln_t, m->qkv_t, m->kv_t, m->ao_t, m->ff_t);
+        }
+        else
+        {
+            // freq queries attend the current time tokens; time queries attend the freq tokens from BEFORE
+            // this layer's update (old_x, src/crosstransformer.cpp:286-295): normalise both key sets first.
+            f.layer_norm(m->tq, m->kn_f, B * TT, d, m->lay[i].n2w, m->lay[i].n2b);
+            f.layer_norm(m->xq, m->kn_t, B * TF, d, m->lay_t[i].n2w, m->lay_t[i].n2b);
+            f.tlayer(m->lay[i], m->xq, TF, m->kn_f, TT, m->ln_f, m->qkv_f, m->kv_f, m->ao_f, m->ff_f);
+            f.tlayer(m->lay_t[i], m->tq, TT, m->kn_t, TF, m->ln_t, m->qkv_t, m->kv_t, m->ao_t, m->ff_t);
+        }
+    }
+    const float *dec_in_f = m->xq, *dec_in_t = m->tq;
+    if (m->arch == DMX_ARCH_HTDEMUCS_4S)
+    {
+        f.gemm(f.linear(m->xq, d, m->down, m->x3d, 384, TF), PC_GEMM_XFMR);
+        f.gemm(f.linear(m->tq, d, m->down_t, m->xt3d, 384, TT), PC_GEMM_XFMR);
+        dec_in_f = m->x3d;
+        dec_in_t = m->xt3d;
+    }
+
+    // ---- decoders (src/model_inference.cpp:314-344, src/encdec.cpp:166-361) ----
+    for (int i = 0; i < 4; ++i)
+    {
+        const DecW &fd = m->dec[i];
+        const DecW &td = m->tdec[i];
+        const int C = fd.C, F = FREQS[4 - i], Lin = TLENS[4 - i], Lout = TLENS[3 - i];
+        {
+            // (x + skip) -> 3x3 conv -> GLU
+            GemmParams p = f.base(dec_in_f, C, C, fd.rewrite, m->cA_f, C, F, T, F, T);
+            p.A2 = m->e[3 - i];
+            p.ntaps = 9;
+            for (int kh = 0; kh < 3; ++kh)
+                for (int kw = 0; kw < 3; ++kw)
+                {
+                    p.du[kh * 3 + kw] = kh - 1;
+                    p.dv[kh * 3 + kw] = kw - 1;
+                }
+            p.glu = 1;
+            p.Nco = C;
+            f.gemm(p, PC_GEMM_CONV);
+            f.dconv(m->cA_f, F, T, fd.dc, m->h_f, m->y2_f, 1);
+            // ConvTranspose k(8,1) s(4,1) along frequency as a 2-tap GEMM, crop [2, 2+4F)
+            GemmParams q = f.base(m->cA_f, C, C, fd.convtr, m->dx[i], fd.Cout, F, T, F + 1, T);
+            q.ntaps = 2;
+            q.du[0] = -1;
+            q.du[1] = 0;
+            q.dv[0] = q.dv[1] = 0;
+            q.Nco = fd.Cout;
+            q.Uout = 4 * F;
+            q.Vout = T;
+            q.ous = 4;
+            q.our = 1;
+            q.ouo = -2;
+            q.act = i < 3 ? 1 : 0;
+            f.gemm(q, PC_GEMM_CONV);
+        }
+        {
+            GemmParams p = f.base(dec_in_t, C, C, td.rewrite, m->cA_t, C, 1, Lin, 1, Lin);
+            p.A2 = m->te[3 - i];
+            p.ntaps = 3;
+            for (int t = 0; t < 3; ++t)
+            {
+                p.du[t] = 0;
+                p.dv[t] = t - 1;
+            }
+            p.glu = 1;
+            p.Nco = C;
+            f.gemm(p, PC_GEMM_CONV);
+            f.dconv(m->cA_t, 1, Lin, td.dc, m->h_t, m->y2_t, 0);
+            GemmParams q = f.base(m->cA_t, C, C, td.convtr, m->dxt[i], td.Cout, 1, Lin, 1, Lin + 1);
+            q.ntaps = 2;
+            q.dv[0] = -1;
+            q.dv[1] = 0;
+            q.du[0] = q.du[1] = 0;
+            q.Nco = td.Cout;
+            q.Uout = 1;
+            q.Vout = Lout;
+            q.ous = 0;
+            q.ovs = 4;
+            q.ovr = 1;
+            q.ovo = -2;
+            q.act = i < 3 ? 1 : 0;
+            f.gemm(q, PC_GEMM_CONV);
+        }
+        dec_in_f = m->dx[i];
+        dec_in_t = m->dxt[i];
+    }
+    if (f.rc)
+        return -1;
+
+    // ---- de-normalise, per-source iSTFT, add time branch (src/model_inference.cpp:352-474) ----
+    {
+        // algorithmic bytes of iSTFT + mix (66.0 MB / segment for 4 sources)
+        ProfScope ps(m, PC_ISTFT_FRAMES, 0.0,
+                     (double)B * ((double)4 * S * NBINS * T * 4 + (double)2 * S * SEG * 4 + (double)S * 2 * SEG * 4));
+        if (launch_istft(m->dx[3], B, S, m->meanstd_x, m->window, m->tw, m->wss, m->dxt[3], m->meanstd_t, m->frames,
+                         d_out, st))
+            return -1;
+    }
+
+    m->taps.clear();
+    set_tap(m, "x", m->spec, NBINS, T, 4);
+    set_tap(m, "xt", m->xt_in, 1, SEG, 2);
+    for (int i = 0; i < 4; ++i)
+    {
+        const std::string si = std::to_string(i);
+        set_tap(m, ("saved_" + si).c_str(), m->e[i], FREQS[i + 1], T, CH[i + 1]);
+        set_tap(m, ("savedt_" + si).c_str(), m->te[i], 1, TLENS[i + 1], CH[i + 1]);
+    }
+    set_tap(m, "x_3_up", m->xq, 8, T, d);
+    set_tap(m, "xt_3_up", m->tq, 1, TLEN3, d);
+    set_tap(m, "x_3", const_cast<float *>(m->arch == DMX_ARCH_HTDEMUCS_4S ? m->x3d : m->xq), 8, T,
+            m->arch == DMX_ARCH_HTDEMUCS_4S ? 384 : d);
+    set_tap(m, "xt_3", const_cast<float *>(m->arch == DMX_ARCH_HTDEMUCS_4S ? m->xt3d : m->tq), 1, TLEN3,
+            m->arch == DMX_ARCH_HTDEMUCS_4S ? 384 : d);
+    const char *fn[4] = {"x_2", "x_1", "x_0", "x_out"};
+    const char *tn[4] = {"xt_2", "xt_1", "xt_0", "xt_out"};
+    for (int i = 0; i < 4; ++i)
+    {
+        set_tap(m, fn[i], m->dx[i], FREQS[3 - i], T, m->dec[i].Cout);
+        set_tap(m, tn[i], m->dxt[i], 1, TLENS[3 - i], m->tdec[i].Cout);
+    }
+    return 0;
+}
+
+} // namespace dmx

@@ -1,0 +1,155 @@
+// Device-side model: packed weights, workspace and the htdemucs forward orchestration.
+#pragma once
+#include "kernels.cuh"
+#include "demucs_b200.h"
+
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace dmx
+{
+
+struct HostTensor
+{
+    std::vector<float> data;
+    std::vector<int> shape;
+    size_t numel() const { return data.size(); }
+};
+
+// A GEMM B-operand: fp32 [Kpad][ldw] zero padded (+ padded bias).
+struct Packed
+{
+    float *W = nullptr;
+    float *bias = nullptr;
+    int K = 0, N = 0, ldw = 0;
+};
+
+struct DConvW
+{
+    Packed c1[2], c2[2];
+    float *g1w[2], *g1b[2], *g2w[2], *g2b[2], *scale[2];
+    int C = 0, hid = 0;
+};
+
+struct EncW
+{
+    Packed conv, rewrite;
+    DConvW dc;
+    int Cin = 0, C = 0;
+};
+
+struct DecW
+{
+    Packed rewrite, convtr;
+    DConvW dc;
+    int C = 0, Cout = 0;
+};
+
+struct TLayerW
+{
+    bool cross = false;
+    Packed qkv, q, kv, out, ff1, ff2;
+    float *n1w, *n1b, *n2w, *n2b, *n3w, *n3b, *now_, *nob, *g1, *g2;
+};
+
+// Per-kernel-class CUDA-event timing (bench.py's roofline): events are recorded on the model's own
+// stream around every launch while profiling is on.
+enum ProfClass
+{
+    PC_STFT = 0,
+    PC_ISTFT_FRAMES,
+    PC_ISTFT_OLA,
+    PC_POINTWISE,
+    PC_GEMM_CONV,
+    PC_GEMM_DCONV,
+    PC_GEMM_XFMR,
+    PC_ATTENTION,
+    PC_TRACK,
+    PC_COUNT
+};
+
+struct ProfRec
+{
+    int cls;
+    cudaEvent_t e0, e1;
+};
+
+struct Profiler
+{
+    bool on = false;
+    std::vector<cudaEvent_t> pool;
+    size_t used = 0;
+    std::vector<ProfRec> recs;
+    double flops[PC_COUNT] = {0};
+    double bytes[PC_COUNT] = {0};
+    cudaEvent_t get();
+};
+
+struct Tap
+{
+    float *ptr = nullptr;
+    int64_t d1 = 0, d2 = 0, C = 0; // per batch item dims (channels-last)
+};
+
+} // namespace dmx
+
+struct dmx_model
+{
+    int arch = 0, S = 4, d_model = 512, device = 0, maxB = 1, precision = 0;
+    bool finalized = false;
+    std::map<std::string, dmx::HostTensor> host;
+    std::vector<void *> allocs;
+    cudaStream_t stream = nullptr;
+    std::mutex mtx;
+    int64_t launches = 0;
+    dmx::Profiler prof;
+
+    // weights
+    dmx::EncW enc[4], tenc[4];
+    dmx::DecW dec[4], tdec[4];
+    float *freq_emb2 = nullptr;
+    dmx::Packed up, up_t, down, down_t;
+    float *nin_w, *nin_b, *nint_w, *nint_b, *pe2d, *pe1d;
+    dmx::TLayerW lay[5], lay_t[5];
+    float *window = nullptr, *tw = nullptr, *wss = nullptr;
+
+    // workspace (all sized for maxB)
+    float *mix, *spec, *xt_in, *cA_f, *cA_t, *e[4], *te[4], *dx[4], *dxt[4];
+    float *h_f, *y2_f, *h_t, *y2_t;
+    float *up_f, *up_tt, *xq, *tq, *ln_f, *ln_t, *kn_f, *kn_t, *qkv_f, *qkv_t, *kv_f, *kv_t, *ao_f, *ao_t, *ff_f,
+        *ff_t, *x3d, *xt3d;
+    float *frames, *seg_out;
+    float *meanstd_x, *meanstd_t;
+    double *stats = nullptr;
+    size_t stats_cap = 0, stats_used = 0;
+    int lastB = 0;
+    std::map<std::string, dmx::Tap> taps;
+
+    // track-level buffers (grow only)
+    float *d_audio = nullptr, *d_y = nullptr, *d_out = nullptr;
+    size_t cap_audio = 0, cap_y = 0, cap_out = 0;
+    double *track_stats = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr; // device time of the last track-level call
+};
+
+namespace dmx
+{
+int model_finalize(dmx_model *m);
+int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out); // d_out: [B][S][SEG][2]
+// RAII: brackets the launches issued inside its scope with events when profiling is on
+struct ProfScope
+{
+    dmx_model *m;
+    cudaEvent_t e1 = nullptr;
+    ProfScope(dmx_model *m_, int cls, double flops = 0.0, double bytes = 0.0);
+    ~ProfScope();
+};
+int track_forward_shard(dmx_model *m, const float *d_audio, int64_t L, int shift, int rank, int world, float *d_y,
+                        dmx_progress_fn cb, void *user);
+int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, const float *d_y_all, int world,
+                      float *d_out);
+int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
+                   void *user);
+} // namespace dmx

@@ -1,0 +1,294 @@
+// Track-level orchestration on device: the reference's demucs_inference / shift_inference /
+// split_inference / segment_inference (src/model_apply.cpp:60-288) with segments batched.
+//   normalise by the mono mean / unbiased std           (:72-82)
+//   zero-pad 0.5 s each side, shift by `offset`           (:103-121)
+//   7.8 s segments at stride 0.75*7.8 s, short last chunk centre-padded with zeros (:21-43,:200-204,:260-261)
+//   triangular-weighted overlap-add, divide by the weight sum (:171-179,:207-246)
+//   trim to the original length, de-normalise            (:129-135,:88)
+// The overlap-add is a gather (each output sample is covered by at most two segments), so no atomics
+// and no zero-initialised accumulator are needed; terms are added in increasing segment order like
+// the reference's loop.
+#include "model.cuh"
+
+#include <utility>
+
+namespace dmx
+{
+
+// sum / sumsq of the mono signal (mean over the two channels), n frames
+__global__ void __launch_bounds__(256) mono_stats_kernel(const float2 *__restrict__ a, int64_t n, double *stats)
+{
+    double ds = 0, dss = 0;
+    float s = 0.f, ss = 0.f;
+    int cnt = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    {
+        const float2 v = __ldg(&a[i]);
+        const float mono = (v.x + v.y) * 0.5f;
+        s += mono;
+        ss += mono * mono;
+        if (++cnt == 64)
+        {
+            ds += s;
+            dss += ss;
+            s = ss = 0.f;
+            cnt = 0;
+        }
+    }
+    ds += s;
+    dss += ss;
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        ds += __shfl_xor_sync(0xffffffffu, ds, o);
+        dss += __shfl_xor_sync(0xffffffffu, dss, o);
+    }
+    __shared__ double red[2][8];
+    if ((threadIdx.x & 31) == 0)
+    {
+        red[0][threadIdx.x >> 5] = ds;
+        red[1][threadIdx.x >> 5] = dss;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double x = 0, y = 0;
+        for (int i = 0; i < 8; ++i)
+        {
+            x += red[0][i];
+            y += red[1][i];
+        }
+        atomicAdd(&stats[0], x);
+        atomicAdd(&stats[1], y);
+    }
+}
+
+__device__ __forceinline__ void track_mean_std(const double *stats, int64_t n, float &mean, float &stdv)
+{
+    const double s = stats[0], ss = stats[1];
+    const double m = s / (double)n;
+    double var = (ss - s * m) / ((double)n - 1.0);
+    if (var < 0)
+        var = 0;
+    mean = (float)m;
+    stdv = (float)sqrt(var);
+}
+
+// segs[j][i], j = blockIdx.y: normalised, shifted, centre zero padded segment k = k0 + j*kstride
+__global__ void __launch_bounds__(256) extract_segments_kernel(const float2 *__restrict__ audio, int64_t L, int offset,
+                                                               int64_t Ls, const double *__restrict__ stats, int k0,
+                                                               int kstride, float2 *__restrict__ segs)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= SEG)
+        return;
+    const int k = k0 + blockIdx.y * kstride;
+    float mean, stdv;
+    track_mean_std(stats, L, mean, stdv);
+    const int64_t off = (int64_t)k * SEG_STRIDE;
+    const int64_t nk = (Ls - off) < SEG ? (Ls - off) : SEG;
+    const int left = (int)((SEG - nk) / 2);
+    float2 v = make_float2(0.f, 0.f);
+    const int64_t j = i - left;
+    if (j >= 0 && j < nk)
+    {
+        const int64_t src = off + j + offset - MAX_SHIFT; // index into the un-padded track
+        if (src >= 0 && src < L)
+        {
+            const float2 a = __ldg(&audio[src]);
+            v.x = (a.x - mean) / stdv;
+            v.y = (a.y - mean) / stdv;
+        }
+    }
+    segs[(size_t)blockIdx.y * SEG + i] = v;
+}
+
+// out (S, 2, L) Eigen column-major: index s + S*(ch + 2*t)
+// y holds segment k in slot (k % world)*cnt + k / world (the layout a gather of round-robin shards gives;
+// world = 1: slot = k).
+__global__ void __launch_bounds__(256) overlap_add_kernel(const float2 *__restrict__ y, // [slots][S][SEG]
+                                                          int S, int nseg, int world, int cnt, int64_t L, int offset,
+                                                          int64_t Ls, const double *__restrict__ stats,
+                                                          float *__restrict__ out)
+{
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t0 >= L)
+        return;
+    float mean, stdv;
+    track_mean_std(stats, L, mean, stdv);
+    const int64_t t = t0 + MAX_SHIFT - offset; // position in the shifted track
+    const int khi = (int)(t / SEG_STRIDE);
+    const float h = (float)(SEG / 2);
+    for (int s = 0; s < S; ++s)
+    {
+        float2 num = make_float2(0.f, 0.f);
+        float den = 0.f;
+        for (int k = khi - 1; k <= khi; ++k)
+        {
+            if (k < 0 || k >= nseg)
+                continue;
+            const int64_t off = (int64_t)k * SEG_STRIDE;
+            const int64_t nk = (Ls - off) < SEG ? (Ls - off) : SEG;
+            const int64_t i = t - off;
+            if (i < 0 || i >= nk)
+                continue;
+            const int left = (int)((SEG - nk) / 2);
+            const int ii = (int)i;
+            const float w = (float)(ii + 1 < SEG - ii ? ii + 1 : SEG - ii) / h;
+            const size_t slot = (size_t)(k % world) * cnt + (size_t)(k / world);
+            const float2 v = __ldg(&y[(slot * S + s) * SEG + left + ii]);
+            num.x += w * v.x;
+            num.y += w * v.y;
+            den += w;
+        }
+        out[s + (size_t)S * (0 + 2 * t0)] = (num.x / den) * stdv + mean;
+        out[s + (size_t)S * (1 + 2 * t0)] = (num.y / den) * stdv + mean;
+    }
+}
+
+static int ensure(float **p, size_t *cap, size_t n)
+{
+    if (*cap >= n)
+        return 0;
+    if (*p)
+        DMX_CUDA(cudaFree(*p));
+    *p = nullptr;
+    *cap = 0;
+    DMX_CUDA(cudaMalloc(reinterpret_cast<void **>(p), n * sizeof(float)));
+    *cap = n;
+    return 0;
+}
+
+int num_segments(int64_t L, int shift)
+{
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    return (int)((Ls + SEG_STRIDE - 1) / SEG_STRIDE);
+}
+
+// Messages of the reference's per-segment progress callbacks (src/model_inference.cpp:156-344), fired
+// after each batch completes (a batched device forward has no truthful mid-segment progress).
+static const char *const kStageMsgs[26] = {
+    "Time encoder 0", "Freq encoder 0", "Time encoder 1", "Freq encoder 1", "Time encoder 2", "Freq encoder 2",
+    "Time encoder 3", "Freq encoder 3", "Freq (crosstransformer): layer 0", "Time (crosstransformer): layer 0",
+    "Freq (crosstransformer): layer 1", "Time (crosstransformer): layer 1", "Freq (crosstransformer): layer 2",
+    "Time (crosstransformer): layer 2", "Freq (crosstransformer): layer 3", "Time (crosstransformer): layer 3",
+    "Freq (crosstransformer): layer 4", "Time (crosstransformer): layer 4", "Freq: decoder 0", "Time: decoder 0",
+    "Freq: decoder 1", "Time: decoder 1", "Freq: decoder 2", "Time: decoder 2", "Freq: decoder 3", "Time: decoder 3"};
+
+static int track_stats(dmx_model *m, const float *d_audio, int64_t L)
+{
+    cudaStream_t st = m->stream;
+    DMX_CUDA(cudaMemsetAsync(m->track_stats, 0, 2 * sizeof(double), st));
+    {
+        ProfScope ps(m, PC_TRACK, 0.0, (double)L * 8.0);
+        mono_stats_kernel<<<592, 256, 0, st>>>((const float2 *)d_audio, L, m->track_stats);
+    }
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+static int check_track_args(int64_t L, int shift, int rank, int world)
+{
+    if (L < 2)
+    {
+        set_error("separate: track too short");
+        return -1;
+    }
+    if (shift < 0 || shift >= MAX_SHIFT)
+    {
+        set_error("separate: shift_offset must be in [0, 22050)");
+        return -1;
+    }
+    if (world < 1 || rank < 0 || rank >= world)
+    {
+        set_error("separate: bad rank/world");
+        return -1;
+    }
+    return 0;
+}
+
+// Forward of this rank's share of the track's segments: k = rank, rank + world, ...  Results go to
+// d_y[j] (j = k / world), each [S][SEG][2].  No inter-rank communication here: segments are independent
+// given the track statistics, which every rank computes from the full track.
+int track_forward_shard(dmx_model *m, const float *d_audio, int64_t L, int shift, int rank, int world, float *d_y,
+                        dmx_progress_fn cb, void *user)
+{
+    if (check_track_args(L, shift, rank, world))
+        return -1;
+    cudaStream_t st = m->stream;
+    const int S = m->S;
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    const int nseg = num_segments(L, shift);
+    DMX_CUDA(cudaEventRecord(m->ev0, st));
+    if (track_stats(m, d_audio, L))
+        return -1;
+    const int nloc = rank < nseg ? (nseg - rank + world - 1) / world : 0;
+    for (int j0 = 0; j0 < nloc; j0 += m->maxB)
+    {
+        const int nb = (nloc - j0) < m->maxB ? (nloc - j0) : m->maxB;
+        {
+            ProfScope ps(m, PC_TRACK, 0.0, (double)nb * SEG * 16.0);
+            extract_segments_kernel<<<dim3((SEG + 255) / 256, nb), 256, 0, st>>>(
+                (const float2 *)d_audio, L, shift, Ls, m->track_stats, rank + j0 * world, world, (float2 *)m->mix);
+        }
+        DMX_LAUNCH_CHECK();
+        if (model_forward(m, m->mix, nb, d_y + (size_t)j0 * S * SEG * 2))
+            return -1;
+        if (cb)
+        {
+            // keep the reference's per-segment message sequence with monotone progress values
+            DMX_CUDA(cudaStreamSynchronize(st));
+            for (int j = j0; j < j0 + nb; ++j)
+                for (int sidx = 0; sidx < 26; ++sidx)
+                    cb(((float)j + (float)(sidx + 1) / 26.0f) / (float)nloc, kStageMsgs[sidx], user);
+        }
+    }
+    DMX_CUDA(cudaEventRecord(m->ev1, st));
+    DMX_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// Weighted overlap-add of all segments (gathered in round-robin shard order), trim, de-normalise.
+int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, const float *d_y_all, int world,
+                      float *d_out)
+{
+    if (check_track_args(L, shift, 0, world))
+        return -1;
+    cudaStream_t st = m->stream;
+    const int S = m->S;
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    const int nseg = num_segments(L, shift);
+    const int cnt = (nseg + world - 1) / world;
+    DMX_CUDA(cudaEventRecord(m->ev0, st));
+    if (track_stats(m, d_audio, L))
+        return -1;
+    {
+        ProfScope ps(m, PC_TRACK, 0.0, (double)L * S * 8.0 * 2.3);
+        overlap_add_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>((const float2 *)d_y_all, S, nseg, world, cnt, L,
+                                                                       shift, Ls, m->track_stats, d_out);
+    }
+    DMX_LAUNCH_CHECK();
+    DMX_CUDA(cudaEventRecord(m->ev1, st));
+    DMX_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
+                   void *user)
+{
+    if (check_track_args(L, shift, 0, 1))
+        return -1;
+    const int nseg = num_segments(L, shift);
+    if (ensure(&m->d_y, &m->cap_y, (size_t)nseg * m->S * SEG * 2))
+        return -1;
+    cudaEvent_t e0 = m->ev2;
+    DMX_CUDA(cudaEventRecord(e0, m->stream));
+    if (track_forward_shard(m, d_audio, L, shift, 0, 1, m->d_y, cb, user))
+        return -1;
+    if (track_overlap_add(m, d_audio, L, shift, m->d_y, 1, d_out))
+        return -1;
+    // whole-call device time: from before the shard to the end of the overlap-add
+    std::swap(m->ev0, m->ev2);
+    return 0;
+}
+
+} // namespace dmx

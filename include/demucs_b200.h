@@ -1,0 +1,136 @@
+/* demucs_b200 -- C ABI of the B200-native (sm_100a) inference hot path of sevagh/demucs.cpp.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  The host side of the
+ * reference's C++17 API (src/model.hpp: load_demucs_model / demucs_inference and their v3 twins) is
+ * a thin shim over these entry points (see INTEGRATION.md and compat/model.hpp).  Every function
+ * returns 0 on success and non-zero on failure (message via dmx_last_error()); nothing throws and
+ * there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ *
+ * Data conventions (identical to the reference):
+ *   audio in   : float32, L stereo frames interleaved L,R,L,R = Eigen::MatrixXf(2, L) column-major
+ *   stems out  : float32 (S, 2, L) Eigen column-major, i.e. index s + S*(ch + 2*t); source order
+ *                drums, bass, other, vocals(, guitar, piano)        (cli-apps/demucs.cpp:185-204)
+ *   weights    : the reference's ggml-style f16 file (scripts/convert-pth-to-ggml.py:111-140)
+ */
+#ifndef DEMUCS_B200_H
+#define DEMUCS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C"
+{
+#endif
+
+    typedef struct dmx_model dmx_model;
+
+    /* Progress callback, same meaning as demucscpp::ProgressCallback (src/model.hpp:17):
+     * fraction in [0,1] and a message.  Invoked on the calling thread only. */
+    typedef void (*dmx_progress_fn)(float progress, const char *message, void *user);
+
+    /* Precision modes (BASELINE.json north_star: "bf16 mode" and "fp32 mode"). */
+    enum
+    {
+        DMX_PRECISION_FP32 = 0, /* CUDA-core fp32 everywhere; per-layer tolerance 1e-4 */
+        DMX_PRECISION_BF16 = 1  /* bf16 tensor-core GEMM operands, fp32 accumulate/residual/statistics */
+    };
+
+    /* Architectures, selected by the file magic (src/model_load.cpp:77-102, :1331). */
+    enum
+    {
+        DMX_ARCH_HTDEMUCS_4S = 4, /* 'dmc4' 0x646d6334: htdemucs and each htdemucs_ft member */
+        DMX_ARCH_HTDEMUCS_6S = 6, /* 'dmc6' 0x646d6336 */
+        DMX_ARCH_HDEMUCS_V3 = 3   /* 'dmc3' 0x646d6333 (hdemucs_mmi) */
+    };
+
+    /* Number of visible CUDA devices (0 if none); the library never falls back to the CPU. */
+    int dmx_device_count(void);
+
+    /* Last error message of the calling thread ("" if none). */
+    const char *dmx_last_error(void);
+
+    /* ---- model construction: replaces demucscpp::load_demucs_model (src/model.hpp:649-650,
+     *      src/model_load.cpp:50-1090).  Either load a whole ggml-f16 file, or create an empty
+     *      model and feed tensors one by one (what the reference's in-memory loader,
+     *      src_wasm/model_load.hpp:73, does), then finalize.  `max_batch` = number of 7.8 s
+     *      segments processed per launch (workspace is sized for it). ---- */
+    dmx_model *dmx_model_load_file(const char *ggml_path, int device, int max_batch);
+    dmx_model *dmx_model_create(int arch, int device, int max_batch);
+    /* name = PyTorch state_dict key; data = f16 bits, row-major, `ne` = squeezed shape
+     * (record layout of src/model_load.cpp:120-147). */
+    int dmx_model_set_tensor(dmx_model *m, const char *name, const uint16_t *f16, const int32_t *ne, int n_dims);
+    /* Checks that every tensor of the architecture is present with the right element count
+     * (src/model_load.cpp:1065-1070,1096-1105 reject unknown/mis-sized tensors), repacks to the
+     * GEMM layouts and uploads to the device. */
+    int dmx_model_finalize(dmx_model *m);
+    void dmx_model_free(dmx_model *m);
+
+    int dmx_model_arch(const dmx_model *m);    /* DMX_ARCH_* */
+    int dmx_model_sources(const dmx_model *m); /* 4 or 6 (demucs_model::is_4sources, src/model.hpp:287) */
+    int dmx_model_max_batch(const dmx_model *m);
+    int dmx_model_set_precision(dmx_model *m, int precision);
+
+    /* ---- whole-track separation: replaces demucscpp::demucs_inference (src/model.hpp:658-660,
+     *      src/model_apply.cpp:60-288): normalise by the mono mean/std, zero-pad 0.5 s, shift by
+     *      `shift_offset` samples (the reference draws rand() % 22050, src/model_apply.cpp:114; the
+     *      caller passes it so results are reproducible), split into 7.8 s segments with 25 %
+     *      overlap, run the per-segment forward, triangular-weighted overlap-add, de-normalise.
+     *      audio/out are HOST buffers; copies are inside the call. ---- */
+    int dmx_separate(dmx_model *m, const float *audio_lr, int64_t n_frames, int shift_offset, float *out,
+                     dmx_progress_fn cb, void *user);
+
+    /* Same with DEVICE-resident audio and output (cudaMalloc'd by the caller, e.g. a torch tensor's
+     * data_ptr); stream = 0 uses the model's own stream.  Asynchronous w.r.t. the host only up to the
+     * internal synchronisation at the end of the call. */
+    int dmx_separate_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset,
+                            float *d_out);
+
+    /* ---- multi-GPU building blocks (one process per GPU; the reference's only parallel strategy is the
+     *      chunk-level std::thread fan-out of cli-apps/threaded_inference.hpp:110-123, which this
+     *      replaces with segment-level sharding): rank r of `world` runs segments r, r+world, ... of the
+     *      track into d_y (device, [ceil(nseg/world)][S][343980][2]); after the shards are gathered
+     *      rank-major into d_y_all ([world][ceil(nseg/world)][S][343980][2]) one rank overlap-adds. ---- */
+    int dmx_forward_shard_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset, int rank,
+                                 int world, float *d_y);
+    int dmx_overlap_add_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset,
+                               const float *d_y_all, int world, float *d_out);
+    /* Device milliseconds (CUDA events on the model's stream) of the last separate / shard / overlap-add call. */
+    double dmx_last_device_ms(dmx_model *m);
+
+    /* Number of segments demucs_inference cuts a track of n_frames into for this shift
+     * (src/model_apply.cpp:186,200). */
+    int dmx_num_segments(int64_t n_frames, int shift_offset);
+
+    /* ---- per-segment forward: replaces demucscpp::model_inference (src/model.hpp:662-666,
+     *      src/model_inference.cpp:48-475) on a batch of full 343980-frame segments.
+     *      segs: host (B, 343980, 2) interleaved; out: host (B, S, 343980, 2). ---- */
+    int dmx_forward_segments(dmx_model *m, const float *segs, int n_segments, float *out);
+
+    /* Test hook standing in for the reference's public per-segment scratch struct
+     * (demucs_segment_buffers, src/model.hpp:569-647): copies a named activation left by the last
+     * dmx_forward_segments call to the host.  dims[4] receives (B, d1, d2, C) of the channels-last
+     * device layout; returns the element count, or -1.  With dst == NULL only dims are filled. */
+    int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capacity, int64_t dims[4]);
+
+    /* Kernel launches issued by this model's forward passes so far (for bench.py's gpu_launches). */
+    int64_t dmx_launch_count(const dmx_model *m);
+
+    /* ---- measurement hook (no reference counterpart; the reference has no tracing):
+     *      between begin and end every kernel launch of this model is bracketed by CUDA events on the
+     *      model's stream and accumulated per kernel class.  Arrays have dmx_profile_classes() entries:
+     *      device milliseconds, launch counts, algorithmic FLOPs and algorithmic bytes per class. ---- */
+    int dmx_profile_classes(void);
+    const char *dmx_profile_class_name(int cls);
+    int dmx_profile_begin(dmx_model *m);
+    int dmx_profile_end(dmx_model *m, double *ms, int64_t *launches, double *flops, double *bytes);
+
+    /* ---- stand-alone DSP pair: replaces demucscpp::stft / demucscpp::istft (src/dsp.hpp:103-104,
+     *      src/dsp.cpp:51-117) on one 343980-frame stereo segment, through the same kernels the
+     *      forward uses.  spec: host (2048, 336, 4) = [bin][frame](ReL, ImL, ReR, ImR), un-normalised. */
+    int dmx_stft_segment(dmx_model *m, const float *seg_lr, float *spec);
+    int dmx_istft_segment(dmx_model *m, const float *spec, float *seg_lr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEMUCS_B200_H */
