@@ -30,7 +30,7 @@ EXPORTS = [
     "dmx_model_set_precision", "dmx_separate", "dmx_separate_device", "dmx_num_segments", "dmx_forward_segments",
     "dmx_debug_tap", "dmx_launch_count", "dmx_stft_segment", "dmx_istft_segment", "dmx_profile_classes",
     "dmx_profile_class_name", "dmx_profile_begin", "dmx_profile_end", "dmx_forward_shard_device",
-    "dmx_overlap_add_device", "dmx_last_device_ms",
+    "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
 ]
 
 _lib = None
@@ -70,6 +70,7 @@ def lib():
         L.dmx_overlap_add_device.argtypes = [vp, vp, i64, ci, vp, ci, vp]
         L.dmx_last_device_ms.restype = ctypes.c_double
         L.dmx_last_device_ms.argtypes = [vp]
+        L.dmx_stft_segments_noalloc.argtypes = [vp, vp, ci, vp, vp, vp]
         L.dmx_profile_class_name.restype = ctypes.c_char_p
         L.dmx_profile_class_name.argtypes = [ci]
         L.dmx_profile_begin.argtypes = [vp]

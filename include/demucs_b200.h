@@ -130,6 +130,28 @@ extern "C"
     int dmx_stft_segment(dmx_model *m, const float *seg_lr, float *spec);
     int dmx_istft_segment(dmx_model *m, const float *spec, float *seg_lr);
 
+    /* ---- allocation-free batched segment STFT.  No counterpart in the reference (its stft,
+     *      src/dsp.cpp:51-86, works on host vectors it owns); this is an extra for callers that are not
+     *      allowed to allocate device memory when they call in -- real-time audio threads, hosts that
+     *      run from a fixed pre-reserved pool, code inside a no-allocation region.  Same computation
+     *      and same kernel as dmx_stft_segment, but: input and output are DEVICE buffers the caller
+     *      owns (d_segs (n, 343980, 2) interleaved -> d_spec (n, 2048, 336, 4); optional d_meanstd
+     *      (n, 2) receives each segment's spectrogram mean and unbiased std, may be NULL), and the
+     *      kernel's statistics workspace is a fixed array inside the library image instead of
+     *      cudaMalloc'd memory.  The call performs no cudaMalloc/cudaFree and calls no allocating
+     *      routine.  Limits and caveats:
+     *        - at most DMX_NOALLOC_MAX_SEGMENTS segments per call, larger n is rejected with an error;
+     *        - the workspace (1 KiB) exists on every GPU that loads the library, until process exit;
+     *        - all calls on a device share it: it is cleared at the start of each call, and calls
+     *          whose GPU work overlaps race with each other -- serialise them;
+     *        - the first call on each device resolves the workspace's device address; make that first
+     *          call before beginning any stream capture;
+     *        - `stream` is a cudaStream_t to enqueue on (the call then returns without waiting), or
+     *          NULL to use the model's own stream and wait for completion. ---- */
+#define DMX_NOALLOC_MAX_SEGMENTS 64
+    int dmx_stft_segments_noalloc(dmx_model *m, const float *d_segs, int n_segments, float *d_spec, float *d_meanstd,
+                                  void *stream);
+
 #ifdef __cplusplus
 }
 #endif
