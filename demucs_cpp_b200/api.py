@@ -31,6 +31,7 @@ EXPORTS = [
     "dmx_debug_tap", "dmx_launch_count", "dmx_stft_segment", "dmx_istft_segment", "dmx_profile_classes",
     "dmx_profile_class_name", "dmx_profile_begin", "dmx_profile_end", "dmx_forward_shard_device",
     "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
+    "dmx_debug_linear",
 ]
 
 _lib = None
@@ -71,6 +72,7 @@ def lib():
         L.dmx_last_device_ms.restype = ctypes.c_double
         L.dmx_last_device_ms.argtypes = [vp]
         L.dmx_stft_segments_noalloc.argtypes = [vp, vp, ci, vp, vp, vp]
+        L.dmx_debug_linear.argtypes = [ci, ci, ci, ci, ci, vp, vp, vp, ci, vp, ci, vp]
         L.dmx_profile_class_name.restype = ctypes.c_char_p
         L.dmx_profile_class_name.argtypes = [ci]
         L.dmx_profile_begin.argtypes = [vp]
@@ -221,6 +223,21 @@ class DemucsModel:
         out = np.empty((SEG, 2), dtype=np.float32)
         _check(lib().dmx_istft_segment(self._h, _p(s), _p(out)), "dmx_istft_segment")
         return np.ascontiguousarray(out.T)
+
+
+def debug_linear(A, W, bias=None, act=0, precision=PRECISION_FP32, device=0, iters=0):
+    """act(A (M,K) @ W (N,K)^T + bias) through the production GEMM kernels (test hook).
+    With iters > 0 returns (out, average kernel ms)."""
+    A = np.ascontiguousarray(A, dtype=np.float32)
+    W = np.ascontiguousarray(W, dtype=np.float32)
+    M, K = A.shape
+    N = W.shape[0]
+    out = np.empty((M, N), dtype=np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, dtype=np.float32)
+    ms = ctypes.c_float(0.0)
+    _check(lib().dmx_debug_linear(device, precision, M, N, K, _p(A), _p(W), None if b is None else _p(b), act,
+                                  _p(out), iters, ctypes.byref(ms)), "dmx_debug_linear")
+    return (out, ms.value) if iters > 0 else out
 
 
 def load_demucs_model(path, **kw):

@@ -496,6 +496,22 @@ int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capaci
     return n;
 }
 
+int dmx_debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
+                     int act, float *out, int iters, float *ms_out)
+{
+    if (!A || !W || !out || M < 1 || N < 1 || K < 1)
+    {
+        set_error("dmx_debug_linear: bad argument");
+        return -1;
+    }
+    if (dmx_device_count() < 1)
+    {
+        set_error("dmx_debug_linear: no CUDA device (this library has no CPU fallback)");
+        return -1;
+    }
+    return debug_linear(device, precision, M, N, K, A, W, bias, act, out, iters, ms_out);
+}
+
 int dmx_stft_segment(dmx_model *m, const float *seg_lr, float *spec)
 {
     if (!m || !seg_lr || !spec)

@@ -1,0 +1,739 @@
+// bf16 tensor-core tap-GEMM for sm_100a: tcgen05.mma (one elected thread issues), fp32 accumulators in
+// TMEM, operands in shared memory in the canonical no-swizzle K-major core-matrix layout.
+//
+//   * A operand (activations, fp32 channels-last in HBM) is gathered per output row by 128 producer
+//     threads -- one tile row each -- with the tap / zero-padding predicates of the implicit GEMM and the
+//     fused prologues (skip add, GroupNorm+GELU) applied in registers, converted to bf16 and stored as
+//     16-byte core-matrix rows (a warp writes 512 contiguous bytes: conflict free).
+//   * B operand (weights) is pre-packed on the host as the exact shared-memory image of every
+//     (n-tile, k-block) and fetched with ONE 1-D bulk async copy (cp.async.bulk ... mbarrier
+//     complete_tx) per stage -- no tensor map needed.
+//   * A 3/4-stage mbarrier ring couples producers and the MMA thread (full[] : 128 row arrivals + the
+//     bulk copy's transaction bytes; empty[] : tcgen05.commit).  The same 128 threads then run the
+//     epilogue: tcgen05.ld of their own TMEM lane (= their output row), bias / GELU / GLU / LayerScale
+//     residual / GroupNorm statistics / transposed-conv scatter, fp32 stores.
+//
+// Tile: 128 rows x BN columns (BN = N rounded to 16, <= 256, chosen per layer), BK = 64.
+#include "kernels.cuh"
+
+#include <cuda_bf16.h>
+
+namespace dmx
+{
+namespace tc
+{
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                 "selp.u32 %0, 1, 0, p;\n"
+                 "}\n"
+                 : "=r"(ok)
+                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug traps (launch error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t n = 0;
+    while (!mbar_try_wait(bar, parity))
+        if (++n > (1u << 22))
+            __trap();
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, SWIZZLE_NONE, K-major: core matrix = 8 rows x 16 bytes;
+// LBO = byte distance between the two K-adjacent core matrices of one UMMA_K=16 slice,
+// SBO = byte distance between 8-row groups.  (bit layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46; // descriptor version for sm_100
+    return d;               // base_offset = 0, lbo_mode = 0, layout_type = SWIZZLE_NONE (0)
+}
+
+// Instruction descriptor for kind::f16: D = F32, A = B = BF16, both K-major, M = 128, N = bn.
+__device__ __forceinline__ uint32_t make_idesc(int bn)
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "setp.ne.b32 p, %4, 0;\n"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+                 "}\n" ::"r"(tmem_d),
+                 "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
+{
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+        v[i] = __uint_as_float(r[i]);
+}
+
+struct RowCoord
+{
+    int b, uo, vo;
+};
+__device__ __forceinline__ RowCoord decode_row(int m, int Uo, int Vo)
+{
+    RowCoord rc;
+    const int per = Uo * Vo;
+    rc.b = m / per;
+    const int r = m - rc.b * per;
+    rc.uo = r / Vo;
+    rc.vo = r - rc.uo * Vo;
+    return rc;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi)
+{
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// Per-row bookkeeping for the epilogue.
+struct RowInfo
+{
+    long long outoff; // element offset in C of (b, uo*ous + ouo, vo*ovs + ovo), channel 0 (may be "virtual")
+    int uu0, vv0;     // that output position (for the bounds checks of the scatter mapping)
+    int uo, item;     // input-row frequency index (row-add table) and statistics item (-1: row invalid)
+};
+
+constexpr int PROD_WARPS = 8;
+constexpr int PROD_THREADS = PROD_WARPS * 32;   // 256: A producers, then epilogue
+constexpr int THREADS = PROD_THREADS + 64;      // + warp 8 (B loader) + warp 9 (MMA issuer)
+constexpr int A_LBO = BM * 16 + 16;             // 2064 B: +16 B pad makes the producers' 16-byte stores conflict free
+constexpr int A_STAGE = 8 * A_LBO;              // 16512 B per stage
+constexpr int EPI_LD = 36;                      // floats per staged row (32 + 4 pad)
+constexpr int EPI_BYTES = PROD_WARPS * 32 * EPI_LD * 4;
+
+// Store 4 consecutive OUTPUT columns nc0..nc0+3 of one row (general mapping: transposed-conv scatter).
+__device__ __forceinline__ void store_group4_scatter(const GemmParams &p, const RowInfo &ri, int nc0, int nlimit,
+                                                     float (&o)[4], float &rs, float &rss)
+{
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+    {
+        const int nc = nc0 + e;
+        if (nc < nlimit)
+        {
+            const int r = nc / p.Nco;
+            const int co = nc - r * p.Nco;
+            const int uu = ri.uu0 + r * p.our, vv = ri.vv0 + r * p.ovr;
+            if (uu >= 0 && uu < p.Uout && vv >= 0 && vv < p.Vout)
+            {
+                float *dst = p.C + ri.outoff + ((long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.ldc + co;
+                float v = o[e];
+                if (p.rowadd)
+                    v += __ldg(p.rowadd + (size_t)ri.uo * p.rowadd_ld + co);
+                if (p.gamma)
+                    v = *dst + __ldg(p.gamma + nc) * v;
+                *dst = v;
+                rs += v;
+                rss += v * v;
+            }
+        }
+    }
+}
+
+template <int STAGES, bool VECA>
+__global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
+                                                          const int bn, const int plain_out)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[STAGES];
+    __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ uint32_t tmem_slot;
+    __shared__ RowInfo rowinfo[BM];
+    __shared__ float2 rowstat[BM]; // (mean, rstd) of the GroupNorm prologue per row
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.x * BM;
+    const int ntile = blockIdx.y;
+    const int n0 = ntile * bn;
+    const int nk = (p.K + BK - 1) / BK;
+    const uint32_t b_stage_bytes = (uint32_t)bn * BK * 2;
+    uint8_t *a_smem = smem;                       // STAGES x A_STAGE
+    uint8_t *b_smem = smem + STAGES * A_STAGE;     // STAGES x bn*128 B
+    uint32_t tmem_cols = 32;
+    while ((int)tmem_cols < bn)
+        tmem_cols <<= 1;
+
+    if (tid == 0)
+    {
+        for (int s = 0; s < STAGES; ++s)
+        {
+            mbar_init(&full_bar[s], PROD_THREADS + 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&tmem_full_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < BM)
+    {
+        const int m = m0 + tid;
+        const bool valid = m < p.M;
+        const RowCoord rc = decode_row(valid ? m : 0, p.Uo, p.Vo);
+        RowInfo ri;
+        ri.uu0 = rc.uo * p.ous + p.ouo;
+        ri.vv0 = rc.vo * p.ovs + p.ovo;
+        ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
+        ri.uo = rc.uo;
+        ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
+        rowinfo[tid] = ri;
+        float pmean = 0.f, prstd = 1.f;
+        if (p.pro == 1 && valid)
+        {
+            const int ui = rc.uo * p.su + p.du[0];
+            const int item = p.pro_per_u ? rc.b * p.Ui + ui : rc.b;
+            stats_to_mean_rstd(p.pro_stats + 2 * (size_t)item, p.pro_count, 1e-5f, pmean, prstd);
+        }
+        rowstat[tid] = make_float2(pmean, prstd);
+    }
+    if (warp == PROD_WARPS)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                     "r"(tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    if (warp < PROD_WARPS)
+    {
+        // ================= A producers =================
+        // A k-block is 128 rows x 8 chunks of 8 values.  Thread t owns chunk column kc = t % 8 of rows
+        // t/8 + 32*i (i = 0..3): the 8 lanes of a row read 256 contiguous bytes (coalesced) and a warp's
+        // 16-byte bf16 stores hit 8 distinct bank groups thanks to the padded LBO.  Per row the thread
+        // keeps a base pointer and a bit mask of the taps that fall inside the input grid, so the inner
+        // loop is: tap offset (once per k-block), predicated 16-byte loads, 4 cvt, one 16-byte store.
+        const int kc = tid & 7;
+        const int r0 = tid >> 3;
+        const float *rp[4];
+        uint32_t rmask[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            const int m = m0 + r0 + 32 * i;
+            rmask[i] = 0;
+            rp[i] = p.A;
+            if (m < p.M)
+            {
+                const RowCoord rc = decode_row(m, p.Uo, p.Vo);
+                const int ui0 = rc.uo * p.su, vi0 = rc.vo * p.sv;
+                rp[i] = p.A + (((long long)rc.b * p.Ui + ui0) * p.Vi + vi0) * p.lda;
+                for (int t = 0; t < p.ntaps; ++t)
+                {
+                    const int ui = ui0 + p.du[t], vi = vi0 + p.dv[t];
+                    if (ui >= 0 && ui < p.Ui && vi >= 0 && vi < p.Vi)
+                        rmask[i] |= 1u << t;
+                }
+            }
+        }
+        const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
+        for (int kb = 0; kb < nk; ++kb)
+        {
+            const int s = kb % STAGES;
+            const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+            const int k = kb * BK + kc * 8;
+            uint4 pk[4];
+            if (VECA)
+            {
+                const bool h0 = k < p.K, h1 = k + 4 < p.K;
+                int tap0 = 0, tap1 = 0, c0 = 0, c1 = 0;
+                long long toff0 = 0, toff1 = 0;
+                if (h0)
+                {
+                    tap0 = k / p.Cin;
+                    c0 = k - tap0 * p.Cin;
+                    toff0 = ((long long)p.du[tap0] * p.Vi + p.dv[tap0]) * p.lda + c0;
+                }
+                if (h1)
+                {
+                    tap1 = (k + 4) / p.Cin;
+                    c1 = (k + 4) - tap1 * p.Cin;
+                    toff1 = ((long long)p.du[tap1] * p.Vi + p.dv[tap1]) * p.lda + c1;
+                }
+                float4 lo[4], hi[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                {
+                    const bool v0 = h0 && ((rmask[i] >> tap0) & 1u), v1 = h1 && ((rmask[i] >> tap1) & 1u);
+                    lo[i] = v0 ? __ldg(reinterpret_cast<const float4 *>(rp[i] + toff0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    hi[i] = v1 ? __ldg(reinterpret_cast<const float4 *>(rp[i] + toff1)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                if (p.A2)
+                {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                    {
+                        const bool v0 = h0 && ((rmask[i] >> tap0) & 1u), v1 = h1 && ((rmask[i] >> tap1) & 1u);
+                        if (v0)
+                        {
+                            const float4 t = __ldg(reinterpret_cast<const float4 *>(rp[i] + a2d + toff0));
+                            lo[i].x += t.x;
+                            lo[i].y += t.y;
+                            lo[i].z += t.z;
+                            lo[i].w += t.w;
+                        }
+                        if (v1)
+                        {
+                            const float4 t = __ldg(reinterpret_cast<const float4 *>(rp[i] + a2d + toff1));
+                            hi[i].x += t.x;
+                            hi[i].y += t.y;
+                            hi[i].z += t.z;
+                            hi[i].w += t.w;
+                        }
+                    }
+                }
+                if (p.pro == 1)
+                {
+                    float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), b0 = w0, w1 = w0, b1 = w0;
+                    if (h0)
+                    {
+                        w0 = __ldg(reinterpret_cast<const float4 *>(p.pro_w + c0));
+                        b0 = __ldg(reinterpret_cast<const float4 *>(p.pro_b + c0));
+                    }
+                    if (h1)
+                    {
+                        w1 = __ldg(reinterpret_cast<const float4 *>(p.pro_w + c1));
+                        b1 = __ldg(reinterpret_cast<const float4 *>(p.pro_b + c1));
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                    {
+                        const float2 ms = rowstat[r0 + 32 * i];
+                        if (h0 && ((rmask[i] >> tap0) & 1u))
+                        {
+                            lo[i].x = gelu_erf((lo[i].x - ms.x) * ms.y * w0.x + b0.x);
+                            lo[i].y = gelu_erf((lo[i].y - ms.x) * ms.y * w0.y + b0.y);
+                            lo[i].z = gelu_erf((lo[i].z - ms.x) * ms.y * w0.z + b0.z);
+                            lo[i].w = gelu_erf((lo[i].w - ms.x) * ms.y * w0.w + b0.w);
+                        }
+                        if (h1 && ((rmask[i] >> tap1) & 1u))
+                        {
+                            hi[i].x = gelu_erf((hi[i].x - ms.x) * ms.y * w1.x + b1.x);
+                            hi[i].y = gelu_erf((hi[i].y - ms.x) * ms.y * w1.y + b1.y);
+                            hi[i].z = gelu_erf((hi[i].z - ms.x) * ms.y * w1.z + b1.z);
+                            hi[i].w = gelu_erf((hi[i].w - ms.x) * ms.y * w1.w + b1.w);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                {
+                    pk[i].x = pack_bf16x2(lo[i].x, lo[i].y);
+                    pk[i].y = pack_bf16x2(lo[i].z, lo[i].w);
+                    pk[i].z = pack_bf16x2(hi[i].x, hi[i].y);
+                    pk[i].w = pack_bf16x2(hi[i].z, hi[i].w);
+                }
+            }
+            else
+            {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                {
+                    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                    const float2 ms = rowstat[r0 + 32 * i];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e)
+                    {
+                        const int ke = k + e;
+                        if (ke < p.K)
+                        {
+                            const int tap = ke / p.Cin;
+                            const int c = ke - tap * p.Cin;
+                            if ((rmask[i] >> tap) & 1u)
+                            {
+                                const long long off = ((long long)p.du[tap] * p.Vi + p.dv[tap]) * p.lda + c;
+                                float t = __ldg(rp[i] + off);
+                                if (p.A2)
+                                    t += __ldg(rp[i] + a2d + off);
+                                if (p.pro == 1)
+                                    t = gelu_erf((t - ms.x) * ms.y * __ldg(&p.pro_w[c]) + __ldg(&p.pro_b[c]));
+                                v[e] = t;
+                            }
+                        }
+                    }
+                    pk[i].x = pack_bf16x2(v[0], v[1]);
+                    pk[i].y = pack_bf16x2(v[2], v[3]);
+                    pk[i].z = pack_bf16x2(v[4], v[5]);
+                    pk[i].w = pack_bf16x2(v[6], v[7]);
+                }
+            }
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            uint8_t *dst = a_smem + s * A_STAGE + kc * A_LBO + r0 * 16; // core (row/8, kc): kc*LBO + row*16
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                *reinterpret_cast<uint4 *>(dst + i * (32 * 16)) = pk[i];
+            fence_proxy_async(); // make the generic-proxy stores visible to the tensor core's async proxy
+            mbar_arrive(&full_bar[s]);
+        }
+
+        // ================= epilogue =================
+        // Warps w and w+4 share TMEM lanes / tile rows 32*(w%4)..+31 and alternate over the 32-column
+        // chunks.  Per chunk each lane pulls its own row's raw accumulators from TMEM and stages them in
+        // shared memory (the drained pipeline buffers); the warp then re-reads them transposed so that
+        // 8 lanes write 128 contiguous bytes of one output row: coalesced stores / residual reads.  Bias,
+        // GELU, GLU, row-add, LayerScale residual and the statistics are applied on the transposed side.
+        mbar_wait(&tmem_full_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3, hsel = warp >> 2;
+        float *stage = reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD);
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N; // never beyond N nor into the next column tile
+        const int nlimit = p.glu ? (ntile_end >> 1) : ntile_end;   // valid OUTPUT columns
+        const int gpr = p.glu ? 4 : 8;                             // 4-column output groups per row per chunk
+        const int rows_per_it = 32 / gpr;
+        const int g = lane % gpr, rsub = lane / gpr;
+        int cur_item = -1;
+        double st_s = 0.0, st_ss = 0.0;
+        for (int c0 = 32 * hsel; c0 < bn; c0 += 64)
+        {
+            float val[32];
+            tmem_ld16(lane_addr + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&val[0]));
+            if (c0 + 16 < bn)
+                tmem_ld16(lane_addr + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&val[16]));
+            else
+            {
+#pragma unroll
+                for (int j = 16; j < 32; ++j)
+                    val[j] = 0.f;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4 *>(&stage[lane * EPI_LD + j]) = make_float4(val[j], val[j + 1], val[j + 2], val[j + 3]);
+            __syncwarp();
+            const int nbase = n0 + c0;                          // first RAW column of the chunk
+            // this lane's raw columns: plain 4g..4g+3, GLU 8g..8g+7 (-> outputs 4g..4g+3)
+            const int rawc = nbase + (p.glu ? 8 * g : 4 * g);
+            const int outc = (p.glu ? (nbase >> 1) : nbase) + 4 * g;
+            float bias[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (p.bias)
+            {
+                const float4 b0 = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc)); // zero padded to ldw
+                bias[0] = b0.x;
+                bias[1] = b0.y;
+                bias[2] = b0.z;
+                bias[3] = b0.w;
+                if (p.glu)
+                {
+                    const float4 b1 = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc + 4));
+                    bias[4] = b1.x;
+                    bias[5] = b1.y;
+                    bias[6] = b1.z;
+                    bias[7] = b1.w;
+                }
+            }
+            float4 gam = make_float4(0.f, 0.f, 0.f, 0.f);
+            const bool full4 = outc + 4 <= nlimit;
+            if (p.gamma && full4)
+                gam = __ldg(reinterpret_cast<const float4 *>(p.gamma + outc));
+            for (int it = 0; it < gpr; ++it)
+            {
+                const int rl = it * rows_per_it + rsub;
+                const RowInfo ri = rowinfo[q * 32 + rl];
+                float rs = 0.f, rss = 0.f;
+                if (ri.item >= 0) // row inside the problem
+                {
+                    float o[4];
+                    if (p.glu)
+                    {
+                        const float4 t0 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 8 * g]);
+                        const float4 t1 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 8 * g + 4]);
+                        float r8[8] = {t0.x + bias[0], t0.y + bias[1], t0.z + bias[2], t0.w + bias[3],
+                                       t1.x + bias[4], t1.y + bias[5], t1.z + bias[6], t1.w + bias[7]};
+                        if (p.act == 1)
+                        {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e)
+                                r8[e] = gelu_erf(r8[e]);
+                        }
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            o[e] = r8[2 * e] * sigmoid_ref(r8[2 * e + 1]);
+                    }
+                    else
+                    {
+                        const float4 t0 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 4 * g]);
+                        o[0] = t0.x + bias[0];
+                        o[1] = t0.y + bias[1];
+                        o[2] = t0.z + bias[2];
+                        o[3] = t0.w + bias[3];
+                        if (p.act == 1)
+                        {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                o[e] = gelu_erf(o[e]);
+                        }
+                    }
+                    if (plain_out && full4)
+                    {
+                        // identity mapping: output row == GEMM row, 16-byte aligned groups
+                        float *dst = p.C + ri.outoff + outc;
+                        if (p.rowadd)
+                        {
+                            const float4 ra = __ldg(reinterpret_cast<const float4 *>(p.rowadd + (size_t)ri.uo * p.rowadd_ld + outc));
+                            o[0] += ra.x;
+                            o[1] += ra.y;
+                            o[2] += ra.z;
+                            o[3] += ra.w;
+                        }
+                        if (p.gamma)
+                        {
+                            const float4 old = *reinterpret_cast<const float4 *>(dst);
+                            o[0] = old.x + gam.x * o[0];
+                            o[1] = old.y + gam.y * o[1];
+                            o[2] = old.z + gam.z * o[2];
+                            o[3] = old.w + gam.w * o[3];
+                        }
+                        *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+                        rs = o[0] + o[1] + o[2] + o[3];
+                        rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
+                    }
+                    else if (outc < nlimit)
+                        store_group4_scatter(p, ri, outc, nlimit, o, rs, rss);
+                }
+                if (p.stats)
+                {
+                    if (ri.item != cur_item)
+                    {
+                        if (cur_item >= 0)
+                        {
+                            atomicAdd(&p.stats[2 * (size_t)cur_item + 0], st_s);
+                            atomicAdd(&p.stats[2 * (size_t)cur_item + 1], st_ss);
+                        }
+                        cur_item = ri.item;
+                        st_s = 0.0;
+                        st_ss = 0.0;
+                    }
+                    st_s += (double)rs;
+                    st_ss += (double)rss;
+                }
+            }
+        }
+        if (p.stats)
+        {
+            // one item per warp in the common case: reduce across lanes before touching global memory
+            const int item0 = __shfl_sync(0xffffffffu, cur_item, 0);
+            if (__all_sync(0xffffffffu, cur_item == item0))
+            {
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
+                    st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
+                }
+                if (lane == 0 && item0 >= 0)
+                {
+                    atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
+                    atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
+                }
+            }
+            else if (cur_item >= 0)
+            {
+                atomicAdd(&p.stats[2 * (size_t)cur_item + 0], st_s);
+                atomicAdd(&p.stats[2 * (size_t)cur_item + 1], st_ss);
+            }
+        }
+        tc_fence_before();
+    }
+    else if (warp == PROD_WARPS)
+    {
+        // ================= B loader: one bulk copy per stage =================
+        if (lane == 0)
+        {
+            const uint8_t *src = reinterpret_cast<const uint8_t *>(Wb) + (size_t)ntile * nk * b_stage_bytes;
+            for (int kb = 0; kb < nk; ++kb)
+            {
+                const int s = kb % STAGES;
+                const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                mbar_wait(&empty_bar[s], ph ^ 1u);
+                mbar_arrive_expect_tx(&full_bar[s], b_stage_bytes);
+                bulk_g2s(b_smem + (size_t)s * b_stage_bytes, src + (size_t)kb * b_stage_bytes, b_stage_bytes, &full_bar[s]);
+            }
+        }
+    }
+    else
+    {
+        // ================= MMA issuer: a single thread =================
+        if (lane == 0)
+        {
+            const uint32_t idesc = make_idesc(bn);
+            const uint32_t b_lbo = (uint32_t)bn * 16, sbo = 128;
+            for (int kb = 0; kb < nk; ++kb)
+            {
+                const int s = kb % STAGES;
+                const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(a_smem + s * A_STAGE);
+                const uint32_t b_base = smem_u32(b_smem + (size_t)s * b_stage_bytes);
+#pragma unroll
+                for (int j = 0; j < BK / 16; ++j)
+                {
+                    const uint64_t ad = make_desc(a_base + j * 2 * A_LBO, A_LBO, sbo);
+                    const uint64_t bd = make_desc(b_base + j * 2 * b_lbo, b_lbo, sbo);
+                    umma(tmem_base, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]); // frees the stage once these MMAs have read it
+            }
+            umma_commit(&tmem_full_bar);    // accumulator complete
+        }
+    }
+    __syncthreads();
+    if (warp == PROD_WARPS)
+    {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+    }
+}
+
+} // namespace tc
+
+// Column-tile width for a layer with N output columns: N itself (rounded up to 16) when it fits one
+// tile, otherwise the largest multiple-of-16 divisor of N that is <= 256.
+int tc_tile_n(int N)
+{
+    const int n16 = (N + 15) / 16 * 16;
+    if (n16 <= 256)
+        return n16;
+    for (int bn = 256; bn >= 64; bn -= 16)
+        if (N % bn == 0)
+            return bn;
+    return 256;
+}
+
+size_t tc_packed_elems(int K, int N)
+{
+    const int bn = tc_tile_n(N);
+    const int nkb = (K + tc::BK - 1) / tc::BK, nt = (N + bn - 1) / bn;
+    return (size_t)nt * nkb * bn * tc::BK;
+}
+
+// Host-side index of element (k, n) in the packed bf16 image: [n-tile][k-block][kc = (k%64)/8][n%bn][k%8]
+size_t tc_packed_index(int K, int N, int k, int n)
+{
+    const int bn = tc_tile_n(N);
+    const int nkb = (K + tc::BK - 1) / tc::BK;
+    const int nt = n / bn, nn = n % bn, kb = k / tc::BK, kr = k % tc::BK;
+    return (((size_t)nt * nkb + kb) * 8 + kr / 8) * ((size_t)bn * 8) + (size_t)nn * 8 + (kr % 8);
+}
+
+template <int STAGES> static int tc_set_attr()
+{
+    const int max_smem = 227 * 1024 - 8 * 1024;
+    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    return 0;
+}
+
+int tc_init_device() { return tc_set_attr<1>() || tc_set_attr<2>() || tc_set_attr<3>(); }
+
+template <int STAGES>
+static int tc_launch(const GemmParams &p, const __nv_bfloat16 *w, int bn, bool vec, int plain, cudaStream_t st)
+{
+    dim3 grid((p.M + tc::BM - 1) / tc::BM, (p.N + bn - 1) / bn);
+    int smem = STAGES * (tc::A_STAGE + bn * tc::BK * 2);
+    if (smem < tc::EPI_BYTES)
+        smem = tc::EPI_BYTES; // the epilogue stages its transposition in the pipeline buffers
+    if (vec)
+        tc::gemm_tc_kernel<STAGES, true><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
+    else
+        tc::gemm_tc_kernel<STAGES, false><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
+{
+    if (p.M <= 0 || p.N <= 0 || p.K <= 0 || !Wb)
+    {
+        set_error("launch_gemm_tc: bad problem");
+        return -1;
+    }
+    if (p.glu && (p.N % 2))
+    {
+        set_error("launch_gemm_tc: GLU needs an even N");
+        return -1;
+    }
+    if (p.ntaps > 16)
+    {
+        set_error("launch_gemm_tc: too many taps");
+        return -1;
+    }
+    const int bn = tc_tile_n(p.N);
+    const int nout = p.glu ? p.N / 2 : p.N;
+    const bool vec = (p.Cin % 4 == 0) && (p.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) &&
+                     (!p.A2 || (reinterpret_cast<uintptr_t>(p.A2) & 15) == 0);
+    // identity output mapping with 16-byte aligned rows -> the epilogue's fast path
+    const int plain = (p.ous == 1 && p.ovs == 1 && p.our == 0 && p.ovr == 0 && p.ouo == 0 && p.ovo == 0 &&
+                       p.Uout == p.Uo && p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 &&
+                       (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0))
+                          ? 1
+                          : 0;
+    const __nv_bfloat16 *w = static_cast<const __nv_bfloat16 *>(Wb);
+    const int nk = (p.K + tc::BK - 1) / tc::BK;
+    if (nk == 1)
+        return tc_launch<1>(p, w, bn, vec, plain, st);
+    if (nk == 2)
+        return tc_launch<2>(p, w, bn, vec, plain, st);
+    return tc_launch<3>(p, w, bn, vec, plain, st);
+}
+
+} // namespace dmx

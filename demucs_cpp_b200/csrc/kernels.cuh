@@ -36,6 +36,7 @@ struct GemmParams
     // B operand: packed fp32 [Kpad][ldw], zero padded
     const float *W = nullptr;
     int ldw = 0;
+    const void *Wb = nullptr; // bf16 image for the tensor-core kernel (gemm_tc.cu), same (k, n) contents
     const float *bias = nullptr;
     int N = 0;
     // epilogue
@@ -53,6 +54,13 @@ struct GemmParams
 };
 
 int launch_gemm(const GemmParams &p, cudaStream_t st);
+
+// gemm_tc.cu: the same operator on tcgen05 tensor cores (bf16 operands, fp32 accumulate in TMEM)
+int tc_init_device();
+int tc_tile_n(int N);
+size_t tc_packed_elems(int K, int N);
+size_t tc_packed_index(int K, int N, int k, int n);
+int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // fft.cu

@@ -103,6 +103,16 @@ static int upload_vec(dmx_model *m, float **dst, const std::string &name, size_t
 
 static inline int round_up(int x, int k) { return (x + k - 1) / k * k; }
 
+static inline uint16_t f32_to_bf16_bits(float f)
+{
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u)
+        return (uint16_t)((u >> 16) | 0x40); // NaN
+    u += 0x7fffu + ((u >> 16) & 1u);          // round to nearest even
+    return (uint16_t)(u >> 16);
+}
+
 // Generic packer: element (k, n) of the GEMM B operand given by f(k, n); bias by fb(n).
 // If glu: output columns are interleaved so that packed 2j = original j, packed 2j+1 = original j + N/2.
 template <typename FW, typename FB>
@@ -122,6 +132,16 @@ static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb)
     }
     if (upload(m, &p.W, w) || upload(m, &p.bias, b))
         return -1;
+    // bf16 image for the tcgen05 kernel: same (k, n) contents, round-to-nearest-even, zero padded
+    {
+        std::vector<uint16_t> wb(tc_packed_elems(K, N), 0);
+        for (int n = 0; n < N; ++n)
+            for (int k = 0; k < K; ++k)
+                wb[tc_packed_index(K, N, k, n)] = f32_to_bf16_bits(w[(size_t)k * p.ldw + n]);
+        if (dev_alloc(m, &p.Wb, wb.size() * sizeof(uint16_t)))
+            return -1;
+        DMX_CUDA(cudaMemcpy(p.Wb, wb.data(), wb.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    }
     return 0;
 }
 
@@ -317,7 +337,7 @@ int model_finalize(dmx_model *m)
     DMX_CUDA(cudaEventCreate(&m->ev0));
     DMX_CUDA(cudaEventCreate(&m->ev1));
     DMX_CUDA(cudaEventCreate(&m->ev2));
-    if (fft_init_device())
+    if (fft_init_device() || tc_init_device())
         return -1;
     const bool is4 = m->arch == DMX_ARCH_HTDEMUCS_4S;
     m->S = is4 ? 4 : 6;
@@ -485,7 +505,10 @@ struct Fwd
         if (rc)
             return;
         ProfScope ps(m, cls, 2.0 * (double)p.M * (double)p.N * (double)p.K);
-        rc = launch_gemm(p, st);
+        if (m->precision == DMX_PRECISION_BF16 && p.Wb)
+            rc = launch_gemm_tc(p, p.Wb, st);
+        else
+            rc = launch_gemm(p, st);
     }
     // common fields: single batch grid (U, V) in and out, plain output mapping
     GemmParams base(const float *Ain, int lda, int Cin, const Packed &w, float *C, int ldc, int Ui, int Vi, int Uo,
@@ -497,6 +520,7 @@ struct Fwd
         p.Cin = Cin;
         p.K = w.K;
         p.W = w.W;
+        p.Wb = w.Wb;
         p.ldw = w.ldw;
         p.bias = w.bias;
         p.N = w.N;
@@ -634,11 +658,6 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     if (B < 1 || B > m->maxB)
     {
         set_error("model_forward: batch exceeds max_batch");
-        return -1;
-    }
-    if (m->precision != DMX_PRECISION_FP32)
-    {
-        set_error("model_forward: precision mode not available in this build");
         return -1;
     }
     cudaStream_t st = m->stream;
@@ -866,6 +885,97 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         set_tap(m, tn[i], m->dxt[i], 1, TLENS[3 - i], m->tdec[i].Cout);
     }
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Test hook: out[M][N] = act(A[M][K] x W[N][K]^T + bias) through the production GEMM kernels (fp32 CUDA-core
+// or bf16 tcgen05 path), with temporary device buffers.  Lets the tests check the tensor-core kernel's
+// operand layouts and descriptors in isolation against numpy.
+int debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
+                 int act, float *out, int iters, float *ms_out)
+{
+    DMX_CUDA(cudaSetDevice(device));
+    dmx_model tmp;
+    tmp.device = device;
+    int rc = 0;
+    float *dA = nullptr, *dC = nullptr;
+    Packed pk;
+    do
+    {
+        if ((rc = tc_init_device()))
+            break;
+        rc = pack(
+            &tmp, pk, K, N, false, [=](int k, int n) { return W[(size_t)n * K + k]; },
+            [=](int n) { return bias ? bias[n] : 0.f; });
+        if (rc)
+            break;
+        if ((rc = dev_alloc_t(&tmp, &dA, (size_t)M * K)) || (rc = dev_alloc_t(&tmp, &dC, (size_t)M * N)))
+            break;
+        if (cudaMemcpy(dA, A, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaMemset(dC, 0, (size_t)M * N * sizeof(float)) != cudaSuccess)
+        {
+            set_error("debug_linear: copy failed");
+            rc = -1;
+            break;
+        }
+        GemmParams p;
+        p.A = dA;
+        p.lda = K;
+        p.Cin = K;
+        p.K = K;
+        p.W = pk.W;
+        p.Wb = pk.Wb;
+        p.ldw = pk.ldw;
+        p.bias = pk.bias;
+        p.N = N;
+        p.Ui = p.Uo = 1;
+        p.Vi = p.Vo = M;
+        p.M = M;
+        p.C = dC;
+        p.ldc = N;
+        p.Nco = N;
+        p.Uout = 1;
+        p.Vout = M;
+        p.act = act;
+        rc = precision == DMX_PRECISION_BF16 ? launch_gemm_tc(p, pk.Wb, 0) : launch_gemm(p, 0);
+        if (rc)
+            break;
+        if (iters > 0 && ms_out)
+        {
+            cudaEvent_t e0, e1;
+            cudaEventCreate(&e0);
+            cudaEventCreate(&e1);
+            cudaDeviceSynchronize();
+            cudaEventRecord(e0, 0);
+            for (int it = 0; it < iters && !rc; ++it)
+                rc = precision == DMX_PRECISION_BF16 ? launch_gemm_tc(p, pk.Wb, 0) : launch_gemm(p, 0);
+            cudaEventRecord(e1, 0);
+            cudaEventSynchronize(e1);
+            float t = 0.f;
+            cudaEventElapsedTime(&t, e0, e1);
+            *ms_out = t / (float)iters;
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+            if (rc)
+                break;
+        }
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess)
+        {
+            set_error(std::string("debug_linear: kernel failed: ") + cudaGetErrorString(e));
+            rc = -1;
+            break;
+        }
+        if (cudaMemcpy(out, dC, (size_t)M * N * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+        {
+            set_error("debug_linear: copy back failed");
+            rc = -1;
+        }
+    } while (0);
+    for (void *q : tmp.allocs)
+        cudaFree(q);
+    tmp.allocs.clear();
+    return rc;
 }
 
 } // namespace dmx

@@ -23,6 +23,7 @@ struct Packed
 {
     float *W = nullptr;
     float *bias = nullptr;
+    void *Wb = nullptr; // bf16 tensor-core image
     int K = 0, N = 0, ldw = 0;
 };
 
@@ -137,6 +138,8 @@ struct dmx_model
 namespace dmx
 {
 int model_finalize(dmx_model *m);
+int debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
+                 int act, float *out, int iters, float *ms_out);
 int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out); // d_out: [B][S][SEG][2]
 // RAII: brackets the launches issued inside its scope with events when profiling is on
 struct ProfScope

@@ -112,6 +112,14 @@ extern "C"
      * device layout; returns the element count, or -1.  With dst == NULL only dims are filled. */
     int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capacity, int64_t dims[4]);
 
+    /* Test hook for the GEMM kernels in isolation (stands in for the reference's GemmConv* tests,
+     * test/test_layers.cpp:856-1387): out (M,N) = act(A (M,K) x W (N,K)^T + bias) through the production
+     * fp32 CUDA-core kernel (precision 0) or the bf16 tcgen05 kernel (precision 1); act 1 = GELU.
+     * All pointers are host buffers.  With iters > 0 the kernel is additionally launched `iters` times
+     * back to back and its average device time (CUDA events) is returned in *ms_out. */
+    int dmx_debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W,
+                         const float *bias, int act, float *out, int iters, float *ms_out);
+
     /* Kernel launches issued by this model's forward passes so far (for bench.py's gpu_launches). */
     int64_t dmx_launch_count(const dmx_model *m);
 
