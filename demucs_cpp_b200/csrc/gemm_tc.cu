@@ -543,7 +543,15 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
                             o[2] = old.z + gam.z * o[2];
                             o[3] = old.w + gam.w * o[3];
                         }
-                        *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+                        if (p.out_bf16)
+                        {
+                            uint2 pk2;
+                            pk2.x = pack_bf16x2(o[0], o[1]);
+                            pk2.y = pack_bf16x2(o[2], o[3]);
+                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + ri.outoff + outc) = pk2;
+                        }
+                        else
+                            *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
                         rs = o[0] + o[1] + o[2] + o[3];
                         rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
                     }
@@ -727,6 +735,11 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
                        (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0))
                           ? 1
                           : 0;
+    if (p.out_bf16 && (!plain || p.gamma || (nout % 4)))
+    {
+        set_error("launch_gemm_tc: bf16 output needs the identity mapping, no residual and N % 4 == 0");
+        return -1;
+    }
     const __nv_bfloat16 *w = static_cast<const __nv_bfloat16 *>(Wb);
     const int nk = (p.K + tc::BK - 1) / tc::BK;
     if (nk == 1)

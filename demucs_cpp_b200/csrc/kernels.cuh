@@ -47,6 +47,7 @@ struct GemmParams
     const float *gamma = nullptr;  // out = C_old + gamma[n]*val           (LayerScale residual)
     double *stats = nullptr;       // accumulate (sum, sumsq) of the stored values per item
     int stat_per_u = 0;
+    int out_bf16 = 0;              // tensor-core kernel only, identity mapping only: C holds bf16 (ldc in elements)
     // output mapping
     float *C = nullptr;
     int ldc = 0, Nco = 0;
@@ -93,5 +94,10 @@ int launch_group_norm_apply(float *x, int B, int rows_per_item, int C, const dou
 // (src/layers.cpp:442-482).  Q: [B*T][ldq], K/V: [B*S][ldk|ldv]; O: [B*T][ldo].
 int launch_attention(const float *Q, int ldq, const float *K, int ldk, const float *V, int ldv, float *O, int ldo,
                      int B, int T, int S, int heads, int dh, cudaStream_t st);
+
+// attention_tc.cu: the same attention on tcgen05 tensor cores; Q/K/V bf16, O fp32
+int attention_tc_init_device();
+int launch_attention_tc(const void *Q, int ldq, const void *K, int ldk, const void *V, int ldv, float *O, int ldo, int B,
+                        int T, int S, int heads, int dh, cudaStream_t st);
 
 } // namespace dmx

@@ -337,7 +337,7 @@ int model_finalize(dmx_model *m)
     DMX_CUDA(cudaEventCreate(&m->ev0));
     DMX_CUDA(cudaEventCreate(&m->ev1));
     DMX_CUDA(cudaEventCreate(&m->ev2));
-    if (fft_init_device() || tc_init_device())
+    if (fft_init_device() || tc_init_device() || attention_tc_init_device())
         return -1;
     const bool is4 = m->arch == DMX_ARCH_HTDEMUCS_4S;
     m->S = is4 ? 4 : 6;
@@ -597,23 +597,45 @@ struct Fwd
     {
         const int d = m->d_model, dh = d / 8;
         layer_norm(q, ln, B * Tq, d, L.n1w, L.n1b);
+        // bf16 mode: the projections write Q/K/V as bf16 (same buffers, half the bytes) for the tensor-core
+        // attention; fp32 mode keeps everything fp32 on the CUDA-core kernels.
+        const bool tcm = m->precision == DMX_PRECISION_BF16;
         if (!L.cross)
         {
-            gemm(linear(ln, d, L.qkv, qkv, 3 * d, Tq), PC_GEMM_XFMR);
+            GemmParams pq = linear(ln, d, L.qkv, qkv, 3 * d, Tq);
+            pq.out_bf16 = tcm;
+            gemm(pq, PC_GEMM_XFMR);
             if (!rc)
             {
                 ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tq * d);
-                rc = launch_attention(qkv, 3 * d, qkv + d, 3 * d, qkv + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
+                if (tcm)
+                {
+                    const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
+                    rc = launch_attention_tc(qb, 3 * d, qb + d, 3 * d, qb + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
+                }
+                else
+                    rc = launch_attention(qkv, 3 * d, qkv + d, 3 * d, qkv + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
             }
         }
         else
         {
-            gemm(linear(ln, d, L.q, qkv, d, Tq), PC_GEMM_XFMR);
-            gemm(linear(kn, d, L.kv, kv, 2 * d, Tk), PC_GEMM_XFMR);
+            GemmParams pq = linear(ln, d, L.q, qkv, d, Tq);
+            pq.out_bf16 = tcm;
+            gemm(pq, PC_GEMM_XFMR);
+            GemmParams pkv = linear(kn, d, L.kv, kv, 2 * d, Tk);
+            pkv.out_bf16 = tcm;
+            gemm(pkv, PC_GEMM_XFMR);
             if (!rc)
             {
                 ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tk * d);
-                rc = launch_attention(qkv, d, kv, 2 * d, kv + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
+                if (tcm)
+                {
+                    const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
+                    const uint16_t *kb = reinterpret_cast<const uint16_t *>(kv);
+                    rc = launch_attention_tc(qb, d, kb, 2 * d, kb + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
+                }
+                else
+                    rc = launch_attention(qkv, d, kv, 2 * d, kv + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
             }
         }
         GemmParams po = linear(ao, d, L.out, q, d, Tq);
