@@ -39,10 +39,10 @@ def check_summary(name, full, gsub, gstat, tol):
 _models = {}
 
 
-def model(arch="htdemucs_4s", stress=False, max_batch=4):
-    key = (arch, stress, max_batch)
+def model(arch="htdemucs_4s", stress=False, max_batch=4, precision=api.PRECISION_FP32):
+    key = (arch, stress, max_batch, precision)
     if key not in _models:
-        _models[key] = api.DemucsModel(weights.cached_weights(arch, 0, stress), max_batch=max_batch)
+        _models[key] = api.DemucsModel(weights.cached_weights(arch, 0, stress), max_batch=max_batch, precision=precision)
     return _models[key]
 
 
@@ -182,3 +182,61 @@ def test_separate_full_size_properties():
     assert util.snr_db(out, ref) >= 100.0
     out2 = m.demucs_inference(2.5 * audio, shift_offset=4033)
     assert util.snr_db(out2, 2.5 * out) >= SNR_FP32
+
+
+# ------------------------------------------------------------------------------------------- bf16 mode (tcgen05)
+def bf16_round(x):
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) >> 16 << 16
+    return u.astype(np.uint32).view(np.float32)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 16, 64), (300, 48, 100), (257, 6, 6), (1000, 384, 512), (129, 96, 1536),
+                                   (512, 2048, 512)])
+def test_gemm_kernels_in_isolation(M, N, K):
+    """The tap-GEMM kernels alone (the reference's GemmConv* tests, test/test_layers.cpp:856-1387, play this
+    role there): fp32 CUDA-core kernel vs fp64 numpy within 1e-4, tcgen05 kernel vs the same product with
+    bf16-rounded operands within 1e-4 (so operand layouts / descriptors are exact) and vs the unrounded
+    product within the bf16 bar of 1e-2."""
+    rng = np.random.default_rng(M + N + K)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    W = (rng.standard_normal((N, K)) / np.sqrt(K)).astype(np.float32)
+    b = rng.standard_normal(N).astype(np.float32)
+    ref = A.astype(np.float64) @ W.astype(np.float64).T + b
+    assert util.max_rel_err(api.debug_linear(A, W, b, precision=api.PRECISION_FP32), ref) <= TOL_FP32
+    out = api.debug_linear(A, W, b, precision=api.PRECISION_BF16)
+    ref_b = bf16_round(A).astype(np.float64) @ bf16_round(W).astype(np.float64).T + b
+    assert util.max_rel_err(out, ref_b) <= TOL_FP32
+    assert util.max_rel_err(out, ref) <= TOL_BF16
+
+
+@pytest.mark.parametrize("arch,stress,tag", [("htdemucs_4s", False, "htdemucs_4s"),
+                                             ("htdemucs_6s", False, "htdemucs_6s")])
+def test_bf16_forward_matches_reference_golden(golden_dir, arch, stress, tag):
+    """bf16 mode at BASELINE.json's bf16 bar: every stage <= 1e-2 max relative error, stems >= 40 dB."""
+    g = np.load(os.path.join(golden_dir, "segment_%s.npz" % tag))
+    m = model(arch, stress, precision=api.PRECISION_BF16)
+    out = m.model_inference(util.synth_audio(util.SEG)[None])[0]
+    for n in util.STAGE_TAPS:
+        if n + ".sub" not in g.files:
+            continue
+        check_summary(n, util.tap_to_cfirst(m.tap(n))[0], g[n + ".sub"], g[n + ".stat"], TOL_BF16)
+    check_summary("targets", out, g["targets.sub"], g["targets.stat"], TOL_BF16)
+    assert util.snr_db(out.reshape(-1)[sub_idx(out.size)], g["targets.sub"]) >= SNR_BF16
+
+
+def test_bf16_stress_weights_stem_snr():
+    """LayerScale = 0.3 everywhere (residual branches at full strength): stems must still clear 40 dB."""
+    m = model("htdemucs_4s", True, precision=api.PRECISION_BF16)
+    seg = util.synth_audio(util.SEG, seed=31)
+    out = m.model_inference(seg[None])[0]
+    _, tens = weights.read_ggml(weights.cached_weights("htdemucs_4s", 0, True))
+    with torch.no_grad():
+        ref = O.segment_forward(O.Weights(tens, torch.float32), torch.from_numpy(seg)).numpy()
+    assert util.snr_db(out, ref) >= SNR_BF16
+
+
+def test_bf16_separate_matches_reference_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "separate_htdemucs_4s_10s.npz"))
+    out = model(precision=api.PRECISION_BF16).demucs_inference(util.synth_audio(441000), shift_offset=int(g["shift"][0]))
+    assert util.snr_db(out.reshape(-1)[sub_idx(out.size)], g["sub"]) >= SNR_BF16

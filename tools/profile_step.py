@@ -1,0 +1,34 @@
+"""One batch of 8 segments of the bench workload, bracketed by cudaProfilerStart/Stop, for ncu:
+  ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file X python tools/profile_step.py
+Same model, precision and segments-per-launch as bench.py; the track is cut to exactly 8 segments."""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from demucs_cpp_b200 import api, weights  # noqa: E402
+from demucs_cpp_b200.synth import synth_audio  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--precision", default="bf16")
+ap.add_argument("--batch", type=int, default=8)
+ap.add_argument("--arch", default="htdemucs_4s")
+args = ap.parse_args()
+L = 8 * 257985 - 22050 + 4033 - 1000          # -> exactly 8 segments at shift 4033
+assert api.num_segments(L, 4033) == 8
+m = api.DemucsModel(weights.cached_weights(args.arch, 0), max_batch=args.batch,
+                    precision=api.PRECISION_BF16 if args.precision == "bf16" else api.PRECISION_FP32)
+d_audio = torch.from_numpy(np.ascontiguousarray(synth_audio(L).T)).cuda()
+d_out = torch.empty((L, 2, m.nb_sources), dtype=torch.float32, device="cuda")
+for _ in range(2):
+    m.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), 4033)
+torch.cuda.synchronize()
+torch.cuda.profiler.start()
+m.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), 4033)
+torch.cuda.synchronize()
+torch.cuda.profiler.stop()
+print("device ms for 8 segments: %.2f" % m.last_device_ms)
