@@ -200,18 +200,43 @@ static int pack_linear(dmx_model *m, Packed &p, const std::string &wname, const 
         [=](int n) { return bd[row0 + n]; });
 }
 
+static int upload_vec_padded(dmx_model *m, float **dst, const std::string &name, size_t n, size_t npad)
+{
+    const HostTensor *t = get(m, name, n);
+    if (!t)
+        return -1;
+    std::vector<float> v(t->data);
+    v.resize(npad, 0.f);
+    return upload(m, dst, v);
+}
+
 static int pack_dconv(dmx_model *m, DConvW &d, const std::string &prefix, int C)
 {
     d.C = C;
     d.hid = C / 8;
+    // The hidden tensor is stored with its channel count rounded up to a multiple of 4 (6 -> 8) so that its
+    // rows stay 16-byte aligned for vector loads; the pad channels carry zero GroupNorm / conv weights.
+    d.hidp = round_up(d.hid, 4);
     for (int j = 0; j < 2; ++j)
     {
         const std::string p = prefix + ".dconv.layers." + std::to_string(j) + ".";
         if (pack_conv(m, d.c1[j], p + "0.weight", p + "0.bias", d.hid, C, 3, false))
             return -1;
-        if (pack_conv(m, d.c2[j], p + "3.weight", p + "3.bias", 2 * C, d.hid, 1, false))
-            return -1;
-        if (upload_vec(m, &d.g1w[j], p + "1.weight", d.hid) || upload_vec(m, &d.g1b[j], p + "1.bias", d.hid) ||
+        {
+            const HostTensor *w = get(m, p + "3.weight", (size_t)2 * C * d.hid);
+            const HostTensor *b = get(m, p + "3.bias", 2 * C);
+            if (!w || !b)
+                return -1;
+            const float *wd = w->data.data();
+            const float *bd = b->data.data();
+            const int hid = d.hid;
+            if (pack(
+                    m, d.c2[j], d.hidp, 2 * C, false, [=](int k, int n) { return k < hid ? wd[(size_t)n * hid + k] : 0.f; },
+                    [=](int n) { return bd[n]; }))
+                return -1;
+        }
+        if (upload_vec_padded(m, &d.g1w[j], p + "1.weight", d.hid, d.hidp) ||
+            upload_vec_padded(m, &d.g1b[j], p + "1.bias", d.hid, d.hidp) ||
             upload_vec(m, &d.g2w[j], p + "4.weight", 2 * C) || upload_vec(m, &d.g2b[j], p + "4.bias", 2 * C) ||
             upload_vec(m, &d.scale[j], p + "6.scale", C))
             return -1;
@@ -442,9 +467,9 @@ int model_finalize(dmx_model *m)
         rc |= A(&m->dx[i], (size_t)FREQS[3 - i] * T * m->dec[i].Cout);
         rc |= A(&m->dxt[i], (size_t)TLENS[3 - i] * m->tdec[i].Cout);
     }
-    rc |= A(&m->h_f, (size_t)512 * T * 6);
+    rc |= A(&m->h_f, (size_t)512 * T * 8);
     rc |= A(&m->y2_f, (size_t)512 * T * 96);
-    rc |= A(&m->h_t, (size_t)TLEN0 * 6);
+    rc |= A(&m->h_t, (size_t)TLEN0 * 8);
     rc |= A(&m->y2_t, (size_t)TLEN0 * 96);
     const size_t TF = 8 * T, TT = TLEN3;
     rc |= A(&m->up_f, TF * d);
@@ -471,6 +496,9 @@ int model_finalize(dmx_model *m)
     rc |= A(&m->meanstd_t, 2);
     if (rc)
         return -1;
+    // pad channels of the DConv hidden tensors are never written: they must hold finite values
+    DMX_CUDA(cudaMemset(m->h_f, 0, B * (size_t)512 * T * 8 * sizeof(float)));
+    DMX_CUDA(cudaMemset(m->h_t, 0, B * (size_t)TLEN0 * 8 * sizeof(float)));
     // statistics arena: (sum, sumsq) doubles; DConv needs up to 512 items per batch element and layer
     m->stats_cap = B * 2 * (size_t)(2 * 2 * 2 * (512 + 128 + 32 + 8) * 2 + 16 * 2 * 2 + 64);
     if (dev_alloc_t(m, &m->stats, m->stats_cap) || dev_alloc_t(m, &m->track_stats, 2))
@@ -547,13 +575,13 @@ struct Fwd
     // frequency rows (per_u = 1) or whole batch elements (time branch, U = 1).
     void dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u)
     {
-        const int C = w.C, hid = w.hid;
+        const int C = w.C, hid = w.hid, hidp = w.hidp;
         const size_t items = (size_t)B * (per_u ? U : 1);
         for (int j = 0; j < 2; ++j)
         {
             const int dil = 1 << j;
             double *s1 = stat_slots(items), *s2 = stat_slots(items);
-            GemmParams p = base(x, C, C, w.c1[j], h, hid, U, V, U, V);
+            GemmParams p = base(x, C, C, w.c1[j], h, hidp, U, V, U, V);
             p.ntaps = 3;
             for (int t = 0; t < 3; ++t)
             {
@@ -563,7 +591,7 @@ struct Fwd
             p.stats = s1;
             p.stat_per_u = per_u;
             gemm(p, PC_GEMM_DCONV);
-            GemmParams q = base(h, hid, hid, w.c2[j], y2, 2 * C, U, V, U, V);
+            GemmParams q = base(h, hidp, hidp, w.c2[j], y2, 2 * C, U, V, U, V);
             q.pro = 1;
             q.pro_stats = s1;
             q.pro_count = per_u ? (double)V * hid : (double)U * V * hid;

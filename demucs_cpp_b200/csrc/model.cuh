@@ -31,7 +31,7 @@ struct DConvW
 {
     Packed c1[2], c2[2];
     float *g1w[2], *g1b[2], *g2w[2], *g2b[2], *scale[2];
-    int C = 0, hid = 0;
+    int C = 0, hid = 0, hidp = 0;
 };
 
 struct EncW
