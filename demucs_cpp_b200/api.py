@@ -31,7 +31,7 @@ EXPORTS = [
     "dmx_debug_tap", "dmx_launch_count", "dmx_stft_segment", "dmx_istft_segment", "dmx_profile_classes",
     "dmx_profile_class_name", "dmx_profile_begin", "dmx_profile_end", "dmx_forward_shard_device",
     "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
-    "dmx_debug_linear",
+    "dmx_debug_linear", "dmx_profile_sequence",
 ]
 
 _lib = None
@@ -77,6 +77,7 @@ def lib():
         L.dmx_profile_class_name.argtypes = [ci]
         L.dmx_profile_begin.argtypes = [vp]
         L.dmx_profile_end.argtypes = [vp, vp, vp, vp, vp]
+        L.dmx_profile_sequence.argtypes = [vp, vp, ci]
         L.dmx_stft_segment.argtypes = [vp, vp, vp]
         L.dmx_istft_segment.argtypes = [vp, vp, vp]
         _lib = L
@@ -136,6 +137,13 @@ class DemucsModel:
 
     def profile_begin(self):
         _check(lib().dmx_profile_begin(self._h), "dmx_profile_begin")
+
+    def profile_sequence(self):
+        """Class name of every launch scope since profile_begin(), in order (call before profile_end())."""
+        n = lib().dmx_profile_sequence(self._h, None, 0)
+        buf = np.zeros(max(n, 1), dtype=np.int32)
+        lib().dmx_profile_sequence(self._h, _p(buf), n)
+        return [lib().dmx_profile_class_name(int(c)).decode() for c in buf[:n]]
 
     def profile_end(self):
         """-> {class name: {"ms", "launches", "flops", "bytes"}} accumulated since profile_begin()."""

@@ -267,6 +267,17 @@ int dmx_profile_begin(dmx_model *m)
     return 0;
 }
 
+int dmx_profile_sequence(dmx_model *m, int *cls_out, int capacity)
+{
+    if (!m)
+        return -1;
+    std::lock_guard<std::mutex> lk(m->mtx);
+    const int n = (int)m->prof.recs.size();
+    for (int i = 0; i < n && i < capacity && cls_out; ++i)
+        cls_out[i] = m->prof.recs[i].cls;
+    return n;
+}
+
 int dmx_profile_end(dmx_model *m, double *ms, int64_t *launches, double *flops, double *bytes)
 {
     if (!m)

@@ -131,6 +131,9 @@ extern "C"
     const char *dmx_profile_class_name(int cls);
     int dmx_profile_begin(dmx_model *m);
     int dmx_profile_end(dmx_model *m, double *ms, int64_t *launches, double *flops, double *bytes);
+    /* Class index of every bracketed launch scope since dmx_profile_begin, in launch order (call before
+     * dmx_profile_end); returns the number of scopes.  Used to attribute an ncu launch list to classes. */
+    int dmx_profile_sequence(dmx_model *m, int *cls_out, int capacity);
 
     /* ---- stand-alone DSP pair: replaces demucscpp::stft / demucscpp::istft (src/dsp.hpp:103-104,
      *      src/dsp.cpp:51-117) on one 343980-frame stereo segment, through the same kernels the

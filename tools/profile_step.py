@@ -27,8 +27,15 @@ d_out = torch.empty((L, 2, m.nb_sources), dtype=torch.float32, device="cuda")
 for _ in range(2):
     m.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), 4033)
 torch.cuda.synchronize()
+m.profile_begin()
 torch.cuda.profiler.start()
 m.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), 4033)
 torch.cuda.synchronize()
 torch.cuda.profiler.stop()
+seq = m.profile_sequence()
+prof = m.profile_end()
+import json
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+with open(os.path.join(ROOT, "gpurun_out", "profile_step_classes.json"), "w") as f:
+    json.dump({"sequence": seq, "classes": prof}, f)
 print("device ms for 8 segments: %.2f" % m.last_device_ms)
