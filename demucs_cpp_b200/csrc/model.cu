@@ -6,18 +6,10 @@
 // views (kernels.cuh) and no transpose/shuffle of the reference is ever
 // materialised; transformer tokens are simply the rows of the [8][336][C] bottleneck (row f*336+t),
 // with the 2-D positional table built in that order.
-#include "model.cuh"
-
-#include <cmath>
-#include <cstring>
+#include "model_common.cuh"
 
 namespace dmx
 {
-
-static const int FREQS[5] = {2048, 512, 128, 32, 8};
-static const int TLENS[5] = {SEG, TLEN0, TLEN1, TLEN2, TLEN3};
-static const int CH[5] = {0, 48, 96, 192, 384}; // CH[i+1] = channels after encoder i
-static const int T = LE;
 
 // ------------------------------------------------------------------------------------------------
 // profiling
@@ -54,196 +46,6 @@ ProfScope::~ProfScope()
         cudaEventRecord(e1, m->stream);
 }
 
-// ------------------------------------------------------------------------------------------------
-// allocation helpers
-static int dev_alloc(dmx_model *m, void **p, size_t bytes)
-{
-    DMX_CUDA(cudaMalloc(p, bytes ? bytes : 16));
-    m->allocs.push_back(*p);
-    return 0;
-}
-
-template <typename Tp> static int dev_alloc_t(dmx_model *m, Tp **p, size_t n)
-{
-    return dev_alloc(m, reinterpret_cast<void **>(p), n * sizeof(Tp));
-}
-
-static int upload(dmx_model *m, float **dst, const std::vector<float> &v)
-{
-    if (dev_alloc_t(m, dst, v.size()))
-        return -1;
-    DMX_CUDA(cudaMemcpy(*dst, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice));
-    return 0;
-}
-
-static const HostTensor *get(dmx_model *m, const std::string &name, size_t numel)
-{
-    auto it = m->host.find(name);
-    if (it == m->host.end())
-    {
-        set_error("model: missing tensor " + name);
-        return nullptr;
-    }
-    if (it->second.numel() != numel)
-    {
-        set_error("model: tensor " + name + " has " + std::to_string(it->second.numel()) + " elements, expected " +
-                  std::to_string(numel));
-        return nullptr;
-    }
-    return &it->second;
-}
-
-static int upload_vec(dmx_model *m, float **dst, const std::string &name, size_t n)
-{
-    const HostTensor *t = get(m, name, n);
-    if (!t)
-        return -1;
-    return upload(m, dst, t->data);
-}
-
-static inline int round_up(int x, int k) { return (x + k - 1) / k * k; }
-
-static inline uint16_t f32_to_bf16_bits(float f)
-{
-    uint32_t u;
-    memcpy(&u, &f, 4);
-    if ((u & 0x7fffffffu) > 0x7f800000u)
-        return (uint16_t)((u >> 16) | 0x40); // NaN
-    u += 0x7fffu + ((u >> 16) & 1u);          // round to nearest even
-    return (uint16_t)(u >> 16);
-}
-
-// Generic packer: element (k, n) of the GEMM B operand given by f(k, n); bias by fb(n).
-// If glu: output columns are interleaved so that packed 2j = original j, packed 2j+1 = original j + N/2.
-template <typename FW, typename FB>
-static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb)
-{
-    p.K = K;
-    p.N = N;
-    p.ldw = round_up(N, 128);
-    const int Kpad = round_up(K, 16);
-    std::vector<float> w((size_t)Kpad * p.ldw, 0.f), b(p.ldw, 0.f);
-    for (int n = 0; n < N; ++n)
-    {
-        const int src = glu ? ((n & 1) ? (n >> 1) + N / 2 : (n >> 1)) : n;
-        for (int k = 0; k < K; ++k)
-            w[(size_t)k * p.ldw + n] = fw(k, src);
-        b[n] = fb(src);
-    }
-    if (upload(m, &p.W, w) || upload(m, &p.bias, b))
-        return -1;
-    // bf16 image for the tcgen05 kernel: same (k, n) contents, round-to-nearest-even, zero padded
-    {
-        std::vector<uint16_t> wb(tc_packed_elems(K, N), 0);
-        for (int n = 0; n < N; ++n)
-            for (int k = 0; k < K; ++k)
-                wb[tc_packed_index(K, N, k, n)] = f32_to_bf16_bits(w[(size_t)k * p.ldw + n]);
-        if (dev_alloc(m, &p.Wb, wb.size() * sizeof(uint16_t)))
-            return -1;
-        DMX_CUDA(cudaMemcpy(p.Wb, wb.data(), wb.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
-    }
-    return 0;
-}
-
-// Conv weight (Cout, Cin, ntaps) row-major -> B[tap*Cin + c][cout]   (src/conv.hpp:97-110 equivalent)
-static int pack_conv(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cout, int Cin,
-                     int ntaps, bool glu)
-{
-    const HostTensor *w = get(m, wname, (size_t)Cout * Cin * ntaps);
-    const HostTensor *b = get(m, bname, Cout);
-    if (!w || !b)
-        return -1;
-    const float *wd = w->data.data();
-    const float *bd = b->data.data();
-    return pack(
-        m, p, Cin * ntaps, Cout, glu,
-        [=](int k, int n) {
-            const int tap = k / Cin, c = k % Cin;
-            return wd[((size_t)n * Cin + c) * ntaps + tap];
-        },
-        [=](int n) { return bd[n]; });
-}
-
-// ConvTranspose k=8, s=4 weight (Cin, Cout, 8) -> two taps (x[i-1] with k=r+4, x[i] with k=r),
-// N = 4*Cout columns n = r*Cout + co   (src/conv.hpp:264-474 equivalent)
-static int pack_convtr(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cin, int Cout)
-{
-    const HostTensor *w = get(m, wname, (size_t)Cin * Cout * 8);
-    const HostTensor *b = get(m, bname, Cout);
-    if (!w || !b)
-        return -1;
-    const float *wd = w->data.data();
-    const float *bd = b->data.data();
-    return pack(
-        m, p, 2 * Cin, 4 * Cout, false,
-        [=](int k, int n) {
-            const int tap = k / Cin, c = k % Cin;
-            const int r = n / Cout, co = n % Cout;
-            const int kk = tap == 0 ? r + 4 : r;
-            return wd[((size_t)c * Cout + co) * 8 + kk];
-        },
-        [=](int n) { return bd[n % Cout]; });
-}
-
-// Linear weight rows [row0, row0+N) of an (out, in) matrix -> B[in][n]
-static int pack_linear(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int out_total,
-                       int in, int row0, int N)
-{
-    const HostTensor *w = get(m, wname, (size_t)out_total * in);
-    const HostTensor *b = get(m, bname, out_total);
-    if (!w || !b)
-        return -1;
-    const float *wd = w->data.data();
-    const float *bd = b->data.data();
-    return pack(
-        m, p, in, N, false, [=](int k, int n) { return wd[(size_t)(row0 + n) * in + k]; },
-        [=](int n) { return bd[row0 + n]; });
-}
-
-static int upload_vec_padded(dmx_model *m, float **dst, const std::string &name, size_t n, size_t npad)
-{
-    const HostTensor *t = get(m, name, n);
-    if (!t)
-        return -1;
-    std::vector<float> v(t->data);
-    v.resize(npad, 0.f);
-    return upload(m, dst, v);
-}
-
-static int pack_dconv(dmx_model *m, DConvW &d, const std::string &prefix, int C)
-{
-    d.C = C;
-    d.hid = C / 8;
-    // The hidden tensor is stored with its channel count rounded up to a multiple of 4 (6 -> 8) so that its
-    // rows stay 16-byte aligned for vector loads; the pad channels carry zero GroupNorm / conv weights.
-    d.hidp = round_up(d.hid, 4);
-    for (int j = 0; j < 2; ++j)
-    {
-        const std::string p = prefix + ".dconv.layers." + std::to_string(j) + ".";
-        if (pack_conv(m, d.c1[j], p + "0.weight", p + "0.bias", d.hid, C, 3, false))
-            return -1;
-        {
-            const HostTensor *w = get(m, p + "3.weight", (size_t)2 * C * d.hid);
-            const HostTensor *b = get(m, p + "3.bias", 2 * C);
-            if (!w || !b)
-                return -1;
-            const float *wd = w->data.data();
-            const float *bd = b->data.data();
-            const int hid = d.hid;
-            if (pack(
-                    m, d.c2[j], d.hidp, 2 * C, false, [=](int k, int n) { return k < hid ? wd[(size_t)n * hid + k] : 0.f; },
-                    [=](int n) { return bd[n]; }))
-                return -1;
-        }
-        if (upload_vec_padded(m, &d.g1w[j], p + "1.weight", d.hid, d.hidp) ||
-            upload_vec_padded(m, &d.g1b[j], p + "1.bias", d.hid, d.hidp) ||
-            upload_vec(m, &d.g2w[j], p + "4.weight", 2 * C) || upload_vec(m, &d.g2b[j], p + "4.bias", 2 * C) ||
-            upload_vec(m, &d.scale[j], p + "6.scale", C))
-            return -1;
-    }
-    return 0;
-}
-
 static int pack_tlayer(dmx_model *m, TLayerW &L, const std::string &p, bool cross, int d)
 {
     L.cross = cross;
@@ -269,42 +71,6 @@ static int pack_tlayer(dmx_model *m, TLayerW &L, const std::string &p, bool cros
     if (cross && (upload_vec(m, &L.n3w, p + "norm3.weight", d) || upload_vec(m, &L.n3b, p + "norm3.bias", d)))
         return -1;
     return 0;
-}
-
-// ------------------------------------------------------------------------------------------------
-// constant tables, computed exactly like the reference does (float libm calls)
-static std::vector<float> make_window()
-{
-    // src/dsp.hpp:59-75
-    const float PI = 3.14159265359F;
-    std::vector<float> w(NFFT);
-    const float floatN = (float)(NFFT + 1);
-    for (int n = 0; n < NFFT; ++n)
-        w[n] = 0.5F * (1.0F - cosf(2.0F * PI * (float)n / (floatN - 1)));
-    return w;
-}
-
-static std::vector<float> make_wss(const std::vector<float> &w)
-{
-    // src/dsp.hpp:77-100 with nb_frames = 340
-    const int nb_frames = PADDED / HOP + 1;
-    std::vector<float> out(OLA_LEN, 0.f);
-    for (int i = 0; i < nb_frames; ++i)
-        for (int j = 0; j < NFFT; ++j)
-            out[i * HOP + j] += w[j] * w[j];
-    return out;
-}
-
-static std::vector<float> make_twiddles()
-{
-    std::vector<float> t(2 * NFFT);
-    for (int k = 0; k < NFFT; ++k)
-    {
-        const double a = -2.0 * M_PI * (double)k / (double)NFFT;
-        t[2 * k] = (float)cos(a);
-        t[2 * k + 1] = (float)sin(a);
-    }
-    return t;
 }
 
 // 2-D sinusoidal embedding (src/crosstransformer.cpp:7-53) in token order row = f*T + t.
@@ -352,11 +118,8 @@ int model_finalize(dmx_model *m)
 {
     if (m->finalized)
         return 0;
-    if (m->arch != DMX_ARCH_HTDEMUCS_4S && m->arch != DMX_ARCH_HTDEMUCS_6S)
-    {
-        set_error("model_finalize: architecture not implemented on the CUDA path (hdemucs_mmi v3 is a later round)");
-        return -1;
-    }
+    if (m->arch == DMX_ARCH_HDEMUCS_V3)
+        return model_v3_finalize(m);
     DMX_CUDA(cudaSetDevice(m->device));
     DMX_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
     DMX_CUDA(cudaEventCreate(&m->ev0));
@@ -507,205 +270,10 @@ int model_finalize(dmx_model *m)
     return 0;
 }
 
-// ------------------------------------------------------------------------------------------------
-// forward helpers
-struct Fwd
-{
-    dmx_model *m;
-    int B;
-    cudaStream_t st;
-    int rc = 0;
-
-    double *stat_slots(size_t items)
-    {
-        double *p = m->stats + m->stats_used;
-        m->stats_used += 2 * items;
-        if (m->stats_used > m->stats_cap)
-        {
-            set_error("statistics arena overflow");
-            rc = -1;
-            return m->stats;
-        }
-        return p;
-    }
-    void gemm(const GemmParams &p, int cls)
-    {
-        if (rc)
-            return;
-        // algorithmic bytes: the input grid read once (+ skip tensor), the output written once (+ residual read)
-        const double nout = p.glu ? p.N / 2 : p.N;
-        const double esz_out = p.out_bf16 ? 2.0 : 4.0;
-        double bytes = (double)B * p.Ui * p.Vi * p.Cin * 4.0 * (p.A2 ? 2.0 : 1.0) + (double)p.M * nout * esz_out;
-        if (p.gamma)
-            bytes += (double)p.M * nout * 4.0;
-        ProfScope ps(m, cls, 2.0 * (double)p.M * (double)p.N * (double)p.K, bytes);
-        if (m->precision == DMX_PRECISION_BF16 && p.Wb)
-            rc = launch_gemm_tc(p, p.Wb, st);
-        else
-            rc = launch_gemm(p, st);
-    }
-    // common fields: single batch grid (U, V) in and out, plain output mapping
-    GemmParams base(const float *Ain, int lda, int Cin, const Packed &w, float *C, int ldc, int Ui, int Vi, int Uo,
-                    int Vo)
-    {
-        GemmParams p;
-        p.A = Ain;
-        p.lda = lda;
-        p.Cin = Cin;
-        p.K = w.K;
-        p.W = w.W;
-        p.Wb = w.Wb;
-        p.ldw = w.ldw;
-        p.bias = w.bias;
-        p.N = w.N;
-        p.Ui = Ui;
-        p.Vi = Vi;
-        p.Uo = Uo;
-        p.Vo = Vo;
-        p.M = B * Uo * Vo;
-        p.C = C;
-        p.ldc = ldc;
-        p.Nco = w.N;
-        p.Uout = Uo;
-        p.Vout = Vo;
-        return p;
-    }
-
-    // DConv residual branch (src/layers.cpp:152-375) in place on x [B][U][V][C]; GroupNorm items are
-    // frequency rows (per_u = 1) or whole batch elements (time branch, U = 1).
-    void dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u)
-    {
-        const int C = w.C, hid = w.hid, hidp = w.hidp;
-        const size_t items = (size_t)B * (per_u ? U : 1);
-        for (int j = 0; j < 2; ++j)
-        {
-            const int dil = 1 << j;
-            double *s1 = stat_slots(items), *s2 = stat_slots(items);
-            GemmParams p = base(x, C, C, w.c1[j], h, hidp, U, V, U, V);
-            p.ntaps = 3;
-            for (int t = 0; t < 3; ++t)
-            {
-                p.du[t] = 0;
-                p.dv[t] = (t - 1) * dil;
-            }
-            p.stats = s1;
-            p.stat_per_u = per_u;
-            gemm(p, PC_GEMM_DCONV);
-            GemmParams q = base(h, hidp, hidp, w.c2[j], y2, 2 * C, U, V, U, V);
-            q.pro = 1;
-            q.pro_stats = s1;
-            q.pro_count = per_u ? (double)V * hid : (double)U * V * hid;
-            q.pro_w = w.g1w[j];
-            q.pro_b = w.g1b[j];
-            q.pro_per_u = per_u;
-            q.stats = s2;
-            q.stat_per_u = per_u;
-            gemm(q, PC_GEMM_DCONV);
-            if (!rc)
-            {
-                ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * U * V * C * 4.0 * 4.0);
-                rc = launch_gn_glu_residual(y2, x, B, U, V, C, s2, per_u, w.g2w[j], w.g2b[j], w.scale[j], st);
-            }
-        }
-    }
-
-    void layer_norm(const float *x, float *y, int rows, int C, const float *w, const float *b, const float *add = nullptr,
-                    int add_rows = 0)
-    {
-        if (rc)
-            return;
-        ProfScope ps(m, PC_POINTWISE, 0.0, (double)rows * C * 8.0);
-        rc = launch_layer_norm(x, y, rows, C, w, b, add, add_rows, st);
-    }
-
-    // tokens-as-rows linear layer: [B*Tn][Cin] x W -> [B*Tn][N]
-    GemmParams linear(const float *x, int Cin, const Packed &w, float *y, int ldc, int Tn)
-    {
-        return base(x, Cin, Cin, w, y, ldc, 1, Tn, 1, Tn);
-    }
-
-    // one transformer layer (src/layers.cpp:377-531) on q [B*Tq][d]; kn = already-normalised key source
-    // for cross layers (nullptr for self attention).
-    void tlayer(const TLayerW &L, float *q, int Tq, const float *kn, int Tk, float *ln, float *qkv, float *kv, float *ao,
-                float *ff)
-    {
-        const int d = m->d_model, dh = d / 8;
-        layer_norm(q, ln, B * Tq, d, L.n1w, L.n1b);
-        // bf16 mode: the projections write Q/K/V as bf16 (same buffers, half the bytes) for the tensor-core
-        // attention; fp32 mode keeps everything fp32 on the CUDA-core kernels.
-        const bool tcm = m->precision == DMX_PRECISION_BF16;
-        if (!L.cross)
-        {
-            GemmParams pq = linear(ln, d, L.qkv, qkv, 3 * d, Tq);
-            pq.out_bf16 = tcm;
-            gemm(pq, PC_GEMM_XFMR);
-            if (!rc)
-            {
-                ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tq * d);
-                if (tcm)
-                {
-                    const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
-                    rc = launch_attention_tc(qb, 3 * d, qb + d, 3 * d, qb + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
-                }
-                else
-                    rc = launch_attention(qkv, 3 * d, qkv + d, 3 * d, qkv + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
-            }
-        }
-        else
-        {
-            GemmParams pq = linear(ln, d, L.q, qkv, d, Tq);
-            pq.out_bf16 = tcm;
-            gemm(pq, PC_GEMM_XFMR);
-            GemmParams pkv = linear(kn, d, L.kv, kv, 2 * d, Tk);
-            pkv.out_bf16 = tcm;
-            gemm(pkv, PC_GEMM_XFMR);
-            if (!rc)
-            {
-                ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tk * d);
-                if (tcm)
-                {
-                    const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
-                    const uint16_t *kb = reinterpret_cast<const uint16_t *>(kv);
-                    rc = launch_attention_tc(qb, d, kb, 2 * d, kb + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
-                }
-                else
-                    rc = launch_attention(qkv, d, kv, 2 * d, kv + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
-            }
-        }
-        GemmParams po = linear(ao, d, L.out, q, d, Tq);
-        po.gamma = L.g1;
-        gemm(po, PC_GEMM_XFMR);
-        // pre-FFN norm: norm3 for cross layers, norm2 for self layers (src/crosstransformer.cpp:111-113)
-        layer_norm(q, ln, B * Tq, d, L.cross ? L.n3w : L.n2w, L.cross ? L.n3b : L.n2b);
-        GemmParams p1 = linear(ln, d, L.ff1, ff, 4 * d, Tq);
-        p1.act = 1;
-        gemm(p1, PC_GEMM_XFMR);
-        GemmParams p2 = linear(ff, 4 * d, L.ff2, q, d, Tq);
-        p2.gamma = L.g2;
-        double *s = stat_slots(B);
-        p2.stats = s;
-        p2.stat_per_u = 0;
-        gemm(p2, PC_GEMM_XFMR);
-        if (!rc)
-        {
-            ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * Tq * d * 8.0);
-            rc = launch_group_norm_apply(q, B, Tq, d, s, L.now_, L.nob, st);
-        }
-    }
-};
-
-static void set_tap(dmx_model *m, const char *name, float *p, int64_t d1, int64_t d2, int64_t C)
-{
-    Tap t;
-    t.ptr = p;
-    t.d1 = d1;
-    t.d2 = d2;
-    t.C = C;
-    m->taps[name] = t;
-}
-
 int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
 {
+    if (m->arch == DMX_ARCH_HDEMUCS_V3)
+        return model_v3_forward(m, d_mix, B, d_out);
     if (!m->finalized)
     {
         set_error("model_forward: model not finalized");

@@ -68,6 +68,7 @@ enum ProfClass
     PC_GEMM_XFMR,
     PC_ATTENTION,
     PC_TRACK,
+    PC_LSTM,
     PC_COUNT
 };
 
@@ -86,6 +87,29 @@ struct Profiler
     double flops[PC_COUNT] = {0};
     double bytes[PC_COUNT] = {0};
     cudaEvent_t get();
+};
+
+// hdemucs_mmi (v3) DConv with BiLSTM + LocalState attention (src/layers.cpp:896-1113), one sub-block
+struct DConvLaW
+{
+    Packed c1, ih0, ih1, lin, qkcd, proj, c2;
+    float *whh_t[2][2]; // [layer][direction]: W_hh transposed to [H][4H]
+    float *g1w, *g1b, *g2w, *g2b, *scale;
+};
+
+struct V3Model
+{
+    EncW enc[4], tenc[4];
+    Packed tenc4, enc4_conv, enc4_rw, enc5_conv, enc5_rw;
+    float *e4n1w, *e4n1b, *e4n2w, *e4n2b, *e5n1w, *e5n1b, *e5n2w, *e5n2b;
+    DConvLaW la[2][2]; // [encoder 4|5][sub-block]
+    Packed d0_rw, d0_ct, d1_rw, d1_ct, td0_ct;
+    float *d0n1w, *d0n1b, *d0n2w, *d0n2b, *d1n1w, *d1n1b, *d1n2w, *d1n2b, *td0n2w, *td0n2b;
+    DecW cdec[4], ctdec[4];
+    float *ones = nullptr;
+    // workspace
+    float *xt4, *g4, *r4, *x4, *y5, *g5, *r5, *x5, *d0r, *d0g, *d0ct, *xd0, *d1r, *pre, *d1ct, *x3, *td0ct, *xt3;
+    float *hraw, *seq, *lpre, *l0, *l1, *lo, *qk, *att, *y2la;
 };
 
 struct Tap
@@ -111,6 +135,7 @@ struct dmx_model
     dmx::EncW enc[4], tenc[4];
     dmx::DecW dec[4], tdec[4];
     float *freq_emb2 = nullptr;
+    dmx::V3Model *v3 = nullptr;
     dmx::Packed up, up_t, down, down_t;
     float *nin_w, *nin_b, *nint_w, *nint_b, *pe2d, *pe1d;
     dmx::TLayerW lay[5], lay_t[5];
@@ -138,6 +163,8 @@ struct dmx_model
 namespace dmx
 {
 int model_finalize(dmx_model *m);
+int model_v3_finalize(dmx_model *m);
+int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out);
 int debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
                  int act, float *out, int iters, float *ms_out);
 int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out); // d_out: [B][S][SEG][2]

@@ -174,6 +174,13 @@ static const char *const kStageMsgs[26] = {
     "Freq (crosstransformer): layer 4", "Time (crosstransformer): layer 4", "Freq: decoder 0", "Time: decoder 0",
     "Freq: decoder 1", "Time: decoder 1", "Freq: decoder 2", "Time: decoder 2", "Freq: decoder 3", "Time: decoder 3"};
 
+// v3: 22 callbacks per segment (src/model_inference.cpp:584-734)
+static const char *const kStageMsgsV3[22] = {
+    "Time encoder 0", "Freq encoder 0", "Time encoder 1", "Freq encoder 1", "Time encoder 2", "Freq encoder 2",
+    "Time encoder 3", "Freq encoder 3", "Time encoder 4", "Freq encoder 4", "Shared encoder 5", "Shared decoder 0",
+    "Freq decoder 1", "Time decoder 1", "Freq decoder 2", "Time decoder 2", "Freq decoder 3", "Time decoder 3",
+    "Freq decoder 4", "Time decoder 4", "Freq decoder 5", "Time decoder 5"};
+
 static int track_stats(dmx_model *m, const float *d_audio, int64_t L)
 {
     cudaStream_t st = m->stream;
@@ -237,9 +244,12 @@ int track_forward_shard(dmx_model *m, const float *d_audio, int64_t L, int shift
         {
             // keep the reference's per-segment message sequence with monotone progress values
             DMX_CUDA(cudaStreamSynchronize(st));
+            const bool v3 = m->arch == DMX_ARCH_HDEMUCS_V3;
+            const int nmsg = v3 ? 22 : 26;
             for (int j = j0; j < j0 + nb; ++j)
-                for (int sidx = 0; sidx < 26; ++sidx)
-                    cb(((float)j + (float)(sidx + 1) / 26.0f) / (float)nloc, kStageMsgs[sidx], user);
+                for (int sidx = 0; sidx < nmsg; ++sidx)
+                    cb(((float)j + (float)(sidx + 1) / (float)nmsg) / (float)nloc, v3 ? kStageMsgsV3[sidx] : kStageMsgs[sidx],
+                       user);
         }
     }
     DMX_CUDA(cudaEventRecord(m->ev1, st));

@@ -144,9 +144,11 @@ class Weights:
     def __init__(self, tensors, dtype=torch.float32):
         self.t = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dtype) for k, v in tensors.items()}
         self.dtype = dtype
-        self.S = self.t["decoder.3.conv_tr.weight"].shape[1] // 4
+        self.is_v3 = "tencoder.4.conv.weight" in self.t
+        last = "decoder.5.conv_tr.weight" if self.is_v3 else "decoder.3.conv_tr.weight"
+        self.S = self.t[last].shape[1] // 4
         self.is_4s = "channel_upsampler.weight" in self.t
-        self.d_model = self.t["crosstransformer.norm_in.weight"].shape[0]
+        self.d_model = 0 if self.is_v3 else self.t["crosstransformer.norm_in.weight"].shape[0]
 
     def __getitem__(self, k):
         return self.t[k]
@@ -358,6 +360,188 @@ def segment_forward(W, mix, taps=None):
     return out
 
 
+# ----------------------------------------------------------------------------- hdemucs_mmi (v3)
+def group_norm_g(x, w, b, groups, eps=1e-5):
+    """demucscpp_v3::groupnorm::generalized_group_norm (src/layers.hpp:130-170): statistics per group over
+    (dim0, C/G, W) JOINTLY, N-1 variance.  x: (dim0, C, W)."""
+    d0, C, Wd = x.shape
+    xg = x.reshape(d0, groups, C // groups, Wd)
+    m, v = var_unbiased(xg, (0, 2, 3))
+    y = ((xg - m) / torch.sqrt(v + eps)).reshape(d0, C, Wd)
+    return y * w[None, :, None] + b[None, :, None]
+
+
+def lstm_bidir2(W, p, x):
+    """demucscpp_v3::lstm_forward (src/lstm.cpp:68-147): 2-layer bidirectional LSTM over the WHOLE sequence
+    (no 200-step framing), PyTorch gate order i,f,g,o, zero initial state.  x: (T, in) -> (T, 2h)."""
+    inp = x
+    for layer in range(2):
+        outs = []
+        for rev, suf in ((False, ""), (True, "_reverse")):
+            wih, whh = W[p + "weight_ih_l%d%s" % (layer, suf)], W[p + "weight_hh_l%d%s" % (layer, suf)]
+            bias = W[p + "bias_ih_l%d%s" % (layer, suf)] + W[p + "bias_hh_l%d%s" % (layer, suf)]
+            hsz = whh.shape[1]
+            pre = inp @ wih.T + bias                      # input projections of all steps
+            h = torch.zeros(hsz, dtype=x.dtype)
+            c = torch.zeros(hsz, dtype=x.dtype)
+            out = torch.empty(inp.shape[0], hsz, dtype=x.dtype)
+            steps = range(inp.shape[0] - 1, -1, -1) if rev else range(inp.shape[0])
+            for t in steps:
+                g = pre[t] + whh @ h
+                i_t = 1.0 / (1.0 + torch.exp(-g[:hsz]))
+                f_t = 1.0 / (1.0 + torch.exp(-g[hsz:2 * hsz]))
+                g_t = torch.tanh(g[2 * hsz:3 * hsz])
+                o_t = 1.0 / (1.0 + torch.exp(-g[3 * hsz:]))
+                c = f_t * c + i_t * g_t
+                h = o_t * torch.tanh(c)
+                out[t] = h
+            outs.append(out)
+        inp = torch.cat(outs, dim=1)
+    return inp
+
+
+def local_attention(W, p, x):
+    """demucscpp_v3::local_attention (src/layers.cpp:533-721).  x: (C, T) -> x + proj(attn).  4 heads, 4 decay
+    channels; dots[t, s] = <K[:, t], Q[:, s]>/sqrt(dh) + sum_n kernel[n, |t-s|] * 0.5*sigmoid(qd[h*4+n, s]);
+    diagonal := -100; softmax over t (keys) for each query s."""
+    C, T = x.shape
+    nh, nd = 4, 4
+    dh = C // nh
+    q = W[p + "query.weight"] @ x + W[p + "query.bias"][:, None]
+    k = W[p + "key.weight"] @ x + W[p + "key.bias"][:, None]
+    cont = W[p + "content.weight"] @ x + W[p + "content.bias"][:, None]
+    qd = W[p + "query_decay.weight"] @ x + W[p + "query_decay.bias"][:, None]
+    qd = 0.5 / (1.0 + torch.exp(-qd))                                     # :595-596
+    idx = torch.arange(T)
+    delta = (idx[:, None] - idx[None, :]).abs().to(x.dtype)               # |t - s|
+    out = torch.empty_like(x)
+    for h in range(nh):
+        sl = slice(h * dh, (h + 1) * dh)
+        dots = k[sl].T @ q[sl] / math.sqrt(float(dh))                     # [t, s]
+        for n in range(nd):
+            dots = dots + (-(n + 1) * delta / math.sqrt(float(nd))) * qd[h * nd + n][None, :]
+        dots = torch.where(torch.eye(T, dtype=torch.bool), torch.full_like(dots, -100.0), dots)
+        w = torch.softmax(dots, dim=0)                                    # over keys t
+        out[sl] = cont[sl] @ w                                            # out[c, s] = sum_t w[t, s] content[c, t]
+    return x + W[p + "proj.weight"] @ out + W[p + "proj.bias"][:, None]
+
+
+def dconv_v3(W, prefix, y):
+    """apply_dconv_v3 (src/layers.cpp:723-894): like dconv() with hidden = C/4."""
+    return dconv(W, prefix, y)
+
+
+def dconv_v3_lstm_attn(W, prefix, y):
+    """apply_dconv_v3_encoder_4_5 (src/layers.cpp:896-1113).  y: (1, C, T).  Per sub-block:
+    conv k3 dil -> GN(1)+GELU -> BiLSTM(2 layers)+Linear+skip -> LocalAttention -> 1x1 -> GN(1) -> GLU -> scale -> +=."""
+    for d in range(2):
+        p = "%s.dconv.layers.%d." % (prefix, d)
+        dil = 2 ** d
+        h = F.conv1d(y, W[p + "0.weight"], W[p + "0.bias"], padding=dil, dilation=dil)
+        h = gelu(group_norm1(h, W[p + "1.weight"], W[p + "1.bias"]))[0]            # (hid, T)
+        seq = h.T                                                                   # (T, hid)
+        lo = lstm_bidir2(W, p + "3.lstm.", seq) @ W[p + "3.linear.weight"].T + W[p + "3.linear.bias"] + seq
+        h = local_attention(W, p + "4.", lo.T)[None]                                # (1, hid, T)
+        h = F.conv1d(h, W[p + "5.weight"][:, :, None], W[p + "5.bias"])
+        h = glu(group_norm1(h, W[p + "6.weight"], W[p + "6.bias"]), 1)
+        y = y + h * W[p + "8.scale"][None, :, None]
+    return y
+
+
+def segment_forward_v3(W, mix, taps=None):
+    """demucscpp_v3::model_v3_inference (src/model_inference.cpp:477-856).  mix: (2, 343980) -> (4, 2, 343980)."""
+    dt = W.dtype
+    mix = mix.to(dt)
+    tp = taps if taps is not None else {}
+    padded = mirror_pad_edge(mix, PAD, PAD_END)
+    z = stft(padded)[:, :NFFT // 2, 2:2 + LE]
+    x = torch.stack([z[0].real, z[0].imag, z[1].real, z[1].imag]).to(dt)
+    mean, var = var_unbiased(x, (0, 1, 2))
+    std = torch.sqrt(var)
+    x = (x - mean) / (std + 1e-5)
+    meant, vart = var_unbiased(mix, (0, 1))
+    stdt = torch.sqrt(vart)
+    xt = (mix - meant) / (stdt + 1e-5)
+    tp["x"], tp["xt"] = x, xt[None]
+    saved, savedt = [], []
+    for i in range(4):                                                   # :586-655 (encdec.cpp:363-517)
+        xt = time_encoder(W, i, xt)
+        x = freq_encoder(W, i, x)
+        if i == 0:
+            x = x + 2.0 * W["freq_emb.embedding.weight"].T[:, :, None]
+        saved.append(x)
+        savedt.append(xt)
+        tp["saved_%d" % i], tp["savedt_%d" % i] = x, xt[None]
+    # tencoder 4: plain conv, no activation (encdec.cpp:519-530)
+    xt4 = conv1d_ceil(xt[None], W["tencoder.4.conv.weight"], W["tencoder.4.conv.bias"], 4, 2)   # (1, 768, 336)
+    tp["xt_4"] = xt4
+    # encoder 4 (encdec.cpp:532-573): k(8,1) s(4,1) conv collapses 8 bins to 1, + inject, GN(4)+GELU, DConv, 1x1, GN(4), GLU
+    y = F.conv2d(x[None], W["encoder.4.conv.weight"][..., None], W["encoder.4.conv.bias"], stride=(4, 1))[0]  # (768,1,336)
+    y = y.permute(1, 0, 2) + xt4                                          # (1, 768, 336)
+    y = gelu(group_norm_g(y, W["encoder.4.norm1.weight"], W["encoder.4.norm1.bias"], 4))
+    y = dconv_v3_lstm_attn(W, "encoder.4", y)
+    y = F.conv1d(y, W["encoder.4.rewrite.weight"][:, :, None], W["encoder.4.rewrite.bias"])
+    y = group_norm_g(y, W["encoder.4.norm2.weight"], W["encoder.4.norm2.bias"], 4)
+    x4 = glu(y, 1)                                                        # (1, 768, 336)
+    tp["saved_4"] = x4.permute(1, 0, 2)                                   # reference keeps it as (768, 1, 336)
+    # shared encoder 5 (encdec.cpp:575-615)
+    y = conv1d_ceil(x4, W["encoder.5.conv.weight"], W["encoder.5.conv.bias"], 2, 1)               # (1, 1536, 168)
+    y = gelu(group_norm_g(y, W["encoder.5.norm1.weight"], W["encoder.5.norm1.bias"], 4))
+    y = dconv_v3_lstm_attn(W, "encoder.5", y)
+    y = F.conv1d(y, W["encoder.5.rewrite.weight"][:, :, None], W["encoder.5.rewrite.bias"])
+    y = group_norm_g(y, W["encoder.5.norm2.weight"], W["encoder.5.norm2.bias"], 4)
+    x5 = glu(y, 1)                                                        # (1, 1536, 168)
+    tp["x_shared_5"] = x5
+    # shared decoder 0 (encdec.cpp:617-656): input = skip only
+    y = F.conv1d(x5, W["decoder.0.rewrite.weight"], W["decoder.0.rewrite.bias"], padding=1)
+    y = glu(group_norm_g(y, W["decoder.0.norm1.weight"], W["decoder.0.norm1.bias"], 4), 1)
+    y = F.conv_transpose1d(y, W["decoder.0.conv_tr.weight"], W["decoder.0.conv_tr.bias"], stride=2)
+    y = gelu(group_norm_g(y, W["decoder.0.norm2.weight"], W["decoder.0.norm2.bias"], 4))
+    xd0 = y[:, :, 1:1 + LE]                                               # (1, 768, 336)
+    tp["x_4"] = xd0
+    # freq decoder 1 (encdec.cpp:658-698): returns `pre`, seeds the time decoder chain
+    y = (xd0.permute(1, 0, 2) + x4.permute(1, 0, 2))[None]                # (1, 768, 1, 336)
+    y = F.conv2d(y, W["decoder.1.rewrite.weight"], W["decoder.1.rewrite.bias"], padding=1)[0]     # (1536, 1, 336)
+    y = group_norm_g(y.permute(1, 0, 2), W["decoder.1.norm1.weight"], W["decoder.1.norm1.bias"], 4).permute(1, 0, 2)
+    pre = glu(y, 0)                                                       # (768, 1, 336)
+    y = F.conv_transpose2d(pre[None], W["decoder.1.conv_tr.weight"][..., None], W["decoder.1.conv_tr.bias"],
+                           stride=(4, 1))[0]                              # (384, 8, 336)
+    x = gelu(group_norm_g(y.permute(1, 0, 2), W["decoder.1.norm2.weight"], W["decoder.1.norm2.bias"], 4)).permute(1, 0, 2)
+    tp["x_3"] = x
+    # time decoder 0 (encdec.cpp:700-726)
+    y = F.conv_transpose1d(pre.permute(1, 0, 2), W["tdecoder.0.conv_tr.weight"], W["tdecoder.0.conv_tr.bias"], stride=4)
+    y = gelu(group_norm_g(y, W["tdecoder.0.norm2.weight"], W["tdecoder.0.norm2.bias"], 4))
+    xt = y[0, :, 2:2 + TLEN[4]]                                           # (384, 1344)
+    tp["xt_3"] = xt[None]
+    # common decoders, no DConv (encdec.cpp:728-863)
+    names = ["2", "1", "0", "out"]
+    for l in range(4):
+        pf, pt = "decoder.%d" % (l + 2), "tdecoder.%d" % (l + 1)
+        y = F.conv2d((x + saved[3 - l])[None], W[pf + ".rewrite.weight"], W[pf + ".rewrite.bias"], padding=1)[0]
+        y = glu(y, 0)
+        y = F.conv_transpose2d(y[None], W[pf + ".conv_tr.weight"][..., None], W[pf + ".conv_tr.bias"], stride=(4, 1))[0]
+        if l < 3:
+            y = gelu(y)
+        x = y[:, 2:y.shape[1] - 2, :]
+        yt = F.conv1d((xt + savedt[3 - l])[None], W[pt + ".rewrite.weight"], W[pt + ".rewrite.bias"], padding=1)
+        yt = glu(yt, 1)
+        yt = F.conv_transpose1d(yt, W[pt + ".conv_tr.weight"], W[pt + ".conv_tr.bias"], stride=4)[0]
+        if l < 3:
+            yt = gelu(yt)
+        xt = yt[:, 2:2 + TLEN[3 - l]]
+        tp["x_" + names[l]], tp["xt_" + names[l]] = x, xt[None]
+    x = x * std + mean
+    xt = xt * stdt + meant
+    out = torch.empty(4, 2, SEG, dtype=dt)
+    for s_ in range(4):
+        xs = x[4 * s_:4 * s_ + 4]
+        zc = torch.complex(torch.stack([xs[0], xs[2]]), torch.stack([xs[1], xs[3]]))
+        zc = F.pad(zc, (2, 2, 0, 1))
+        w = istft(zc, SEG + PAD + PAD_END)
+        out[s_] = w[:, PAD:PAD + SEG] + xt[2 * s_:2 * s_ + 2]
+    return out
+
+
 # ----------------------------------------------------------------------------- track level
 def segment_plan(length):
     """Chunk (offset, length) list of split_inference (src/model_apply.cpp:200-204)."""
@@ -377,7 +561,8 @@ def separate(W, audio, shift_offset, forward=None):
     """demucscpp::demucs_inference (src/model_apply.cpp:60-288) with the random shift
     (`rand() % 22050`, :114) passed in explicitly.  audio: (2, L) -> (S, 2, L)."""
     dt = W.dtype
-    forward = forward or (lambda m: segment_forward(W, m))
+    forward = forward or ((lambda m: segment_forward_v3(W, m)) if getattr(W, "is_v3", False)
+                          else (lambda m: segment_forward(W, m)))
     a = torch.as_tensor(audio).to(dt)
     L = a.shape[1]
     ref = a.mean(dim=0)                                                  # :72

@@ -16,6 +16,13 @@ STAGE_TAPS = ["x", "xt", "saved_0", "savedt_0", "saved_1", "savedt_1", "saved_2"
 from demucs_cpp_b200.synth import synth_audio  # noqa: E402,F401
 
 
+STAGE_TAPS_V3 = ["x", "xt", "saved_0", "savedt_0", "saved_1", "savedt_1", "saved_2", "savedt_2", "saved_3", "savedt_3",
+                 "saved_4", "x_shared_5", "x_4", "x_3", "xt_3", "x_2", "xt_2", "x_1", "xt_1", "x_0", "xt_0", "x_out", "xt_out"]
+# the subset of the v3 taps that the reference's own scratch struct keeps after a forward (oracle/ref_harness.cpp)
+REF_TAPS_V3 = ["x", "saved_0", "savedt_0", "saved_1", "savedt_1", "saved_2", "savedt_2", "saved_3", "savedt_3", "saved_4",
+               "x_shared_5", "x_out", "xt_out"]
+
+
 def max_rel_err(a, b):
     """max |a-b| / max |b|  -- the per-layer metric of BASELINE.md §4."""
     a = np.asarray(a, dtype=np.float64)
@@ -40,8 +47,8 @@ def oracle_tap_to_cfirst(name, t):
     """Oracle / reference tap in the reference's logical order -> (C, positions).
     Freq taps are (C, F, T); time taps are (1, C, L)."""
     a = np.asarray(t)
-    if name.startswith("xt") or name.startswith("savedt"):
-        a = a[0]
+    if name.startswith("xt") or name.startswith("savedt") or name in ("x_shared_5", "x_4"):
+        a = a[0]                      # (1, C, L) time-like tensors
     return a.reshape(a.shape[0], -1)
 
 

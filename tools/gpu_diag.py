@@ -45,13 +45,15 @@ def main():
     t0 = time.time()
     out = m.model_inference(segs)
     print("gpu forward (second call, incl. H2D/D2H) %.3fs, launches so far %d" % (time.time() - t0, m.launch_count))
-    taps = {n: m.tap(n) for n in util.STAGE_TAPS if not (args.arch != "htdemucs_4s" and n.endswith("_up"))}
+    v3 = args.arch == "hdemucs_mmi"
+    names = util.STAGE_TAPS_V3 if v3 else [n for n in util.STAGE_TAPS if not (args.arch != "htdemucs_4s" and n.endswith("_up"))]
+    taps = {n: m.tap(n) for n in names}
     rows = []
     for b in range(args.batch):
         otaps = {}
         t0 = time.time()
         with torch.no_grad():
-            oref = O.segment_forward(W, torch.from_numpy(segs[b]), otaps).numpy()
+            oref = (O.segment_forward_v3 if v3 else O.segment_forward)(W, torch.from_numpy(segs[b]), otaps).numpy()
         print("oracle forward b=%d %.1fs" % (b, time.time() - t0))
         for n in taps:
             a = util.tap_to_cfirst(taps[n])[b]
