@@ -183,9 +183,19 @@ def run_reference(args):
     return 0
 
 
+WORKLOADS = {
+    "htdemucs_4s": "htdemucs 4-source, random-init weights (seed 0, ggml f16), 3-minute synthetic stereo 44.1 kHz track = 31 "
+                   "overlapping 7.8 s segments (BASELINE.json configs[1])",
+    "htdemucs_6s": "htdemucs_6s 6-source, random-init weights, 3-minute synthetic track, 31 segments (BASELINE.json configs[2])",
+    "htdemucs_ft": "htdemucs_ft bag of 4 fine-tuned 4-source models (random-init, seeds 0-3), 3-minute synthetic track, "
+                   "4 x 31 = 124 (model, segment) units, stem i from model i (BASELINE.json configs[3])",
+    "hdemucs_mmi": "hdemucs_mmi v3 hybrid (BiLSTM + local attention), random-init weights, 3-minute synthetic track, 31 "
+                   "segments (BASELINE.json configs[4])",
+}
+
+
 def workload_config(args, world):
-    return {"workload": "htdemucs 4-source, random-init weights (seed 0, ggml f16), 3-minute synthetic stereo 44.1 kHz "
-                        "track = 31 overlapping 7.8 s segments (BASELINE.json configs[1])",
+    return {"workload": WORKLOADS[getattr(args, "model", "htdemucs_4s")],
             "segments": 31, "segments_per_launch": args.batch, "precision": args.precision, "shift_offset": SHIFT,
             "l2": "inputs larger than L2: 63.5 MB track + %.1f GB of per-batch activations stream through the 126 MB L2 "
                   "every step" % (0.52 * args.batch),
@@ -205,6 +215,8 @@ def main():
                     help="bf16: tcgen05 GEMMs/attention with bf16 operands, fp32 accumulate/residual/statistics (stems >= 40 dB "
                          "vs the reference); fp32: CUDA-core path (stems >= 80 dB)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--model", default="htdemucs_4s", choices=["htdemucs_4s", "htdemucs_6s", "hdemucs_mmi", "htdemucs_ft"],
+                    help="htdemucs_4s = BASELINE.json configs[1] (the headline); the others are configs[2..4]")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -225,9 +237,18 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    path = weights.cached_weights("htdemucs_4s", 0)
-    model = api.DemucsModel(path, device=local_rank, max_batch=args.batch,
-                            precision=api.PRECISION_BF16 if args.precision == "bf16" else api.PRECISION_FP32)
+    prec = api.PRECISION_BF16 if args.precision == "bf16" else api.PRECISION_FP32
+    if args.model == "htdemucs_ft":
+        # bag of four fine-tuned 4-source models: four sequential passes, each with its own random shift (the
+        # successive rand() % 22050 draws of a fresh process), stem i taken from model i (cli-apps/demucs_ft.cpp:221-241)
+        models = [api.DemucsModel(weights.cached_weights("htdemucs_4s", seed), device=local_rank, max_batch=args.batch,
+                                  precision=prec) for seed in range(4)]
+        shifts = [4033, 12436, 5427, 6865]
+    else:
+        models = [api.DemucsModel(weights.cached_weights(args.model, 0), device=local_rank, max_batch=args.batch,
+                                  precision=prec)]
+        shifts = [SHIFT]
+    model = models[0]
     S = model.nb_sources
     L = TRACK_SECONDS * SR
     audio = synth_audio(L)                                           # (2, L)
@@ -246,27 +267,34 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    d_bag = torch.empty((L, 2, S), dtype=torch.float32, device=dev) if len(models) > 1 else None
+
     def step_device():
-        """one separation with inputs resident in HBM; returns device ms of this rank's kernels"""
-        if world == 1:
-            model.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), SHIFT)
-            return model.last_device_ms
-        model.forward_shard_device(d_audio.data_ptr(), L, SHIFT, rank, world, d_y.data_ptr())
-        ms = model.last_device_ms
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        dist.gather(d_y, list(d_y_all.unbind(0)) if rank == 0 else None, dst=0)
-        ev1.record()
-        torch.cuda.synchronize()
-        ms += ev0.elapsed_time(ev1)
-        if rank == 0:
-            model.overlap_add_device(d_audio.data_ptr(), L, SHIFT, d_y_all.data_ptr(), world, d_out.data_ptr())
-            ms += model.last_device_ms
+        """one separation (all bag members) with inputs resident in HBM; returns device ms of this rank's work"""
+        ms = 0.0
+        for i, (mdl, shift) in enumerate(zip(models, shifts)):
+            if world == 1:
+                mdl.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), shift)
+                ms += mdl.last_device_ms
+            else:
+                mdl.forward_shard_device(d_audio.data_ptr(), L, shift, rank, world, d_y.data_ptr())
+                ms += mdl.last_device_ms
+                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ev0.record()
+                dist.gather(d_y, list(d_y_all.unbind(0)) if rank == 0 else None, dst=0)
+                ev1.record()
+                torch.cuda.synchronize()
+                ms += ev0.elapsed_time(ev1)
+                if rank == 0:
+                    mdl.overlap_add_device(d_audio.data_ptr(), L, shift, d_y_all.data_ptr(), world, d_out.data_ptr())
+                    ms += mdl.last_device_ms
+            if d_bag is not None and rank == 0:
+                d_bag[:, :, i].copy_(d_out[:, :, i])            # stem i from model i
         return ms
 
     def step_e2e():
         """the same through host buffers: pinned host audio -> device, stems -> pinned host"""
-        if world == 1:
+        if world == 1 and len(models) == 1:
             r = api.lib().dmx_separate(model._h, h_audio.data_ptr(), L, SHIFT, h_out.data_ptr(),
                                        api.ctypes.cast(None, api.PROGRESS_FN), None)
             if r != 0:
@@ -276,7 +304,7 @@ def main():
         torch.cuda.synchronize()
         step_device()
         if rank == 0:
-            h_out.copy_(d_out, non_blocking=True)
+            h_out.copy_(d_out if d_bag is None else d_bag, non_blocking=True)
             torch.cuda.synchronize()
 
     # ---- device-resident timing ----
@@ -286,17 +314,26 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = model.launch_count
-    model.profile_begin()
+    launches0 = sum(mm.launch_count for mm in models)
+    for mm in models:
+        mm.profile_begin()
     t0 = time.perf_counter()
     dev_ms = 0.0
     for _ in range(args.steps):
         dev_ms += step_device()
     sync_all()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    prof = model.profile_end()
+    prof = None
+    for mm in models:
+        pr = mm.profile_end()
+        if prof is None:
+            prof = pr
+        else:
+            for k in pr:
+                for f in pr[k]:
+                    prof[k][f] += pr[k][f]
     clocks = sampler.stop() if rank == 0 else None
-    launches = model.launch_count - launches0
+    launches = sum(mm.launch_count for mm in models) - launches0
 
     # ---- end-to-end timing ----
     for _ in range(2):
@@ -381,7 +418,8 @@ def main():
     # ---- CPU baseline: the reference's own code on this box's host cores, bounded sample ----
     if world == 1 and not args.no_cpu_baseline:
         if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdemucs_ref.so")):
-            model.close()
+            for mm in models:
+                mm.close()
             cores = os.cpu_count() or 1
             with quiet_stdout():
                 times, _ = time_reference_segments(1, cores, 1, 0, budget_s=60.0)

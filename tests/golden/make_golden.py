@@ -43,7 +43,8 @@ def golden_segment(arch, stress, tag):
     mix = util.synth_audio(util.SEG)
     out = m.segment(mix)
     d = {}
-    names = [n for n in util.STAGE_TAPS if not (arch != "htdemucs_4s" and n.endswith("_up"))]
+    names = util.REF_TAPS_V3 if arch == "hdemucs_mmi" else \
+        [n for n in util.STAGE_TAPS if not (arch != "htdemucs_4s" and n.endswith("_up"))]
     for n in names:
         v = util.ref_view_to_cfirst(n, m.view(n))
         d[n + ".sub"], d[n + ".stat"] = summarize(v)
@@ -85,8 +86,14 @@ def golden_dsp():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "v3":
+        golden_segment("hdemucs_mmi", False, "hdemucs_mmi")
+        golden_segment("hdemucs_mmi", True, "hdemucs_mmi_stress")
+        sys.exit(0)
     golden_dsp()
     golden_segment("htdemucs_4s", False, "htdemucs_4s")
     golden_segment("htdemucs_4s", True, "htdemucs_4s_stress")
     golden_segment("htdemucs_6s", False, "htdemucs_6s")
     golden_separate()
+    golden_segment("hdemucs_mmi", False, "hdemucs_mmi")
+    golden_segment("hdemucs_mmi", True, "hdemucs_mmi_stress")

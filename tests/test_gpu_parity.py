@@ -93,12 +93,14 @@ def test_istft_matches_oracle_full():
 # ------------------------------------------------------------------------------------------- forward
 @pytest.mark.parametrize("arch,stress,tag", [("htdemucs_4s", False, "htdemucs_4s"),
                                              ("htdemucs_4s", True, "htdemucs_4s_stress"),
-                                             ("htdemucs_6s", False, "htdemucs_6s")])
+                                             ("htdemucs_6s", False, "htdemucs_6s"),
+                                             ("hdemucs_mmi", False, "hdemucs_mmi"),
+                                             ("hdemucs_mmi", True, "hdemucs_mmi_stress")])
 def test_forward_matches_reference_golden(golden_dir, arch, stress, tag):
     g = np.load(os.path.join(golden_dir, "segment_%s.npz" % tag))
     m = model(arch, stress)
     out = m.model_inference(util.synth_audio(util.SEG)[None])[0]
-    for n in util.STAGE_TAPS:
+    for n in (util.STAGE_TAPS_V3 if arch == "hdemucs_mmi" else util.STAGE_TAPS):
         if n + ".sub" not in g.files:
             continue
         check_summary(n, util.tap_to_cfirst(m.tap(n))[0], g[n + ".sub"], g[n + ".stat"], TOL_FP32)
@@ -106,7 +108,7 @@ def test_forward_matches_reference_golden(golden_dir, arch, stress, tag):
     assert util.snr_db(out.reshape(-1)[sub_idx(out.size)], g["targets.sub"]) >= SNR_FP32
 
 
-@pytest.mark.parametrize("arch,stress", [("htdemucs_4s", True), ("htdemucs_6s", True)])
+@pytest.mark.parametrize("arch,stress", [("htdemucs_4s", True), ("htdemucs_6s", True), ("hdemucs_mmi", True)])
 def test_forward_matches_oracle_full_batched(arch, stress):
     """Every stage tensor in full, batch of 3 different segments incl. a centre-padded short chunk."""
     base = util.synth_audio(util.SEG + 5000, seed=21)
@@ -116,12 +118,13 @@ def test_forward_matches_oracle_full_batched(arch, stress):
     out = m.model_inference(segs)
     _, tens = weights.read_ggml(weights.cached_weights(arch, 0, stress))
     W = O.Weights(tens, torch.float32)
-    names = [n for n in util.STAGE_TAPS if not (arch != "htdemucs_4s" and n.endswith("_up"))]
+    names = util.STAGE_TAPS_V3 if W.is_v3 else [n for n in util.STAGE_TAPS if not (arch != "htdemucs_4s" and n.endswith("_up"))]
     taps = {n: util.tap_to_cfirst(m.tap(n)) for n in names}
+    fwd = O.segment_forward_v3 if W.is_v3 else O.segment_forward
     for b in range(3):
         ot = {}
         with torch.no_grad():
-            ref = O.segment_forward(W, torch.from_numpy(segs[b]), ot).numpy()
+            ref = fwd(W, torch.from_numpy(segs[b]), ot).numpy()
         for n in names:
             err = util.max_rel_err(taps[n][b], util.oracle_tap_to_cfirst(n, ot[n].numpy()))
             assert err <= TOL_FP32, "b=%d %s max rel err %.3e" % (b, n, err)
@@ -211,13 +214,14 @@ def test_gemm_kernels_in_isolation(M, N, K):
 
 
 @pytest.mark.parametrize("arch,stress,tag", [("htdemucs_4s", False, "htdemucs_4s"),
-                                             ("htdemucs_6s", False, "htdemucs_6s")])
+                                             ("htdemucs_6s", False, "htdemucs_6s"),
+                                             ("hdemucs_mmi", False, "hdemucs_mmi")])
 def test_bf16_forward_matches_reference_golden(golden_dir, arch, stress, tag):
     """bf16 mode at BASELINE.json's bf16 bar: every stage <= 1e-2 max relative error, stems >= 40 dB."""
     g = np.load(os.path.join(golden_dir, "segment_%s.npz" % tag))
     m = model(arch, stress, precision=api.PRECISION_BF16)
     out = m.model_inference(util.synth_audio(util.SEG)[None])[0]
-    for n in util.STAGE_TAPS:
+    for n in (util.STAGE_TAPS_V3 if arch == "hdemucs_mmi" else util.STAGE_TAPS):
         if n + ".sub" not in g.files:
             continue
         check_summary(n, util.tap_to_cfirst(m.tap(n))[0], g[n + ".sub"], g[n + ".stat"], TOL_BF16)
@@ -240,3 +244,18 @@ def test_bf16_separate_matches_reference_golden(golden_dir):
     g = np.load(os.path.join(golden_dir, "separate_htdemucs_4s_10s.npz"))
     out = model(precision=api.PRECISION_BF16).demucs_inference(util.synth_audio(441000), shift_offset=int(g["shift"][0]))
     assert util.snr_db(out.reshape(-1)[sub_idx(out.size)], g["sub"]) >= SNR_BF16
+
+
+def test_v3_separate_matches_oracle_pipeline():
+    """hdemucs_mmi through demucs_v3_inference's replacement on the 10 s clip (2 segments, ragged second one),
+    incl. the v3 progress-callback sequence (22 messages per segment, src/model_inference.cpp:584-734)."""
+    m = model("hdemucs_mmi")
+    audio = util.synth_audio(441000)
+    calls = []
+    out = m.demucs_inference(audio, cb=lambda p, msg: calls.append((p, msg)), shift_offset=4033)
+    _, tens = weights.read_ggml(weights.cached_weights("hdemucs_mmi", 0))
+    with torch.no_grad():
+        ref = O.separate(O.Weights(tens, torch.float32), audio, 4033).numpy()
+    assert out.shape == (4, 2, 441000)
+    assert util.snr_db(out, ref) >= SNR_FP32 and util.max_rel_err(out, ref) <= TOL_FP32
+    assert len(calls) == 22 * 2 and calls[8][1] == "Time encoder 4" and calls[-1][1] == "Time decoder 5"

@@ -48,15 +48,18 @@ def test_stft_istft_against_reference(golden_dir, torch_threads):
 
 @pytest.mark.parametrize("arch,stress,tag", [("htdemucs_4s", False, "htdemucs_4s"),
                                              ("htdemucs_4s", True, "htdemucs_4s_stress"),
-                                             ("htdemucs_6s", False, "htdemucs_6s")])
+                                             ("htdemucs_6s", False, "htdemucs_6s"),
+                                             ("hdemucs_mmi", False, "hdemucs_mmi"),
+                                             ("hdemucs_mmi", True, "hdemucs_mmi_stress")])
 def test_segment_forward_against_reference(golden_dir, torch_threads, arch, stress, tag):
     g = np.load(os.path.join(golden_dir, "segment_%s.npz" % tag))
     _, tens = weights.read_ggml(weights.cached_weights(arch, 0, stress))
     W = O.Weights(tens, torch.float32)
     taps = {}
+    fwd = O.segment_forward_v3 if W.is_v3 else O.segment_forward
     with torch.no_grad():
-        out = O.segment_forward(W, torch.from_numpy(util.synth_audio(util.SEG)), taps).numpy()
-    for n in util.STAGE_TAPS:
+        out = fwd(W, torch.from_numpy(util.synth_audio(util.SEG)), taps).numpy()
+    for n in (util.STAGE_TAPS_V3 if W.is_v3 else util.STAGE_TAPS):
         if n + ".sub" not in g.files:
             continue
         check_summary(n, util.oracle_tap_to_cfirst(n, taps[n].numpy()), g[n + ".sub"], g[n + ".stat"])
