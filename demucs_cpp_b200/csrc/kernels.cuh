@@ -93,8 +93,8 @@ int launch_group_norm_apply(float *x, int B, int rows_per_item, int C, const dou
 // v3_kernels.cu (hdemucs_mmi)
 int launch_group_norm_g(const float *x, float *y, int B, int rows_in, int rows_out, int row0, int C, int G,
                         double *stats_zeroed, const float *w, const float *b, int act, int glu, cudaStream_t st);
-int launch_lstm_recurrent(const float *pre, const float *whh_t_fwd, const float *whh_t_bwd, float *out, int B, int T,
-                          int H, cudaStream_t st);
+int launch_lstm_recurrent(const float *pre, const float *whh_fwd, const float *whh_bwd, const float *whh_t_fwd,
+                          const float *whh_t_bwd, float *out, int B, int T, int H, cudaStream_t st);
 int launch_local_attention(const float *qkcd, float *out, int B, int T, int C, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------

@@ -93,7 +93,8 @@ struct Profiler
 struct DConvLaW
 {
     Packed c1, ih0, ih1, lin, qkcd, proj, c2;
-    float *whh_t[2][2]; // [layer][direction]: W_hh transposed to [H][4H]
+    float *whh_t[2][2]; // [layer][direction]: W_hh transposed to [H][4H] (fallback kernel)
+    float *whh[2][2];   // W_hh as stored, [4H][H] (cluster kernel keeps its rows in registers)
     float *g1w, *g1b, *g2w, *g2b, *scale;
 };
 

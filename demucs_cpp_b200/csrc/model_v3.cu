@@ -50,7 +50,7 @@ static int pack_la(dmx_model *m, DConvLaW &w, const std::string &p, int C, int h
             for (int j = 0; j < G4; ++j)
                 for (int k = 0; k < hid; ++k)
                     t[(size_t)k * G4 + j] = hh->data[(size_t)j * hid + k];
-            if (upload(m, &w.whh_t[layer][dir], t))
+            if (upload(m, &w.whh_t[layer][dir], t) || upload(m, &w.whh[layer][dir], hh->data))
                 return -1;
         }
     }
@@ -284,13 +284,13 @@ static void dconv_la(Fwd &f, float *x, int Tn, int C, int hid, const DConvLaW *w
         if (!f.rc)
         {
             ProfScope ps(m, PC_LSTM, 2.0 * B * Tn * 2.0 * 4.0 * hid * hid);
-            f.rc = launch_lstm_recurrent(v->lpre, w.whh_t[0][0], w.whh_t[0][1], v->l0, B, Tn, hid, f.st);
+            f.rc = launch_lstm_recurrent(v->lpre, w.whh[0][0], w.whh[0][1], w.whh_t[0][0], w.whh_t[0][1], v->l0, B, Tn, hid, f.st);
         }
         f.gemm(f.linear(v->l0, 2 * hid, w.ih1, v->lpre, 8 * hid, Tn), PC_GEMM_DCONV);
         if (!f.rc)
         {
             ProfScope ps(m, PC_LSTM, 2.0 * B * Tn * 2.0 * 4.0 * hid * hid);
-            f.rc = launch_lstm_recurrent(v->lpre, w.whh_t[1][0], w.whh_t[1][1], v->l1, B, Tn, hid, f.st);
+            f.rc = launch_lstm_recurrent(v->lpre, w.whh[1][0], w.whh[1][1], w.whh_t[1][0], w.whh_t[1][1], v->l1, B, Tn, hid, f.st);
         }
         // Linear(2h -> h) + skip: lo = seq + W l1 + b
         if (!f.rc && cudaMemcpyAsync(v->lo, v->seq, (size_t)B * Tn * hid * sizeof(float), cudaMemcpyDeviceToDevice, f.st) !=

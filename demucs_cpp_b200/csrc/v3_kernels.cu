@@ -2,6 +2,8 @@
 // and LocalState attention.  All tensors channels-last fp32: [B][rows][C].
 #include "kernels.cuh"
 
+#include <cooperative_groups.h>
+
 namespace dmx
 {
 
@@ -181,9 +183,187 @@ __global__ void lstm_recurrent_kernel(const float *__restrict__ pre, const float
     }
 }
 
-int launch_lstm_recurrent(const float *pre, const float *whh_t_fwd, const float *whh_t_bwd, float *out, int B, int T,
-                          int H, cudaStream_t st)
+// ------------------------------------------------------------------------------------------------
+// Cluster-persistent LSTM recurrence.  One thread-block CLUSTER per direction runs the chains of ALL batch
+// items: CTA c of the cluster owns 24 hidden units (their 4 x 24 = 96 gate rows of W_hh) and keeps those
+// weights in REGISTERS for the whole sequence (thread = (row, quarter of the K range): H/4 weights each).
+// Per step every CTA computes its rows for all batch items from the full hidden state in shared memory,
+// the 24 x B new hidden values are written straight into every CTA's shared memory over DSMEM, and one
+// cluster barrier ends the step.  Cluster size = H / 24: 8 CTAs for H = 192, 16 CTAs for H = 384.
+//   whh : W_hh as stored by PyTorch, [4H][H] row-major, for this direction
+constexpr int LSTM_UNITS = 24;   // hidden units per CTA
+constexpr int LSTM_ROWS = 96;    // gate rows per CTA
+constexpr int LSTM_THREADS = 384;
+constexpr int LSTM_BMAX = 8;
+
+template <int H>
+__global__ void __launch_bounds__(LSTM_THREADS, 1)
+    lstm_cluster_kernel(const float *__restrict__ pre, const float *__restrict__ whh_fwd,
+                        const float *__restrict__ whh_bwd, float *__restrict__ out, int B, int T)
 {
+    constexpr int NC = H / LSTM_UNITS; // cluster size
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int crank = (int)cluster.block_rank();
+    const int dir = blockIdx.x / NC;
+    const float *W = dir == 0 ? whh_fwd : whh_bwd;
+
+    __shared__ __align__(16) float hbuf[2][LSTM_BMAX][H];       // full hidden state of every batch item, double buffered
+    __shared__ float gates[LSTM_BMAX][LSTM_ROWS];               // this CTA's gate pre-activations
+
+    const int tid = threadIdx.x;
+    // Mat-vec mapping: warp wi owns 8 of the CTA's 96 gate rows, lane l the K indices l, l+32, ... (KJ of them).
+    // Every hidden value is read from shared memory once per warp (conflict free) and reused for 8 rows; the
+    // 32 partial sums (8 rows x 4 batch items) of a half-batch are combined with a transposing butterfly
+    // (31 shuffles) that leaves lane v = row_local*4 + b_local with the finished dot product.
+    constexpr int KJ = H / 32;
+    const int wi = tid >> 5, lane = tid & 31;
+    float w[8][KJ];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+    {
+        const int row = wi * 8 + r;
+        const int grow = (row / LSTM_UNITS) * H + crank * LSTM_UNITS + (row % LSTM_UNITS);
+#pragma unroll
+        for (int j = 0; j < KJ; ++j)
+            w[r][j] = __ldg(&W[(size_t)grow * H + lane + 32 * j]);
+    }
+    // this lane finishes (row = wi*8 + lane/4, batch = half*4 + lane%4)
+    const int frow = wi * 8 + (lane >> 2);
+    const int fgrow = (frow / LSTM_UNITS) * H + crank * LSTM_UNITS + (frow % LSTM_UNITS);
+    for (int i = tid; i < 2 * LSTM_BMAX * H; i += LSTM_THREADS)
+        (&hbuf[0][0][0])[i] = 0.f;
+    // cell state: thread (unit, b) for tid < 24 * B
+    const int ub = tid / LSTM_UNITS, uu = tid % LSTM_UNITS;
+    float c = 0.f;
+    cluster.sync();
+
+    const int G4 = 4 * H;
+    int cur = 0;
+    for (int step = 0; step < T; ++step)
+    {
+        const int t = dir == 0 ? step : T - 1 - step;
+        // input-projection terms of this step: issued first so their L2 latency hides behind the mat-vec
+        float prev[2];
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf)
+        {
+            const int b = hf * 4 + (lane & 3);
+            prev[hf] = b < B ? __ldg(&pre[(((size_t)b * T + t) * 2 + dir) * G4 + fgrow]) : 0.f;
+        }
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf)
+        {
+            if (hf * 4 >= B)
+                break;
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                v[i] = 0.f;
+#pragma unroll
+            for (int j = 0; j < KJ; ++j)
+            {
+                float hv[4];
+#pragma unroll
+                for (int bl = 0; bl < 4; ++bl)
+                    hv[bl] = hbuf[cur][hf * 4 + bl][lane + 32 * j];
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+#pragma unroll
+                    for (int bl = 0; bl < 4; ++bl)
+                        v[r * 4 + bl] = fmaf(w[r][j], hv[bl], v[r * 4 + bl]);
+            }
+            // transposing butterfly: after the five rounds lane l holds the full sum of value index l
+#pragma unroll
+            for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1)
+            {
+                const bool up = (lane & off) != 0;
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                {
+                    if (i < n / 2)
+                    {
+                        const float keep = up ? v[i + n / 2] : v[i];
+                        const float send = up ? v[i] : v[i + n / 2];
+                        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+                    }
+                }
+            }
+            const int b = hf * 4 + (lane & 3);
+            if (b < B)
+                gates[b][frow] = v[0] + prev[hf];
+        }
+        __syncthreads();
+        {
+            // threads (unit, b) for tid < 24*B finish the cell; whole warps stay converged for the shuffles
+            const bool live = tid < LSTM_UNITS * B;
+            float h = 0.f;
+            if (live)
+            {
+                const float gi = gates[ub][uu], gf = gates[ub][LSTM_UNITS + uu], gg = gates[ub][2 * LSTM_UNITS + uu],
+                            go = gates[ub][3 * LSTM_UNITS + uu];
+                const float i_t = 1.0f / (1.0f + expf(-gi));
+                const float f_t = 1.0f / (1.0f + expf(-gf));
+                const float g_t = tanhf(gg);
+                const float o_t = 1.0f / (1.0f + expf(-go));
+                c = f_t * c + i_t * g_t;
+                h = o_t * tanhf(c);
+                out[((size_t)ub * T + t) * (2 * H) + dir * H + crank * LSTM_UNITS + uu] = h;
+            }
+            // four consecutive units sit in four consecutive lanes (24 % 4 == 0): gather them so the broadcast
+            // into every CTA's shared memory (DSMEM) is one 16-byte store per destination instead of four
+            const float h1 = __shfl_down_sync(0xffffffffu, h, 1);
+            const float h2 = __shfl_down_sync(0xffffffffu, h, 2);
+            const float h3 = __shfl_down_sync(0xffffffffu, h, 3);
+            if (live && (uu & 3) == 0)
+            {
+                float *local = &hbuf[cur ^ 1][ub][crank * LSTM_UNITS + uu];
+                const float4 hv = make_float4(h, h1, h2, h3);
+#pragma unroll
+                for (int r = 0; r < NC; ++r)
+                    *reinterpret_cast<float4 *>(cluster.map_shared_rank(local, r)) = hv;
+            }
+        }
+        cluster.sync(); // all writes of step's h landed everywhere; nobody still reads hbuf[cur]
+        cur ^= 1;
+    }
+}
+
+template <int H> static int lstm_cluster_launch(const float *pre, const float *whh_fwd, const float *whh_bwd, float *out,
+                                                int B, int T, cudaStream_t st)
+{
+    constexpr int NC = H / LSTM_UNITS;
+    static bool attr_done = false; // per process; the attribute is per function, harmless to repeat per device
+    if (NC > 8 && !attr_done)
+    {
+        DMX_CUDA(cudaFuncSetAttribute(lstm_cluster_kernel<H>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    }
+    attr_done = attr_done || NC <= 8;
+    if (NC > 8)
+        DMX_CUDA(cudaFuncSetAttribute(lstm_cluster_kernel<H>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * NC);
+    cfg.blockDim = dim3(LSTM_THREADS);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = NC;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    DMX_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<H>, pre, whh_fwd, whh_bwd, out, B, T));
+    return 0;
+}
+
+// whh_*: [4H][H] row-major (PyTorch layout); whh_t_*: the same transposed [H][4H] for the fallback kernel.
+int launch_lstm_recurrent(const float *pre, const float *whh_fwd, const float *whh_bwd, const float *whh_t_fwd,
+                          const float *whh_t_bwd, float *out, int B, int T, int H, cudaStream_t st)
+{
+    if ((H == 192 || H == 384) && B <= LSTM_BMAX)
+        return H == 192 ? lstm_cluster_launch<192>(pre, whh_fwd, whh_bwd, out, B, T, st)
+                        : lstm_cluster_launch<384>(pre, whh_fwd, whh_bwd, out, B, T, st);
     if (H > 1024)
     {
         set_error("lstm: hidden size > 1024");
