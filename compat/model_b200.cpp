@@ -1,0 +1,91 @@
+// compat/model_b200.cpp -- the reference's CLI-tier API (compat/model.hpp) over the C ABI.
+// Eigen::MatrixXf(2, L) and Eigen::Tensor3dXf(S, 2, L) are column-major, which is exactly the interleaved
+// L,R / source-fastest layout the ABI takes: no copies or transposes on either side.
+#include "model.hpp"
+
+#include "demucs_b200.h"
+
+#include <cstdlib>
+#include <iostream>
+
+namespace
+{
+int env_int(const char *name, int dflt)
+{
+    const char *v = std::getenv(name);
+    return v ? std::atoi(v) : dflt;
+}
+
+std::shared_ptr<void> load(const std::string &path, int want_v3, bool *is4)
+{
+    // DEMUCS_DEVICE / DEMUCS_MAX_BATCH / DEMUCS_PRECISION (fp32 | bf16): the CLIs take positional arguments only
+    dmx_model *h = dmx_model_load_file(path.c_str(), env_int("DEMUCS_DEVICE", 0), env_int("DEMUCS_MAX_BATCH", 8));
+    if (!h)
+    {
+        std::cerr << "load_demucs_model: " << dmx_last_error() << std::endl;
+        return nullptr;
+    }
+    const bool v3 = dmx_model_arch(h) == DMX_ARCH_HDEMUCS_V3;
+    if (v3 != (want_v3 != 0))
+    {
+        std::cerr << "load_demucs_model: invalid model data (bad magic)" << std::endl; // src/model_load.cpp:97-102,1331-1336
+        dmx_model_free(h);
+        return nullptr;
+    }
+    const char *prec = std::getenv("DEMUCS_PRECISION");
+    if (prec && std::string(prec) == "bf16")
+        dmx_model_set_precision(h, DMX_PRECISION_BF16);
+    if (is4)
+        *is4 = dmx_model_sources(h) == 4;
+    return std::shared_ptr<void>(h, [](void *p) { dmx_model_free(static_cast<dmx_model *>(p)); });
+}
+
+void trampoline(float p, const char *msg, void *user)
+{
+    (*static_cast<demucscpp::ProgressCallback *>(user))(p, std::string(msg));
+}
+
+Eigen::Tensor3dXf separate(void *handle, const Eigen::MatrixXf &audio, demucscpp::ProgressCallback cb)
+{
+    dmx_model *h = static_cast<dmx_model *>(handle);
+    if (!h || audio.rows() != 2)
+    {
+        std::cerr << "demucs_inference: model not loaded or audio is not (2, L)" << std::endl;
+        std::exit(1);
+    }
+    const int S = dmx_model_sources(h);
+    Eigen::Tensor3dXf out(S, 2, audio.cols());
+    const int offset = rand() % 22050; // src/model_apply.cpp:114 (unseeded glibc rand, like the reference)
+    std::cout << "1., apply model w/ shift, offset: " << offset << std::endl;
+    if (dmx_separate(h, audio.data(), (int64_t)audio.cols(), offset, out.data(), cb ? trampoline : nullptr, &cb) != 0)
+    {
+        std::cerr << "demucs_inference: " << dmx_last_error() << std::endl;
+        std::exit(1);
+    }
+    return out;
+}
+} // namespace
+
+bool demucscpp::load_demucs_model(const std::string &model_file, struct demucs_model *model)
+{
+    model->b200 = load(model_file, 0, &model->is_4sources);
+    return (bool)model->b200;
+}
+
+Eigen::Tensor3dXf demucscpp::demucs_inference(const struct demucs_model &model, const Eigen::MatrixXf &full_audio,
+                                              ProgressCallback cb)
+{
+    return separate(model.b200.get(), full_audio, cb);
+}
+
+bool demucscpp_v3::load_demucs_v3_model(const std::string &model_file, struct demucs_v3_model *model)
+{
+    model->b200 = load(model_file, 1, nullptr);
+    return (bool)model->b200;
+}
+
+Eigen::Tensor3dXf demucscpp_v3::demucs_v3_inference(const struct demucs_v3_model &model,
+                                                    const Eigen::MatrixXf &full_audio, demucscpp::ProgressCallback cb)
+{
+    return separate(model.b200.get(), full_audio, cb);
+}
