@@ -246,7 +246,8 @@ int dmx_model_max_batch(const dmx_model *m) { return m ? m->maxB : -1; }
 int64_t dmx_launch_count(const dmx_model *m) { return m ? m->launches : -1; }
 
 static const char *const kProfNames[PC_COUNT] = {"stft",      "istft",      "istft_ola",        "pointwise", "gemm_conv",
-                                                 "gemm_dconv", "gemm_transformer", "attention", "track",     "lstm"};
+                                                 "gemm_dconv", "gemm_transformer", "attention", "track",     "lstm",
+                                                 "dconv_fused"};
 
 int dmx_profile_classes(void) { return PC_COUNT; }
 

@@ -744,7 +744,9 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     const int nk = (p.K + tc::BK - 1) / tc::BK;
     if (nk == 1)
         return tc_launch<1>(p, w, bn, vec, plain, st);
-    if (nk == 2)
+    // wide tiles: two stages keep the CTA under half of the shared memory so two CTAs share an SM (one's
+    // epilogue overlaps the other's main loop)
+    if (nk == 2 || bn > 128)
         return tc_launch<2>(p, w, bn, vec, plain, st);
     return tc_launch<3>(p, w, bn, vec, plain, st);
 }

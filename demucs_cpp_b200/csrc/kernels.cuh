@@ -90,6 +90,13 @@ int launch_group_norm_apply(float *x, int B, int rows_per_item, int C, const dou
                             const float *b, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
+// dconv_fused.cu: whole DConv branch of a frequency row resident in shared memory (C = 48 / 96 levels)
+bool dconv_fused_supported(int C, int hid, int V);
+int dconv_fused_param_floats(int C, int hid);
+int dconv_fused_init_device();
+int launch_dconv_fused(float *x, const float *params, int items, int C, int hid, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
 // v3_kernels.cu (hdemucs_mmi)
 int launch_group_norm_g(const float *x, float *y, int B, int rows_in, int rows_out, int row0, int C, int G,
                         double *stats_zeroed, const float *w, const float *b, int act, int glu, cudaStream_t st);

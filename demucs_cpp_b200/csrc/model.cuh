@@ -32,6 +32,7 @@ struct DConvW
     Packed c1[2], c2[2];
     float *g1w[2], *g1b[2], *g2w[2], *g2b[2], *scale[2];
     int C = 0, hid = 0, hidp = 0;
+    float *fused = nullptr; // parameter block of the fused shared-memory kernel (dconv_fused.cu), if the shape has one
 };
 
 struct EncW
@@ -69,6 +70,7 @@ enum ProfClass
     PC_ATTENTION,
     PC_TRACK,
     PC_LSTM,
+    PC_DCONV_FUSED,
     PC_COUNT
 };
 

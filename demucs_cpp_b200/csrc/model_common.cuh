@@ -204,6 +204,43 @@ static int pack_dconv(dmx_model *m, DConvW &d, const std::string &prefix, int C,
             upload_vec(m, &d.scale[j], p + "6.scale", C))
             return -1;
     }
+    if (dconv_fused_supported(C, d.hid, LE))
+    {
+        // parameter block of the fused kernel: per sub-block W1[3][C][HID] | b1 | g1w | g1b | W2[2C][HID] | b2 | g2w | g2b | scale
+        std::vector<float> blk;
+        blk.reserve(dconv_fused_param_floats(C, d.hid));
+        const int hid = d.hid;
+        for (int j = 0; j < 2; ++j)
+        {
+            const std::string p = prefix + ".dconv.layers." + std::to_string(j) + ".";
+            const HostTensor *w1 = get(m, p + "0.weight", (size_t)hid * C * 3), *b1 = get(m, p + "0.bias", hid);
+            const HostTensor *g1w = get(m, p + "1.weight", hid), *g1b = get(m, p + "1.bias", hid);
+            const HostTensor *w2 = get(m, p + "3.weight", (size_t)2 * C * hid), *b2 = get(m, p + "3.bias", 2 * C);
+            const HostTensor *g2w = get(m, p + "4.weight", 2 * C), *g2b = get(m, p + "4.bias", 2 * C);
+            const HostTensor *sc = get(m, p + "6.scale", C);
+            if (!w1 || !b1 || !g1w || !g1b || !w2 || !b2 || !g2w || !g2b || !sc)
+                return -1;
+            for (int tap = 0; tap < 3; ++tap)
+                for (int c = 0; c < C; ++c)
+                    for (int jj = 0; jj < hid; ++jj)
+                        blk.push_back(w1->data[((size_t)jj * C + c) * 3 + tap]);
+            blk.insert(blk.end(), b1->data.begin(), b1->data.end());
+            blk.insert(blk.end(), g1w->data.begin(), g1w->data.end());
+            blk.insert(blk.end(), g1b->data.begin(), g1b->data.end());
+            blk.insert(blk.end(), w2->data.begin(), w2->data.end());
+            blk.insert(blk.end(), b2->data.begin(), b2->data.end());
+            blk.insert(blk.end(), g2w->data.begin(), g2w->data.end());
+            blk.insert(blk.end(), g2b->data.begin(), g2b->data.end());
+            blk.insert(blk.end(), sc->data.begin(), sc->data.end());
+        }
+        if ((int)blk.size() != dconv_fused_param_floats(C, hid))
+        {
+            set_error("pack_dconv: fused parameter block size mismatch");
+            return -1;
+        }
+        if (upload(m, &d.fused, blk))
+            return -1;
+    }
     return 0;
 }
 
@@ -312,6 +349,16 @@ struct Fwd
     void dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u)
     {
         const int C = w.C, hid = w.hid, hidp = w.hidp;
+        if (per_u && w.fused && dconv_fused_supported(C, hid, V))
+        {
+            if (rc)
+                return;
+            // one HBM read + one write of x; MACs: 2 sub-blocks x (k3 conv + the 1x1 conv evaluated twice)
+            ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
+                         (double)B * U * V * C * 8.0);
+            rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
+            return;
+        }
         const size_t items = (size_t)B * (per_u ? U : 1);
         for (int j = 0; j < 2; ++j)
         {
