@@ -113,7 +113,8 @@ template <int DH>
 __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat16 *__restrict__ Q, int ldq,
                                                                const __nv_bfloat16 *__restrict__ K, int ldk,
                                                                const __nv_bfloat16 *__restrict__ V, int ldv,
-                                                               float *__restrict__ O, int ldo, int T, int S, float scale)
+                                                               float *__restrict__ O, int ldo, int T, int S, float scale,
+                                                               uint4 *__restrict__ Opk, int heads)
 {
     constexpr int DCH = DH / 8;                    // 16-byte chunks per row of Q/K/V
     constexpr uint32_t LBO_R = BQ * 16 + PAD;      // 2064
@@ -276,10 +277,29 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
     if (row < T)
     {
         const float inv = 1.0f / l_run;
-        float *dst = O + ((size_t)b * T + row) * ldo + h * DH;
+        if (Opk)
+        {
+            // tile-packed bf16: the out-projection GEMM's A image, [row/128][d/8][row%128][8]
+            const size_t grow = (size_t)b * T + row;
+            const int nch = heads * DH / 8;
 #pragma unroll
-        for (int i = 0; i < DH; i += 4)
-            *reinterpret_cast<float4 *>(dst + i) = make_float4(o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv);
+            for (int i = 0; i < DH; i += 8)
+            {
+                uint4 pk;
+                pk.x = pack_bf16x2(o[i] * inv, o[i + 1] * inv);
+                pk.y = pack_bf16x2(o[i + 2] * inv, o[i + 3] * inv);
+                pk.z = pack_bf16x2(o[i + 4] * inv, o[i + 5] * inv);
+                pk.w = pack_bf16x2(o[i + 6] * inv, o[i + 7] * inv);
+                Opk[((grow >> 7) * nch + (h * DH + i) / 8) * 128 + (grow & 127)] = pk;
+            }
+        }
+        else
+        {
+            float *dst = O + ((size_t)b * T + row) * ldo + h * DH;
+#pragma unroll
+            for (int i = 0; i < DH; i += 4)
+                *reinterpret_cast<float4 *>(dst + i) = make_float4(o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv);
+        }
     }
     __syncthreads();
     if (warp == 0)
@@ -308,7 +328,7 @@ int attention_tc_init_device()
 
 // Q/K/V: bf16, O: fp32.  Leading dimensions in elements; all must be multiples of 8 (16-byte rows).
 int launch_attention_tc(const void *Q, int ldq, const void *K, int ldk, const void *V, int ldv, float *O, int ldo, int B,
-                        int T, int S, int heads, int dh, cudaStream_t st)
+                        int T, int S, int heads, int dh, cudaStream_t st, void *Opk)
 {
     if ((ldq | ldk | ldv) % 8 || ldo % 4)
     {
@@ -321,10 +341,10 @@ int launch_attention_tc(const void *Q, int ldq, const void *K, int ldk, const vo
                         *v = static_cast<const __nv_bfloat16 *>(V);
     if (dh == 64)
         atc::attention_tc_kernel<64><<<grid, atc::THREADS, atc::smem_bytes<64>(), st>>>(q, ldq, k, ldk, v, ldv, O, ldo, T, S,
-                                                                                          scale);
+                                                                                          scale, (uint4 *)Opk, heads);
     else if (dh == 48)
         atc::attention_tc_kernel<48><<<grid, atc::THREADS, atc::smem_bytes<48>(), st>>>(q, ldq, k, ldk, v, ldv, O, ldo, T, S,
-                                                                                          scale);
+                                                                                          scale, (uint4 *)Opk, heads);
     else
     {
         set_error("attention_tc: unsupported head dim");

@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
     {
         for (int s = 0; s < STAGES; ++s)
         {
-            mbar_init(&full_bar[s], PROD_THREADS + 1);
+            mbar_init(&full_bar[s], p.Apk ? 1u : (uint32_t)(PROD_THREADS + 1));
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&tmem_full_bar, 1);
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
             }
         }
         const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
-        for (int kb = 0; kb < nk; ++kb)
+        for (int kb = 0; kb < (p.Apk ? 0 : nk); ++kb) // packed-A mode: the operand is bulk-copied, nothing to gather
         {
             const int s = kb % STAGES;
             const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
@@ -543,7 +543,18 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
                             o[2] = old.z + gam.z * o[2];
                             o[3] = old.w + gam.w * o[3];
                         }
-                        if (p.out_bf16)
+                        if (p.out_pack)
+                        {
+                            // tile-packed bf16 for a consumer GEMM with K = ldc: [row/128][col/8][row%128][col%8]
+                            const int mrow = m0 + q * 32 + rl;
+                            const size_t off = ((size_t)(mrow >> 7) * (p.ldc >> 3) + (outc >> 3)) * 1024 + (size_t)(mrow & 127) * 8 +
+                                               (outc & 7);
+                            uint2 pk2;
+                            pk2.x = pack_bf16x2(o[0], o[1]);
+                            pk2.y = pack_bf16x2(o[2], o[3]);
+                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + off) = pk2;
+                        }
+                        else if (p.out_bf16)
                         {
                             uint2 pk2;
                             pk2.x = pack_bf16x2(o[0], o[1]);
@@ -612,7 +623,16 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
                 const int s = kb % STAGES;
                 const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
                 mbar_wait(&empty_bar[s], ph ^ 1u);
-                mbar_arrive_expect_tx(&full_bar[s], b_stage_bytes);
+                if (p.Apk)
+                {
+                    // tile-packed bf16 activations: the k-block's A operand is one contiguous 16 KB image
+                    const uint8_t *asrc = reinterpret_cast<const uint8_t *>(p.Apk) +
+                                          ((size_t)blockIdx.x * nk + kb) * (size_t)(BM * BK * 2);
+                    mbar_arrive_expect_tx(&full_bar[s], b_stage_bytes + BM * BK * 2);
+                    bulk_g2s(a_smem + s * A_STAGE, asrc, BM * BK * 2, &full_bar[s]);
+                }
+                else
+                    mbar_arrive_expect_tx(&full_bar[s], b_stage_bytes);
                 bulk_g2s(b_smem + (size_t)s * b_stage_bytes, src + (size_t)kb * b_stage_bytes, b_stage_bytes, &full_bar[s]);
             }
         }
@@ -624,6 +644,7 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
         {
             const uint32_t idesc = make_idesc(bn);
             const uint32_t b_lbo = (uint32_t)bn * 16, sbo = 128;
+            const uint32_t a_lbo = p.Apk ? (uint32_t)(BM * 16) : (uint32_t)A_LBO;
             for (int kb = 0; kb < nk; ++kb)
             {
                 const int s = kb % STAGES;
@@ -635,7 +656,7 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
 #pragma unroll
                 for (int j = 0; j < BK / 16; ++j)
                 {
-                    const uint64_t ad = make_desc(a_base + j * 2 * A_LBO, A_LBO, sbo);
+                    const uint64_t ad = make_desc(a_base + j * 2 * a_lbo, a_lbo, sbo);
                     const uint64_t bd = make_desc(b_base + j * 2 * b_lbo, b_lbo, sbo);
                     umma(tmem_base, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
                 }
@@ -735,9 +756,14 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
                        (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0))
                           ? 1
                           : 0;
-    if (p.out_bf16 && (!plain || p.gamma || (nout % 4)))
+    if ((p.out_bf16 || p.out_pack) && (!plain || p.gamma || (nout % 4) || (p.out_pack && (p.ldc % 8))))
     {
-        set_error("launch_gemm_tc: bf16 output needs the identity mapping, no residual and N % 4 == 0");
+        set_error("launch_gemm_tc: bf16 / packed output needs the identity mapping, no residual and N % 4 == 0");
+        return -1;
+    }
+    if (p.Apk && (p.K % tc::BK))
+    {
+        set_error("launch_gemm_tc: packed A needs K % 64 == 0");
         return -1;
     }
     const __nv_bfloat16 *w = static_cast<const __nv_bfloat16 *>(Wb);

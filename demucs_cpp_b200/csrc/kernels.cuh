@@ -48,6 +48,8 @@ struct GemmParams
     double *stats = nullptr;       // accumulate (sum, sumsq) of the stored values per item
     int stat_per_u = 0;
     int out_bf16 = 0;              // tensor-core kernel only, identity mapping only: C holds bf16 (ldc in elements)
+    int out_pack = 0;              // ... C holds TILE-PACKED bf16 [row/128][ldc/8][row%128][8]: the next GEMM's A image
+    const void *Apk = nullptr;     // tensor-core kernel only: A operand given as tile-packed bf16 (1x1 / linear only)
     // output mapping
     float *C = nullptr;
     int ldc = 0, Nco = 0;
@@ -82,6 +84,8 @@ int launch_normalize_input(float *x, int B, size_t n_per_item, const double *sta
 // DConv tail: x[r][c] += scale[c] * GN(y)[r][c] * sigmoid(GN(y)[r][c+C])  (src/layers.cpp:240-253)
 int launch_gn_glu_residual(const float *y, float *x, int B, int U, int V, int C, const double *stats,
                            int per_u, const float *gw, const float *gb, const float *scale, cudaStream_t st);
+// LayerNorm writing TILE-PACKED bf16 (the tcgen05 GEMM's A image, see GemmParams::Apk) instead of fp32 rows
+int launch_layer_norm_pack(const float *x, void *ypk, int rows, int C, const float *w, const float *b, cudaStream_t st);
 // LayerNorm over the last dim (unbiased var), optional additive table add[row % add_rows][c]
 int launch_layer_norm(const float *x, float *y, int rows, int C, const float *w, const float *b,
                       const float *add, int add_rows, cudaStream_t st);
@@ -113,6 +117,6 @@ int launch_attention(const float *Q, int ldq, const float *K, int ldk, const flo
 // attention_tc.cu: the same attention on tcgen05 tensor cores; Q/K/V bf16, O fp32
 int attention_tc_init_device();
 int launch_attention_tc(const void *Q, int ldq, const void *K, int ldk, const void *V, int ldv, float *O, int ldo, int B,
-                        int T, int S, int heads, int dh, cudaStream_t st);
+                        int T, int S, int heads, int dh, cudaStream_t st, void *Opk = nullptr);
 
 } // namespace dmx

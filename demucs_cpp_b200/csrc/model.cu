@@ -391,8 +391,8 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         {
             // freq queries attend the current time tokens; time queries attend the freq tokens from BEFORE
             // this layer's update (old_x, src/crosstransformer.cpp:286-295): normalise both key sets first.
-            f.layer_norm(m->tq, m->kn_f, B * TT, d, m->lay[i].n2w, m->lay[i].n2b);
-            f.layer_norm(m->xq, m->kn_t, B * TF, d, m->lay_t[i].n2w, m->lay_t[i].n2b);
+            f.layer_norm_a(m->tq, m->kn_f, B * TT, d, m->lay[i].n2w, m->lay[i].n2b);
+            f.layer_norm_a(m->xq, m->kn_t, B * TF, d, m->lay_t[i].n2w, m->lay_t[i].n2b);
             f.tlayer(m->lay[i], m->xq, TF, m->kn_f, TT, m->ln_f, m->qkv_f, m->kv_f, m->ao_f, m->ff_f);
             f.tlayer(m->lay_t[i], m->tq, TT, m->kn_t, TF, m->ln_t, m->qkv_t, m->kv_t, m->ao_t, m->ff_t);
         }

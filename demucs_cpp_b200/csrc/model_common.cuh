@@ -419,19 +419,43 @@ struct Fwd
         return base(x, Cin, Cin, w, y, ldc, 1, Tn, 1, Tn);
     }
 
+    // LayerNorm feeding a GEMM: bf16 mode writes the tcgen05 kernel's tile-packed A image, fp32 mode plain rows
+    void layer_norm_a(const float *x, float *y, int rows, int C, const float *w, const float *b)
+    {
+        if (m->precision != DMX_PRECISION_BF16)
+        {
+            layer_norm(x, y, rows, C, w, b);
+            return;
+        }
+        if (rc)
+            return;
+        ProfScope ps(m, PC_POINTWISE, 0.0, (double)rows * C * 6.0);
+        rc = launch_layer_norm_pack(x, y, rows, C, w, b, st);
+    }
+
+    // linear layer whose A operand is tile-packed bf16 (bf16 mode) or fp32 rows (fp32 mode)
+    GemmParams linear_a(const float *x, int Cin, const Packed &w, float *y, int ldc, int Tn)
+    {
+        GemmParams p = linear(x, Cin, w, y, ldc, Tn);
+        if (m->precision == DMX_PRECISION_BF16)
+            p.Apk = x;
+        return p;
+    }
+
     // one transformer layer (src/layers.cpp:377-531) on q [B*Tq][d]; kn = already-normalised key source
-    // for cross layers (nullptr for self attention).
+    // for cross layers (nullptr for self attention; produced by layer_norm_a).
+    // bf16 mode: every GEMM operand inside the layer travels as bf16 -- LayerNorm, attention and FFN1 write the
+    // next GEMM's tile-packed A image directly, the projections write Q/K/V as bf16 rows -- while the residual
+    // stream q, the statistics and the softmax stay fp32.
     void tlayer(const TLayerW &L, float *q, int Tq, const float *kn, int Tk, float *ln, float *qkv, float *kv, float *ao,
                 float *ff)
     {
         const int d = m->d_model, dh = d / 8;
-        layer_norm(q, ln, B * Tq, d, L.n1w, L.n1b);
-        // bf16 mode: the projections write Q/K/V as bf16 (same buffers, half the bytes) for the tensor-core
-        // attention; fp32 mode keeps everything fp32 on the CUDA-core kernels.
         const bool tcm = m->precision == DMX_PRECISION_BF16;
+        layer_norm_a(q, ln, B * Tq, d, L.n1w, L.n1b);
         if (!L.cross)
         {
-            GemmParams pq = linear(ln, d, L.qkv, qkv, 3 * d, Tq);
+            GemmParams pq = linear_a(ln, d, L.qkv, qkv, 3 * d, Tq);
             pq.out_bf16 = tcm;
             gemm(pq, PC_GEMM_XFMR);
             if (!rc)
@@ -440,7 +464,7 @@ struct Fwd
                 if (tcm)
                 {
                     const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
-                    rc = launch_attention_tc(qb, 3 * d, qb + d, 3 * d, qb + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
+                    rc = launch_attention_tc(qb, 3 * d, qb + d, 3 * d, qb + 2 * d, 3 * d, nullptr, d, B, Tq, Tq, 8, dh, st, ao);
                 }
                 else
                     rc = launch_attention(qkv, 3 * d, qkv + d, 3 * d, qkv + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
@@ -448,10 +472,10 @@ struct Fwd
         }
         else
         {
-            GemmParams pq = linear(ln, d, L.q, qkv, d, Tq);
+            GemmParams pq = linear_a(ln, d, L.q, qkv, d, Tq);
             pq.out_bf16 = tcm;
             gemm(pq, PC_GEMM_XFMR);
-            GemmParams pkv = linear(kn, d, L.kv, kv, 2 * d, Tk);
+            GemmParams pkv = linear_a(kn, d, L.kv, kv, 2 * d, Tk);
             pkv.out_bf16 = tcm;
             gemm(pkv, PC_GEMM_XFMR);
             if (!rc)
@@ -461,21 +485,22 @@ struct Fwd
                 {
                     const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
                     const uint16_t *kb = reinterpret_cast<const uint16_t *>(kv);
-                    rc = launch_attention_tc(qb, d, kb, 2 * d, kb + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
+                    rc = launch_attention_tc(qb, d, kb, 2 * d, kb + d, 2 * d, nullptr, d, B, Tq, Tk, 8, dh, st, ao);
                 }
                 else
                     rc = launch_attention(qkv, d, kv, 2 * d, kv + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
             }
         }
-        GemmParams po = linear(ao, d, L.out, q, d, Tq);
+        GemmParams po = linear_a(ao, d, L.out, q, d, Tq);
         po.gamma = L.g1;
         gemm(po, PC_GEMM_XFMR);
         // pre-FFN norm: norm3 for cross layers, norm2 for self layers (src/crosstransformer.cpp:111-113)
-        layer_norm(q, ln, B * Tq, d, L.cross ? L.n3w : L.n2w, L.cross ? L.n3b : L.n2b);
-        GemmParams p1 = linear(ln, d, L.ff1, ff, 4 * d, Tq);
+        layer_norm_a(q, ln, B * Tq, d, L.cross ? L.n3w : L.n2w, L.cross ? L.n3b : L.n2b);
+        GemmParams p1 = linear_a(ln, d, L.ff1, ff, 4 * d, Tq);
         p1.act = 1;
+        p1.out_pack = tcm;
         gemm(p1, PC_GEMM_XFMR);
-        GemmParams p2 = linear(ff, 4 * d, L.ff2, q, d, Tq);
+        GemmParams p2 = linear_a(ff, 4 * d, L.ff2, q, d, Tq);
         p2.gamma = L.g2;
         double *s = stat_slots(B);
         p2.stats = s;

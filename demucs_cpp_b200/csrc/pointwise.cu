@@ -2,6 +2,8 @@
 // reference's UNBIASED one, statistics are carried as double (sum, sumsq).
 #include "kernels.cuh"
 
+#include <cuda_bf16.h>
+
 namespace dmx
 {
 
@@ -231,6 +233,87 @@ int launch_layer_norm(const float *x, float *y, int rows, int C, const float *w,
         return -1;
     }
     layer_norm_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, y, rows, C, w, b, add, add_rows > 0 ? add_rows : 1);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm whose output is the tcgen05 GEMM's A-operand image: bf16, tile-packed [row/128][C/8][row%128][8].
+// One warp per row; lane l owns the 8-channel chunks l, l+32 (C <= 512).
+__global__ void __launch_bounds__(256) layer_norm_pack_kernel(const float *__restrict__ x, uint4 *__restrict__ ypk, int rows,
+                                                              int C, const float *__restrict__ w, const float *__restrict__ b)
+{
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows)
+        return;
+    const int nch = C / 8;
+    const float *xr = x + (size_t)row * C;
+    float v[2][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+    {
+        const int ch = lane + 32 * i;
+        if (ch < nch)
+        {
+            const float4 a = __ldg(reinterpret_cast<const float4 *>(xr + ch * 8));
+            const float4 c = __ldg(reinterpret_cast<const float4 *>(xr + ch * 8 + 4));
+            v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
+            v[i][4] = c.x; v[i][5] = c.y; v[i][6] = c.z; v[i][7] = c.w;
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                s += v[i][e];
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s / (float)C;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+        if (lane + 32 * i < nch)
+        {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+            {
+                const float d = v[i][e] - mean;
+                q += d * d;
+            }
+        }
+    for (int o = 16; o > 0; o >>= 1)
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = 1.0f / sqrtf(q / (float)(C - 1) + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+    {
+        const int ch = lane + 32 * i;
+        if (ch < nch)
+        {
+            float o8[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                o8[e] = (v[i][e] - mean) * rstd * __ldg(&w[ch * 8 + e]) + __ldg(&b[ch * 8 + e]);
+            uint4 pk;
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(o8[0], o8[1]), h1 = __floats2bfloat162_rn(o8[2], o8[3]),
+                           h2 = __floats2bfloat162_rn(o8[4], o8[5]), h3 = __floats2bfloat162_rn(o8[6], o8[7]);
+            pk.x = *reinterpret_cast<uint32_t *>(&h0);
+            pk.y = *reinterpret_cast<uint32_t *>(&h1);
+            pk.z = *reinterpret_cast<uint32_t *>(&h2);
+            pk.w = *reinterpret_cast<uint32_t *>(&h3);
+            ypk[((size_t)(row >> 7) * nch + ch) * 128 + (row & 127)] = pk;
+        }
+    }
+}
+
+int launch_layer_norm_pack(const float *x, void *ypk, int rows, int C, const float *w, const float *b, cudaStream_t st)
+{
+    if (C % 8 || C > 512)
+    {
+        set_error("layer_norm_pack: C must be a multiple of 8 and <= 512");
+        return -1;
+    }
+    layer_norm_pack_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, (uint4 *)ypk, rows, C, w, b);
     DMX_LAUNCH_CHECK();
     return 0;
 }
