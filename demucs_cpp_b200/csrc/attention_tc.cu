@@ -23,7 +23,6 @@ namespace atc
 constexpr int BQ = 128;   // queries per CTA (UMMA M)
 constexpr int BKEY = 128; // keys per tile
 constexpr int THREADS = 128;
-constexpr int PAD = 16;   // bytes added to the K-direction core stride: conflict-free 16-byte stores
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
@@ -103,39 +102,59 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi)
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
-// DH = head dim (64 or 48).  smem tiles:
-//   Qs: K-major, rows = queries, k = dh   : chunk (row, kc) at kc*LBO_R + row*16,  LBO_R = 128*16 + PAD
-//   Ks: K-major, rows = keys,    k = dh   : same geometry
-//   Ps: K-major, rows = queries, k = keys : chunk (row, kc) at kc*LBO_R + row*16,  16 chunks
-//   Vs: MN-major, mn = dh, k = keys       : chunk (key, dg) at dg*SBO_V + key*16,  SBO_V = 128*16 + PAD
-//       (k-groups of 8 keys are 128 B apart = LBO_V)
-template <int DH>
-__global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat16 *__restrict__ Q, int ldq,
-                                                               const __nv_bfloat16 *__restrict__ K, int ldk,
-                                                               const __nv_bfloat16 *__restrict__ V, int ldv,
-                                                               float *__restrict__ O, int ldo, int T, int S, float scale,
-                                                               uint4 *__restrict__ Opk, int heads)
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
 {
-    constexpr int DCH = DH / 8;                    // 16-byte chunks per row of Q/K/V
-    constexpr uint32_t LBO_R = BQ * 16 + PAD;      // 2064
-    constexpr uint32_t SBO_V = BKEY * 16 + PAD;    // 2064
-    constexpr uint32_t Q_BYTES = DCH * LBO_R, K_BYTES = DCH * LBO_R, V_BYTES = DCH * SBO_V, P_BYTES = 16 * LBO_R;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// DH = head dim (64 or 48).  Q / K / V arrive TILE-PACKED (the projection GEMM's epilogue writes them that way), so
+// a (128 rows x DH) tile of one head is ONE contiguous image that is already the tcgen05 operand layout:
+//   [DH/8 chunks][128 rows][8 bf16]  = K-major for Q and K (rows = queries / keys), MN-major for V (mn = dh, k = keys)
+// and is fetched with a single bulk async copy per tile; K/V tiles are double buffered so the copies of tile j+1 run
+// under the MMAs and the softmax of tile j.  No thread touches the operands.
+template <int DH>
+__global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat16 *__restrict__ Qp, int ldq8, int qc8,
+                                                               const __nv_bfloat16 *__restrict__ Kp, int ldk8, int kc8,
+                                                               const __nv_bfloat16 *__restrict__ Vp, int ldv8, int vc8,
+                                                               uint4 *__restrict__ Opk, int T, int Tpad, int S, int Spad,
+                                                               int heads, float scale)
+{
+    constexpr int DCH = DH / 8;                   // 16-byte chunks per row
+    constexpr uint32_t LBO = BQ * 16;             // 2048: chunk stride inside a packed tile
+    constexpr uint32_t TILE = DCH * LBO;          // bytes of a 128 x DH tile
+    constexpr uint32_t P_BYTES = 16 * LBO;
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t *Qs = smem, *Ks = Qs + Q_BYTES, *Vs = Ks + K_BYTES, *Ps = Vs + V_BYTES;
-    __shared__ __align__(8) uint64_t mma_bar;
+    uint8_t *Qs = smem, *Ks = Qs + TILE, *Vs = Ks + 2 * TILE, *Ps = Vs + 2 * TILE;
+    __shared__ __align__(8) uint64_t mma_bar, q_full, kv_full[2], kv_empty[2];
     __shared__ uint32_t tmem_slot;
     (void)P_BYTES;
 
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int q0 = blockIdx.x * BQ;
+    const int qt = blockIdx.x;
     const int h = blockIdx.y, b = blockIdx.z;
-    const __nv_bfloat16 *Qb = Q + (size_t)b * T * ldq + h * DH;
-    const __nv_bfloat16 *Kb = K + (size_t)b * S * ldk + h * DH;
-    const __nv_bfloat16 *Vb = V + (size_t)b * S * ldv + h * DH;
+    const int q0 = qt * BQ;
+    const int ntiles = (S + BKEY - 1) / BKEY;
+    // packed tile (item b, row tile rt, head h) of a matrix with ld8 chunks per row and first chunk c8:
+    auto tile_ptr = [&](const __nv_bfloat16 *base, int ld8, int c8, int rows_pad, int rt) {
+        return reinterpret_cast<const uint8_t *>(base) +
+               (((size_t)(b * (rows_pad >> 7) + rt) * ld8 + c8 + h * DCH) * (size_t)LBO);
+    };
 
     if (tid == 0)
     {
         mbar_init(&mma_bar, 1);
+        mbar_init(&q_full, 1);
+        mbar_init(&kv_full[0], 1);
+        mbar_init(&kv_full[1], 1);
+        mbar_init(&kv_empty[0], 1);
+        mbar_init(&kv_empty[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0)
@@ -145,18 +164,17 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    // Q tile: chunk (row, kc): 8 lanes of a row read DH*2 contiguous bytes
-    for (int idx = tid; idx < BQ * DCH; idx += THREADS)
-    {
-        const int row = idx / DCH, kc = idx % DCH;
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (q0 + row < T)
-            v = __ldg(reinterpret_cast<const uint4 *>(Qb + (size_t)(q0 + row) * ldq + kc * 8));
-        *reinterpret_cast<uint4 *>(Qs + kc * LBO_R + row * 16) = v;
-    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (tid == 0)
+    {
+        mbar_arrive_expect_tx(&q_full, TILE);
+        bulk_g2s(Qs, tile_ptr(Qp, ldq8, qc8, Tpad, qt), TILE, &q_full);
+        mbar_arrive_expect_tx(&kv_full[0], 2 * TILE);
+        bulk_g2s(Ks, tile_ptr(Kp, ldk8, kc8, Spad, 0), TILE, &kv_full[0]);
+        bulk_g2s(Vs, tile_ptr(Vp, ldv8, vc8, Spad, 0), TILE, &kv_full[0]);
+    }
     const uint32_t tmem_S = tmem_slot, tmem_PV = tmem_slot + 128;
     const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
     const uint32_t idesc_s = make_idesc(BKEY, 0), idesc_pv = make_idesc(DH, 1);
@@ -168,39 +186,37 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
     float m_run = -INFINITY, l_run = 0.f;
     uint32_t phase = 0;
 
-    for (int k0 = 0; k0 < S; k0 += BKEY)
+    for (int j = 0; j < ntiles; ++j)
     {
-        // ---- K and V tiles (previous tile's MMAs have completed: every thread waited on mma_bar) ----
-        for (int idx = tid; idx < BKEY * DCH; idx += THREADS)
-        {
-            const int key = idx / DCH, c = idx % DCH;
-            uint4 kv = make_uint4(0u, 0u, 0u, 0u), vv = kv;
-            if (k0 + key < S)
-            {
-                kv = __ldg(reinterpret_cast<const uint4 *>(Kb + (size_t)(k0 + key) * ldk + c * 8));
-                vv = __ldg(reinterpret_cast<const uint4 *>(Vb + (size_t)(k0 + key) * ldv + c * 8));
-            }
-            *reinterpret_cast<uint4 *>(Ks + c * LBO_R + key * 16) = kv;
-            *reinterpret_cast<uint4 *>(Vs + c * SBO_V + key * 16) = vv;
-        }
-        fence_proxy_async();
-        __syncthreads();
-        // ---- S = Q K^T ----
+        const int buf = j & 1;
+        const int k0 = j * BKEY;
         if (tid == 0)
         {
+            // prefetch tile j+1 into the other buffer once the MMAs that read it (tile j-1) have completed
+            if (j + 1 < ntiles)
+            {
+                const int nb = (j + 1) & 1;
+                if (j + 1 >= 2)
+                    mbar_wait(&kv_empty[nb], (uint32_t)(((j + 1) / 2 - 1) & 1));
+                mbar_arrive_expect_tx(&kv_full[nb], 2 * TILE);
+                bulk_g2s(Ks + nb * TILE, tile_ptr(Kp, ldk8, kc8, Spad, j + 1), TILE, &kv_full[nb]);
+                bulk_g2s(Vs + nb * TILE, tile_ptr(Vp, ldv8, vc8, Spad, j + 1), TILE, &kv_full[nb]);
+            }
+            if (j == 0)
+                mbar_wait(&q_full, 0);
+            mbar_wait(&kv_full[buf], (uint32_t)((j / 2) & 1));
             tc_fence_after();
-            const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks);
+            const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks + buf * TILE);
 #pragma unroll
-            for (int j = 0; j < DH / 16; ++j)
-                umma(tmem_S, make_desc(qa + j * 2 * LBO_R, LBO_R, 128), make_desc(ka + j * 2 * LBO_R, LBO_R, 128), idesc_s,
-                     j > 0 ? 1u : 0u);
+            for (int jj = 0; jj < DH / 16; ++jj)
+                umma(tmem_S, make_desc(qa + jj * 2 * LBO, LBO, 128), make_desc(ka + jj * 2 * LBO, LBO, 128), idesc_s,
+                     jj > 0 ? 1u : 0u);
             umma_commit(&mma_bar);
         }
         mbar_wait(&mma_bar, phase);
         phase ^= 1u;
         tc_fence_after();
-        // ---- streaming softmax on this thread's row ----
-        // two passes over the TMEM row (TMEM reads are cheap; keeping all 128 scores live would spill)
+        // ---- streaming softmax on this thread's row: two passes over the TMEM row ----
         float corr;
         {
             float mx = -INFINITY;
@@ -210,9 +226,9 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
                 float s[16];
                 tmem_ld16(tmem_S + lane_off + (uint32_t)c, s);
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    if (k0 + c + j < S)
-                        mx = fmaxf(mx, s[j]);
+                for (int jj = 0; jj < 16; ++jj)
+                    if (k0 + c + jj < S)
+                        mx = fmaxf(mx, s[jj]);
             }
             mx *= scale; // scale > 0: max commutes with it
             const float m_new = fmaxf(m_run, mx);
@@ -225,39 +241,40 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
                 tmem_ld16(tmem_S + lane_off + (uint32_t)c, s);
                 float pv[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
+                for (int jj = 0; jj < 16; ++jj)
                 {
-                    pv[j] = (k0 + c + j < S) ? __expf(s[j] * scale - m_new) : 0.f;
-                    rs += pv[j];
+                    pv[jj] = (k0 + c + jj < S) ? __expf(s[jj] * scale - m_new) : 0.f;
+                    rs += pv[jj];
                 }
                 uint4 pk;
                 pk.x = pack_bf16x2(pv[0], pv[1]);
                 pk.y = pack_bf16x2(pv[2], pv[3]);
                 pk.z = pack_bf16x2(pv[4], pv[5]);
                 pk.w = pack_bf16x2(pv[6], pv[7]);
-                *reinterpret_cast<uint4 *>(Ps + (c / 8) * LBO_R + tid * 16) = pk;
+                *reinterpret_cast<uint4 *>(Ps + (c / 8) * LBO + tid * 16) = pk;
                 pk.x = pack_bf16x2(pv[8], pv[9]);
                 pk.y = pack_bf16x2(pv[10], pv[11]);
                 pk.z = pack_bf16x2(pv[12], pv[13]);
                 pk.w = pack_bf16x2(pv[14], pv[15]);
-                *reinterpret_cast<uint4 *>(Ps + (c / 8 + 1) * LBO_R + tid * 16) = pk;
+                *reinterpret_cast<uint4 *>(Ps + (c / 8 + 1) * LBO + tid * 16) = pk;
             }
             l_run = l_run * corr + rs;
             m_run = m_new;
         }
         tc_fence_before();
-        fence_proxy_async();
+        fence_proxy_async(); // P was written through the generic proxy
         __syncthreads();
         // ---- PV = P V ----
         if (tid == 0)
         {
             tc_fence_after();
-            const uint32_t pa = smem_u32(Ps), va = smem_u32(Vs);
+            const uint32_t pa = smem_u32(Ps), va = smem_u32(Vs + buf * TILE);
 #pragma unroll
-            for (int j = 0; j < BKEY / 16; ++j)
-                umma(tmem_PV, make_desc(pa + j * 2 * LBO_R, LBO_R, 128), make_desc(va + j * 256, 128, SBO_V), idesc_pv,
-                     j > 0 ? 1u : 0u);
+            for (int jj = 0; jj < BKEY / 16; ++jj)
+                umma(tmem_PV, make_desc(pa + jj * 2 * LBO, LBO, 128), make_desc(va + jj * 256, 128, LBO), idesc_pv,
+                     jj > 0 ? 1u : 0u);
             umma_commit(&mma_bar);
+            umma_commit(&kv_empty[buf]); // K/V buffer reusable once everything issued so far has completed
         }
         mbar_wait(&mma_bar, phase);
         phase ^= 1u;
@@ -276,29 +293,19 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
     const int row = q0 + tid;
     if (row < T)
     {
+        // tile-packed bf16 (flat rows): the out-projection GEMM's A image, [row/128][d/8][row%128][8]
         const float inv = 1.0f / l_run;
-        if (Opk)
-        {
-            // tile-packed bf16: the out-projection GEMM's A image, [row/128][d/8][row%128][8]
-            const size_t grow = (size_t)b * T + row;
-            const int nch = heads * DH / 8;
+        const size_t grow = (size_t)b * T + row;
+        const int nch = heads * DCH;
 #pragma unroll
-            for (int i = 0; i < DH; i += 8)
-            {
-                uint4 pk;
-                pk.x = pack_bf16x2(o[i] * inv, o[i + 1] * inv);
-                pk.y = pack_bf16x2(o[i + 2] * inv, o[i + 3] * inv);
-                pk.z = pack_bf16x2(o[i + 4] * inv, o[i + 5] * inv);
-                pk.w = pack_bf16x2(o[i + 6] * inv, o[i + 7] * inv);
-                Opk[((grow >> 7) * nch + (h * DH + i) / 8) * 128 + (grow & 127)] = pk;
-            }
-        }
-        else
+        for (int i = 0; i < DH; i += 8)
         {
-            float *dst = O + ((size_t)b * T + row) * ldo + h * DH;
-#pragma unroll
-            for (int i = 0; i < DH; i += 4)
-                *reinterpret_cast<float4 *>(dst + i) = make_float4(o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv);
+            uint4 pk;
+            pk.x = pack_bf16x2(o[i] * inv, o[i + 1] * inv);
+            pk.y = pack_bf16x2(o[i + 2] * inv, o[i + 3] * inv);
+            pk.z = pack_bf16x2(o[i + 4] * inv, o[i + 5] * inv);
+            pk.w = pack_bf16x2(o[i + 6] * inv, o[i + 7] * inv);
+            Opk[((grow >> 7) * nch + h * DCH + i / 8) * 128 + (grow & 127)] = pk;
         }
     }
     __syncthreads();
@@ -309,11 +316,7 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
     }
 }
 
-template <int DH> static int smem_bytes()
-{
-    constexpr int DCH = DH / 8;
-    return DCH * (BQ * 16 + PAD) * 2 + DCH * (BKEY * 16 + PAD) + 16 * (BQ * 16 + PAD);
-}
+template <int DH> static int smem_bytes() { return (DH / 8) * (BQ * 16) * 5 + 16 * (BQ * 16); }
 
 } // namespace atc
 
@@ -326,25 +329,24 @@ int attention_tc_init_device()
     return 0;
 }
 
-// Q/K/V: bf16, O: fp32.  Leading dimensions in elements; all must be multiples of 8 (16-byte rows).
-int launch_attention_tc(const void *Q, int ldq, const void *K, int ldk, const void *V, int ldv, float *O, int ldo, int B,
-                        int T, int S, int heads, int dh, cudaStream_t st, void *Opk)
+int launch_attention_tc(const void *Qp, int ldq, int q_col, const void *Kp, int ldk, int k_col, const void *Vp, int ldv,
+                        int v_col, void *Opk, int B, int T, int Tpad, int S, int Spad, int heads, int dh, cudaStream_t st)
 {
-    if ((ldq | ldk | ldv) % 8 || ldo % 4)
+    if ((ldq | ldk | ldv | q_col | k_col | v_col) % 8 || (Tpad | Spad) % 128 || Tpad < T || Spad < S)
     {
-        set_error("attention_tc: leading dimensions must be multiples of 8 (bf16) / 4 (fp32)");
+        set_error("attention_tc: packed operands need 8-column alignment and 128-row padded items");
         return -1;
     }
     const float scale = 1.0f / sqrtf((float)dh);
     dim3 grid((T + atc::BQ - 1) / atc::BQ, heads, B);
-    const __nv_bfloat16 *q = static_cast<const __nv_bfloat16 *>(Q), *k = static_cast<const __nv_bfloat16 *>(K),
-                        *v = static_cast<const __nv_bfloat16 *>(V);
+    const __nv_bfloat16 *q = static_cast<const __nv_bfloat16 *>(Qp), *k = static_cast<const __nv_bfloat16 *>(Kp),
+                        *v = static_cast<const __nv_bfloat16 *>(Vp);
     if (dh == 64)
-        atc::attention_tc_kernel<64><<<grid, atc::THREADS, atc::smem_bytes<64>(), st>>>(q, ldq, k, ldk, v, ldv, O, ldo, T, S,
-                                                                                          scale, (uint4 *)Opk, heads);
+        atc::attention_tc_kernel<64><<<grid, atc::THREADS, atc::smem_bytes<64>(), st>>>(
+            q, ldq / 8, q_col / 8, k, ldk / 8, k_col / 8, v, ldv / 8, v_col / 8, (uint4 *)Opk, T, Tpad, S, Spad, heads, scale);
     else if (dh == 48)
-        atc::attention_tc_kernel<48><<<grid, atc::THREADS, atc::smem_bytes<48>(), st>>>(q, ldq, k, ldk, v, ldv, O, ldo, T, S,
-                                                                                          scale, (uint4 *)Opk, heads);
+        atc::attention_tc_kernel<48><<<grid, atc::THREADS, atc::smem_bytes<48>(), st>>>(
+            q, ldq / 8, q_col / 8, k, ldk / 8, k_col / 8, v, ldv / 8, v_col / 8, (uint4 *)Opk, T, Tpad, S, Spad, heads, scale);
     else
     {
         set_error("attention_tc: unsupported head dim");

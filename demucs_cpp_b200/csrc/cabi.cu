@@ -323,8 +323,9 @@ int dmx_model_set_precision(dmx_model *m, int precision)
         set_error("dmx_model_set_precision: bad argument");
         return -1;
     }
+    std::lock_guard<std::mutex> lk(m->mtx);
     m->precision = precision;
-    return 0;
+    return model_zero_attention_pads(m);
 }
 
 int dmx_num_segments(int64_t n_frames, int shift_offset) { return num_segments(n_frames, shift_offset); }

@@ -147,6 +147,7 @@ struct RowInfo
     long long outoff; // element offset in C of (b, uo*ous + ouo, vo*ovs + ovo), channel 0 (may be "virtual")
     int uu0, vv0;     // that output position (for the bounds checks of the scatter mapping)
     int uo, item;     // input-row frequency index (row-add table) and statistics item (-1: row invalid)
+    int prow, pad_;   // row index in the tile-packed output space (out_pack)
 };
 
 constexpr int PROD_WARPS = 8;
@@ -232,6 +233,8 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
         ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
         ri.uo = rc.uo;
         ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
+        ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m; // per-item padding to whole 128-row tiles
+        ri.pad_ = 0;
         rowinfo[tid] = ri;
         float pmean = 0.f, prstd = 1.f;
         if (p.pro == 1 && valid)
@@ -546,7 +549,7 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
                         if (p.out_pack)
                         {
                             // tile-packed bf16 for a consumer GEMM with K = ldc: [row/128][col/8][row%128][col%8]
-                            const int mrow = m0 + q * 32 + rl;
+                            const int mrow = ri.prow;
                             const size_t off = ((size_t)(mrow >> 7) * (p.ldc >> 3) + (outc >> 3)) * 1024 + (size_t)(mrow & 127) * 8 +
                                                (outc & 7);
                             uint2 pk2;

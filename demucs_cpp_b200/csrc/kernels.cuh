@@ -50,6 +50,7 @@ struct GemmParams
     int out_bf16 = 0;              // tensor-core kernel only, identity mapping only: C holds bf16 (ldc in elements)
     int out_pack = 0;              // ... C holds TILE-PACKED bf16 [row/128][ldc/8][row%128][8]: the next GEMM's A image
     const void *Apk = nullptr;     // tensor-core kernel only: A operand given as tile-packed bf16 (1x1 / linear only)
+    int pack_T = 0;                // out_pack: rows per batch item in the packed space (multiple of 128), 0 = flat rows
     // output mapping
     float *C = nullptr;
     int ldc = 0, Nco = 0;
@@ -116,7 +117,9 @@ int launch_attention(const float *Q, int ldq, const float *K, int ldk, const flo
 
 // attention_tc.cu: the same attention on tcgen05 tensor cores; Q/K/V bf16, O fp32
 int attention_tc_init_device();
-int launch_attention_tc(const void *Q, int ldq, const void *K, int ldk, const void *V, int ldv, float *O, int ldo, int B,
-                        int T, int S, int heads, int dh, cudaStream_t st, void *Opk = nullptr);
+// Q/K/V are TILE-PACKED bf16 ([item*Tpad/128 + tile][ld/8][128][8], per-item rows padded to Tpad / Spad); q_col,
+// k_col, v_col = first column of the tensor inside its packed matrix; output tile-packed bf16 (flat rows), d = heads*dh.
+int launch_attention_tc(const void *Qp, int ldq, int q_col, const void *Kp, int ldk, int k_col, const void *Vp, int ldv,
+                        int v_col, void *Opk, int B, int T, int Tpad, int S, int Spad, int heads, int dh, cudaStream_t st);
 
 } // namespace dmx

@@ -267,6 +267,22 @@ int model_finalize(dmx_model *m)
     if (dev_alloc_t(m, &m->stats, m->stats_cap) || dev_alloc_t(m, &m->track_stats, 2))
         return -1;
     m->finalized = true;
+    return model_zero_attention_pads(m);
+}
+
+// The tensor-core attention reads Q/K/V as tile-packed bf16 with every item's rows padded to whole 128-row
+// tiles; pad rows are never written by the projections, so they must hold zeros (0 x garbage could be NaN in
+// the P.V product).  Called at finalize and whenever the precision mode changes (fp32 mode reuses the buffers).
+int model_zero_attention_pads(dmx_model *m)
+{
+    if (!m->finalized || m->arch == DMX_ARCH_HDEMUCS_V3)
+        return 0;
+    const size_t B = (size_t)m->maxB, d = (size_t)m->d_model, TF = 8 * T, TT = TLEN3;
+    DMX_CUDA(cudaSetDevice(m->device));
+    DMX_CUDA(cudaMemset(m->qkv_f, 0, B * TF * 3 * d * sizeof(float)));
+    DMX_CUDA(cudaMemset(m->qkv_t, 0, B * TT * 3 * d * sizeof(float)));
+    DMX_CUDA(cudaMemset(m->kv_f, 0, B * TT * 2 * d * sizeof(float)));
+    DMX_CUDA(cudaMemset(m->kv_t, 0, B * TF * 2 * d * sizeof(float)));
     return 0;
 }
 

@@ -167,6 +167,7 @@ namespace dmx
 {
 int model_finalize(dmx_model *m);
 int model_v3_finalize(dmx_model *m);
+int model_zero_attention_pads(dmx_model *m);
 int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out);
 int debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
                  int act, float *out, int iters, float *ms_out);

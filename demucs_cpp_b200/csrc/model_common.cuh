@@ -456,15 +456,16 @@ struct Fwd
         if (!L.cross)
         {
             GemmParams pq = linear_a(ln, d, L.qkv, qkv, 3 * d, Tq);
-            pq.out_bf16 = tcm;
+            pq.out_pack = tcm; // Q | K | V tile-packed, per-item rows padded to whole tiles: attention operand images
+            pq.pack_T = tcm ? round_up(Tq, 128) : 0;
             gemm(pq, PC_GEMM_XFMR);
             if (!rc)
             {
                 ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tq * d);
                 if (tcm)
                 {
-                    const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
-                    rc = launch_attention_tc(qb, 3 * d, qb + d, 3 * d, qb + 2 * d, 3 * d, nullptr, d, B, Tq, Tq, 8, dh, st, ao);
+                    rc = launch_attention_tc(qkv, 3 * d, 0, qkv, 3 * d, d, qkv, 3 * d, 2 * d, ao, B, Tq, round_up(Tq, 128), Tq,
+                                             round_up(Tq, 128), 8, dh, st);
                 }
                 else
                     rc = launch_attention(qkv, 3 * d, qkv + d, 3 * d, qkv + 2 * d, 3 * d, ao, d, B, Tq, Tq, 8, dh, st);
@@ -473,19 +474,20 @@ struct Fwd
         else
         {
             GemmParams pq = linear_a(ln, d, L.q, qkv, d, Tq);
-            pq.out_bf16 = tcm;
+            pq.out_pack = tcm;
+            pq.pack_T = tcm ? round_up(Tq, 128) : 0;
             gemm(pq, PC_GEMM_XFMR);
             GemmParams pkv = linear_a(kn, d, L.kv, kv, 2 * d, Tk);
-            pkv.out_bf16 = tcm;
+            pkv.out_pack = tcm;
+            pkv.pack_T = tcm ? round_up(Tk, 128) : 0;
             gemm(pkv, PC_GEMM_XFMR);
             if (!rc)
             {
                 ProfScope ps(m, PC_ATTENTION, 4.0 * B * (double)Tq * Tk * d);
                 if (tcm)
                 {
-                    const uint16_t *qb = reinterpret_cast<const uint16_t *>(qkv);
-                    const uint16_t *kb = reinterpret_cast<const uint16_t *>(kv);
-                    rc = launch_attention_tc(qb, d, kb, 2 * d, kb + d, 2 * d, nullptr, d, B, Tq, Tk, 8, dh, st, ao);
+                    rc = launch_attention_tc(qkv, d, 0, kv, 2 * d, 0, kv, 2 * d, d, ao, B, Tq, round_up(Tq, 128), Tk,
+                                             round_up(Tk, 128), 8, dh, st);
                 }
                 else
                     rc = launch_attention(qkv, d, kv, 2 * d, kv + d, 2 * d, ao, d, B, Tq, Tk, 8, dh, st);
