@@ -3,11 +3,13 @@
 //
 // One CTA = 128 queries of one (batch item, head).  Per 128-key tile:
 //     S  = Q K^T   tcgen05.mma  M=128, N=128, K=dh   (Q, K: K-major canonical smem tiles)     -> TMEM cols [0,128)
-//     each thread owns one query row: tcgen05.ld its S row, scale, running max / sum in fp32, P = exp(S - m)
-//     written as bf16 into the canonical K-major A-operand layout (conflict-free 16-byte stores)
-//     PV = P V     tcgen05.mma  M=128, N=dh,  K=128  (V: MN-major canonical tile, i.e. stored as it lies in
-//                                                      memory, dh contiguous)                   -> TMEM cols [128,128+dh)
-//     O  = O * exp(m_old - m_new) + PV   in registers (fp32)
+//     256 threads: thread (row, half) owns 64 of the 128 keys of its query row: tcgen05.ld that half row, running
+//     max / sum in fp32 (log2 domain), P = exp2(S*c - m) written as bf16 into the canonical K-major A-operand
+//     layout (conflict-free 16-byte stores).  The two halves keep SEPARATE (m, l, O) streams, so no per-tile
+//     exchange between them is needed: they are merged once at the end through shared memory.
+//     PV_h = P_h V_h  tcgen05.mma  M=128, N=dh, K=64 per half (V: MN-major canonical tile, i.e. stored as it lies
+//                                                      in memory, dh contiguous)      -> TMEM cols [128+h*dh, ...)
+//     O_h = O_h * exp2(m_old - m_new) + PV_h   in registers (fp32)
 // Q/K/V arrive as bf16 (the QKV projection's epilogue writes them that way); the output is fp32 because it
 // feeds the out-projection's fp32 A-gather.  The T x S score matrix never leaves the SM.
 // Reference: src/layers.cpp:442-482 (heads = contiguous dh-wide column blocks, max-subtracted softmax).
@@ -22,7 +24,7 @@ namespace atc
 
 constexpr int BQ = 128;   // queries per CTA (UMMA M)
 constexpr int BKEY = 128; // keys per tile
-constexpr int THREADS = 128;
+constexpr int THREADS = 256; // two threads per query row (one per 64-key half of a tile)
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
@@ -83,18 +85,42 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float *v)
+// 32 consecutive TMEM columns of this thread's lane.  The wait names the registers as in/out operands so that no
+// use of them can be scheduled above it.
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t *r)
 {
-    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]),
+                   "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+                   "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                   "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]),
+                   "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]),
+                   "+r"(r[30]), "+r"(r[31])::"memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t *r)
+{
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
                  "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
                    "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
                  : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i)
-        v[i] = __uint_as_float(r[i]);
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])::"memory");
+}
+__device__ __forceinline__ float ex2f(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi)
 {
@@ -120,23 +146,23 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint3
 // and is fetched with a single bulk async copy per tile; K/V tiles are double buffered so the copies of tile j+1 run
 // under the MMAs and the softmax of tile j.  No thread touches the operands.
 template <int DH>
-__global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat16 *__restrict__ Qp, int ldq8, int qc8,
-                                                               const __nv_bfloat16 *__restrict__ Kp, int ldk8, int kc8,
-                                                               const __nv_bfloat16 *__restrict__ Vp, int ldv8, int vc8,
-                                                               uint4 *__restrict__ Opk, int T, int Tpad, int S, int Spad,
-                                                               int heads, float scale)
+__global__ void __launch_bounds__(THREADS, 2)
+    attention_tc_kernel(const __nv_bfloat16 *__restrict__ Qp, int ldq8, int qc8, const __nv_bfloat16 *__restrict__ Kp,
+                        int ldk8, int kc8, const __nv_bfloat16 *__restrict__ Vp, int ldv8, int vc8,
+                        uint4 *__restrict__ Opk, int T, int Tpad, int S, int Spad, int heads, float scale_log2)
 {
     constexpr int DCH = DH / 8;                   // 16-byte chunks per row
     constexpr uint32_t LBO = BQ * 16;             // 2048: chunk stride inside a packed tile
     constexpr uint32_t TILE = DCH * LBO;          // bytes of a 128 x DH tile
-    constexpr uint32_t P_BYTES = 16 * LBO;
+    constexpr int HK = BKEY / 2;                  // keys per thread per tile
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t *Qs = smem, *Ks = Qs + TILE, *Vs = Ks + 2 * TILE, *Ps = Vs + 2 * TILE;
     __shared__ __align__(8) uint64_t mma_bar, q_full, kv_full[2], kv_empty[2];
     __shared__ uint32_t tmem_slot;
-    (void)P_BYTES;
 
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int half = warp >> 2;      // which 64 keys of every tile
+    const int row = tid & (BQ - 1);  // query row == TMEM lane (warp % 4 selects the lane quadrant)
     const int qt = blockIdx.x;
     const int h = blockIdx.y, b = blockIdx.z;
     const int q0 = qt * BQ;
@@ -175,21 +201,22 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
         bulk_g2s(Ks, tile_ptr(Kp, ldk8, kc8, Spad, 0), TILE, &kv_full[0]);
         bulk_g2s(Vs, tile_ptr(Vp, ldv8, vc8, Spad, 0), TILE, &kv_full[0]);
     }
-    const uint32_t tmem_S = tmem_slot, tmem_PV = tmem_slot + 128;
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tmem_S = tmem_slot + lane_off + (uint32_t)(half * HK);
+    const uint32_t tmem_PV = tmem_slot + lane_off + 128u + (uint32_t)(half * DH);
     const uint32_t idesc_s = make_idesc(BKEY, 0), idesc_pv = make_idesc(DH, 1);
+    uint8_t *Prow = Ps + (half * (HK / 8)) * LBO + row * 16;
 
     float o[DH];
 #pragma unroll
     for (int i = 0; i < DH; ++i)
         o[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;
+    float m_run = -INFINITY, l_run = 0.f; // log2 domain
     uint32_t phase = 0;
 
     for (int j = 0; j < ntiles; ++j)
     {
         const int buf = j & 1;
-        const int k0 = j * BKEY;
         if (tid == 0)
         {
             // prefetch tile j+1 into the other buffer once the MMAs that read it (tile j-1) have completed
@@ -209,54 +236,74 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
             const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks + buf * TILE);
 #pragma unroll
             for (int jj = 0; jj < DH / 16; ++jj)
-                umma(tmem_S, make_desc(qa + jj * 2 * LBO, LBO, 128), make_desc(ka + jj * 2 * LBO, LBO, 128), idesc_s,
+                umma(tmem_slot, make_desc(qa + jj * 2 * LBO, LBO, 128), make_desc(ka + jj * 2 * LBO, LBO, 128), idesc_s,
                      jj > 0 ? 1u : 0u);
             umma_commit(&mma_bar);
         }
         mbar_wait(&mma_bar, phase);
         phase ^= 1u;
         tc_fence_after();
-        // ---- streaming softmax on this thread's row: two passes over the TMEM row ----
+        // ---- streaming softmax on this thread's half row: two passes over its 64 TMEM columns ----
+        // keys beyond S exist only in the last tile; nvalid = how many of this thread's 64 keys are real
+        const int nvalid = min(HK, max(0, S - j * BKEY - half * HK));
         float corr;
         {
             float mx = -INFINITY;
 #pragma unroll
-            for (int c = 0; c < BKEY; c += 16)
+            for (int c = 0; c < HK; c += 32)
             {
-                float s[16];
-                tmem_ld16(tmem_S + lane_off + (uint32_t)c, s);
+                uint32_t s[32];
+                tmem_ld32(tmem_S + (uint32_t)c, s);
+                if (nvalid == HK)
+                {
 #pragma unroll
-                for (int jj = 0; jj < 16; ++jj)
-                    if (k0 + c + jj < S)
-                        mx = fmaxf(mx, s[jj]);
+                    for (int jj = 0; jj < 32; ++jj)
+                        mx = fmaxf(mx, __uint_as_float(s[jj]));
+                }
+                else
+                {
+#pragma unroll
+                    for (int jj = 0; jj < 32; ++jj)
+                        if (c + jj < nvalid)
+                            mx = fmaxf(mx, __uint_as_float(s[jj]));
+                }
             }
-            mx *= scale; // scale > 0: max commutes with it
-            const float m_new = fmaxf(m_run, mx);
-            corr = (m_run == -INFINITY) ? 0.f : __expf(m_run - m_new);
+            const float m_new = fmaxf(m_run, mx * scale_log2); // scale > 0: max commutes with it
+            corr = (m_run == -INFINITY) ? 0.f : ex2f(m_run - m_new);
+            // a half with no real key yet keeps m = -inf; give the exponent a finite offset (its p are forced to 0)
+            const float m_sub = (m_new == -INFINITY) ? 0.f : m_new;
             float rs = 0.f;
 #pragma unroll
-            for (int c = 0; c < BKEY; c += 16)
+            for (int c = 0; c < HK; c += 32)
             {
-                float s[16];
-                tmem_ld16(tmem_S + lane_off + (uint32_t)c, s);
-                float pv[16];
-#pragma unroll
-                for (int jj = 0; jj < 16; ++jj)
+                uint32_t s[32];
+                tmem_ld32(tmem_S + (uint32_t)c, s);
+                float pv[32];
+                if (nvalid == HK)
                 {
-                    pv[jj] = (k0 + c + jj < S) ? __expf(s[jj] * scale - m_new) : 0.f;
-                    rs += pv[jj];
+#pragma unroll
+                    for (int jj = 0; jj < 32; ++jj)
+                        pv[jj] = ex2f(fmaf(__uint_as_float(s[jj]), scale_log2, -m_sub));
                 }
-                uint4 pk;
-                pk.x = pack_bf16x2(pv[0], pv[1]);
-                pk.y = pack_bf16x2(pv[2], pv[3]);
-                pk.z = pack_bf16x2(pv[4], pv[5]);
-                pk.w = pack_bf16x2(pv[6], pv[7]);
-                *reinterpret_cast<uint4 *>(Ps + (c / 8) * LBO + tid * 16) = pk;
-                pk.x = pack_bf16x2(pv[8], pv[9]);
-                pk.y = pack_bf16x2(pv[10], pv[11]);
-                pk.z = pack_bf16x2(pv[12], pv[13]);
-                pk.w = pack_bf16x2(pv[14], pv[15]);
-                *reinterpret_cast<uint4 *>(Ps + (c / 8 + 1) * LBO + tid * 16) = pk;
+                else
+                {
+#pragma unroll
+                    for (int jj = 0; jj < 32; ++jj)
+                        pv[jj] = (c + jj < nvalid) ? ex2f(fmaf(__uint_as_float(s[jj]), scale_log2, -m_sub)) : 0.f;
+                }
+#pragma unroll
+                for (int jj = 0; jj < 32; ++jj)
+                    rs += pv[jj];
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                {
+                    uint4 pk;
+                    pk.x = pack_bf16x2(pv[8 * q], pv[8 * q + 1]);
+                    pk.y = pack_bf16x2(pv[8 * q + 2], pv[8 * q + 3]);
+                    pk.z = pack_bf16x2(pv[8 * q + 4], pv[8 * q + 5]);
+                    pk.w = pack_bf16x2(pv[8 * q + 6], pv[8 * q + 7]);
+                    *reinterpret_cast<uint4 *>(Prow + (c / 8 + q) * LBO) = pk;
+                }
             }
             l_run = l_run * corr + rs;
             m_run = m_new;
@@ -264,47 +311,67 @@ __global__ void __launch_bounds__(THREADS) attention_tc_kernel(const __nv_bfloat
         tc_fence_before();
         fence_proxy_async(); // P was written through the generic proxy
         __syncthreads();
-        // ---- PV = P V ----
+        // ---- PV_h = P_h V_h for both key halves ----
         if (tid == 0)
         {
             tc_fence_after();
             const uint32_t pa = smem_u32(Ps), va = smem_u32(Vs + buf * TILE);
 #pragma unroll
             for (int jj = 0; jj < BKEY / 16; ++jj)
-                umma(tmem_PV, make_desc(pa + jj * 2 * LBO, LBO, 128), make_desc(va + jj * 256, 128, LBO), idesc_pv,
-                     jj > 0 ? 1u : 0u);
+                umma(tmem_slot + 128u + (uint32_t)((jj / 4) * DH), make_desc(pa + jj * 2 * LBO, LBO, 128),
+                     make_desc(va + jj * 256, 128, LBO), idesc_pv, (jj & 3) ? 1u : 0u);
             umma_commit(&mma_bar);
             umma_commit(&kv_empty[buf]); // K/V buffer reusable once everything issued so far has completed
         }
         mbar_wait(&mma_bar, phase);
         phase ^= 1u;
         tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < DH; c += 16)
         {
-            float pv[DH];
+            uint32_t pv[16];
+            tmem_ld16(tmem_PV + (uint32_t)c, pv);
 #pragma unroll
-            for (int c = 0; c < DH; c += 16)
-                tmem_ld16(tmem_PV + lane_off + (uint32_t)c, &pv[c]);
-#pragma unroll
-            for (int i = 0; i < DH; ++i)
-                o[i] = o[i] * corr + pv[i];
+            for (int i = 0; i < 16; ++i)
+                o[c + i] = fmaf(o[c + i], corr, __uint_as_float(pv[i]));
         }
         tc_fence_before();
     }
-    const int row = q0 + tid;
-    if (row < T)
+    // ---- merge the two key halves of every row (all MMAs and copies have completed: operand smem is free) ----
+    float *mg = reinterpret_cast<float *>(smem); // [DH + 2][128]
+    __syncthreads();
+    if (half == 1)
     {
+        mg[row] = m_run;
+        mg[BQ + row] = l_run;
+#pragma unroll
+        for (int i = 0; i < DH; ++i)
+            mg[(2 + i) * BQ + row] = o[i];
+    }
+    __syncthreads();
+    const int grow_i = q0 + row;
+    if (half == 0 && grow_i < T)
+    {
+        const float m1 = mg[row], l1 = mg[BQ + row];
+        const float m = fmaxf(m_run, m1); // half 0 always holds real keys: m_run is finite
+        const float a0 = ex2f(m_run - m), a1 = (m1 == -INFINITY) ? 0.f : ex2f(m1 - m);
+        const float inv = 1.0f / (l_run * a0 + l1 * a1);
+        const float w0 = a0 * inv, w1 = a1 * inv;
         // tile-packed bf16 (flat rows): the out-projection GEMM's A image, [row/128][d/8][row%128][8]
-        const float inv = 1.0f / l_run;
-        const size_t grow = (size_t)b * T + row;
+        const size_t grow = (size_t)b * T + grow_i;
         const int nch = heads * DCH;
 #pragma unroll
         for (int i = 0; i < DH; i += 8)
         {
+            float r[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+                r[e] = o[i + e] * w0 + mg[(2 + i + e) * BQ + row] * w1;
             uint4 pk;
-            pk.x = pack_bf16x2(o[i] * inv, o[i + 1] * inv);
-            pk.y = pack_bf16x2(o[i + 2] * inv, o[i + 3] * inv);
-            pk.z = pack_bf16x2(o[i + 4] * inv, o[i + 5] * inv);
-            pk.w = pack_bf16x2(o[i + 6] * inv, o[i + 7] * inv);
+            pk.x = pack_bf16x2(r[0], r[1]);
+            pk.y = pack_bf16x2(r[2], r[3]);
+            pk.z = pack_bf16x2(r[4], r[5]);
+            pk.w = pack_bf16x2(r[6], r[7]);
             Opk[((grow >> 7) * nch + h * DCH + i / 8) * 128 + (grow & 127)] = pk;
         }
     }
@@ -337,7 +404,7 @@ int launch_attention_tc(const void *Qp, int ldq, int q_col, const void *Kp, int 
         set_error("attention_tc: packed operands need 8-column alignment and 128-row padded items");
         return -1;
     }
-    const float scale = 1.0f / sqrtf((float)dh);
+    const float scale = 1.4426950408889634f / sqrtf((float)dh); // log2(e) folded in: the kernel works with exp2
     dim3 grid((T + atc::BQ - 1) / atc::BQ, heads, B);
     const __nv_bfloat16 *q = static_cast<const __nv_bfloat16 *>(Qp), *k = static_cast<const __nv_bfloat16 *>(Kp),
                         *v = static_cast<const __nv_bfloat16 *>(Vp);

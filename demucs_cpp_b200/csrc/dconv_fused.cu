@@ -14,7 +14,8 @@ namespace dmx
 {
 
 constexpr int DF_T = LE;          // 336 frames
-constexpr int DF_THREADS = 352;   // 11 warps: one thread per frame (336 live)
+constexpr int DF_HALF = DF_T / 2; // each thread owns frames t and t + 168: every weight fetched from shared memory
+constexpr int DF_THREADS = 192;   // feeds two positions (halves the shared-memory traffic per FMA); 168 live threads
 
 // Packed parameter block per DConv (floats), for sub-block d = 0, 1 at offset d * stride:
 //   W1[3][C][HID] | b1[HID] | g1w[HID] | g1b[HID] | W2[2C][HID] | b2[2C] | g2w[2C] | g2b[2C] | scale[C]
@@ -67,8 +68,8 @@ __global__ void __launch_bounds__(DF_THREADS) dconv_fused_kernel(float *__restri
         d[2] = v.z;
         d[3] = v.w;
     }
-    const int t = tid;
-    const bool live = t < DF_T;
+    const bool live = tid < DF_HALF;
+    const int tp[2] = {tid, tid + DF_HALF};
 
 #pragma unroll 1
     for (int sub = 0; sub < 2; ++sub)
@@ -81,28 +82,32 @@ __global__ void __launch_bounds__(DF_THREADS) dconv_fused_kernel(float *__restri
         const float *W1 = ps, *b1 = W1 + 3 * C * HID, *g1w = b1 + HID, *g1b = g1w + HID;
         const float *W2 = g1b + HID, *b2 = W2 + 2 * C * HID, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C, *scale = g2b + 2 * C;
 
-        // ---- conv k3, dilation dil, zero padded: h[t][j] ----
-        float h[HID];
+        // ---- conv k3, dilation dil, zero padded: h[p][j] for this thread's two frames ----
+        float h[2][HID];
 #pragma unroll
-        for (int j = 0; j < HID; ++j)
-            h[j] = b1[j];
+        for (int p = 0; p < 2; ++p)
+#pragma unroll
+            for (int j = 0; j < HID; ++j)
+                h[p][j] = b1[j];
         if (live)
         {
 #pragma unroll
             for (int tap = 0; tap < 3; ++tap)
             {
-                const int ts = t + (tap - 1) * dil;
-                if (ts >= 0 && ts < DF_T)
-                {
-                    const float *xr = xs + ts * LD;
-                    const float *w = W1 + tap * C * HID;
+                const int t0 = tp[0] + (tap - 1) * dil, t1 = tp[1] + (tap - 1) * dil;
+                const bool v0 = t0 >= 0 && t0 < DF_T, v1 = t1 >= 0 && t1 < DF_T;
+                const float *x0 = xs + (v0 ? t0 : 0) * LD, *x1 = xs + (v1 ? t1 : 0) * LD;
+                const float *w = W1 + tap * C * HID;
 #pragma unroll 4
-                    for (int c = 0; c < C; ++c)
-                    {
-                        const float xv = xr[c];
+                for (int c = 0; c < C; ++c)
+                {
+                    const float a0 = v0 ? x0[c] : 0.f, a1 = v1 ? x1[c] : 0.f;
 #pragma unroll
-                        for (int j = 0; j < HID; ++j)
-                            h[j] = fmaf(w[c * HID + j], xv, h[j]);
+                    for (int j = 0; j < HID; ++j)
+                    {
+                        const float wv = w[c * HID + j];
+                        h[0][j] = fmaf(wv, a0, h[0][j]);
+                        h[1][j] = fmaf(wv, a1, h[1][j]);
                     }
                 }
             }
@@ -112,11 +117,13 @@ __global__ void __launch_bounds__(DF_THREADS) dconv_fused_kernel(float *__restri
         {
             float a = 0.f, b = 0.f;
 #pragma unroll
-            for (int j = 0; j < HID; ++j)
-            {
-                a += h[j];
-                b += h[j] * h[j];
-            }
+            for (int p = 0; p < 2; ++p)
+#pragma unroll
+                for (int j = 0; j < HID; ++j)
+                {
+                    a += h[p][j];
+                    b += h[p][j] * h[p][j];
+                }
             s1 = a;
             s2 = b;
         }
@@ -128,8 +135,10 @@ __global__ void __launch_bounds__(DF_THREADS) dconv_fused_kernel(float *__restri
             var = var < 0.0 ? 0.0 : var;
             const float mean = (float)m, rstd = (float)(1.0 / sqrt(var + 1e-5));
 #pragma unroll
-            for (int j = 0; j < HID; ++j)
-                h[j] = gelu_erf((h[j] - mean) * rstd * g1w[j] + g1b[j]);
+            for (int p = 0; p < 2; ++p)
+#pragma unroll
+                for (int j = 0; j < HID; ++j)
+                    h[p][j] = gelu_erf((h[p][j] - mean) * rstd * g1w[j] + g1b[j]);
         }
         // ---- 1x1 conv to 2C channels, pass A: statistics only ----
         s1 = 0.0;
@@ -140,18 +149,22 @@ __global__ void __launch_bounds__(DF_THREADS) dconv_fused_kernel(float *__restri
 #pragma unroll 4
             for (int n = 0; n < 2 * C; ++n)
             {
-                float y = b2[n];
+                float y0 = b2[n], y1 = y0;
 #pragma unroll
                 for (int j = 0; j < HID; ++j)
-                    y = fmaf(W2[n * HID + j], h[j], y);
-                a += y;
-                b += y * y;
+                {
+                    const float wv = W2[n * HID + j];
+                    y0 = fmaf(wv, h[0][j], y0);
+                    y1 = fmaf(wv, h[1][j], y1);
+                }
+                a += y0 + y1;
+                b += y0 * y0 + y1 * y1;
             }
             s1 = a;
             s2 = b;
         }
         block_sum2(s1, s2, red);
-        // ---- pass B: recompute, GroupNorm, GLU, LayerScale, residual into the resident row ----
+        // ---- pass B: recompute, GroupNorm, GLU, LayerScale, residual into the resident rows ----
         if (live)
         {
             const double n = (double)DF_T * 2 * C;
@@ -159,20 +172,25 @@ __global__ void __launch_bounds__(DF_THREADS) dconv_fused_kernel(float *__restri
             double var = (s2 - s1 * m) / (n - 1.0);
             var = var < 0.0 ? 0.0 : var;
             const float mean = (float)m, rstd = (float)(1.0 / sqrt(var + 1e-5));
-            float *xr = xs + t * LD;
+            float *xr0 = xs + tp[0] * LD, *xr1 = xs + tp[1] * LD;
 #pragma unroll 2
             for (int c = 0; c < C; ++c)
             {
-                float ya = b2[c], yg = b2[C + c];
+                float ya0 = b2[c], yg0 = b2[C + c], ya1 = ya0, yg1 = yg0;
 #pragma unroll
                 for (int j = 0; j < HID; ++j)
                 {
-                    ya = fmaf(W2[c * HID + j], h[j], ya);
-                    yg = fmaf(W2[(C + c) * HID + j], h[j], yg);
+                    const float wa = W2[c * HID + j], wg = W2[(C + c) * HID + j];
+                    ya0 = fmaf(wa, h[0][j], ya0);
+                    yg0 = fmaf(wg, h[0][j], yg0);
+                    ya1 = fmaf(wa, h[1][j], ya1);
+                    yg1 = fmaf(wg, h[1][j], yg1);
                 }
-                const float va = (ya - mean) * rstd * g2w[c] + g2b[c];
-                const float vg = (yg - mean) * rstd * g2w[C + c] + g2b[C + c];
-                xr[c] += scale[c] * (va * sigmoid_ref(vg));
+                const float ga = rstd * g2w[c], gg = rstd * g2w[C + c], sc = scale[c];
+                const float va0 = (ya0 - mean) * ga + g2b[c], vg0 = (yg0 - mean) * gg + g2b[C + c];
+                const float va1 = (ya1 - mean) * ga + g2b[c], vg1 = (yg1 - mean) * gg + g2b[C + c];
+                xr0[c] += sc * (va0 * sigmoid_ref(vg0));
+                xr1[c] += sc * (va1 * sigmoid_ref(vg1));
             }
         }
     }
