@@ -124,14 +124,13 @@ struct RowCoord
 {
     int b, uo, vo;
 };
-__device__ __forceinline__ RowCoord decode_row(int m, int Uo, int Vo)
+__device__ __forceinline__ RowCoord decode_row(int m, const GemmParams &p)
 {
     RowCoord rc;
-    const int per = Uo * Vo;
-    rc.b = m / per;
-    const int r = m - rc.b * per;
-    rc.uo = r / Vo;
-    rc.vo = r - rc.uo * Vo;
+    rc.b = fast_div(m, p.div_per);
+    const int r = m - rc.b * (p.Uo * p.Vo);
+    rc.uo = fast_div(r, p.div_vo);
+    rc.vo = r - rc.uo * p.Vo;
     return rc;
 }
 
@@ -226,7 +225,7 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
     {
         const int m = m0 + tid;
         const bool valid = m < p.M;
-        const RowCoord rc = decode_row(valid ? m : 0, p.Uo, p.Vo);
+        const RowCoord rc = decode_row(valid ? m : 0, p);
         RowInfo ri;
         ri.uu0 = rc.uo * p.ous + p.ouo;
         ri.vv0 = rc.vo * p.ovs + p.ovo;
@@ -277,15 +276,12 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
             rp[i] = p.A;
             if (m < p.M)
             {
-                const RowCoord rc = decode_row(m, p.Uo, p.Vo);
+                const RowCoord rc = decode_row(m, p);
                 const int ui0 = rc.uo * p.su, vi0 = rc.vo * p.sv;
                 rp[i] = p.A + (((long long)rc.b * p.Ui + ui0) * p.Vi + vi0) * p.lda;
                 for (int t = 0; t < p.ntaps; ++t)
-                {
-                    const int ui = ui0 + p.du[t], vi = vi0 + p.dv[t];
-                    if (ui >= 0 && ui < p.Ui && vi >= 0 && vi < p.Vi)
+                    if ((unsigned)(ui0 + p.du[t]) < (unsigned)p.Ui && (unsigned)(vi0 + p.dv[t]) < (unsigned)p.Vi)
                         rmask[i] |= 1u << t;
-                }
             }
         }
         const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
@@ -751,6 +747,10 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     }
     const int bn = tc_tile_n(p.N);
     const int nout = p.glu ? p.N / 2 : p.N;
+    GemmParams q = p;
+    auto recip = [](int d) { return d <= 1 ? 0ull : ~0ull / (unsigned long long)d + 1ull; };
+    q.div_per = recip(p.Uo * p.Vo);
+    q.div_vo = recip(p.Vo);
     const bool vec = (p.Cin % 4 == 0) && (p.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) &&
                      (!p.A2 || (reinterpret_cast<uintptr_t>(p.A2) & 15) == 0);
     // identity output mapping with 16-byte aligned rows -> the epilogue's fast path
@@ -772,12 +772,12 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     const __nv_bfloat16 *w = static_cast<const __nv_bfloat16 *>(Wb);
     const int nk = (p.K + tc::BK - 1) / tc::BK;
     if (nk == 1)
-        return tc_launch<1>(p, w, bn, vec, plain, st);
+        return tc_launch<1>(q, w, bn, vec, plain, st);
     // wide tiles: two stages keep the CTA under half of the shared memory so two CTAs share an SM (one's
     // epilogue overlaps the other's main loop)
     if (nk == 2 || bn > 128)
-        return tc_launch<2>(p, w, bn, vec, plain, st);
-    return tc_launch<3>(p, w, bn, vec, plain, st);
+        return tc_launch<2>(q, w, bn, vec, plain, st);
+    return tc_launch<3>(q, w, bn, vec, plain, st);
 }
 
 } // namespace dmx
