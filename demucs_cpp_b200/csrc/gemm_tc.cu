@@ -186,8 +186,42 @@ __device__ __forceinline__ void store_group4_scatter(const GemmParams &p, const 
     }
 }
 
+// The same for mappings whose channel groups never straddle a phase (Nco % 4 == 0, aligned rows): one phase
+// decode, one bounds check and one 16-byte store per group.
+__device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, const RowInfo &ri, int nc0, float (&o)[4],
+                                                         float &rs, float &rss)
+{
+    const int r = fast_div(nc0, p.div_nco);
+    const int co = nc0 - r * p.Nco;
+    const int uu = ri.uu0 + r * p.our, vv = ri.vv0 + r * p.ovr;
+    if ((unsigned)uu < (unsigned)p.Uout && (unsigned)vv < (unsigned)p.Vout)
+    {
+        float *dst = p.C + ri.outoff + ((long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.ldc + co;
+        if (p.rowadd)
+        {
+            const float4 ra = __ldg(reinterpret_cast<const float4 *>(p.rowadd + (size_t)ri.uo * p.rowadd_ld + co));
+            o[0] += ra.x;
+            o[1] += ra.y;
+            o[2] += ra.z;
+            o[3] += ra.w;
+        }
+        if (p.gamma)
+        {
+            const float4 g = __ldg(reinterpret_cast<const float4 *>(p.gamma + nc0));
+            const float4 old = *reinterpret_cast<const float4 *>(dst);
+            o[0] = old.x + g.x * o[0];
+            o[1] = old.y + g.y * o[1];
+            o[2] = old.z + g.z * o[2];
+            o[3] = old.w + g.w * o[3];
+        }
+        *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+        rs = o[0] + o[1] + o[2] + o[3];
+        rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
+    }
+}
+
 template <int STAGES, bool VECA>
-__global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
+__global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
                                                           const int bn, const int plain_out)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -522,7 +556,9 @@ __global__ void __launch_bounds__(THREADS) gemm_tc_kernel(const GemmParams p, co
                                 o[e] = gelu_erf(o[e]);
                         }
                     }
-                    if (plain_out && full4)
+                    if (plain_out == 2 && full4)
+                        store_group4_scatter_vec(p, ri, outc, o, rs, rss);
+                    else if (plain_out == 1 && full4)
                     {
                         // identity mapping: output row == GEMM row, 16-byte aligned groups
                         float *dst = p.C + ri.outoff + outc;
@@ -751,6 +787,7 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     auto recip = [](int d) { return d <= 1 ? 0ull : ~0ull / (unsigned long long)d + 1ull; };
     q.div_per = recip(p.Uo * p.Vo);
     q.div_vo = recip(p.Vo);
+    q.div_nco = recip(p.Nco);
     const bool vec = (p.Cin % 4 == 0) && (p.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) &&
                      (!p.A2 || (reinterpret_cast<uintptr_t>(p.A2) & 15) == 0);
     // identity output mapping with 16-byte aligned rows -> the epilogue's fast path
@@ -758,6 +795,12 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
                        p.Uout == p.Uo && p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 &&
                        (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0))
                           ? 1
+                          : 0;
+    // scatter mapping (transposed convolutions) whose 4-column groups stay inside one phase and are 16-byte aligned
+    const int vscat = (!plain && (p.Nco % 4) == 0 && (nout % 4) == 0 && (p.ldc % 4) == 0 &&
+                       (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0) &&
+                       (!p.gamma || (reinterpret_cast<uintptr_t>(p.gamma) & 15) == 0))
+                          ? 2
                           : 0;
     if ((p.out_bf16 || p.out_pack) && (!plain || p.gamma || (nout % 4) || (p.out_pack && (p.ldc % 8))))
     {
@@ -772,12 +815,12 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     const __nv_bfloat16 *w = static_cast<const __nv_bfloat16 *>(Wb);
     const int nk = (p.K + tc::BK - 1) / tc::BK;
     if (nk == 1)
-        return tc_launch<1>(q, w, bn, vec, plain, st);
+        return tc_launch<1>(q, w, bn, vec, plain | vscat, st);
     // wide tiles: two stages keep the CTA under half of the shared memory so two CTAs share an SM (one's
     // epilogue overlaps the other's main loop)
     if (nk == 2 || bn > 128)
-        return tc_launch<2>(q, w, bn, vec, plain, st);
-    return tc_launch<3>(q, w, bn, vec, plain, st);
+        return tc_launch<2>(q, w, bn, vec, plain | vscat, st);
+    return tc_launch<3>(q, w, bn, vec, plain | vscat, st);
 }
 
 } // namespace dmx

@@ -55,8 +55,8 @@ struct GemmParams
     float *C = nullptr;
     int ldc = 0, Nco = 0;
     int Uout = 1, Vout = 1, ous = 1, our = 0, ouo = 0, ovs = 1, ovr = 0, ovo = 0;
-    // filled in by launch_gemm_tc: reciprocals for fast_div by Uo*Vo and by Vo (row -> (b, u_o, v_o))
-    unsigned long long div_per = 0, div_vo = 0;
+    // filled in by launch_gemm_tc: reciprocals for fast_div by Uo*Vo, Vo (row -> (b, u_o, v_o)) and Nco
+    unsigned long long div_per = 0, div_vo = 0, div_nco = 0;
 };
 
 int launch_gemm(const GemmParams &p, cudaStream_t st);
