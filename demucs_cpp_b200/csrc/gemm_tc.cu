@@ -14,9 +14,20 @@
 //     residual / GroupNorm statistics / transposed-conv scatter, fp32 stores.
 //
 // Tile: 128 rows x BN columns (BN = N rounded to 16, <= 256, chosen per layer), BK = 64.
+//
+// HALO mode (stride-1 convolutions with >= 3 taps: the 3x3 / k3 decoder rewrites and the dilated k3 convs of the
+// DConv branches): a tile is 128 consecutive positions v of ONE (item, u) line, and the producers stage the
+// input patch -- (u taps) planes x (128 + v-tap span) rows x Cin channels -- ONCE, as bf16 in the canonical
+// layout [plane][Cin/8][row][8].  Every tap's A operand is then just a descriptor into that patch (plane
+// selects du, a 16-byte start-address shift per row selects dv), so each input row crosses L2 -> SM once per
+// tile instead of once per tap (the gather of the 3x3 rewrite ran at the L2 bandwidth limit: 6 GB for a 0.5 GB
+// tensor).  Only the weights still stream through the k-block ring.
 #include "kernels.cuh"
 
 #include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cstdlib>
 
 namespace dmx
 {
@@ -220,7 +231,7 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
     }
 }
 
-template <int STAGES, bool VECA>
+template <int STAGES, bool VECA, bool HALO>
 __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
                                                           const int bn, const int plain_out)
 {
@@ -228,6 +239,7 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
     __shared__ __align__(8) uint64_t full_bar[STAGES];
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ __align__(8) uint64_t a_full_bar; // HALO: the whole patch is staged
     __shared__ uint32_t tmem_slot;
     __shared__ RowInfo rowinfo[BM];
     __shared__ float2 rowstat[BM]; // (mean, rstd) of the GroupNorm prologue per row
@@ -239,8 +251,20 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
     const int n0 = ntile * bn;
     const int nk = (p.K + BK - 1) / BK;
     const uint32_t b_stage_bytes = (uint32_t)bn * BK * 2;
-    uint8_t *a_smem = smem;                       // STAGES x A_STAGE
-    uint8_t *b_smem = smem + STAGES * A_STAGE;     // STAGES x bn*128 B
+    // HALO: tile -> (item hb, line hu, first position hv0); the patch replaces the A ring
+    int hb = 0, hu = 0, hv0 = 0;
+    const int c8n = p.Cin >> 3;
+    const uint32_t h_lbo = (uint32_t)(p.halo_rows | 1) * 16; // odd row count: conflict-free 16-byte producer stores
+    if (HALO)
+    {
+        const int bu = fast_div((int)blockIdx.x, p.div_tpr);
+        hv0 = ((int)blockIdx.x - bu * p.halo_tpr) * BM;
+        hb = fast_div(bu, p.div_uo);
+        hu = bu - hb * p.Uo;
+    }
+    const uint32_t a_bytes = HALO ? (((uint32_t)p.halo_nu * c8n * h_lbo + 127u) & ~127u) : (uint32_t)(STAGES * A_STAGE);
+    uint8_t *a_smem = smem;                       // STAGES x A_STAGE, or the HALO patch
+    uint8_t *b_smem = smem + a_bytes;              // STAGES x bn*128 B
     uint32_t tmem_cols = 32;
     while ((int)tmem_cols < bn)
         tmem_cols <<= 1;
@@ -249,17 +273,28 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
     {
         for (int s = 0; s < STAGES; ++s)
         {
-            mbar_init(&full_bar[s], p.Apk ? 1u : (uint32_t)(PROD_THREADS + 1));
+            mbar_init(&full_bar[s], (p.Apk || HALO) ? 1u : (uint32_t)(PROD_THREADS + 1));
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&tmem_full_bar, 1);
+        mbar_init(&a_full_bar, PROD_THREADS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (tid < BM)
     {
-        const int m = m0 + tid;
-        const bool valid = m < p.M;
-        const RowCoord rc = decode_row(valid ? m : 0, p);
+        int m = m0 + tid;
+        bool valid = m < p.M;
+        RowCoord rc;
+        if (HALO)
+        {
+            valid = hv0 + tid < p.Vo;
+            rc.b = hb;
+            rc.uo = hu;
+            rc.vo = valid ? hv0 + tid : 0;
+            m = (hb * p.Uo + hu) * p.Vo + rc.vo;
+        }
+        else
+            rc = decode_row(valid ? m : 0, p);
         RowInfo ri;
         ri.uu0 = rc.uo * p.ous + p.ouo;
         ri.vv0 = rc.vo * p.ovs + p.ovo;
@@ -298,6 +333,81 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         // 16-byte bf16 stores hit 8 distinct bank groups thanks to the padded LBO.  Per row the thread
         // keeps a base pointer and a bit mask of the taps that fall inside the input grid, so the inner
         // loop is: tap offset (once per k-block), predicated 16-byte loads, 4 cvt, one 16-byte store.
+        if (HALO)
+        {
+            // unit = (patch row, 8-channel chunk), chunk fastest: consecutive lanes read consecutive 32-byte pieces of
+            // the channels-last input (a whole plane of the patch is one contiguous span of memory)
+            const int rows = p.halo_rows;
+            const int total = p.halo_nu * rows * c8n;
+            const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
+            for (int u0 = tid; u0 < total; u0 += 4 * PROD_THREADS)
+            {
+                float4 lo[4], hi[4];
+                int dsto[4];
+                const float *src[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                {
+                    const int u = u0 + i * PROD_THREADS;
+                    dsto[i] = -1;
+                    src[i] = nullptr;
+                    if (u < total)
+                    {
+                        const int prow = fast_div(u, p.div_c8);
+                        const int kcc = u - prow * c8n;
+                        const int plane = fast_div(prow, p.div_rows);
+                        const int r = prow - plane * rows;
+                        const int ui = hu + p.halo_dumin + plane, vi = hv0 + p.halo_dvmin + r;
+                        dsto[i] = (plane * c8n + kcc) * (int)h_lbo + r * 16;
+                        if ((unsigned)ui < (unsigned)p.Ui && (unsigned)vi < (unsigned)p.Vi)
+                            src[i] = p.A + (((long long)hb * p.Ui + ui) * p.Vi + vi) * p.lda + kcc * 8;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                {
+                    lo[i] = hi[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (src[i])
+                    {
+                        lo[i] = __ldg(reinterpret_cast<const float4 *>(src[i]));
+                        hi[i] = __ldg(reinterpret_cast<const float4 *>(src[i] + 4));
+                    }
+                }
+                if (p.A2)
+                {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (src[i])
+                        {
+                            const float4 t0 = __ldg(reinterpret_cast<const float4 *>(src[i] + a2d));
+                            const float4 t1 = __ldg(reinterpret_cast<const float4 *>(src[i] + a2d + 4));
+                            lo[i].x += t0.x;
+                            lo[i].y += t0.y;
+                            lo[i].z += t0.z;
+                            lo[i].w += t0.w;
+                            hi[i].x += t1.x;
+                            hi[i].y += t1.y;
+                            hi[i].z += t1.z;
+                            hi[i].w += t1.w;
+                        }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (dsto[i] >= 0)
+                    {
+                        uint4 pk;
+                        pk.x = pack_bf16x2(lo[i].x, lo[i].y);
+                        pk.y = pack_bf16x2(lo[i].z, lo[i].w);
+                        pk.z = pack_bf16x2(hi[i].x, hi[i].y);
+                        pk.w = pack_bf16x2(hi[i].z, hi[i].w);
+                        *reinterpret_cast<uint4 *>(a_smem + dsto[i]) = pk;
+                    }
+            }
+            fence_proxy_async();
+            mbar_arrive(&a_full_bar);
+        }
+        else
+        {
         const int kc = tid & 7;
         const int r0 = tid >> 3;
         const float *rp[4];
@@ -457,6 +567,8 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
             fence_proxy_async(); // make the generic-proxy stores visible to the tensor core's async proxy
             mbar_arrive(&full_bar[s]);
         }
+
+        } // !HALO
 
         // ================= epilogue =================
         // Warps w and w+4 share TMEM lanes / tile rows 32*(w%4)..+31 and alternate over the 32-column
@@ -686,14 +798,39 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
                 const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
-                const uint32_t a_base = smem_u32(a_smem + s * A_STAGE);
+                const uint32_t a_base = smem_u32(a_smem + (HALO ? 0 : s * A_STAGE));
                 const uint32_t b_base = smem_u32(b_smem + (size_t)s * b_stage_bytes);
-#pragma unroll
-                for (int j = 0; j < BK / 16; ++j)
+                if (HALO)
                 {
-                    const uint64_t ad = make_desc(a_base + j * 2 * a_lbo, a_lbo, sbo);
-                    const uint64_t bd = make_desc(b_base + j * 2 * b_lbo, b_lbo, sbo);
-                    umma(tmem_base, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+                    if (kb == 0)
+                    {
+                        mbar_wait(&a_full_bar, 0);
+                        tc_fence_after();
+                    }
+                    // k = tap*Cin + c, Cin % 16 == 0: a 16-wide k step lies inside one tap; its A operand is the patch
+                    // plane of that tap's du, chunks c/8 and c/8+1, rows shifted by the tap's dv
+                    for (int j = 0; j < BK / 16; ++j)
+                    {
+                        const int k = kb * BK + j * 16;
+                        if (k >= p.K)
+                            break;
+                        const int tap = k / p.Cin, c = k - tap * p.Cin;
+                        const uint32_t aoff = (uint32_t)((p.du[tap] - p.halo_dumin) * c8n + (c >> 3)) * h_lbo +
+                                              (uint32_t)(p.dv[tap] - p.halo_dvmin) * 16u;
+                        const uint64_t ad = make_desc(a_base + aoff, h_lbo, sbo);
+                        const uint64_t bd = make_desc(b_base + j * 2 * b_lbo, b_lbo, sbo);
+                        umma(tmem_base, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+                    }
+                }
+                else
+                {
+#pragma unroll
+                    for (int j = 0; j < BK / 16; ++j)
+                    {
+                        const uint64_t ad = make_desc(a_base + j * 2 * a_lbo, a_lbo, sbo);
+                        const uint64_t bd = make_desc(b_base + j * 2 * b_lbo, b_lbo, sbo);
+                        umma(tmem_base, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+                    }
                 }
                 umma_commit(&empty_bar[s]); // frees the stage once these MMAs have read it
             }
@@ -742,8 +879,10 @@ size_t tc_packed_index(int K, int N, int k, int n)
 template <int STAGES> static int tc_set_attr()
 {
     const int max_smem = 227 * 1024 - 8 * 1024;
-    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    if (STAGES == 3)
+        DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<3, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     return 0;
 }
 
@@ -757,9 +896,9 @@ static int tc_launch(const GemmParams &p, const __nv_bfloat16 *w, int bn, bool v
     if (smem < tc::EPI_BYTES)
         smem = tc::EPI_BYTES; // the epilogue stages its transposition in the pipeline buffers
     if (vec)
-        tc::gemm_tc_kernel<STAGES, true><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
+        tc::gemm_tc_kernel<STAGES, true, false><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
     else
-        tc::gemm_tc_kernel<STAGES, false><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
+        tc::gemm_tc_kernel<STAGES, false, false><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -814,6 +953,40 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     }
     const __nv_bfloat16 *w = static_cast<const __nv_bfloat16 *>(Wb);
     const int nk = (p.K + tc::BK - 1) / tc::BK;
+    // ---- halo mode: same-size stride-1 convolution with >= 3 taps whose input patch fits beside the weight ring ----
+    if (vec && !p.Apk && p.pro == 0 && p.ntaps >= 3 && p.su == 1 && p.sv == 1 && p.Ui == p.Uo && p.Vi == p.Vo &&
+        (p.Cin % 16) == 0 && p.K == p.ntaps * p.Cin && p.lda == p.Cin && !getenv("DMX_NO_HALO"))
+    {
+        int dumin = p.du[0], dumax = p.du[0], dvmin = p.dv[0], dvmax = p.dv[0];
+        for (int t = 1; t < p.ntaps; ++t)
+        {
+            dumin = std::min(dumin, p.du[t]);
+            dumax = std::max(dumax, p.du[t]);
+            dvmin = std::min(dvmin, p.dv[t]);
+            dvmax = std::max(dvmax, p.dv[t]);
+        }
+        const int nu = dumax - dumin + 1, rows = tc::BM + dvmax - dvmin;
+        const size_t patch = (((size_t)nu * (p.Cin / 8) * ((rows | 1) * 16)) + 127) & ~(size_t)127;
+        const size_t total = patch + 3 * (size_t)bn * tc::BK * 2;
+        if (nu <= 3 && dvmax - dvmin <= 16 && total <= 112 * 1024)
+        {
+            q.halo_nu = nu;
+            q.halo_dumin = dumin;
+            q.halo_dvmin = dvmin;
+            q.halo_rows = rows;
+            q.halo_tpr = (p.Vo + tc::BM - 1) / tc::BM;
+            q.div_tpr = recip(q.halo_tpr);
+            q.div_uo = recip(p.Uo);
+            q.div_c8 = recip(p.Cin / 8);
+            q.div_rows = recip(rows);
+            const int items = p.M / (p.Uo * p.Vo);
+            dim3 grid(items * p.Uo * q.halo_tpr, (p.N + bn - 1) / bn);
+            const int smem = (int)std::max(total, (size_t)tc::EPI_BYTES);
+            tc::gemm_tc_kernel<3, true, true><<<grid, tc::THREADS, smem, st>>>(q, w, bn, plain | vscat);
+            DMX_LAUNCH_CHECK();
+            return 0;
+        }
+    }
     if (nk == 1)
         return tc_launch<1>(q, w, bn, vec, plain | vscat, st);
     // wide tiles: two stages keep the CTA under half of the shared memory so two CTAs share an SM (one's
