@@ -3,6 +3,7 @@
 
 #include <cstdio>
 #include <cstring>
+#include <vector>
 #include <cuda_fp16.h>
 
 namespace dmx
@@ -506,6 +507,17 @@ int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capaci
     {
         set_error("dmx_debug_tap: copy failed");
         return -1;
+    }
+    if (t.minus)
+    {
+        std::vector<float> sk((size_t)n);
+        if (cudaMemcpy(sk.data(), t.minus, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+        {
+            set_error("dmx_debug_tap: copy failed");
+            return -1;
+        }
+        for (int64_t i = 0; i < n; ++i)
+            dst[i] -= sk[(size_t)i];
     }
     return n;
 }

@@ -307,6 +307,14 @@ __global__ void __launch_bounds__(G_THREADS) gemm_kernel(const GemmParams p)
                                 if (e < gs)
                                     o[e] += __ldg(radd + e);
                         }
+                        if (p.addC)
+                        {
+                            const float *ad = p.addC + (dst - p.C);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e)
+                                if (e < gs)
+                                    o[e] += __ldg(ad + e);
+                        }
                         const bool al16 = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
                         const bool al8 = (reinterpret_cast<uintptr_t>(dst) & 7) == 0;
                         if (gs == 4 && al16)
@@ -369,6 +377,8 @@ __global__ void __launch_bounds__(G_THREADS) gemm_kernel(const GemmParams p)
                                 float o = val[j0 + e];
                                 if (p.rowadd)
                                     o += __ldg(p.rowadd + (size_t)rc.uo * p.rowadd_ld + co);
+                                if (p.addC)
+                                    o += __ldg(p.addC + (dst - p.C));
                                 if (p.gamma)
                                     o = *dst + gam[j0 + e] * o;
                                 *dst = o;

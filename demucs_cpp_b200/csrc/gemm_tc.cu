@@ -187,6 +187,8 @@ __device__ __forceinline__ void store_group4_scatter(const GemmParams &p, const 
                 float v = o[e];
                 if (p.rowadd)
                     v += __ldg(p.rowadd + (size_t)ri.uo * p.rowadd_ld + co);
+                if (p.addC)
+                    v += __ldg(p.addC + (dst - p.C));
                 if (p.gamma)
                     v = *dst + __ldg(p.gamma + nc) * v;
                 *dst = v;
@@ -215,6 +217,14 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
             o[1] += ra.y;
             o[2] += ra.z;
             o[3] += ra.w;
+        }
+        if (p.addC)
+        {
+            const float4 ad = __ldg(reinterpret_cast<const float4 *>(p.addC + (dst - p.C)));
+            o[0] += ad.x;
+            o[1] += ad.y;
+            o[2] += ad.z;
+            o[3] += ad.w;
         }
         if (p.gamma)
         {
@@ -630,6 +640,18 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
             const bool full4 = outc + 4 <= nlimit;
             if (p.gamma && full4)
                 gam = __ldg(reinterpret_cast<const float4 *>(p.gamma + outc));
+            // Residual / skip operands of the identity mapping: pull all of this lane's rows towards L1 first, so the
+            // loop below does not expose one full memory latency per row (load -> fma -> store chains).
+            const float *pre_src = p.gamma ? p.C : p.addC;
+            if (plain_out == 1 && full4 && pre_src != nullptr)
+            {
+                for (int it = 0; it < gpr; ++it)
+                {
+                    const RowInfo &ri = rowinfo[q * 32 + it * rows_per_it + rsub];
+                    if (ri.item >= 0)
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(pre_src + ri.outoff + outc));
+                }
+            }
             for (int it = 0; it < gpr; ++it)
             {
                 const int rl = it * rows_per_it + rsub;
@@ -681,6 +703,14 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
                             o[1] += ra.y;
                             o[2] += ra.z;
                             o[3] += ra.w;
+                        }
+                        if (p.addC)
+                        {
+                            const float4 ad = *reinterpret_cast<const float4 *>(p.addC + ri.outoff + outc);
+                            o[0] += ad.x;
+                            o[1] += ad.y;
+                            o[2] += ad.z;
+                            o[3] += ad.w;
                         }
                         if (p.gamma)
                         {
@@ -881,8 +911,8 @@ template <int STAGES> static int tc_set_attr()
     const int max_smem = 227 * 1024 - 8 * 1024;
     DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<STAGES, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-    if (STAGES == 3)
-        DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<3, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    if (STAGES == 2)
+        DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
     return 0;
 }
 
@@ -932,16 +962,18 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     // identity output mapping with 16-byte aligned rows -> the epilogue's fast path
     const int plain = (p.ous == 1 && p.ovs == 1 && p.our == 0 && p.ovr == 0 && p.ouo == 0 && p.ovo == 0 &&
                        p.Uout == p.Uo && p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 &&
-                       (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0))
+                       (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0) &&
+                       (!p.addC || (reinterpret_cast<uintptr_t>(p.addC) & 15) == 0))
                           ? 1
                           : 0;
     // scatter mapping (transposed convolutions) whose 4-column groups stay inside one phase and are 16-byte aligned
     const int vscat = (!plain && (p.Nco % 4) == 0 && (nout % 4) == 0 && (p.ldc % 4) == 0 &&
                        (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0) &&
-                       (!p.gamma || (reinterpret_cast<uintptr_t>(p.gamma) & 15) == 0))
+                       (!p.gamma || (reinterpret_cast<uintptr_t>(p.gamma) & 15) == 0) &&
+                       (!p.addC || (reinterpret_cast<uintptr_t>(p.addC) & 15) == 0))
                           ? 2
                           : 0;
-    if ((p.out_bf16 || p.out_pack) && (!plain || p.gamma || (nout % 4) || (p.out_pack && (p.ldc % 8))))
+    if ((p.out_bf16 || p.out_pack) && (!plain || p.gamma || p.addC || (nout % 4) || (p.out_pack && (p.ldc % 8))))
     {
         set_error("launch_gemm_tc: bf16 / packed output needs the identity mapping, no residual and N % 4 == 0");
         return -1;
@@ -955,7 +987,7 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     const int nk = (p.K + tc::BK - 1) / tc::BK;
     // ---- halo mode: same-size stride-1 convolution with >= 3 taps whose input patch fits beside the weight ring ----
     if (vec && !p.Apk && p.pro == 0 && p.ntaps >= 3 && p.su == 1 && p.sv == 1 && p.Ui == p.Uo && p.Vi == p.Vo &&
-        (p.Cin % 16) == 0 && p.K == p.ntaps * p.Cin && p.lda == p.Cin && !getenv("DMX_NO_HALO"))
+        (p.Cin % 16) == 0 && p.K == p.ntaps * p.Cin && p.lda == p.Cin)
     {
         int dumin = p.du[0], dumax = p.du[0], dvmin = p.dv[0], dvmax = p.dv[0];
         for (int t = 1; t < p.ntaps; ++t)
@@ -967,7 +999,7 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
         }
         const int nu = dumax - dumin + 1, rows = tc::BM + dvmax - dvmin;
         const size_t patch = (((size_t)nu * (p.Cin / 8) * ((rows | 1) * 16)) + 127) & ~(size_t)127;
-        const size_t total = patch + 3 * (size_t)bn * tc::BK * 2;
+        const size_t total = patch + 2 * (size_t)bn * tc::BK * 2; // two weight stages: three CTAs share an SM
         if (nu <= 3 && dvmax - dvmin <= 16 && total <= 112 * 1024)
         {
             q.halo_nu = nu;
@@ -982,7 +1014,7 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
             const int items = p.M / (p.Uo * p.Vo);
             dim3 grid(items * p.Uo * q.halo_tpr, (p.N + bn - 1) / bn);
             const int smem = (int)std::max(total, (size_t)tc::EPI_BYTES);
-            tc::gemm_tc_kernel<3, true, true><<<grid, tc::THREADS, smem, st>>>(q, w, bn, plain | vscat);
+            tc::gemm_tc_kernel<2, true, true><<<grid, tc::THREADS, smem, st>>>(q, w, bn, plain | vscat);
             DMX_LAUNCH_CHECK();
             return 0;
         }

@@ -45,6 +45,8 @@ struct GemmParams
     const float *rowadd = nullptr; // out += rowadd[u_o*rowadd_ld + co]   (frequency embedding)
     int rowadd_ld = 0;
     const float *gamma = nullptr;  // out = C_old + gamma[n]*val           (LayerScale residual)
+    const float *addC = nullptr;   // out += addC[same element as C]  (the NEXT decoder's skip, src/encdec.cpp:172, added
+                                   // once here instead of in every tap of that decoder's 3x3 / k3 gather)
     double *stats = nullptr;       // accumulate (sum, sumsq) of the stored values per item
     int stat_per_u = 0;
     int out_bf16 = 0;              // tensor-core kernel only, identity mapping only: C holds bf16 (ldc in elements)

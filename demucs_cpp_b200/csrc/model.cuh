@@ -119,6 +119,7 @@ struct Tap
 {
     float *ptr = nullptr;
     int64_t d1 = 0, d2 = 0, C = 0; // per batch item dims (channels-last)
+    const float *minus = nullptr;   // the buffer holds value + minus (a pre-added decoder skip): the tap reports value
 };
 
 } // namespace dmx

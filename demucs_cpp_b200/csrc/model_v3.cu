@@ -542,7 +542,8 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         const int C = fd.C, F = FREQS[4 - i], Lin = TLENS[4 - i], Lout = TLENS[3 - i];
         {
             GemmParams p = f.base(dec_in_f, C, C, fd.rewrite, m->cA_f, C, F, T, F, T);
-            p.A2 = m->e[3 - i];
+            if (i == 0)
+                p.A2 = m->e[3]; // later decoders find their skip already added by the previous convT's epilogue
             p.ntaps = 9;
             for (int kh = 0; kh < 3; ++kh)
                 for (int kw = 0; kw < 3; ++kw)
@@ -564,11 +565,14 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.our = 1;
             q.ouo = -2;
             q.act = i < 3 ? 1 : 0;
+            if (i < 3)
+                q.addC = m->e[2 - i]; // the next decoder's skip (src/encdec.cpp:172), added once here
             f.gemm(q, PC_GEMM_CONV);
         }
         {
             GemmParams p = f.base(dec_in_t, C, C, td.rewrite, m->cA_t, C, 1, Lin, 1, Lin);
-            p.A2 = m->te[3 - i];
+            if (i == 0)
+                p.A2 = m->te[3];
             p.ntaps = 3;
             for (int t = 0; t < 3; ++t)
             {
@@ -590,6 +594,8 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.ovr = 1;
             q.ovo = -2;
             q.act = i < 3 ? 1 : 0;
+            if (i < 3)
+                q.addC = m->te[2 - i];
             f.gemm(q, PC_GEMM_CONV);
         }
         dec_in_f = m->dx[i];
@@ -622,8 +628,8 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     const char *tn[4] = {"xt_2", "xt_1", "xt_0", "xt_out"};
     for (int i = 0; i < 4; ++i)
     {
-        set_tap(m, fn[i], m->dx[i], FREQS[3 - i], T, v->cdec[i].Cout);
-        set_tap(m, tn[i], m->dxt[i], 1, TLENS[3 - i], v->ctdec[i].Cout);
+        set_tap(m, fn[i], m->dx[i], FREQS[3 - i], T, v->cdec[i].Cout, i < 3 ? m->e[2 - i] : nullptr);
+        set_tap(m, tn[i], m->dxt[i], 1, TLENS[3 - i], v->ctdec[i].Cout, i < 3 ? m->te[2 - i] : nullptr);
     }
     return 0;
 }
