@@ -241,6 +241,442 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
     }
 }
 
+// HALO mode: stage the input patch of tile (item hb, line hu, first position hv0) as bf16 into a_smem.
+// unit = (patch row, 8-channel chunk), chunk fastest: consecutive lanes read consecutive 32-byte pieces of the
+// channels-last input (a whole plane of the patch is one contiguous span of memory).
+__device__ __forceinline__ void halo_stage_patch(const GemmParams &p, const int tid, const int c8n, const uint32_t h_lbo,
+                                                 const int hb, const int hu, const int hv0, uint8_t *a_smem)
+{
+    const int rows = p.halo_rows;
+    const int total = p.halo_nu * rows * c8n;
+    const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
+    for (int u0 = tid; u0 < total; u0 += 4 * PROD_THREADS)
+    {
+        float4 lo[4], hi[4];
+        int dsto[4];
+        const float *src[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            const int u = u0 + i * PROD_THREADS;
+            dsto[i] = -1;
+            src[i] = nullptr;
+            if (u < total)
+            {
+                const int prow = fast_div(u, p.div_c8);
+                const int kcc = u - prow * c8n;
+                const int plane = fast_div(prow, p.div_rows);
+                const int r = prow - plane * rows;
+                const int ui = hu + p.halo_dumin + plane, vi = hv0 + p.halo_dvmin + r;
+                dsto[i] = (plane * c8n + kcc) * (int)h_lbo + r * 16;
+                if ((unsigned)ui < (unsigned)p.Ui && (unsigned)vi < (unsigned)p.Vi)
+                    src[i] = p.A + (((long long)hb * p.Ui + ui) * p.Vi + vi) * p.lda + kcc * 8;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            lo[i] = hi[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (src[i])
+            {
+                lo[i] = __ldg(reinterpret_cast<const float4 *>(src[i]));
+                hi[i] = __ldg(reinterpret_cast<const float4 *>(src[i] + 4));
+            }
+        }
+        if (p.A2)
+        {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (src[i])
+                {
+                    const float4 t0 = __ldg(reinterpret_cast<const float4 *>(src[i] + a2d));
+                    const float4 t1 = __ldg(reinterpret_cast<const float4 *>(src[i] + a2d + 4));
+                    lo[i].x += t0.x;
+                    lo[i].y += t0.y;
+                    lo[i].z += t0.z;
+                    lo[i].w += t0.w;
+                    hi[i].x += t1.x;
+                    hi[i].y += t1.y;
+                    hi[i].z += t1.z;
+                    hi[i].w += t1.w;
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (dsto[i] >= 0)
+            {
+                uint4 pk;
+                pk.x = pack_bf16x2(lo[i].x, lo[i].y);
+                pk.y = pack_bf16x2(lo[i].z, lo[i].w);
+                pk.z = pack_bf16x2(hi[i].x, hi[i].y);
+                pk.w = pack_bf16x2(hi[i].z, hi[i].w);
+                *reinterpret_cast<uint4 *>(a_smem + dsto[i]) = pk;
+            }
+    }
+}
+
+// Gather bookkeeping of a producer thread: base pointer and valid-tap mask of its four tile rows r0 + 32 i.
+__device__ __forceinline__ void producer_rows(const GemmParams &p, const int m0, const int r0, const float *(&rp)[4],
+                                              uint32_t (&rmask)[4])
+{
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+    {
+        const int m = m0 + r0 + 32 * i;
+        rmask[i] = 0;
+        rp[i] = p.A;
+        if (m < p.M)
+        {
+            const RowCoord rc = decode_row(m, p);
+            const int ui0 = rc.uo * p.su, vi0 = rc.vo * p.sv;
+            rp[i] = p.A + (((long long)rc.b * p.Ui + ui0) * p.Vi + vi0) * p.lda;
+            for (int t = 0; t < p.ntaps; ++t)
+                if ((unsigned)(ui0 + p.du[t]) < (unsigned)p.Ui && (unsigned)(vi0 + p.dv[t]) < (unsigned)p.Vi)
+                    rmask[i] |= 1u << t;
+        }
+    }
+}
+
+// One k-block of the A operand for a producer thread: chunk column k..k+7 of its four rows, with the tap /
+// zero-padding predicates, the skip add and the GroupNorm+GELU prologue applied in registers, as packed bf16.
+template <bool VECA>
+__device__ __forceinline__ void gather_kblock(const GemmParams &p, const int k, const int r0, const float *const (&rp)[4],
+                                              const uint32_t (&rmask)[4], const long long a2d, const float2 *rowstat,
+                                              uint4 (&pk)[4])
+{
+    if (VECA)
+    {
+        const bool h0 = k < p.K, h1 = k + 4 < p.K;
+        int tap0 = 0, tap1 = 0, c0 = 0, c1 = 0;
+        long long toff0 = 0, toff1 = 0;
+        if (h0)
+        {
+            tap0 = k / p.Cin;
+            c0 = k - tap0 * p.Cin;
+            toff0 = ((long long)p.du[tap0] * p.Vi + p.dv[tap0]) * p.lda + c0;
+        }
+        if (h1)
+        {
+            tap1 = (k + 4) / p.Cin;
+            c1 = (k + 4) - tap1 * p.Cin;
+            toff1 = ((long long)p.du[tap1] * p.Vi + p.dv[tap1]) * p.lda + c1;
+        }
+        float4 lo[4], hi[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            const bool v0 = h0 && ((rmask[i] >> tap0) & 1u), v1 = h1 && ((rmask[i] >> tap1) & 1u);
+            lo[i] = v0 ? __ldg(reinterpret_cast<const float4 *>(rp[i] + toff0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            hi[i] = v1 ? __ldg(reinterpret_cast<const float4 *>(rp[i] + toff1)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (p.A2)
+        {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+            {
+                const bool v0 = h0 && ((rmask[i] >> tap0) & 1u), v1 = h1 && ((rmask[i] >> tap1) & 1u);
+                if (v0)
+                {
+                    const float4 t = __ldg(reinterpret_cast<const float4 *>(rp[i] + a2d + toff0));
+                    lo[i].x += t.x;
+                    lo[i].y += t.y;
+                    lo[i].z += t.z;
+                    lo[i].w += t.w;
+                }
+                if (v1)
+                {
+                    const float4 t = __ldg(reinterpret_cast<const float4 *>(rp[i] + a2d + toff1));
+                    hi[i].x += t.x;
+                    hi[i].y += t.y;
+                    hi[i].z += t.z;
+                    hi[i].w += t.w;
+                }
+            }
+        }
+        if (p.pro == 1)
+        {
+            float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), b0 = w0, w1 = w0, b1 = w0;
+            if (h0)
+            {
+                w0 = __ldg(reinterpret_cast<const float4 *>(p.pro_w + c0));
+                b0 = __ldg(reinterpret_cast<const float4 *>(p.pro_b + c0));
+            }
+            if (h1)
+            {
+                w1 = __ldg(reinterpret_cast<const float4 *>(p.pro_w + c1));
+                b1 = __ldg(reinterpret_cast<const float4 *>(p.pro_b + c1));
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+            {
+                const float2 ms = rowstat[r0 + 32 * i];
+                if (h0 && ((rmask[i] >> tap0) & 1u))
+                {
+                    lo[i].x = gelu_erf((lo[i].x - ms.x) * ms.y * w0.x + b0.x);
+                    lo[i].y = gelu_erf((lo[i].y - ms.x) * ms.y * w0.y + b0.y);
+                    lo[i].z = gelu_erf((lo[i].z - ms.x) * ms.y * w0.z + b0.z);
+                    lo[i].w = gelu_erf((lo[i].w - ms.x) * ms.y * w0.w + b0.w);
+                }
+                if (h1 && ((rmask[i] >> tap1) & 1u))
+                {
+                    hi[i].x = gelu_erf((hi[i].x - ms.x) * ms.y * w1.x + b1.x);
+                    hi[i].y = gelu_erf((hi[i].y - ms.x) * ms.y * w1.y + b1.y);
+                    hi[i].z = gelu_erf((hi[i].z - ms.x) * ms.y * w1.z + b1.z);
+                    hi[i].w = gelu_erf((hi[i].w - ms.x) * ms.y * w1.w + b1.w);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            pk[i].x = pack_bf16x2(lo[i].x, lo[i].y);
+            pk[i].y = pack_bf16x2(lo[i].z, lo[i].w);
+            pk[i].z = pack_bf16x2(hi[i].x, hi[i].y);
+            pk[i].w = pack_bf16x2(hi[i].z, hi[i].w);
+        }
+    }
+    else
+    {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            const float2 ms = rowstat[r0 + 32 * i];
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+            {
+                const int ke = k + e;
+                if (ke < p.K)
+                {
+                    const int tap = ke / p.Cin;
+                    const int c = ke - tap * p.Cin;
+                    if ((rmask[i] >> tap) & 1u)
+                    {
+                        const long long off = ((long long)p.du[tap] * p.Vi + p.dv[tap]) * p.lda + c;
+                        float t = __ldg(rp[i] + off);
+                        if (p.A2)
+                            t += __ldg(rp[i] + a2d + off);
+                        if (p.pro == 1)
+                            t = gelu_erf((t - ms.x) * ms.y * __ldg(&p.pro_w[c]) + __ldg(&p.pro_b[c]));
+                        v[e] = t;
+                    }
+                }
+            }
+            pk[i].x = pack_bf16x2(v[0], v[1]);
+            pk[i].y = pack_bf16x2(v[2], v[3]);
+            pk[i].z = pack_bf16x2(v[4], v[5]);
+            pk[i].w = pack_bf16x2(v[6], v[7]);
+        }
+    }
+}
+
+// Epilogue of one 128 x bn tile for the TMEM lane quadrant q (tile rows 32q..32q+31), column chunks c_begin,
+// c_begin + c_step, ...  Per 32-column chunk each lane pulls its own row's raw accumulators from TMEM and stages
+// them in shared memory (stage: this warp's private 32 x EPI_LD floats); the warp then re-reads them transposed so
+// that 8 lanes write 128 contiguous bytes of one output row: coalesced stores / residual reads.  Bias, GELU, GLU,
+// row-add, skip add, LayerScale residual and the statistics are applied on the transposed side.
+__device__ __forceinline__ void epilogue_tile(const GemmParams &p, const int bn, const int plain_out, const int n0,
+                                              const uint32_t lane_addr, const RowInfo *rowinfo, float *stage, const int q,
+                                              const int c_begin, const int c_step, const int lane)
+{
+    const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N; // never beyond N nor into the next column tile
+    const int nlimit = p.glu ? (ntile_end >> 1) : ntile_end;   // valid OUTPUT columns
+    const int gpr = p.glu ? 4 : 8;                             // 4-column output groups per row per chunk
+    const int rows_per_it = 32 / gpr;
+    const int g = lane % gpr, rsub = lane / gpr;
+    int cur_item = -1;
+    double st_s = 0.0, st_ss = 0.0;
+    for (int c0 = c_begin; c0 < bn; c0 += c_step)
+    {
+        float val[32];
+        tmem_ld16(lane_addr + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&val[0]));
+        if (c0 + 16 < bn)
+            tmem_ld16(lane_addr + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&val[16]));
+        else
+        {
+#pragma unroll
+            for (int j = 16; j < 32; ++j)
+                val[j] = 0.f;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4 *>(&stage[lane * EPI_LD + j]) = make_float4(val[j], val[j + 1], val[j + 2], val[j + 3]);
+        __syncwarp();
+        const int nbase = n0 + c0;                          // first RAW column of the chunk
+        // this lane's raw columns: plain 4g..4g+3, GLU 8g..8g+7 (-> outputs 4g..4g+3)
+        const int rawc = nbase + (p.glu ? 8 * g : 4 * g);
+        const int outc = (p.glu ? (nbase >> 1) : nbase) + 4 * g;
+        float bias[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (p.bias)
+        {
+            const float4 b0 = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc)); // zero padded to ldw
+            bias[0] = b0.x;
+            bias[1] = b0.y;
+            bias[2] = b0.z;
+            bias[3] = b0.w;
+            if (p.glu)
+            {
+                const float4 b1 = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc + 4));
+                bias[4] = b1.x;
+                bias[5] = b1.y;
+                bias[6] = b1.z;
+                bias[7] = b1.w;
+            }
+        }
+        float4 gam = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool full4 = outc + 4 <= nlimit;
+        if (p.gamma && full4)
+            gam = __ldg(reinterpret_cast<const float4 *>(p.gamma + outc));
+        // Residual / skip operands of the identity mapping: pull all of this lane's rows towards L1 first, so the
+        // loop below does not expose one full memory latency per row (load -> fma -> store chains).
+        const float *pre_src = p.gamma ? p.C : p.addC;
+        if (plain_out == 1 && full4 && pre_src != nullptr)
+        {
+            for (int it = 0; it < gpr; ++it)
+            {
+                const RowInfo &ri = rowinfo[q * 32 + it * rows_per_it + rsub];
+                if (ri.item >= 0)
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(pre_src + ri.outoff + outc));
+            }
+        }
+        for (int it = 0; it < gpr; ++it)
+        {
+            const int rl = it * rows_per_it + rsub;
+            const RowInfo ri = rowinfo[q * 32 + rl];
+            float rs = 0.f, rss = 0.f;
+            if (ri.item >= 0) // row inside the problem
+            {
+                float o[4];
+                if (p.glu)
+                {
+                    const float4 t0 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 8 * g]);
+                    const float4 t1 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 8 * g + 4]);
+                    float r8[8] = {t0.x + bias[0], t0.y + bias[1], t0.z + bias[2], t0.w + bias[3],
+                                   t1.x + bias[4], t1.y + bias[5], t1.z + bias[6], t1.w + bias[7]};
+                    if (p.act == 1)
+                    {
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            r8[e] = gelu_erf(r8[e]);
+                    }
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        o[e] = r8[2 * e] * sigmoid_ref(r8[2 * e + 1]);
+                }
+                else
+                {
+                    const float4 t0 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 4 * g]);
+                    o[0] = t0.x + bias[0];
+                    o[1] = t0.y + bias[1];
+                    o[2] = t0.z + bias[2];
+                    o[3] = t0.w + bias[3];
+                    if (p.act == 1)
+                    {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            o[e] = gelu_erf(o[e]);
+                    }
+                }
+                if (plain_out == 2 && full4)
+                    store_group4_scatter_vec(p, ri, outc, o, rs, rss);
+                else if (plain_out == 1 && full4)
+                {
+                    // identity mapping: output row == GEMM row, 16-byte aligned groups
+                    float *dst = p.C + ri.outoff + outc;
+                    if (p.rowadd)
+                    {
+                        const float4 ra = __ldg(reinterpret_cast<const float4 *>(p.rowadd + (size_t)ri.uo * p.rowadd_ld + outc));
+                        o[0] += ra.x;
+                        o[1] += ra.y;
+                        o[2] += ra.z;
+                        o[3] += ra.w;
+                    }
+                    if (p.addC)
+                    {
+                        const float4 ad = *reinterpret_cast<const float4 *>(p.addC + ri.outoff + outc);
+                        o[0] += ad.x;
+                        o[1] += ad.y;
+                        o[2] += ad.z;
+                        o[3] += ad.w;
+                    }
+                    if (p.gamma)
+                    {
+                        const float4 old = *reinterpret_cast<const float4 *>(dst);
+                        o[0] = old.x + gam.x * o[0];
+                        o[1] = old.y + gam.y * o[1];
+                        o[2] = old.z + gam.z * o[2];
+                        o[3] = old.w + gam.w * o[3];
+                    }
+                    if (p.out_pack)
+                    {
+                        // tile-packed bf16 for a consumer GEMM with K = ldc: [row/128][col/8][row%128][col%8]
+                        const int mrow = ri.prow;
+                        const size_t off = ((size_t)(mrow >> 7) * (p.ldc >> 3) + (outc >> 3)) * 1024 + (size_t)(mrow & 127) * 8 +
+                                           (outc & 7);
+                        uint2 pk2;
+                        pk2.x = pack_bf16x2(o[0], o[1]);
+                        pk2.y = pack_bf16x2(o[2], o[3]);
+                        *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + off) = pk2;
+                    }
+                    else if (p.out_bf16)
+                    {
+                        uint2 pk2;
+                        pk2.x = pack_bf16x2(o[0], o[1]);
+                        pk2.y = pack_bf16x2(o[2], o[3]);
+                        *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + ri.outoff + outc) = pk2;
+                    }
+                    else
+                        *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+                    rs = o[0] + o[1] + o[2] + o[3];
+                    rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
+                }
+                else if (outc < nlimit)
+                    store_group4_scatter(p, ri, outc, nlimit, o, rs, rss);
+            }
+            if (p.stats)
+            {
+                if (ri.item != cur_item)
+                {
+                    if (cur_item >= 0)
+                    {
+                        atomicAdd(&p.stats[2 * (size_t)cur_item + 0], st_s);
+                        atomicAdd(&p.stats[2 * (size_t)cur_item + 1], st_ss);
+                    }
+                    cur_item = ri.item;
+                    st_s = 0.0;
+                    st_ss = 0.0;
+                }
+                st_s += (double)rs;
+                st_ss += (double)rss;
+            }
+        }
+    }
+    if (p.stats)
+    {
+        // one item per warp in the common case: reduce across lanes before touching global memory
+        const int item0 = __shfl_sync(0xffffffffu, cur_item, 0);
+        if (__all_sync(0xffffffffu, cur_item == item0))
+        {
+            for (int o = 16; o > 0; o >>= 1)
+            {
+                st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
+                st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
+            }
+            if (lane == 0 && item0 >= 0)
+            {
+                atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
+                atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
+            }
+        }
+        else if (cur_item >= 0)
+        {
+            atomicAdd(&p.stats[2 * (size_t)cur_item + 0], st_s);
+            atomicAdd(&p.stats[2 * (size_t)cur_item + 1], st_ss);
+        }
+    }
+}
+
 template <int STAGES, bool VECA, bool HALO>
 __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
                                                           const int bn, const int plain_out)
@@ -345,74 +781,7 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         // loop is: tap offset (once per k-block), predicated 16-byte loads, 4 cvt, one 16-byte store.
         if (HALO)
         {
-            // unit = (patch row, 8-channel chunk), chunk fastest: consecutive lanes read consecutive 32-byte pieces of
-            // the channels-last input (a whole plane of the patch is one contiguous span of memory)
-            const int rows = p.halo_rows;
-            const int total = p.halo_nu * rows * c8n;
-            const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
-            for (int u0 = tid; u0 < total; u0 += 4 * PROD_THREADS)
-            {
-                float4 lo[4], hi[4];
-                int dsto[4];
-                const float *src[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                {
-                    const int u = u0 + i * PROD_THREADS;
-                    dsto[i] = -1;
-                    src[i] = nullptr;
-                    if (u < total)
-                    {
-                        const int prow = fast_div(u, p.div_c8);
-                        const int kcc = u - prow * c8n;
-                        const int plane = fast_div(prow, p.div_rows);
-                        const int r = prow - plane * rows;
-                        const int ui = hu + p.halo_dumin + plane, vi = hv0 + p.halo_dvmin + r;
-                        dsto[i] = (plane * c8n + kcc) * (int)h_lbo + r * 16;
-                        if ((unsigned)ui < (unsigned)p.Ui && (unsigned)vi < (unsigned)p.Vi)
-                            src[i] = p.A + (((long long)hb * p.Ui + ui) * p.Vi + vi) * p.lda + kcc * 8;
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                {
-                    lo[i] = hi[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (src[i])
-                    {
-                        lo[i] = __ldg(reinterpret_cast<const float4 *>(src[i]));
-                        hi[i] = __ldg(reinterpret_cast<const float4 *>(src[i] + 4));
-                    }
-                }
-                if (p.A2)
-                {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        if (src[i])
-                        {
-                            const float4 t0 = __ldg(reinterpret_cast<const float4 *>(src[i] + a2d));
-                            const float4 t1 = __ldg(reinterpret_cast<const float4 *>(src[i] + a2d + 4));
-                            lo[i].x += t0.x;
-                            lo[i].y += t0.y;
-                            lo[i].z += t0.z;
-                            lo[i].w += t0.w;
-                            hi[i].x += t1.x;
-                            hi[i].y += t1.y;
-                            hi[i].z += t1.z;
-                            hi[i].w += t1.w;
-                        }
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (dsto[i] >= 0)
-                    {
-                        uint4 pk;
-                        pk.x = pack_bf16x2(lo[i].x, lo[i].y);
-                        pk.y = pack_bf16x2(lo[i].z, lo[i].w);
-                        pk.z = pack_bf16x2(hi[i].x, hi[i].y);
-                        pk.w = pack_bf16x2(hi[i].z, hi[i].w);
-                        *reinterpret_cast<uint4 *>(a_smem + dsto[i]) = pk;
-                    }
-            }
+            halo_stage_patch(p, tid, c8n, h_lbo, hb, hu, hv0, a_smem);
             fence_proxy_async();
             mbar_arrive(&a_full_bar);
         }
@@ -422,22 +791,7 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         const int r0 = tid >> 3;
         const float *rp[4];
         uint32_t rmask[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-        {
-            const int m = m0 + r0 + 32 * i;
-            rmask[i] = 0;
-            rp[i] = p.A;
-            if (m < p.M)
-            {
-                const RowCoord rc = decode_row(m, p);
-                const int ui0 = rc.uo * p.su, vi0 = rc.vo * p.sv;
-                rp[i] = p.A + (((long long)rc.b * p.Ui + ui0) * p.Vi + vi0) * p.lda;
-                for (int t = 0; t < p.ntaps; ++t)
-                    if ((unsigned)(ui0 + p.du[t]) < (unsigned)p.Ui && (unsigned)(vi0 + p.dv[t]) < (unsigned)p.Vi)
-                        rmask[i] |= 1u << t;
-            }
-        }
+        producer_rows(p, m0, r0, rp, rmask);
         const long long a2d = p.A2 ? (p.A2 - p.A) : 0;
         for (int kb = 0; kb < (p.Apk ? 0 : nk); ++kb) // packed-A mode: the operand is bulk-copied, nothing to gather
         {
@@ -445,130 +799,7 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
             const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
             const int k = kb * BK + kc * 8;
             uint4 pk[4];
-            if (VECA)
-            {
-                const bool h0 = k < p.K, h1 = k + 4 < p.K;
-                int tap0 = 0, tap1 = 0, c0 = 0, c1 = 0;
-                long long toff0 = 0, toff1 = 0;
-                if (h0)
-                {
-                    tap0 = k / p.Cin;
-                    c0 = k - tap0 * p.Cin;
-                    toff0 = ((long long)p.du[tap0] * p.Vi + p.dv[tap0]) * p.lda + c0;
-                }
-                if (h1)
-                {
-                    tap1 = (k + 4) / p.Cin;
-                    c1 = (k + 4) - tap1 * p.Cin;
-                    toff1 = ((long long)p.du[tap1] * p.Vi + p.dv[tap1]) * p.lda + c1;
-                }
-                float4 lo[4], hi[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                {
-                    const bool v0 = h0 && ((rmask[i] >> tap0) & 1u), v1 = h1 && ((rmask[i] >> tap1) & 1u);
-                    lo[i] = v0 ? __ldg(reinterpret_cast<const float4 *>(rp[i] + toff0)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    hi[i] = v1 ? __ldg(reinterpret_cast<const float4 *>(rp[i] + toff1)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-                if (p.A2)
-                {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                    {
-                        const bool v0 = h0 && ((rmask[i] >> tap0) & 1u), v1 = h1 && ((rmask[i] >> tap1) & 1u);
-                        if (v0)
-                        {
-                            const float4 t = __ldg(reinterpret_cast<const float4 *>(rp[i] + a2d + toff0));
-                            lo[i].x += t.x;
-                            lo[i].y += t.y;
-                            lo[i].z += t.z;
-                            lo[i].w += t.w;
-                        }
-                        if (v1)
-                        {
-                            const float4 t = __ldg(reinterpret_cast<const float4 *>(rp[i] + a2d + toff1));
-                            hi[i].x += t.x;
-                            hi[i].y += t.y;
-                            hi[i].z += t.z;
-                            hi[i].w += t.w;
-                        }
-                    }
-                }
-                if (p.pro == 1)
-                {
-                    float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), b0 = w0, w1 = w0, b1 = w0;
-                    if (h0)
-                    {
-                        w0 = __ldg(reinterpret_cast<const float4 *>(p.pro_w + c0));
-                        b0 = __ldg(reinterpret_cast<const float4 *>(p.pro_b + c0));
-                    }
-                    if (h1)
-                    {
-                        w1 = __ldg(reinterpret_cast<const float4 *>(p.pro_w + c1));
-                        b1 = __ldg(reinterpret_cast<const float4 *>(p.pro_b + c1));
-                    }
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                    {
-                        const float2 ms = rowstat[r0 + 32 * i];
-                        if (h0 && ((rmask[i] >> tap0) & 1u))
-                        {
-                            lo[i].x = gelu_erf((lo[i].x - ms.x) * ms.y * w0.x + b0.x);
-                            lo[i].y = gelu_erf((lo[i].y - ms.x) * ms.y * w0.y + b0.y);
-                            lo[i].z = gelu_erf((lo[i].z - ms.x) * ms.y * w0.z + b0.z);
-                            lo[i].w = gelu_erf((lo[i].w - ms.x) * ms.y * w0.w + b0.w);
-                        }
-                        if (h1 && ((rmask[i] >> tap1) & 1u))
-                        {
-                            hi[i].x = gelu_erf((hi[i].x - ms.x) * ms.y * w1.x + b1.x);
-                            hi[i].y = gelu_erf((hi[i].y - ms.x) * ms.y * w1.y + b1.y);
-                            hi[i].z = gelu_erf((hi[i].z - ms.x) * ms.y * w1.z + b1.z);
-                            hi[i].w = gelu_erf((hi[i].w - ms.x) * ms.y * w1.w + b1.w);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                {
-                    pk[i].x = pack_bf16x2(lo[i].x, lo[i].y);
-                    pk[i].y = pack_bf16x2(lo[i].z, lo[i].w);
-                    pk[i].z = pack_bf16x2(hi[i].x, hi[i].y);
-                    pk[i].w = pack_bf16x2(hi[i].z, hi[i].w);
-                }
-            }
-            else
-            {
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                {
-                    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                    const float2 ms = rowstat[r0 + 32 * i];
-#pragma unroll
-                    for (int e = 0; e < 8; ++e)
-                    {
-                        const int ke = k + e;
-                        if (ke < p.K)
-                        {
-                            const int tap = ke / p.Cin;
-                            const int c = ke - tap * p.Cin;
-                            if ((rmask[i] >> tap) & 1u)
-                            {
-                                const long long off = ((long long)p.du[tap] * p.Vi + p.dv[tap]) * p.lda + c;
-                                float t = __ldg(rp[i] + off);
-                                if (p.A2)
-                                    t += __ldg(rp[i] + a2d + off);
-                                if (p.pro == 1)
-                                    t = gelu_erf((t - ms.x) * ms.y * __ldg(&p.pro_w[c]) + __ldg(&p.pro_b[c]));
-                                v[e] = t;
-                            }
-                        }
-                    }
-                    pk[i].x = pack_bf16x2(v[0], v[1]);
-                    pk[i].y = pack_bf16x2(v[2], v[3]);
-                    pk[i].z = pack_bf16x2(v[4], v[5]);
-                    pk[i].w = pack_bf16x2(v[6], v[7]);
-                }
-            }
+            gather_kblock<VECA>(p, k, r0, rp, rmask, a2d, rowstat, pk);
             mbar_wait(&empty_bar[s], ph ^ 1u);
             uint8_t *dst = a_smem + s * A_STAGE + kc * A_LBO + r0 * 16; // core (row/8, kc): kc*LBO + row*16
 #pragma unroll
@@ -581,212 +812,13 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         } // !HALO
 
         // ================= epilogue =================
-        // Warps w and w+4 share TMEM lanes / tile rows 32*(w%4)..+31 and alternate over the 32-column
-        // chunks.  Per chunk each lane pulls its own row's raw accumulators from TMEM and stages them in
-        // shared memory (the drained pipeline buffers); the warp then re-reads them transposed so that
-        // 8 lanes write 128 contiguous bytes of one output row: coalesced stores / residual reads.  Bias,
-        // GELU, GLU, row-add, LayerScale residual and the statistics are applied on the transposed side.
+        // Warps w and w+4 share TMEM lanes / tile rows 32*(w%4)..+31 and alternate over the 32-column chunks;
+        // the staging buffers are the drained pipeline buffers.
         mbar_wait(&tmem_full_bar, 0);
         tc_fence_after();
         const int q = warp & 3, hsel = warp >> 2;
-        float *stage = reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD);
-        const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-        const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N; // never beyond N nor into the next column tile
-        const int nlimit = p.glu ? (ntile_end >> 1) : ntile_end;   // valid OUTPUT columns
-        const int gpr = p.glu ? 4 : 8;                             // 4-column output groups per row per chunk
-        const int rows_per_it = 32 / gpr;
-        const int g = lane % gpr, rsub = lane / gpr;
-        int cur_item = -1;
-        double st_s = 0.0, st_ss = 0.0;
-        for (int c0 = 32 * hsel; c0 < bn; c0 += 64)
-        {
-            float val[32];
-            tmem_ld16(lane_addr + (uint32_t)c0, *reinterpret_cast<float(*)[16]>(&val[0]));
-            if (c0 + 16 < bn)
-                tmem_ld16(lane_addr + (uint32_t)(c0 + 16), *reinterpret_cast<float(*)[16]>(&val[16]));
-            else
-            {
-#pragma unroll
-                for (int j = 16; j < 32; ++j)
-                    val[j] = 0.f;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-                *reinterpret_cast<float4 *>(&stage[lane * EPI_LD + j]) = make_float4(val[j], val[j + 1], val[j + 2], val[j + 3]);
-            __syncwarp();
-            const int nbase = n0 + c0;                          // first RAW column of the chunk
-            // this lane's raw columns: plain 4g..4g+3, GLU 8g..8g+7 (-> outputs 4g..4g+3)
-            const int rawc = nbase + (p.glu ? 8 * g : 4 * g);
-            const int outc = (p.glu ? (nbase >> 1) : nbase) + 4 * g;
-            float bias[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (p.bias)
-            {
-                const float4 b0 = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc)); // zero padded to ldw
-                bias[0] = b0.x;
-                bias[1] = b0.y;
-                bias[2] = b0.z;
-                bias[3] = b0.w;
-                if (p.glu)
-                {
-                    const float4 b1 = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc + 4));
-                    bias[4] = b1.x;
-                    bias[5] = b1.y;
-                    bias[6] = b1.z;
-                    bias[7] = b1.w;
-                }
-            }
-            float4 gam = make_float4(0.f, 0.f, 0.f, 0.f);
-            const bool full4 = outc + 4 <= nlimit;
-            if (p.gamma && full4)
-                gam = __ldg(reinterpret_cast<const float4 *>(p.gamma + outc));
-            // Residual / skip operands of the identity mapping: pull all of this lane's rows towards L1 first, so the
-            // loop below does not expose one full memory latency per row (load -> fma -> store chains).
-            const float *pre_src = p.gamma ? p.C : p.addC;
-            if (plain_out == 1 && full4 && pre_src != nullptr)
-            {
-                for (int it = 0; it < gpr; ++it)
-                {
-                    const RowInfo &ri = rowinfo[q * 32 + it * rows_per_it + rsub];
-                    if (ri.item >= 0)
-                        asm volatile("prefetch.global.L1 [%0];" ::"l"(pre_src + ri.outoff + outc));
-                }
-            }
-            for (int it = 0; it < gpr; ++it)
-            {
-                const int rl = it * rows_per_it + rsub;
-                const RowInfo ri = rowinfo[q * 32 + rl];
-                float rs = 0.f, rss = 0.f;
-                if (ri.item >= 0) // row inside the problem
-                {
-                    float o[4];
-                    if (p.glu)
-                    {
-                        const float4 t0 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 8 * g]);
-                        const float4 t1 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 8 * g + 4]);
-                        float r8[8] = {t0.x + bias[0], t0.y + bias[1], t0.z + bias[2], t0.w + bias[3],
-                                       t1.x + bias[4], t1.y + bias[5], t1.z + bias[6], t1.w + bias[7]};
-                        if (p.act == 1)
-                        {
-#pragma unroll
-                            for (int e = 0; e < 8; ++e)
-                                r8[e] = gelu_erf(r8[e]);
-                        }
-#pragma unroll
-                        for (int e = 0; e < 4; ++e)
-                            o[e] = r8[2 * e] * sigmoid_ref(r8[2 * e + 1]);
-                    }
-                    else
-                    {
-                        const float4 t0 = *reinterpret_cast<const float4 *>(&stage[rl * EPI_LD + 4 * g]);
-                        o[0] = t0.x + bias[0];
-                        o[1] = t0.y + bias[1];
-                        o[2] = t0.z + bias[2];
-                        o[3] = t0.w + bias[3];
-                        if (p.act == 1)
-                        {
-#pragma unroll
-                            for (int e = 0; e < 4; ++e)
-                                o[e] = gelu_erf(o[e]);
-                        }
-                    }
-                    if (plain_out == 2 && full4)
-                        store_group4_scatter_vec(p, ri, outc, o, rs, rss);
-                    else if (plain_out == 1 && full4)
-                    {
-                        // identity mapping: output row == GEMM row, 16-byte aligned groups
-                        float *dst = p.C + ri.outoff + outc;
-                        if (p.rowadd)
-                        {
-                            const float4 ra = __ldg(reinterpret_cast<const float4 *>(p.rowadd + (size_t)ri.uo * p.rowadd_ld + outc));
-                            o[0] += ra.x;
-                            o[1] += ra.y;
-                            o[2] += ra.z;
-                            o[3] += ra.w;
-                        }
-                        if (p.addC)
-                        {
-                            const float4 ad = *reinterpret_cast<const float4 *>(p.addC + ri.outoff + outc);
-                            o[0] += ad.x;
-                            o[1] += ad.y;
-                            o[2] += ad.z;
-                            o[3] += ad.w;
-                        }
-                        if (p.gamma)
-                        {
-                            const float4 old = *reinterpret_cast<const float4 *>(dst);
-                            o[0] = old.x + gam.x * o[0];
-                            o[1] = old.y + gam.y * o[1];
-                            o[2] = old.z + gam.z * o[2];
-                            o[3] = old.w + gam.w * o[3];
-                        }
-                        if (p.out_pack)
-                        {
-                            // tile-packed bf16 for a consumer GEMM with K = ldc: [row/128][col/8][row%128][col%8]
-                            const int mrow = ri.prow;
-                            const size_t off = ((size_t)(mrow >> 7) * (p.ldc >> 3) + (outc >> 3)) * 1024 + (size_t)(mrow & 127) * 8 +
-                                               (outc & 7);
-                            uint2 pk2;
-                            pk2.x = pack_bf16x2(o[0], o[1]);
-                            pk2.y = pack_bf16x2(o[2], o[3]);
-                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + off) = pk2;
-                        }
-                        else if (p.out_bf16)
-                        {
-                            uint2 pk2;
-                            pk2.x = pack_bf16x2(o[0], o[1]);
-                            pk2.y = pack_bf16x2(o[2], o[3]);
-                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + ri.outoff + outc) = pk2;
-                        }
-                        else
-                            *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-                        rs = o[0] + o[1] + o[2] + o[3];
-                        rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
-                    }
-                    else if (outc < nlimit)
-                        store_group4_scatter(p, ri, outc, nlimit, o, rs, rss);
-                }
-                if (p.stats)
-                {
-                    if (ri.item != cur_item)
-                    {
-                        if (cur_item >= 0)
-                        {
-                            atomicAdd(&p.stats[2 * (size_t)cur_item + 0], st_s);
-                            atomicAdd(&p.stats[2 * (size_t)cur_item + 1], st_ss);
-                        }
-                        cur_item = ri.item;
-                        st_s = 0.0;
-                        st_ss = 0.0;
-                    }
-                    st_s += (double)rs;
-                    st_ss += (double)rss;
-                }
-            }
-        }
-        if (p.stats)
-        {
-            // one item per warp in the common case: reduce across lanes before touching global memory
-            const int item0 = __shfl_sync(0xffffffffu, cur_item, 0);
-            if (__all_sync(0xffffffffu, cur_item == item0))
-            {
-                for (int o = 16; o > 0; o >>= 1)
-                {
-                    st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
-                    st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
-                }
-                if (lane == 0 && item0 >= 0)
-                {
-                    atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
-                    atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
-                }
-            }
-            else if (cur_item >= 0)
-            {
-                atomicAdd(&p.stats[2 * (size_t)cur_item + 0], st_s);
-                atomicAdd(&p.stats[2 * (size_t)cur_item + 1], st_ss);
-            }
-        }
+        epilogue_tile(p, bn, plain_out, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo,
+                      reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD), q, 32 * hsel, 64, lane);
         tc_fence_before();
     }
     else if (warp == PROD_WARPS)
