@@ -488,6 +488,114 @@ __device__ __forceinline__ void gather_kblock(const GemmParams &p, const int k, 
     }
 }
 
+__device__ __forceinline__ void bulk_s2g(void *gdst, const void *ssrc, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+
+__device__ __forceinline__ bool bulk_ok(const GemmParams &p, const int mode)
+{
+    return mode == 1 && !p.gamma && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && (p.N % (p.glu ? 8 : 4)) == 0;
+}
+
+// Epilogue for row-major fp32 outputs with the identity mapping and no read-modify-write (the convolutions and
+// rewrites of the encoders / decoders, the DConv GEMMs): a lane keeps the row of its TMEM lane, applies bias / GELU /
+// GLU in registers, writes the finished piece of its row (32 raw columns) into its own 144-byte slot of the warp's
+// staging buffer and hands it to the bulk-copy engine (cp.async.bulk shared -> global): the global stores cost one
+// instruction per row piece, are fully contiguous per request, and nothing is exchanged between lanes.  The
+// transposing form below spent ~35 instructions per 4 outputs, and these layers are bound by instruction issue.
+__device__ __forceinline__ void epilogue_tile_bulk(const GemmParams &p, const int bn, const int n0, const uint32_t lane_addr,
+                                                   const RowInfo &ri, float *stage, const int c_begin, const int c_step,
+                                                   const int lane)
+{
+    const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N;
+    const bool valid = ri.item >= 0;
+    float *slot = stage + lane * EPI_LD;
+    float *crow = p.C + ri.outoff;
+    double st_s = 0.0, st_ss = 0.0;
+    for (int c0 = c_begin; c0 < bn; c0 += c_step)
+    {
+        const int rawc0 = n0 + c0;
+        if (rawc0 >= ntile_end)
+            break;
+        float v[32];
+        tmem_ld32(lane_addr + (uint32_t)c0, v);
+        const int nraw = (ntile_end - rawc0) < 32 ? (ntile_end - rawc0) : 32; // multiple of 4 (8 with GLU)
+        if (p.bias)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < nraw)
+                {
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc0 + j));
+                    v[j] += b.x;
+                    v[j + 1] += b.y;
+                    v[j + 2] += b.z;
+                    v[j + 3] += b.w;
+                }
+        }
+        if (p.act == 1)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                v[j] = gelu_erf(v[j]);
+        }
+        int nout = nraw;
+        if (p.glu)
+        {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                v[j] = v[2 * j] * sigmoid_ref(v[2 * j + 1]);
+            nout = nraw >> 1;
+        }
+        float rs = 0.f, rss = 0.f;
+        bulk_wait_read(); // the previous piece has left the slot
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+            if (j < nout)
+            {
+                *reinterpret_cast<float4 *>(slot + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                rs += v[j] + v[j + 1] + v[j + 2] + v[j + 3];
+                rss += v[j] * v[j] + v[j + 1] * v[j + 1] + v[j + 2] * v[j + 2] + v[j + 3] * v[j + 3];
+            }
+        fence_proxy_async();
+        if (valid)
+        {
+            bulk_s2g(crow + (p.glu ? (rawc0 >> 1) : rawc0), slot, (uint32_t)nout * 4u);
+            bulk_commit();
+            st_s += (double)rs;
+            st_ss += (double)rss;
+        }
+    }
+    bulk_wait_read(); // the staging buffer is reused by the next tile / freed at exit
+    if (p.stats)
+    {
+        // one item per warp in the common case: reduce across lanes before touching global memory
+        const int item0 = __shfl_sync(0xffffffffu, ri.item, 0);
+        if (__all_sync(0xffffffffu, ri.item == item0))
+        {
+            for (int o = 16; o > 0; o >>= 1)
+            {
+                st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
+                st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
+            }
+            if (lane == 0 && item0 >= 0)
+            {
+                atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
+                atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
+            }
+        }
+        else if (valid)
+        {
+            atomicAdd(&p.stats[2 * (size_t)ri.item + 0], st_s);
+            atomicAdd(&p.stats[2 * (size_t)ri.item + 1], st_ss);
+        }
+    }
+}
+
 // Epilogue of one 128 x bn tile for the TMEM lane quadrant q (tile rows 32q..32q+31), column chunks c_begin,
 // c_begin + c_step, ...  Per 32-column chunk each lane pulls its own row's raw accumulators from TMEM and stages
 // them in shared memory (stage: this warp's private 32 x EPI_LD floats); the warp then re-reads them transposed so
@@ -835,8 +943,13 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         mbar_wait(&tmem_full_bar, 0);
         tc_fence_after();
         const int q = warp & 3, hsel = warp >> 2;
-        epilogue_tile(p, bn, plain_out, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo,
-                      reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD), q, 32 * hsel, 64, lane);
+        static_assert((EPI_LD * 4) % 16 == 0, "bulk copies need 16-byte aligned row slots");
+        if (bulk_ok(p, plain_out) && !p.no_bulk)
+            epilogue_tile_bulk(p, bn, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo[q * 32 + lane],
+                               reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD), 32 * hsel, 64, lane);
+        else
+            epilogue_tile(p, bn, plain_out, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo,
+                          reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD), q, 32 * hsel, 64, lane);
         tc_fence_before();
     }
     else if (warp == PROD_WARPS)
@@ -1400,6 +1513,8 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     q.div_per = recip(p.Uo * p.Vo);
     q.div_vo = recip(p.Vo);
     q.div_nco = recip(p.Nco);
+    static const int nob = getenv("DMX_NO_BULK") ? 1 : 0;
+    q.no_bulk = nob;
     const bool vec = (p.Cin % 4 == 0) && (p.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) &&
                      (!p.A2 || (reinterpret_cast<uintptr_t>(p.A2) & 15) == 0);
     // identity output mapping with 16-byte aligned rows -> the epilogue's fast path
