@@ -8,7 +8,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libdemucs_b200.so")
-SOURCES = ["fft.cu", "gemm.cu", "gemm_tc.cu", "attention_tc.cu", "pointwise.cu", "dconv_fused.cu", "attention.cu", "model.cu", "model_v3.cu", "v3_kernels.cu", "track.cu", "cabi.cu", "noalloc.cu"]
+SOURCES = ["fft.cu", "gemm.cu", "gemm_tc.cu", "attention_tc.cu", "pointwise.cu", "dconv_fused.cu", "dconv_mma.cu", "attention.cu", "model.cu", "model_v3.cu", "v3_kernels.cu", "track.cu", "cabi.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
               "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", CSRC]
 

@@ -1,0 +1,394 @@
+// bf16-mode twin of dconv_fused.cu: the same fused DConv residual branch (one CTA keeps one frequency row
+// x[T=336][C] resident and runs both sub-blocks on it; reference demucscpp::apply_dconv, src/layers.cpp:152-375,
+// v3 twin :723-894), with the two convolutions of each sub-block on the tensor cores through warp-level
+// mma.sync (bf16 operands, fp32 accumulate) instead of CUDA-core FMAs.
+//
+// Why mma.sync and not tcgen05 here: the GEMMs are 16..32 wide (hidden = C/8 or C/4 channels) and 336 rows long,
+// their operands already sit in this CTA's shared memory and their results are consumed in registers by the
+// GroupNorm / GELU / GLU math of the same thread -- exactly the m16n8k{8,16} fragment shapes.  The accumulator
+// fragment of the k3 conv (16 positions x 8 hidden) IS the A fragment of the following 1x1 conv, so the hidden
+// activations never leave registers.  The SIMT kernel was bound by FMA issue (ncu: 428 M instructions, 72 % issue
+// utilisation for C = 48); here a warp instruction does 2048 / 4096 MACs.
+//
+//     h = conv_k3_dil(x) ; g = GELU(GN1(h)) ; y = W2 g + b2 ; x += scale * GLU(GN2(y))
+// GroupNorm statistics: exact block reductions over the row in double, unbiased variance.  y is evaluated twice
+// (statistics, then normalise-GLU-residual) and never stored.  The residual stream x stays fp32 in shared memory;
+// only the MMA operands (x as the conv input, g, the weights) are rounded to bf16, like every other GEMM of the
+// bf16 mode.
+#include "kernels.cuh"
+
+#include <cuda_bf16.h>
+
+namespace dmx
+{
+namespace dm
+{
+
+constexpr int T = LE;             // 336 frames = 21 m-tiles of 16
+constexpr int WARPS = 7;          // 3 m-tiles per warp
+constexpr int THREADS = WARPS * 32;
+constexpr int MT_PER_WARP = 3;
+constexpr int HALO = 2;           // zero rows on both sides of the bf16 copy (dilations 1 and 2)
+
+__host__ __device__ constexpr int hid_pad(int hid) { return hid <= 8 ? 8 : (hid <= 16 ? 16 : 32); }
+// element strides of the bf16 operand arrays, chosen so that the 8 rows x 4 words of a fragment load fall into
+// 32 different banks: word stride mod 32 must be an odd multiple of 4
+__host__ __device__ constexpr int xld(int C) { return C + 8; }                    // 28 / 52 words
+__host__ __device__ constexpr int k1ld(int C) { return 3 * C + 8; }               // 76 / 148 words
+__host__ __device__ constexpr int w2ld(int hp) { return hp == 8 ? 8 : hp + 8; }   // 4 / 12 / 20 words
+__host__ __device__ constexpr int nvec(int C, int hp) { return 3 * hp + 7 * C; }  // b1 g1w g1b | b2 g2w g2b (2C each) | scale
+__host__ __device__ constexpr size_t smem_bytes(int C, int hid)
+{
+    return (size_t)T * (C + 1) * 4 + (size_t)(T + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 +
+           (size_t)2 * C * w2ld(hid_pad(hid)) * 2 + (size_t)nvec(C, hid_pad(hid)) * 4 + 64;
+}
+// fp32 parameter block shared with dconv_fused.cu, per sub-block:
+//   W1[3][C][HID] | b1[HID] | g1w[HID] | g1b[HID] | W2[2C][HID] | b2[2C] | g2w[2C] | g2b[2C] | scale[C]
+__host__ __device__ constexpr int p_stride(int C, int HID) { return 3 * C * HID + 3 * HID + 2 * C * HID + 6 * C + C; }
+
+__device__ __forceinline__ void mma_k16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                        uint32_t b1)
+{
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+                 "{%0, %1, %2, %3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma_k8(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0)
+{
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(b0));
+}
+__device__ __forceinline__ uint32_t pack2(float lo, float hi)
+{
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+__device__ __forceinline__ uint32_t ld32(const __nv_bfloat16 *p) { return *reinterpret_cast<const uint32_t *>(p); }
+
+__device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
+{
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads(); // red may still be read from the previous reduction
+    if (lane == 0)
+    {
+        red[2 * warp] = a;
+        red[2 * warp + 1] = b;
+    }
+    __syncthreads();
+    double sa = 0.0, sb = 0.0;
+    for (int w = 0; w < WARPS; ++w)
+    {
+        sa += red[2 * w];
+        sb += red[2 * w + 1];
+    }
+    a = sa;
+    b = sb;
+}
+
+template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_kernel(float *__restrict__ x, const float *__restrict__ params)
+{
+    constexpr int HP = hid_pad(HID);
+    constexpr int NT1 = HP / 8;       // n-tiles of the k3 conv
+    constexpr int NT2 = 2 * C / 8;    // n-tiles of the 1x1 conv
+    constexpr int LD = C + 1;
+    constexpr int XLD = xld(C), K1LD = k1ld(C), W2LD = w2ld(HP);
+    constexpr int PS = p_stride(C, HID);
+    extern __shared__ __align__(16) uint8_t smraw[];
+    float *xs = reinterpret_cast<float *>(smraw);                                 // [T][LD] fp32 residual stream
+    float *vec = xs + T * LD;                                                     // small fp32 vectors
+    __nv_bfloat16 *xb = reinterpret_cast<__nv_bfloat16 *>(vec + ((nvec(C, HP) + 3) & ~3)); // [T + 4][XLD]
+    __nv_bfloat16 *w1b = xb + (T + 2 * HALO) * XLD;                               // [HP][K1LD], k = tap*C + c
+    __nv_bfloat16 *w2b = w1b + HP * K1LD;                                         // [2C][W2LD]
+    float *b1 = vec, *g1w = b1 + HP, *g1b = g1w + HP, *b2 = g1b + HP, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C,
+          *scale = g2b + 2 * C;
+    __shared__ double red[2 * WARPS];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    float *xg = x + (size_t)blockIdx.x * T * C;
+
+    // ---- load the row: fp32 copy + bf16 operand copy (halo rows zero) ----
+    for (int i = tid; i < 2 * HALO * XLD / 2; i += THREADS)
+    {
+        const int r = i / (XLD / 2), c2 = i % (XLD / 2);
+        const int row = r < HALO ? r : T + r; // rows 0,1 and T+2,T+3
+        reinterpret_cast<uint32_t *>(xb + row * XLD)[c2] = 0u;
+    }
+    for (int i = tid; i < T * C / 4; i += THREADS)
+    {
+        const float4 v = *reinterpret_cast<const float4 *>(xg + 4 * i);
+        const int tt = (4 * i) / C, c = (4 * i) % C;
+        float *d = xs + tt * LD + c;
+        d[0] = v.x;
+        d[1] = v.y;
+        d[2] = v.z;
+        d[3] = v.w;
+        uint2 pk;
+        pk.x = pack2(v.x, v.y);
+        pk.y = pack2(v.z, v.w);
+        *reinterpret_cast<uint2 *>(xb + (tt + HALO) * XLD + c) = pk;
+    }
+
+#pragma unroll 1
+    for (int sub = 0; sub < 2; ++sub)
+    {
+        const int dil = 1 << sub;
+        const float *P = params + (size_t)sub * PS;
+        __syncthreads(); // previous sub-block done with the weights; xs / xb complete
+        // ---- weights of this sub-block -> bf16 operand layouts, vectors -> fp32 ----
+        for (int i = tid; i < HP * 3 * C; i += THREADS)
+        {
+            const int n = i / (3 * C), k = i - n * (3 * C); // k = tap*C + c
+            const float w = n < HID ? __ldg(P + (size_t)k * HID + n) : 0.f;
+            w1b[n * K1LD + k] = __float2bfloat16(w);
+        }
+        const float *Pb1 = P + 3 * C * HID, *Pg1w = Pb1 + HID, *Pg1b = Pg1w + HID, *PW2 = Pg1b + HID;
+        const float *Pb2 = PW2 + 2 * C * HID, *Pg2w = Pb2 + 2 * C, *Pg2b = Pg2w + 2 * C, *Psc = Pg2b + 2 * C;
+        for (int i = tid; i < 2 * C * HP; i += THREADS)
+        {
+            const int n = i / HP, k = i - n * HP;
+            const float w = k < HID ? __ldg(PW2 + (size_t)n * HID + k) : 0.f;
+            w2b[n * W2LD + k] = __float2bfloat16(w);
+        }
+        for (int i = tid; i < HP; i += THREADS)
+        {
+            b1[i] = i < HID ? __ldg(Pb1 + i) : 0.f;
+            g1w[i] = i < HID ? __ldg(Pg1w + i) : 0.f;
+            g1b[i] = i < HID ? __ldg(Pg1b + i) : 0.f;
+        }
+        for (int i = tid; i < 2 * C; i += THREADS)
+        {
+            b2[i] = __ldg(Pb2 + i);
+            g2w[i] = __ldg(Pg2w + i);
+            g2b[i] = __ldg(Pg2b + i);
+        }
+        for (int i = tid; i < C; i += THREADS)
+            scale[i] = __ldg(Psc + i);
+        __syncthreads();
+
+        // ---- conv k3, dilation dil: h[16 positions][HP] per m-tile, accumulators in the C-fragment layout ----
+        float acc[MT_PER_WARP][NT1][4];
+#pragma unroll
+        for (int i = 0; i < MT_PER_WARP; ++i)
+#pragma unroll
+            for (int nt = 0; nt < NT1; ++nt)
+            {
+                acc[i][nt][0] = acc[i][nt][2] = b1[8 * nt + 2 * t];
+                acc[i][nt][1] = acc[i][nt][3] = b1[8 * nt + 2 * t + 1];
+            }
+#pragma unroll
+        for (int tap = 0; tap < 3; ++tap)
+        {
+            const int shift = (tap - 1) * dil + HALO;
+#pragma unroll 2
+            for (int kc = 0; kc < C / 16; ++kc)
+            {
+                uint32_t bf[NT1][2];
+#pragma unroll
+                for (int nt = 0; nt < NT1; ++nt)
+                {
+                    const __nv_bfloat16 *wp = w1b + (8 * nt + g) * K1LD + tap * C + 16 * kc + 2 * t;
+                    bf[nt][0] = ld32(wp);
+                    bf[nt][1] = ld32(wp + 8);
+                }
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                {
+                    const int row0 = 16 * (warp + WARPS * i) + shift + g;
+                    const __nv_bfloat16 *ap = xb + row0 * XLD + 16 * kc + 2 * t;
+                    const uint32_t a0 = ld32(ap), a1 = ld32(ap + 8 * XLD), a2 = ld32(ap + 8), a3 = ld32(ap + 8 * XLD + 8);
+#pragma unroll
+                    for (int nt = 0; nt < NT1; ++nt)
+                        mma_k16(acc[i][nt], a0, a1, a2, a3, bf[nt][0], bf[nt][1]);
+                }
+            }
+        }
+        // ---- GroupNorm(1) statistics of h (padded hidden channels are exactly zero) ----
+        double s1 = 0.0, s2 = 0.0;
+        {
+            float a = 0.f, b = 0.f;
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+#pragma unroll
+                for (int nt = 0; nt < NT1; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                    {
+                        a += acc[i][nt][e];
+                        b = fmaf(acc[i][nt][e], acc[i][nt][e], b);
+                    }
+            s1 = a;
+            s2 = b;
+        }
+        block_sum2(s1, s2, red);
+        // ---- GN1 + GELU; the C fragments become the A fragments of the 1x1 conv ----
+        uint32_t af[MT_PER_WARP][NT1][2];
+        {
+            const double n = (double)T * HID;
+            const double m = s1 / n;
+            double var = (s2 - s1 * m) / (n - 1.0);
+            var = var < 0.0 ? 0.0 : var;
+            const float mean = (float)m, rstd = (float)(1.0 / sqrt(var + 1e-5));
+#pragma unroll
+            for (int nt = 0; nt < NT1; ++nt)
+            {
+                const int j = 8 * nt + 2 * t;
+                const float w0 = rstd * g1w[j], w1 = rstd * g1w[j + 1], o0 = g1b[j], o1 = g1b[j + 1];
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                {
+                    af[i][nt][0] = pack2(gelu_erf((acc[i][nt][0] - mean) * w0 + o0), gelu_erf((acc[i][nt][1] - mean) * w1 + o1));
+                    af[i][nt][1] = pack2(gelu_erf((acc[i][nt][2] - mean) * w0 + o0), gelu_erf((acc[i][nt][3] - mean) * w1 + o1));
+                }
+            }
+        }
+        // y tile nt (8 output channels) of the three m-tiles: d[i] = b2 + W2[8nt.., :] g
+        auto conv2 = [&](int nt, float (&d)[MT_PER_WARP][4]) {
+            const float bb0 = b2[8 * nt + 2 * t], bb1 = b2[8 * nt + 2 * t + 1];
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+            {
+                d[i][0] = d[i][2] = bb0;
+                d[i][1] = d[i][3] = bb1;
+            }
+            const __nv_bfloat16 *wp = w2b + (8 * nt + g) * W2LD + 2 * t;
+            if (HP == 8)
+            {
+                const uint32_t b0 = ld32(wp);
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                    mma_k8(d[i], af[i][0][0], af[i][0][1], b0);
+            }
+            else
+            {
+#pragma unroll
+                for (int s = 0; s < HP / 16; ++s)
+                {
+                    const uint32_t b0 = ld32(wp + 16 * s), b1v = ld32(wp + 16 * s + 8);
+#pragma unroll
+                    for (int i = 0; i < MT_PER_WARP; ++i)
+                        mma_k16(d[i], af[i][(2 * s) % NT1][0], af[i][(2 * s) % NT1][1], af[i][(2 * s + 1) % NT1][0],
+                                af[i][(2 * s + 1) % NT1][1], b0, b1v);
+                }
+            }
+        };
+        // ---- 1x1 conv to 2C channels, pass A: statistics only ----
+        s1 = 0.0;
+        s2 = 0.0;
+        {
+            float a = 0.f, b = 0.f;
+#pragma unroll 4
+            for (int nt = 0; nt < NT2; ++nt)
+            {
+                float d[MT_PER_WARP][4];
+                conv2(nt, d);
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                    {
+                        a += d[i][e];
+                        b = fmaf(d[i][e], d[i][e], b);
+                    }
+            }
+            s1 = a;
+            s2 = b;
+        }
+        block_sum2(s1, s2, red);
+        // ---- pass B: recompute, GroupNorm, GLU, LayerScale, residual into the resident fp32 rows ----
+        {
+            const double n = (double)T * 2 * C;
+            const double m = s1 / n;
+            double var = (s2 - s1 * m) / (n - 1.0);
+            var = var < 0.0 ? 0.0 : var;
+            const float mean = (float)m, rstd = (float)(1.0 / sqrt(var + 1e-5));
+#pragma unroll 2
+            for (int nt = 0; nt < C / 8; ++nt)
+            {
+                float da[MT_PER_WARP][4], dg[MT_PER_WARP][4];
+                conv2(nt, da);
+                conv2(nt + C / 8, dg);
+                const int c = 8 * nt + 2 * t;
+                const float ga0 = rstd * g2w[c], ga1 = rstd * g2w[c + 1], oa0 = g2b[c], oa1 = g2b[c + 1];
+                const float gg0 = rstd * g2w[C + c], gg1 = rstd * g2w[C + c + 1], og0 = g2b[C + c], og1 = g2b[C + c + 1];
+                const float sc0 = scale[c], sc1 = scale[c + 1];
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                {
+                    float *r0 = xs + (16 * (warp + WARPS * i) + g) * LD + c;
+                    float *r1 = r0 + 8 * LD;
+                    r0[0] += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
+                    r0[1] += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
+                    r1[0] += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
+                    r1[1] += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
+                }
+            }
+        }
+        if (sub == 0)
+        {
+            // the second sub-block convolves the updated row: refresh the bf16 operand copy
+            __syncthreads();
+            for (int i = tid; i < T * C / 2; i += THREADS)
+            {
+                const int tt = (2 * i) / C, c = (2 * i) % C;
+                const float *s = xs + tt * LD + c;
+                *reinterpret_cast<uint32_t *>(xb + (tt + HALO) * XLD + c) = pack2(s[0], s[1]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < T * C / 4; i += THREADS)
+    {
+        const int tt = (4 * i) / C, c = (4 * i) % C;
+        const float *s = xs + tt * LD + c;
+        *reinterpret_cast<float4 *>(xg + 4 * i) = make_float4(s[0], s[1], s[2], s[3]);
+    }
+}
+
+template <int C, int HID> static int set_attr()
+{
+    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem_bytes(C, HID)));
+    return 0;
+}
+template <int C, int HID> static int launch(float *x, const float *params, int items, cudaStream_t st)
+{
+    dconv_mma_kernel<C, HID><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+} // namespace dm
+
+// (96, 24) -- the v3 model's second level -- would need 238 KB of shared memory: it stays on the SIMT kernel
+bool dconv_mma_supported(int C, int hid, int V)
+{
+    return V == dm::T && ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && hid == 12));
+}
+
+int dconv_mma_init_device()
+{
+    return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>();
+}
+
+// x: [items][336][C] in place; items = B * F frequency rows; params: the fp32 block of dconv_fused.cu
+int launch_dconv_mma(float *x, const float *params, int items, int C, int hid, cudaStream_t st)
+{
+    if (C == 48 && hid == 6)
+        return dm::launch<48, 6>(x, params, items, st);
+    if (C == 48 && hid == 12)
+        return dm::launch<48, 12>(x, params, items, st);
+    if (C == 96 && hid == 12)
+        return dm::launch<96, 12>(x, params, items, st);
+    set_error("dconv_mma: unsupported shape");
+    return -1;
+}
+
+} // namespace dmx

@@ -108,6 +108,10 @@ bool dconv_fused_supported(int C, int hid, int V);
 int dconv_fused_param_floats(int C, int hid);
 int dconv_fused_init_device();
 int launch_dconv_fused(float *x, const float *params, int items, int C, int hid, cudaStream_t st);
+// dconv_mma.cu: the same with both convolutions on tensor cores (mma.sync, bf16 operands); bf16 mode only
+bool dconv_mma_supported(int C, int hid, int V);
+int dconv_mma_init_device();
+int launch_dconv_mma(float *x, const float *params, int items, int C, int hid, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // v3_kernels.cu (hdemucs_mmi)

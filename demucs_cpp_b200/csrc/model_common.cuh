@@ -356,7 +356,10 @@ struct Fwd
             // one HBM read + one write of x; MACs: 2 sub-blocks x (k3 conv + the 1x1 conv evaluated twice)
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          (double)B * U * V * C * 8.0);
-            rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
+            if (m->precision == DMX_PRECISION_BF16 && dconv_mma_supported(C, hid, V))
+                rc = launch_dconv_mma(x, w.fused, B * U, C, hid, st);
+            else
+                rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
             return;
         }
         const size_t items = (size_t)B * (per_u ? U : 1);

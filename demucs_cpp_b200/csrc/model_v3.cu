@@ -108,7 +108,8 @@ int model_v3_finalize(dmx_model *m)
     DMX_CUDA(cudaEventCreate(&m->ev0));
     DMX_CUDA(cudaEventCreate(&m->ev1));
     DMX_CUDA(cudaEventCreate(&m->ev2));
-    if (fft_init_device() || tc_init_device() || attention_tc_init_device() || dconv_fused_init_device())
+    if (fft_init_device() || tc_init_device() || attention_tc_init_device() || dconv_fused_init_device() ||
+        dconv_mma_init_device())
         return -1;
     m->S = 4;
     m->d_model = 0;
