@@ -352,6 +352,338 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Time branch (one GroupNorm item = a whole batch element of L samples): the same arithmetic on 336-position tiles
+// of the signal, in three launches per sub-block because the statistics span the item:
+//   phase 0: h = conv_k3_dil(x) + b1 -> hbuf (fp32 [B][L][hs]), (sum, sumsq) of h -> stats1[b]
+//   phase 1: g = GELU(GN1(h)); y = W2 g + b2 in registers only,  (sum, sumsq) of y -> stats2[b]
+//   phase 2: recompute g and y; x += scale * GLU(GN2(y))
+// x is read twice and written once, h (C/8 wide) written once and read twice, y (2C wide) never stored -- against
+// x / h / y passing through three GEMM + pointwise launches with y materialised (src/layers.cpp:152-375).
+template <int C, int HID, int PHASE>
+__global__ void __launch_bounds__(THREADS)
+    dconv_time_kernel(float *__restrict__ x, float *__restrict__ hbuf, const float *__restrict__ P, const int L, const int hs,
+                      const int dil, double *__restrict__ stats1, double *__restrict__ stats2)
+{
+    constexpr int HP = hid_pad(HID);
+    constexpr int NT1 = HP / 8;
+    constexpr int NT2 = 2 * C / 8;
+    constexpr int LD = C + 1;
+    constexpr int XLD = xld(C), K1LD = k1ld(C), W2LD = w2ld(HP);
+    extern __shared__ __align__(16) uint8_t smraw[];
+    // phase 0: xb | w1b | b1      phase 1: w2b | vec      phase 2: xs | w2b | vec
+    __shared__ double red[2 * WARPS];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int b = blockIdx.y;
+    const int p0 = blockIdx.x * T; // first position of the tile
+    float *xg = x + (size_t)b * L * C;
+    float *hg = hbuf + (size_t)b * L * hs;
+    const float *Pb1 = P + 3 * C * HID, *Pg1w = Pb1 + HID, *Pg1b = Pg1w + HID, *PW2 = Pg1b + HID;
+    const float *Pb2 = PW2 + 2 * C * HID, *Pg2w = Pb2 + 2 * C, *Pg2b = Pg2w + 2 * C, *Psc = Pg2b + 2 * C;
+
+    if (PHASE == 0)
+    {
+        __nv_bfloat16 *xb = reinterpret_cast<__nv_bfloat16 *>(smraw); // [T + 4][XLD], row r <-> position p0 + r - 2
+        __nv_bfloat16 *w1b = xb + (T + 2 * HALO) * XLD;
+        float *b1 = reinterpret_cast<float *>(w1b + HP * K1LD);
+        for (int i = tid; i < (T + 2 * HALO) * C / 4; i += THREADS)
+        {
+            const int r = (4 * i) / C, c = (4 * i) % C;
+            const int pos = p0 + r - HALO;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (pos >= 0 && pos < L)
+                v = *reinterpret_cast<const float4 *>(xg + (size_t)pos * C + c);
+            uint2 pk;
+            pk.x = pack2(v.x, v.y);
+            pk.y = pack2(v.z, v.w);
+            *reinterpret_cast<uint2 *>(xb + r * XLD + c) = pk;
+        }
+        for (int i = tid; i < HP * 3 * C; i += THREADS)
+        {
+            const int n = i / (3 * C), k = i - n * (3 * C);
+            w1b[n * K1LD + k] = __float2bfloat16(n < HID ? __ldg(P + (size_t)k * HID + n) : 0.f);
+        }
+        for (int i = tid; i < HP; i += THREADS)
+            b1[i] = i < HID ? __ldg(Pb1 + i) : 0.f;
+        __syncthreads();
+        float acc[MT_PER_WARP][NT1][4];
+#pragma unroll
+        for (int i = 0; i < MT_PER_WARP; ++i)
+#pragma unroll
+            for (int nt = 0; nt < NT1; ++nt)
+            {
+                acc[i][nt][0] = acc[i][nt][2] = b1[8 * nt + 2 * t];
+                acc[i][nt][1] = acc[i][nt][3] = b1[8 * nt + 2 * t + 1];
+            }
+#pragma unroll
+        for (int tap = 0; tap < 3; ++tap)
+        {
+            const int shift = (tap - 1) * dil + HALO;
+#pragma unroll 2
+            for (int kc = 0; kc < C / 16; ++kc)
+            {
+                uint32_t bf[NT1][2];
+#pragma unroll
+                for (int nt = 0; nt < NT1; ++nt)
+                {
+                    const __nv_bfloat16 *wp = w1b + (8 * nt + g) * K1LD + tap * C + 16 * kc + 2 * t;
+                    bf[nt][0] = ld32(wp);
+                    bf[nt][1] = ld32(wp + 8);
+                }
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                {
+                    const int row0 = 16 * (warp + WARPS * i) + shift + g;
+                    const __nv_bfloat16 *ap = xb + row0 * XLD + 16 * kc + 2 * t;
+                    const uint32_t a0 = ld32(ap), a1 = ld32(ap + 8 * XLD), a2 = ld32(ap + 8), a3 = ld32(ap + 8 * XLD + 8);
+#pragma unroll
+                    for (int nt = 0; nt < NT1; ++nt)
+                        mma_k16(acc[i][nt], a0, a1, a2, a3, bf[nt][0], bf[nt][1]);
+                }
+            }
+        }
+        float sa = 0.f, sb = 0.f;
+#pragma unroll
+        for (int i = 0; i < MT_PER_WARP; ++i)
+        {
+            const int q0 = p0 + 16 * (warp + WARPS * i) + g, q1 = q0 + 8;
+#pragma unroll
+            for (int nt = 0; nt < NT1; ++nt)
+            {
+                const int j = 8 * nt + 2 * t;
+                if (j < hs)
+                {
+                    if (q0 < L)
+                    {
+                        *reinterpret_cast<float2 *>(hg + (size_t)q0 * hs + j) = make_float2(acc[i][nt][0], acc[i][nt][1]);
+                        sa += acc[i][nt][0] + acc[i][nt][1];
+                        sb += acc[i][nt][0] * acc[i][nt][0] + acc[i][nt][1] * acc[i][nt][1];
+                    }
+                    if (q1 < L)
+                    {
+                        *reinterpret_cast<float2 *>(hg + (size_t)q1 * hs + j) = make_float2(acc[i][nt][2], acc[i][nt][3]);
+                        sa += acc[i][nt][2] + acc[i][nt][3];
+                        sb += acc[i][nt][2] * acc[i][nt][2] + acc[i][nt][3] * acc[i][nt][3];
+                    }
+                }
+            }
+        }
+        double s1 = sa, s2 = sb;
+        block_sum2(s1, s2, red);
+        if (tid == 0)
+        {
+            atomicAdd(&stats1[2 * b], s1);
+            atomicAdd(&stats1[2 * b + 1], s2);
+        }
+        return;
+    }
+
+    // ---- phases 1 and 2: hidden activations back from hbuf, normalised, as A fragments ----
+    float *xs = reinterpret_cast<float *>(smraw);                             // phase 2 only: [T][LD]
+    float *vec = xs + (PHASE == 2 ? T * LD : 0);
+    __nv_bfloat16 *w2b = reinterpret_cast<__nv_bfloat16 *>(vec + ((nvec(C, HP) + 3) & ~3));
+    float *b1 = vec, *g1w = b1 + HP, *g1b = g1w + HP, *b2 = g1b + HP, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C,
+          *scale = g2b + 2 * C;
+    (void)b1;
+    if (PHASE == 2)
+    {
+        for (int i = tid; i < T * C / 4; i += THREADS)
+        {
+            const int tt = (4 * i) / C, c = (4 * i) % C;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p0 + tt < L)
+                v = *reinterpret_cast<const float4 *>(xg + (size_t)(p0 + tt) * C + c);
+            float *d = xs + tt * LD + c;
+            d[0] = v.x;
+            d[1] = v.y;
+            d[2] = v.z;
+            d[3] = v.w;
+        }
+    }
+    for (int i = tid; i < 2 * C * HP; i += THREADS)
+    {
+        const int n = i / HP, k = i - n * HP;
+        w2b[n * W2LD + k] = __float2bfloat16(k < HID ? __ldg(PW2 + (size_t)n * HID + k) : 0.f);
+    }
+    for (int i = tid; i < HP; i += THREADS)
+    {
+        g1w[i] = i < HID ? __ldg(Pg1w + i) : 0.f;
+        g1b[i] = i < HID ? __ldg(Pg1b + i) : 0.f;
+    }
+    for (int i = tid; i < 2 * C; i += THREADS)
+    {
+        b2[i] = __ldg(Pb2 + i);
+        g2w[i] = __ldg(Pg2w + i);
+        g2b[i] = __ldg(Pg2b + i);
+    }
+    for (int i = tid; i < C; i += THREADS)
+        scale[i] = __ldg(Psc + i);
+    __syncthreads();
+
+    uint32_t af[MT_PER_WARP][NT1][2];
+    {
+        float mean, rstd;
+        stats_to_mean_rstd(stats1 + 2 * b, (double)L * HID, 1e-5f, mean, rstd);
+#pragma unroll
+        for (int nt = 0; nt < NT1; ++nt)
+        {
+            const int j = 8 * nt + 2 * t;
+            const float w0 = rstd * g1w[j], w1 = rstd * g1w[j + 1], o0 = g1b[j], o1 = g1b[j + 1];
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+            {
+                const int q0 = p0 + 16 * (warp + WARPS * i) + g, q1 = q0 + 8;
+                float2 h0 = make_float2(0.f, 0.f), h1 = h0;
+                if (j < hs)
+                {
+                    if (q0 < L)
+                        h0 = *reinterpret_cast<const float2 *>(hg + (size_t)q0 * hs + j);
+                    if (q1 < L)
+                        h1 = *reinterpret_cast<const float2 *>(hg + (size_t)q1 * hs + j);
+                }
+                af[i][nt][0] = pack2(gelu_erf((h0.x - mean) * w0 + o0), gelu_erf((h0.y - mean) * w1 + o1));
+                af[i][nt][1] = pack2(gelu_erf((h1.x - mean) * w0 + o0), gelu_erf((h1.y - mean) * w1 + o1));
+            }
+        }
+    }
+    auto conv2 = [&](int nt, float (&d)[MT_PER_WARP][4]) {
+        const float bb0 = b2[8 * nt + 2 * t], bb1 = b2[8 * nt + 2 * t + 1];
+#pragma unroll
+        for (int i = 0; i < MT_PER_WARP; ++i)
+        {
+            d[i][0] = d[i][2] = bb0;
+            d[i][1] = d[i][3] = bb1;
+        }
+        const __nv_bfloat16 *wp = w2b + (8 * nt + g) * W2LD + 2 * t;
+        if (HP == 8)
+        {
+            const uint32_t b0 = ld32(wp);
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+                mma_k8(d[i], af[i][0][0], af[i][0][1], b0);
+        }
+        else
+        {
+#pragma unroll
+            for (int s = 0; s < HP / 16; ++s)
+            {
+                const uint32_t b0 = ld32(wp + 16 * s), b1v = ld32(wp + 16 * s + 8);
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                    mma_k16(d[i], af[i][(2 * s) % NT1][0], af[i][(2 * s) % NT1][1], af[i][(2 * s + 1) % NT1][0],
+                            af[i][(2 * s + 1) % NT1][1], b0, b1v);
+            }
+        }
+    };
+    bool v0[MT_PER_WARP], v1[MT_PER_WARP];
+#pragma unroll
+    for (int i = 0; i < MT_PER_WARP; ++i)
+    {
+        const int q0 = p0 + 16 * (warp + WARPS * i) + g;
+        v0[i] = q0 < L;
+        v1[i] = q0 + 8 < L;
+    }
+    if (PHASE == 1)
+    {
+        float a = 0.f, bq = 0.f;
+#pragma unroll 4
+        for (int nt = 0; nt < NT2; ++nt)
+        {
+            float d[MT_PER_WARP][4];
+            conv2(nt, d);
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+            {
+                if (v0[i])
+                {
+                    a += d[i][0] + d[i][1];
+                    bq += d[i][0] * d[i][0] + d[i][1] * d[i][1];
+                }
+                if (v1[i])
+                {
+                    a += d[i][2] + d[i][3];
+                    bq += d[i][2] * d[i][2] + d[i][3] * d[i][3];
+                }
+            }
+        }
+        double s1 = a, s2 = bq;
+        block_sum2(s1, s2, red);
+        if (tid == 0)
+        {
+            atomicAdd(&stats2[2 * b], s1);
+            atomicAdd(&stats2[2 * b + 1], s2);
+        }
+        return;
+    }
+    {
+        float mean, rstd;
+        stats_to_mean_rstd(stats2 + 2 * b, (double)L * 2 * C, 1e-5f, mean, rstd);
+#pragma unroll 2
+        for (int nt = 0; nt < C / 8; ++nt)
+        {
+            float da[MT_PER_WARP][4], dg[MT_PER_WARP][4];
+            conv2(nt, da);
+            conv2(nt + C / 8, dg);
+            const int c = 8 * nt + 2 * t;
+            const float ga0 = rstd * g2w[c], ga1 = rstd * g2w[c + 1], oa0 = g2b[c], oa1 = g2b[c + 1];
+            const float gg0 = rstd * g2w[C + c], gg1 = rstd * g2w[C + c + 1], og0 = g2b[C + c], og1 = g2b[C + c + 1];
+            const float sc0 = scale[c], sc1 = scale[c + 1];
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+            {
+                float *r0 = xs + (16 * (warp + WARPS * i) + g) * LD + c;
+                float *r1 = r0 + 8 * LD;
+                r0[0] += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
+                r0[1] += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
+                r1[0] += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
+                r1[1] += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < T * C / 4; i += THREADS)
+    {
+        const int tt = (4 * i) / C, c = (4 * i) % C;
+        if (p0 + tt < L)
+        {
+            const float *sr = xs + tt * LD + c;
+            *reinterpret_cast<float4 *>(xg + (size_t)(p0 + tt) * C + c) = make_float4(sr[0], sr[1], sr[2], sr[3]);
+        }
+    }
+}
+
+__host__ __device__ constexpr size_t time_smem(int C, int hid, int phase)
+{
+    return phase == 0 ? (size_t)(T + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 + hid_pad(hid) * 4 + 16
+                      : (size_t)(phase == 2 ? T * (C + 1) * 4 : 0) + (size_t)((nvec(C, hid_pad(hid)) + 3) & ~3) * 4 +
+                            (size_t)2 * C * w2ld(hid_pad(hid)) * 2 + 16;
+}
+
+template <int C, int HID> static int time_set_attr()
+{
+    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 0)));
+    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 1)));
+    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 2)));
+    return 0;
+}
+
+template <int C, int HID>
+static int time_launch(float *x, float *hbuf, const float *params, int B, int L, int hs, double *const *stats, cudaStream_t st)
+{
+    const dim3 grid((L + T - 1) / T, B);
+    for (int sub = 0; sub < 2; ++sub)
+    {
+        const float *P = params + (size_t)sub * p_stride(C, HID);
+        double *s1 = stats[2 * sub], *s2 = stats[2 * sub + 1];
+        dconv_time_kernel<C, HID, 0><<<grid, THREADS, time_smem(C, HID, 0), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 1><<<grid, THREADS, time_smem(C, HID, 1), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 2><<<grid, THREADS, time_smem(C, HID, 2), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+    }
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
 template <int C, int HID> static int set_attr()
 {
     DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -375,7 +707,31 @@ bool dconv_mma_supported(int C, int hid, int V)
 
 int dconv_mma_init_device()
 {
-    return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>();
+    return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>() || dm::time_set_attr<48, 6>() ||
+           dm::time_set_attr<48, 12>() || dm::time_set_attr<96, 12>() || dm::time_set_attr<96, 24>();
+}
+
+bool dconv_time_mma_supported(int C, int hid, int hs)
+{
+    return (hs % 2) == 0 && hs >= hid &&
+           ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && (hid == 12 || hid == 24)));
+}
+
+// Time branch: x [B][L][C] in place, hbuf [B][L][hs] scratch, stats: four zeroed (sum, sumsq)[B] buffers
+// (sub-block 0 GN1, GN2, sub-block 1 GN1, GN2); six launches.
+int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int L, int C, int hid, int hs,
+                          double *const *stats, cudaStream_t st)
+{
+    if (C == 48 && hid == 6)
+        return dm::time_launch<48, 6>(x, hbuf, params, B, L, hs, stats, st);
+    if (C == 48 && hid == 12)
+        return dm::time_launch<48, 12>(x, hbuf, params, B, L, hs, stats, st);
+    if (C == 96 && hid == 12)
+        return dm::time_launch<96, 12>(x, hbuf, params, B, L, hs, stats, st);
+    if (C == 96 && hid == 24)
+        return dm::time_launch<96, 24>(x, hbuf, params, B, L, hs, stats, st);
+    set_error("dconv_time_mma: unsupported shape");
+    return -1;
 }
 
 // x: [items][336][C] in place; items = B * F frequency rows; params: the fp32 block of dconv_fused.cu

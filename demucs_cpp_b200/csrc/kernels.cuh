@@ -112,6 +112,9 @@ int launch_dconv_fused(float *x, const float *params, int items, int C, int hid,
 bool dconv_mma_supported(int C, int hid, int V);
 int dconv_mma_init_device();
 int launch_dconv_mma(float *x, const float *params, int items, int C, int hid, cudaStream_t st);
+bool dconv_time_mma_supported(int C, int hid, int hs);
+int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int L, int C, int hid, int hs,
+                          double *const *stats, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // v3_kernels.cu (hdemucs_mmi)

@@ -362,6 +362,18 @@ struct Fwd
                 rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
             return;
         }
+        if (!per_u && U == 1 && w.fused && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
+        {
+            if (rc)
+                return;
+            // time branch, bf16 mode: three tensor-core launches per sub-block, y never stored
+            double *sl[4] = {stat_slots(B), stat_slots(B), stat_slots(B), stat_slots(B)};
+            ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
+                         2.0 * (double)B * V * (3.0 * C + 3.0 * hidp) * 4.0);
+            m->launches += 5;
+            rc = launch_dconv_time_mma(x, h, w.fused, B, V, C, hid, hidp, sl, st);
+            return;
+        }
         const size_t items = (size_t)B * (per_u ? U : 1);
         for (int j = 0; j < 2; ++j)
         {
