@@ -386,6 +386,17 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
                 p.du[t] = 0;
                 p.dv[t] = t - 2;
             }
+            if (te.Cin == 2 && TLENS[i] % 2 == 0)
+            {
+                // stereo input: the same convolution over PAIRS of samples (4 values per row, k4 s2 p1) -- identical
+                // K ordering (tap*2 + ch), but rows are 16 bytes, so the gather runs on the vector path
+                p.lda = p.Cin = 4;
+                p.Vi = TLENS[i] / 2;
+                p.ntaps = 4;
+                p.sv = 2;
+                for (int t = 0; t < 4; ++t)
+                    p.dv[t] = t - 1;
+            }
             p.act = 1;
             f.gemm(p, PC_GEMM_CONV);
             f.dconv(m->cA_t, 1, TLENS[i + 1], te.dc, m->h_t, m->y2_t, 0);
