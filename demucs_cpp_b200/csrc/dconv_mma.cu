@@ -121,19 +121,22 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
         const int row = r < HALO ? r : T + r; // rows 0,1 and T+2,T+3
         reinterpret_cast<uint32_t *>(xb + row * XLD)[c2] = 0u;
     }
-    for (int i = tid; i < T * C / 4; i += THREADS)
+    // fp32 rows by 4-byte async copies (the odd row stride rules out wider ones): all of a thread's copies are in
+    // flight at once instead of one exposed load latency per loop iteration; the bf16 copy is made from shared memory
+    for (int i = tid; i < T * C; i += THREADS)
     {
-        const float4 v = *reinterpret_cast<const float4 *>(xg + 4 * i);
-        const int tt = (4 * i) / C, c = (4 * i) % C;
-        float *d = xs + tt * LD + c;
-        d[0] = v.x;
-        d[1] = v.y;
-        d[2] = v.z;
-        d[3] = v.w;
-        uint2 pk;
-        pk.x = pack2(v.x, v.y);
-        pk.y = pack2(v.z, v.w);
-        *reinterpret_cast<uint2 *>(xb + (tt + HALO) * XLD + c) = pk;
+        const int tt = i / C, c = i - tt * C;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(xs + tt * LD + c)),
+                     "l"(xg + i)
+                     : "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    for (int i = tid; i < T * C / 2; i += THREADS)
+    {
+        const int tt = (2 * i) / C, c = (2 * i) % C;
+        const float *sr = xs + tt * LD + c;
+        *reinterpret_cast<uint32_t *>(xb + (tt + HALO) * XLD + c) = pack2(sr[0], sr[1]);
     }
 
 #pragma unroll 1
@@ -387,6 +390,7 @@ __global__ void __launch_bounds__(THREADS)
         __nv_bfloat16 *xb = reinterpret_cast<__nv_bfloat16 *>(smraw); // [T + 4][XLD], row r <-> position p0 + r - 2
         __nv_bfloat16 *w1b = xb + (T + 2 * HALO) * XLD;
         float *b1 = reinterpret_cast<float *>(w1b + HP * K1LD);
+#pragma unroll 6
         for (int i = tid; i < (T + 2 * HALO) * C / 4; i += THREADS)
         {
             const int r = (4 * i) / C, c = (4 * i) % C;
@@ -488,18 +492,18 @@ __global__ void __launch_bounds__(THREADS)
     (void)b1;
     if (PHASE == 2)
     {
-        for (int i = tid; i < T * C / 4; i += THREADS)
+        for (int i = tid; i < T * C; i += THREADS)
         {
-            const int tt = (4 * i) / C, c = (4 * i) % C;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int tt = i / C, c = i - tt * C;
             if (p0 + tt < L)
-                v = *reinterpret_cast<const float4 *>(xg + (size_t)(p0 + tt) * C + c);
-            float *d = xs + tt * LD + c;
-            d[0] = v.x;
-            d[1] = v.y;
-            d[2] = v.z;
-            d[3] = v.w;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(
+                                 (uint32_t)__cvta_generic_to_shared(xs + tt * LD + c)),
+                             "l"(xg + (size_t)p0 * C + i)
+                             : "memory");
+            else
+                xs[tt * LD + c] = 0.f;
         }
+        asm volatile("cp.async.wait_all;" ::: "memory");
     }
     for (int i = tid; i < 2 * C * HP; i += THREADS)
     {
