@@ -315,14 +315,21 @@ def main():
     if rank == 0:
         sampler.start()
     launches0 = sum(mm.launch_count for mm in models)
-    for mm in models:
-        mm.profile_begin()
     t0 = time.perf_counter()
     dev_ms = 0.0
     for _ in range(args.steps):
         dev_ms += step_device()
     sync_all()
     wall_ms = (time.perf_counter() - t0) * 1e3
+    launches = sum(mm.launch_count for mm in models) - launches0
+    # ---- the same K steps again with per-class CUDA events (kernel classes, roofline): bracketing every launch
+    # with events serialises the two branch streams, so this pass is kept out of the timed region above ----
+    for mm in models:
+        mm.profile_begin()
+    prof_dev_ms = 0.0
+    for _ in range(args.steps):
+        prof_dev_ms += step_device()
+    sync_all()
     prof = None
     for mm in models:
         pr = mm.profile_end()
@@ -333,7 +340,6 @@ def main():
                 for f in pr[k]:
                     prof[k][f] += pr[k][f]
     clocks = sampler.stop() if rank == 0 else None
-    launches = sum(mm.launch_count for mm in models) - launches0
 
     # ---- end-to-end timing ----
     for _ in range(2):
@@ -391,7 +397,7 @@ def main():
                 "frac": f_h, "peak_source": peaks["src"] + " copy bandwidth"}
     roof["other_roofline_frac"] = min(f_t, f_h)
     roof["avg_launch_ms"] = dc["ms"] / max(dc["launches"], 1)
-    roof["share_of_step"] = (dc["ms"] / args.steps) / (dev_ms / args.steps)
+    roof["share_of_step"] = dc["ms"] / prof_dev_ms  # share inside the event-bracketed (single-stream) pass
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     roof["traffic"] = None
     if os.path.exists(tp):
@@ -407,6 +413,7 @@ def main():
         "data": "synthetic", "config": workload_config(args, world),
         "ms_per_segment": ms_per_step / nseg,
         "device_ms_per_step": dev_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+        "profiled_pass_ms_per_step": prof_dev_ms / args.steps,
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "ms_per_step": e2e_ms / args.steps,
                 "h2d_bytes_per_step": int(L * 2 * 4 * world), "d2h_bytes_per_step": int(L * 2 * S * 4)},
         "gpu_launches": int(launches),

@@ -275,9 +275,11 @@ int dmx_profile_sequence(dmx_model *m, int *cls_out, int capacity)
     if (!m)
         return -1;
     std::lock_guard<std::mutex> lk(m->mtx);
-    const int n = (int)m->prof.recs.size();
-    for (int i = 0; i < n && i < capacity && cls_out; ++i)
-        cls_out[i] = m->prof.recs[i].cls;
+    int n = 0; // one entry per kernel launch, in launch order
+    for (const ProfRec &r : m->prof.recs)
+        for (int k = 0; k < r.n; ++k, ++n)
+            if (cls_out && n < capacity)
+                cls_out[n] = r.cls;
     return n;
 }
 
@@ -310,7 +312,7 @@ int dmx_profile_end(dmx_model *m, double *ms, int64_t *launches, double *flops, 
         if (ms)
             ms[r.cls] += (double)t;
         if (launches)
-            launches[r.cls] += 1;
+            launches[r.cls] += r.n;
     }
     m->prof.recs.clear();
     m->prof.used = 0;

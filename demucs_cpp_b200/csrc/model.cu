@@ -24,13 +24,14 @@ cudaEvent_t Profiler::get()
     return pool[used++];
 }
 
-ProfScope::ProfScope(dmx_model *m_, int cls, double flops, double bytes) : m(m_)
+ProfScope::ProfScope(dmx_model *m_, int cls, double flops, double bytes, int nlaunch) : m(m_)
 {
-    m->launches++;
+    m->launches += nlaunch;
     if (!m->prof.on)
         return;
     ProfRec r;
     r.cls = cls;
+    r.n = nlaunch;
     r.e0 = m->prof.get();
     r.e1 = m->prof.get();
     e1 = r.e1;
@@ -122,6 +123,9 @@ int model_finalize(dmx_model *m)
         return model_v3_finalize(m);
     DMX_CUDA(cudaSetDevice(m->device));
     DMX_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+    DMX_CUDA(cudaStreamCreateWithFlags(&m->stream2, cudaStreamNonBlocking));
+    DMX_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
+    DMX_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
     DMX_CUDA(cudaEventCreate(&m->ev0));
     DMX_CUDA(cudaEventCreate(&m->ev1));
     DMX_CUDA(cudaEventCreate(&m->ev2));
@@ -334,6 +338,26 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     }
 
     // ---- encoders (src/model_inference.cpp:155-212, src/encdec.cpp:8-164) ----
+    // The time and frequency branches are independent through the encoders and through the decoders: the time
+    // branch runs on a second stream so its small deep-level launches fill SMs the frequency branch leaves idle.
+    // (Profiling mode keeps one stream: its per-class CUDA events bracket launches on m->stream.)
+    cudaStream_t st_t = m->prof.on ? st : m->stream2;
+    auto fork = [&]() -> int {
+        if (st_t == st)
+            return 0;
+        DMX_CUDA(cudaEventRecord(m->ev_fork, st));
+        DMX_CUDA(cudaStreamWaitEvent(st_t, m->ev_fork, 0));
+        return 0;
+    };
+    auto join = [&]() -> int {
+        if (st_t == st)
+            return 0;
+        DMX_CUDA(cudaEventRecord(m->ev_join, st_t));
+        DMX_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
+        return 0;
+    };
+    if (fork())
+        return -1;
     const float *xin_f = m->spec, *xin_t = m->xt_in;
     for (int i = 0; i < 4; ++i)
     {
@@ -341,6 +365,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         const EncW &fe = m->enc[i];
         const int C = fe.C;
         // time: conv k8 s4 p2 (+GELU), ceil-mode length
+        f.st = st_t;
         {
             GemmParams p = f.base(xin_t, te.Cin, te.Cin, te.conv, m->cA_t, C, 1, TLENS[i], 1, TLENS[i + 1]);
             p.ntaps = 8;
@@ -370,6 +395,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             f.gemm(r, PC_GEMM_CONV);
         }
         // freq: conv k8 s4 p2 along frequency (+GELU), frames are independent
+        f.st = st;
         {
             GemmParams p = f.base(xin_f, fe.Cin, fe.Cin, fe.conv, m->cA_f, C, FREQS[i], T, FREQS[i + 1], T);
             p.ntaps = 8;
@@ -396,6 +422,9 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         xin_f = m->e[i];
     }
 
+    f.st = st;
+    if (join())
+        return -1;
     // ---- cross-transformer (src/model_inference.cpp:214-309, src/crosstransformer.cpp:205-339) ----
     const int TF = 8 * T, TT = TLEN3;
     const float *tok_f = m->e[3], *tok_t = m->te[3];
@@ -435,11 +464,14 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     }
 
     // ---- decoders (src/model_inference.cpp:314-344, src/encdec.cpp:166-361) ----
+    if (fork())
+        return -1;
     for (int i = 0; i < 4; ++i)
     {
         const DecW &fd = m->dec[i];
         const DecW &td = m->tdec[i];
         const int C = fd.C, F = FREQS[4 - i], Lin = TLENS[4 - i], Lout = TLENS[3 - i];
+        f.st = st;
         {
             // (x + skip) -> 3x3 conv -> GLU
             GemmParams p = f.base(dec_in_f, C, C, fd.rewrite, m->cA_f, C, F, T, F, T);
@@ -473,6 +505,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
                 q.addC = m->e[2 - i]; // the next decoder's skip (src/encdec.cpp:172), added once here
             f.gemm(q, PC_GEMM_CONV);
         }
+        f.st = st_t;
         {
             GemmParams p = f.base(dec_in_t, C, C, td.rewrite, m->cA_t, C, 1, Lin, 1, Lin);
             if (i == 0)
@@ -507,14 +540,15 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         dec_in_f = m->dx[i];
         dec_in_t = m->dxt[i];
     }
-    if (f.rc)
+    f.st = st;
+    if (f.rc || join())
         return -1;
 
     // ---- de-normalise, per-source iSTFT, add time branch (src/model_inference.cpp:352-474) ----
     {
         // algorithmic bytes of iSTFT + mix (66.0 MB / segment for 4 sources)
         ProfScope ps(m, PC_ISTFT_FRAMES, 0.0,
-                     (double)B * ((double)4 * S * NBINS * T * 4 + (double)2 * S * SEG * 4 + (double)S * 2 * SEG * 4));
+                     (double)B * ((double)4 * S * NBINS * T * 4 + (double)2 * S * SEG * 4 + (double)S * 2 * SEG * 4), 2);
         if (launch_istft(m->dx[3], B, S, m->meanstd_x, m->window, m->tw, m->wss, m->dxt[3], m->meanstd_t, m->frames,
                          d_out, st))
             return -1;

@@ -77,6 +77,7 @@ enum ProfClass
 struct ProfRec
 {
     int cls;
+    int n = 1; // kernel launches inside the scope
     cudaEvent_t e0, e1;
 };
 
@@ -131,6 +132,8 @@ struct dmx_model
     std::map<std::string, dmx::HostTensor> host;
     std::vector<void *> allocs;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;          // time branch of the encoders / decoders (htdemucs), forked from `stream`
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::mutex mtx;
     int64_t launches = 0;
     dmx::Profiler prof;
@@ -178,7 +181,7 @@ struct ProfScope
 {
     dmx_model *m;
     cudaEvent_t e1 = nullptr;
-    ProfScope(dmx_model *m_, int cls, double flops = 0.0, double bytes = 0.0);
+    ProfScope(dmx_model *m_, int cls, double flops = 0.0, double bytes = 0.0, int nlaunch = 1);
     ~ProfScope();
 };
 int track_forward_shard(dmx_model *m, const float *d_audio, int64_t L, int shift, int rank, int world, float *d_y,

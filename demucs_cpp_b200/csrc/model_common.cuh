@@ -369,8 +369,7 @@ struct Fwd
             // time branch, bf16 mode: three tensor-core launches per sub-block, y never stored
             double *sl[4] = {stat_slots(B), stat_slots(B), stat_slots(B), stat_slots(B)};
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
-                         2.0 * (double)B * V * (3.0 * C + 3.0 * hidp) * 4.0);
-            m->launches += 5;
+                         2.0 * (double)B * V * (3.0 * C + 3.0 * hidp) * 4.0, 6);
             rc = launch_dconv_time_mma(x, h, w.fused, B, V, C, hid, hidp, sl, st);
             return;
         }
@@ -423,8 +422,7 @@ struct Fwd
         if (rc)
             return;
         double *s = stat_slots((size_t)B * G);
-        ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * rows_in * C * 8.0 + (double)B * rows_out * (glu ? C / 2 : C) * 4.0);
-        m->launches++;
+        ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * rows_in * C * 8.0 + (double)B * rows_out * (glu ? C / 2 : C) * 4.0, 2);
         rc = launch_group_norm_g(x, y, B, rows_in, rows_out, row0, C, G, s, w, b, act, glu, st);
     }
 

@@ -617,7 +617,7 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         return -1;
     {
         ProfScope ps(m, PC_ISTFT_FRAMES, 0.0,
-                     (double)B * ((double)16 * NBINS * T * 4 + (double)8 * SEG * 4 + (double)4 * 2 * SEG * 4));
+                     (double)B * ((double)16 * NBINS * T * 4 + (double)8 * SEG * 4 + (double)4 * 2 * SEG * 4), 2);
         if (launch_istft(m->dx[3], B, 4, m->meanstd_x, m->window, m->tw, m->wss, m->dxt[3], m->meanstd_t, m->frames, d_out,
                          st))
             return -1;
