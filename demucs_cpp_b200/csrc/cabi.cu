@@ -236,6 +236,13 @@ void dmx_model_free(dmx_model *m)
             cudaFree(m->d_out);
         if (m->stream)
             cudaStreamDestroy(m->stream);
+        if (m->stream2)
+            cudaStreamDestroy(m->stream2);
+        if (m->stream_copy)
+            cudaStreamDestroy(m->stream_copy);
+        for (cudaEvent_t e : {m->ev_fork, m->ev_join, m->ev_copy})
+            if (e)
+                cudaEventDestroy(e);
     }
     delete m->v3;
     delete m;
@@ -432,14 +439,7 @@ int dmx_separate(dmx_model *m, const float *audio_lr, int64_t n_frames, int shif
     const size_t S = (size_t)m->S;
     if (grow(&m->d_audio, &m->cap_audio, (size_t)n_frames * 2) || grow(&m->d_out, &m->cap_out, S * 2 * (size_t)n_frames))
         return -1;
-    DMX_CUDA(cudaMemcpyAsync(m->d_audio, audio_lr, (size_t)n_frames * 2 * sizeof(float), cudaMemcpyHostToDevice,
-                             m->stream));
-    if (track_separate(m, m->d_audio, n_frames, shift_offset, m->d_out, cb, user))
-        return -1;
-    DMX_CUDA(cudaMemcpyAsync(out, m->d_out, S * 2 * (size_t)n_frames * sizeof(float), cudaMemcpyDeviceToHost,
-                             m->stream));
-    DMX_CUDA(cudaStreamSynchronize(m->stream));
-    return 0;
+    return track_separate_host(m, audio_lr, n_frames, shift_offset, out, cb, user);
 }
 
 int dmx_forward_segments(dmx_model *m, const float *segs, int n_segments, float *out)

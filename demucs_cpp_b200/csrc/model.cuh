@@ -134,6 +134,8 @@ struct dmx_model
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;          // time branch of the encoders / decoders (htdemucs), forked from `stream`
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t stream_copy = nullptr;      // device -> host copies of finished output stretches (dmx_separate)
+    cudaEvent_t ev_copy = nullptr;
     std::mutex mtx;
     int64_t launches = 0;
     dmx::Profiler prof;
@@ -190,4 +192,6 @@ int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, 
                       float *d_out);
 int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
                    void *user);
+int track_separate_host(dmx_model *m, const float *h_audio, int64_t L, int shift, float *h_out, dmx_progress_fn cb,
+                        void *user);
 } // namespace dmx

@@ -108,10 +108,10 @@ __global__ void __launch_bounds__(256) extract_segments_kernel(const float2 *__r
 __global__ void __launch_bounds__(256) overlap_add_kernel(const float2 *__restrict__ y, // [slots][S][SEG]
                                                           int S, int nseg, int world, int cnt, int64_t L, int offset,
                                                           int64_t Ls, const double *__restrict__ stats,
-                                                          float *__restrict__ out)
+                                                          float *__restrict__ out, int64_t t_begin, int64_t t_end)
 {
-    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t0 >= L)
+    const int64_t t0 = t_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; // output samples [t_begin, t_end)
+    if (t0 >= t_end)
         return;
     float mean, stdv;
     track_mean_std(stats, L, mean, stdv);
@@ -274,7 +274,7 @@ int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, 
     {
         ProfScope ps(m, PC_TRACK, 0.0, (double)L * S * 8.0 * 2.3);
         overlap_add_kernel<<<(unsigned)((L + 255) / 256), 256, 0, st>>>((const float2 *)d_y_all, S, nseg, world, cnt, L,
-                                                                       shift, Ls, m->track_stats, d_out);
+                                                                       shift, Ls, m->track_stats, d_out, 0, L);
     }
     DMX_LAUNCH_CHECK();
     DMX_CUDA(cudaEventRecord(m->ev1, st));
@@ -297,6 +297,79 @@ int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, flo
     if (track_overlap_add(m, d_audio, L, shift, m->d_y, 1, d_out))
         return -1;
     // whole-call device time: from before the shard to the end of the overlap-add
+    std::swap(m->ev0, m->ev2);
+    return 0;
+}
+
+// Host-buffer form of track_separate (dmx_separate): the same work, pipelined with the transfers.  After each batch of
+// segments the stretch of the output that no later segment touches (everything before the next segment's first
+// sample) is overlap-added and copied to the host on a separate stream while the next batch computes, so only the
+// last stretch of the 4 x stereo stems (254 MB for a 3-minute track) is exposed after the final forward.
+int track_separate_host(dmx_model *m, const float *h_audio, int64_t L, int shift, float *h_out, dmx_progress_fn cb,
+                        void *user)
+{
+    if (check_track_args(L, shift, 0, 1))
+        return -1;
+    cudaStream_t st = m->stream;
+    const int S = m->S;
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    const int nseg = num_segments(L, shift);
+    if (ensure(&m->d_y, &m->cap_y, (size_t)nseg * S * SEG * 2))
+        return -1;
+    if (!m->stream_copy)
+    {
+        DMX_CUDA(cudaStreamCreateWithFlags(&m->stream_copy, cudaStreamNonBlocking));
+        DMX_CUDA(cudaEventCreateWithFlags(&m->ev_copy, cudaEventDisableTiming));
+    }
+    DMX_CUDA(cudaEventRecord(m->ev2, st));
+    DMX_CUDA(cudaMemcpyAsync(m->d_audio, h_audio, (size_t)L * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (track_stats(m, m->d_audio, L))
+        return -1;
+    int64_t t_prev = 0;
+    for (int j0 = 0; j0 < nseg; j0 += m->maxB)
+    {
+        const int nb = (nseg - j0) < m->maxB ? (nseg - j0) : m->maxB;
+        {
+            ProfScope ps(m, PC_TRACK, 0.0, (double)nb * SEG * 16.0);
+            extract_segments_kernel<<<dim3((SEG + 255) / 256, nb), 256, 0, st>>>(
+                (const float2 *)m->d_audio, L, shift, Ls, m->track_stats, j0, 1, (float2 *)m->mix);
+        }
+        DMX_LAUNCH_CHECK();
+        if (model_forward(m, m->mix, nb, m->d_y + (size_t)j0 * S * SEG * 2))
+            return -1;
+        // samples of the (unshifted) track before segment j0 + nb begins are final now
+        int64_t t_end = (int64_t)(j0 + nb) * SEG_STRIDE - (MAX_SHIFT - shift);
+        if (j0 + nb >= nseg || t_end > L)
+            t_end = L;
+        if (t_end > t_prev)
+        {
+            {
+                ProfScope ps(m, PC_TRACK, 0.0, (double)(t_end - t_prev) * S * 8.0 * 2.3);
+                overlap_add_kernel<<<(unsigned)((t_end - t_prev + 255) / 256), 256, 0, st>>>(
+                    (const float2 *)m->d_y, S, nseg, 1, nseg, L, shift, Ls, m->track_stats, m->d_out, t_prev, t_end);
+            }
+            DMX_LAUNCH_CHECK();
+            DMX_CUDA(cudaEventRecord(m->ev_copy, st));
+            DMX_CUDA(cudaStreamWaitEvent(m->stream_copy, m->ev_copy, 0));
+            DMX_CUDA(cudaMemcpyAsync(h_out + (size_t)S * 2 * t_prev, m->d_out + (size_t)S * 2 * t_prev,
+                                     (size_t)S * 2 * (size_t)(t_end - t_prev) * sizeof(float), cudaMemcpyDeviceToHost,
+                                     m->stream_copy));
+            t_prev = t_end;
+        }
+        if (cb)
+        {
+            DMX_CUDA(cudaStreamSynchronize(st));
+            const bool v3 = m->arch == DMX_ARCH_HDEMUCS_V3;
+            const int nmsg = v3 ? 22 : 26;
+            for (int j = j0; j < j0 + nb; ++j)
+                for (int sidx = 0; sidx < nmsg; ++sidx)
+                    cb(((float)j + (float)(sidx + 1) / (float)nmsg) / (float)nseg, v3 ? kStageMsgsV3[sidx] : kStageMsgs[sidx],
+                       user);
+        }
+    }
+    DMX_CUDA(cudaEventRecord(m->ev1, st));
+    DMX_CUDA(cudaStreamSynchronize(st));
+    DMX_CUDA(cudaStreamSynchronize(m->stream_copy));
     std::swap(m->ev0, m->ev2);
     return 0;
 }
