@@ -371,7 +371,6 @@ __global__ void __launch_bounds__(THREADS)
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;
     constexpr int NT2 = 2 * C / 8;
-    constexpr int LD = C + 1;
     constexpr int XLD = xld(C), K1LD = k1ld(C), W2LD = w2ld(HP);
     extern __shared__ __align__(16) uint8_t smraw[];
     // phase 0: xb | w1b | b1      phase 1: w2b | vec      phase 2: xs | w2b | vec
@@ -484,27 +483,11 @@ __global__ void __launch_bounds__(THREADS)
     }
 
     // ---- phases 1 and 2: hidden activations back from hbuf, normalised, as A fragments ----
-    float *xs = reinterpret_cast<float *>(smraw);                             // phase 2 only: [T][LD]
-    float *vec = xs + (PHASE == 2 ? T * LD : 0);
+    float *vec = reinterpret_cast<float *>(smraw);
     __nv_bfloat16 *w2b = reinterpret_cast<__nv_bfloat16 *>(vec + ((nvec(C, HP) + 3) & ~3));
     float *b1 = vec, *g1w = b1 + HP, *g1b = g1w + HP, *b2 = g1b + HP, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C,
           *scale = g2b + 2 * C;
     (void)b1;
-    if (PHASE == 2)
-    {
-        for (int i = tid; i < T * C; i += THREADS)
-        {
-            const int tt = i / C, c = i - tt * C;
-            if (p0 + tt < L)
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(
-                                 (uint32_t)__cvta_generic_to_shared(xs + tt * LD + c)),
-                             "l"(xg + (size_t)p0 * C + i)
-                             : "memory");
-            else
-                xs[tt * LD + c] = 0.f;
-        }
-        asm volatile("cp.async.wait_all;" ::: "memory");
-    }
     for (int i = tid; i < 2 * C * HP; i += THREADS)
     {
         const int n = i / HP, k = i - n * HP;
@@ -636,23 +619,25 @@ __global__ void __launch_bounds__(THREADS)
 #pragma unroll
             for (int i = 0; i < MT_PER_WARP; ++i)
             {
-                float *r0 = xs + (16 * (warp + WARPS * i) + g) * LD + c;
-                float *r1 = r0 + 8 * LD;
-                r0[0] += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
-                r0[1] += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
-                r1[0] += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
-                r1[1] += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
+                // the residual goes straight to global memory in the fragment layout: per request 8 rows x 32
+                // contiguous bytes (whole sectors), no shared-memory copy of x and no block barrier in this phase
+                float2 *r0 = reinterpret_cast<float2 *>(xg + (size_t)(p0 + 16 * (warp + WARPS * i) + g) * C + c);
+                float2 *r1 = reinterpret_cast<float2 *>(reinterpret_cast<float *>(r0) + 8 * C);
+                if (v0[i])
+                {
+                    float2 xv = *r0;
+                    xv.x += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
+                    xv.y += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
+                    *r0 = xv;
+                }
+                if (v1[i])
+                {
+                    float2 xv = *r1;
+                    xv.x += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
+                    xv.y += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
+                    *r1 = xv;
+                }
             }
-        }
-    }
-    __syncthreads();
-    for (int i = tid; i < T * C / 4; i += THREADS)
-    {
-        const int tt = (4 * i) / C, c = (4 * i) % C;
-        if (p0 + tt < L)
-        {
-            const float *sr = xs + tt * LD + c;
-            *reinterpret_cast<float4 *>(xg + (size_t)(p0 + tt) * C + c) = make_float4(sr[0], sr[1], sr[2], sr[3]);
         }
     }
 }
@@ -660,8 +645,7 @@ __global__ void __launch_bounds__(THREADS)
 __host__ __device__ constexpr size_t time_smem(int C, int hid, int phase)
 {
     return phase == 0 ? (size_t)(T + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 + hid_pad(hid) * 4 + 16
-                      : (size_t)(phase == 2 ? T * (C + 1) * 4 : 0) + (size_t)((nvec(C, hid_pad(hid)) + 3) & ~3) * 4 +
-                            (size_t)2 * C * w2ld(hid_pad(hid)) * 2 + 16;
+                      : (size_t)((nvec(C, hid_pad(hid)) + 3) & ~3) * 4 + (size_t)2 * C * w2ld(hid_pad(hid)) * 2 + 16;
 }
 
 template <int C, int HID> static int time_set_attr()
