@@ -498,11 +498,11 @@ __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.w
 
 __device__ __forceinline__ bool bulk_ok(const GemmParams &p, const int mode)
 {
-    return mode == 1 && !p.gamma && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && (p.N % (p.glu ? 8 : 4)) == 0;
+    return mode == 1 && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && (p.N % (p.glu ? 8 : 4)) == 0;
 }
 
-// Epilogue for row-major fp32 outputs with the identity mapping and no read-modify-write (the convolutions and
-// rewrites of the encoders / decoders, the DConv GEMMs): a lane keeps the row of its TMEM lane, applies bias / GELU /
+// Epilogue for row-major fp32 outputs with the identity mapping (the convolutions and rewrites of the encoders /
+// decoders, the DConv GEMMs, the LayerScale-residual linears of the transformer): a lane keeps the row of its TMEM lane, applies bias / GELU /
 // GLU in registers, writes the finished piece of its row (32 raw columns) into its own 144-byte slot of the warp's
 // staging buffer and hands it to the bulk-copy engine (cp.async.bulk shared -> global): the global stores cost one
 // instruction per row piece, are fully contiguous per request, and nothing is exchanged between lanes.  The
@@ -550,6 +550,23 @@ __device__ __forceinline__ void epilogue_tile_bulk(const GemmParams &p, const in
             for (int j = 0; j < 16; ++j)
                 v[j] = v[2 * j] * sigmoid_ref(v[2 * j + 1]);
             nout = nraw >> 1;
+        }
+        if (p.gamma && valid)
+        {
+            // LayerScale residual: the lane reads the old piece of its own row (the residual stream is L2 resident)
+            const float *orow = crow + (p.glu ? (rawc0 >> 1) : rawc0);
+            const float *grow = p.gamma + (p.glu ? (rawc0 >> 1) : rawc0);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < nout)
+                {
+                    const float4 o = *reinterpret_cast<const float4 *>(orow + j);
+                    const float4 gm = __ldg(reinterpret_cast<const float4 *>(grow + j));
+                    v[j] = o.x + gm.x * v[j];
+                    v[j + 1] = o.y + gm.y * v[j + 1];
+                    v[j + 2] = o.z + gm.z * v[j + 2];
+                    v[j + 3] = o.w + gm.w * v[j + 3];
+                }
         }
         float rs = 0.f, rss = 0.f;
         bulk_wait_read(); // the previous piece has left the slot
@@ -1287,6 +1304,9 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
             const uint32_t lane_addr = tmem_base + (uint32_t)acc * acc_cols + ((uint32_t)(q * 32) << 16);
             if (packed_direct)
                 epilogue_tile_packed(p, bn, nt * bn, lane_addr, my_prow, 32 * csel, 32 * (P_EPI_WARPS / 4));
+            else if (bulk_ok(p, plain_out) && !p.no_bulk)
+                epilogue_tile_bulk(p, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], stage, 32 * csel,
+                                   32 * (P_EPI_WARPS / 4), lane);
             else
                 epilogue_tile(p, bn, plain_out, nt * bn, lane_addr, rowinfo, stage, q, 32 * csel, 32 * (P_EPI_WARPS / 4), lane);
             tc_fence_before();
