@@ -696,17 +696,19 @@ bool dconv_mma_supported(int C, int hid, int V)
 int dconv_mma_init_device()
 {
     return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>() || dm::time_set_attr<48, 6>() ||
-           dm::time_set_attr<48, 12>() || dm::time_set_attr<96, 12>() || dm::time_set_attr<96, 24>();
+           dm::time_set_attr<48, 12>() || dm::time_set_attr<96, 12>() || dm::time_set_attr<96, 24>() ||
+           dm::time_set_attr<192, 24>();
 }
 
 bool dconv_time_mma_supported(int C, int hid, int hs)
 {
     return (hs % 2) == 0 && hs >= hid &&
-           ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && (hid == 12 || hid == 24)));
+           ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && (hid == 12 || hid == 24)) || (C == 192 && hid == 24));
 }
 
-// Time branch: x [B][L][C] in place, hbuf [B][L][hs] scratch, stats: four zeroed (sum, sumsq)[B] buffers
-// (sub-block 0 GN1, GN2, sub-block 1 GN1, GN2); six launches.
+// Tiled form: x [B][L][C] in place (B GroupNorm items of L positions: batch elements of the time branch, or
+// frequency rows with L = 336), hbuf [B][L][hs] scratch, stats: four zeroed (sum, sumsq)[B] buffers (sub-block 0 GN1,
+// GN2, sub-block 1 GN1, GN2); six launches.
 int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int L, int C, int hid, int hs,
                           double *const *stats, cudaStream_t st)
 {
@@ -718,6 +720,8 @@ int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int
         return dm::time_launch<96, 12>(x, hbuf, params, B, L, hs, stats, st);
     if (C == 96 && hid == 24)
         return dm::time_launch<96, 24>(x, hbuf, params, B, L, hs, stats, st);
+    if (C == 192 && hid == 24)
+        return dm::time_launch<192, 24>(x, hbuf, params, B, L, hs, stats, st);
     set_error("dconv_time_mma: unsupported shape");
     return -1;
 }

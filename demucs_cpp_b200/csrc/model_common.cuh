@@ -204,7 +204,7 @@ static int pack_dconv(dmx_model *m, DConvW &d, const std::string &prefix, int C,
             upload_vec(m, &d.scale[j], p + "6.scale", C))
             return -1;
     }
-    if (dconv_fused_supported(C, d.hid, LE))
+    if (dconv_fused_supported(C, d.hid, LE) || dconv_time_mma_supported(C, d.hid, d.hidp))
     {
         // parameter block of the fused kernel: per sub-block W1[3][C][HID] | b1 | g1w | g1b | W2[2C][HID] | b2 | g2w | g2b | scale
         std::vector<float> blk;
@@ -362,15 +362,18 @@ struct Fwd
                 rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
             return;
         }
-        if (!per_u && U == 1 && w.fused && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
+        if ((per_u || U == 1) && w.fused && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
         {
             if (rc)
                 return;
-            // time branch, bf16 mode: three tensor-core launches per sub-block, y never stored
-            double *sl[4] = {stat_slots(B), stat_slots(B), stat_slots(B), stat_slots(B)};
-            ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
-                         2.0 * (double)B * V * (3.0 * C + 3.0 * hidp) * 4.0, 6);
-            rc = launch_dconv_time_mma(x, h, w.fused, B, V, C, hid, hidp, sl, st);
+            // bf16 mode, tiled form: three tensor-core launches per sub-block, y never stored.  GroupNorm items are
+            // the batch elements (time branch) or the B*U frequency rows (the 192-channel level, too wide for the
+            // row-resident kernel above)
+            const int items = per_u ? B * U : B;
+            double *sl[4] = {stat_slots(items), stat_slots(items), stat_slots(items), stat_slots(items)};
+            ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
+                         2.0 * (double)B * U * V * (3.0 * C + 3.0 * hidp) * 4.0, 6);
+            rc = launch_dconv_time_mma(x, h, w.fused, items, V, C, hid, hidp, sl, st);
             return;
         }
         const size_t items = (size_t)B * (per_u ? U : 1);
