@@ -19,6 +19,8 @@
 
 #include <cuda_bf16.h>
 
+#include <cstring>
+
 namespace dmx
 {
 namespace dm
@@ -45,6 +47,26 @@ __host__ __device__ constexpr size_t smem_bytes(int C, int hid)
 // fp32 parameter block shared with dconv_fused.cu, per sub-block:
 //   W1[3][C][HID] | b1[HID] | g1w[HID] | g1b[HID] | W2[2C][HID] | b2[2C] | g2w[2C] | g2b[2C] | scale[C]
 __host__ __device__ constexpr int p_stride(int C, int HID) { return 3 * C * HID + 3 * HID + 2 * C * HID + 6 * C + C; }
+
+// Pre-packed parameters (built once at model finalize by dconv_mma_pack): per sub-block, exactly the shared-memory
+// images the kernels use -- w1b [HP][K1LD] bf16 (k = tap*C + c, zero padded) | w2b [2C][W2LD] bf16 | vec fp32
+// (b1 g1w g1b [HP each] | b2 g2w g2b [2C each] | scale [C], rounded up to 4 floats) -- so a CTA fetches them with
+// 16-byte async copies instead of converting fp32 weights element by element (that conversion, a dependent L2 load
+// per element, was most of the run time of the short tiled kernels).
+__host__ __device__ constexpr int pk_w1_bytes(int C, int hp) { return hp * k1ld(C) * 2; }
+__host__ __device__ constexpr int pk_w2_bytes(int C, int hp) { return 2 * C * w2ld(hp) * 2; }
+__host__ __device__ constexpr int pk_vec_bytes(int C, int hp) { return ((nvec(C, hp) + 3) & ~3) * 4; }
+__host__ __device__ constexpr int pk_sub_bytes(int C, int hp) { return pk_w1_bytes(C, hp) + pk_w2_bytes(C, hp) + pk_vec_bytes(C, hp); }
+
+__device__ __forceinline__ void copy16_async(void *sdst, const void *gsrc, int bytes)
+{
+    for (int i = threadIdx.x * 16; i < bytes; i += THREADS * 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(reinterpret_cast<uint8_t *>(sdst) + i)),
+                     "l"(reinterpret_cast<const uint8_t *>(gsrc) + i)
+                     : "memory");
+}
+__device__ __forceinline__ void async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ void mma_k16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
                                         uint32_t b1)
@@ -92,14 +114,13 @@ __device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
     b = sb;
 }
 
-template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_kernel(float *__restrict__ x, const float *__restrict__ params)
+template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_kernel(float *__restrict__ x, const uint8_t *__restrict__ params)
 {
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;       // n-tiles of the k3 conv
     constexpr int NT2 = 2 * C / 8;    // n-tiles of the 1x1 conv
     constexpr int LD = C + 1;
     constexpr int XLD = xld(C), K1LD = k1ld(C), W2LD = w2ld(HP);
-    constexpr int PS = p_stride(C, HID);
     extern __shared__ __align__(16) uint8_t smraw[];
     float *xs = reinterpret_cast<float *>(smraw);                                 // [T][LD] fp32 residual stream
     float *vec = xs + T * LD;                                                     // small fp32 vectors
@@ -143,37 +164,13 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
     for (int sub = 0; sub < 2; ++sub)
     {
         const int dil = 1 << sub;
-        const float *P = params + (size_t)sub * PS;
+        const uint8_t *P = params + (size_t)sub * pk_sub_bytes(C, HP);
         __syncthreads(); // previous sub-block done with the weights; xs / xb complete
-        // ---- weights of this sub-block -> bf16 operand layouts, vectors -> fp32 ----
-        for (int i = tid; i < HP * 3 * C; i += THREADS)
-        {
-            const int n = i / (3 * C), k = i - n * (3 * C); // k = tap*C + c
-            const float w = n < HID ? __ldg(P + (size_t)k * HID + n) : 0.f;
-            w1b[n * K1LD + k] = __float2bfloat16(w);
-        }
-        const float *Pb1 = P + 3 * C * HID, *Pg1w = Pb1 + HID, *Pg1b = Pg1w + HID, *PW2 = Pg1b + HID;
-        const float *Pb2 = PW2 + 2 * C * HID, *Pg2w = Pb2 + 2 * C, *Pg2b = Pg2w + 2 * C, *Psc = Pg2b + 2 * C;
-        for (int i = tid; i < 2 * C * HP; i += THREADS)
-        {
-            const int n = i / HP, k = i - n * HP;
-            const float w = k < HID ? __ldg(PW2 + (size_t)n * HID + k) : 0.f;
-            w2b[n * W2LD + k] = __float2bfloat16(w);
-        }
-        for (int i = tid; i < HP; i += THREADS)
-        {
-            b1[i] = i < HID ? __ldg(Pb1 + i) : 0.f;
-            g1w[i] = i < HID ? __ldg(Pg1w + i) : 0.f;
-            g1b[i] = i < HID ? __ldg(Pg1b + i) : 0.f;
-        }
-        for (int i = tid; i < 2 * C; i += THREADS)
-        {
-            b2[i] = __ldg(Pb2 + i);
-            g2w[i] = __ldg(Pg2w + i);
-            g2b[i] = __ldg(Pg2b + i);
-        }
-        for (int i = tid; i < C; i += THREADS)
-            scale[i] = __ldg(Psc + i);
+        // ---- parameters of this sub-block: pre-packed shared-memory images ----
+        copy16_async(w1b, P, pk_w1_bytes(C, HP));
+        copy16_async(w2b, P + pk_w1_bytes(C, HP), pk_w2_bytes(C, HP));
+        copy16_async(vec, P + pk_w1_bytes(C, HP) + pk_w2_bytes(C, HP), pk_vec_bytes(C, HP));
+        async_wait_all();
         __syncthreads();
 
         // ---- conv k3, dilation dil: h[16 positions][HP] per m-tile, accumulators in the C-fragment layout ----
@@ -363,14 +360,15 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
 //   phase 2: recompute g and y; x += scale * GLU(GN2(y))
 // x is read twice and written once, h (C/8 wide) written once and read twice, y (2C wide) never stored -- against
 // x / h / y passing through three GEMM + pointwise launches with y materialised (src/layers.cpp:152-375).
-template <int C, int HID, int PHASE>
+template <int C, int HID, int PHASE, int MTW>
 __global__ void __launch_bounds__(THREADS)
-    dconv_time_kernel(float *__restrict__ x, float *__restrict__ hbuf, const float *__restrict__ P, const int L, const int hs,
+    dconv_time_kernel(float *__restrict__ x, float *__restrict__ hbuf, const uint8_t *__restrict__ P, const int L, const int hs,
                       const int dil, double *__restrict__ stats1, double *__restrict__ stats2)
 {
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;
     constexpr int NT2 = 2 * C / 8;
+    constexpr int TT = 16 * WARPS * MTW; // positions per tile: MTW m-tiles of 16 per warp
     constexpr int XLD = xld(C), K1LD = k1ld(C), W2LD = w2ld(HP);
     extern __shared__ __align__(16) uint8_t smraw[];
     // phase 0: xb | w1b | b1      phase 1: w2b | vec      phase 2: xs | w2b | vec
@@ -378,19 +376,16 @@ __global__ void __launch_bounds__(THREADS)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
     const int b = blockIdx.y;
-    const int p0 = blockIdx.x * T; // first position of the tile
+    const int p0 = blockIdx.x * TT; // first position of the tile
     float *xg = x + (size_t)b * L * C;
     float *hg = hbuf + (size_t)b * L * hs;
-    const float *Pb1 = P + 3 * C * HID, *Pg1w = Pb1 + HID, *Pg1b = Pg1w + HID, *PW2 = Pg1b + HID;
-    const float *Pb2 = PW2 + 2 * C * HID, *Pg2w = Pb2 + 2 * C, *Pg2b = Pg2w + 2 * C, *Psc = Pg2b + 2 * C;
-
     if (PHASE == 0)
     {
         __nv_bfloat16 *xb = reinterpret_cast<__nv_bfloat16 *>(smraw); // [T + 4][XLD], row r <-> position p0 + r - 2
-        __nv_bfloat16 *w1b = xb + (T + 2 * HALO) * XLD;
+        __nv_bfloat16 *w1b = xb + (TT + 2 * HALO) * XLD;
         float *b1 = reinterpret_cast<float *>(w1b + HP * K1LD);
 #pragma unroll 6
-        for (int i = tid; i < (T + 2 * HALO) * C / 4; i += THREADS)
+        for (int i = tid; i < (TT + 2 * HALO) * C / 4; i += THREADS)
         {
             const int r = (4 * i) / C, c = (4 * i) % C;
             const int pos = p0 + r - HALO;
@@ -402,17 +397,13 @@ __global__ void __launch_bounds__(THREADS)
             pk.y = pack2(v.z, v.w);
             *reinterpret_cast<uint2 *>(xb + r * XLD + c) = pk;
         }
-        for (int i = tid; i < HP * 3 * C; i += THREADS)
-        {
-            const int n = i / (3 * C), k = i - n * (3 * C);
-            w1b[n * K1LD + k] = __float2bfloat16(n < HID ? __ldg(P + (size_t)k * HID + n) : 0.f);
-        }
-        for (int i = tid; i < HP; i += THREADS)
-            b1[i] = i < HID ? __ldg(Pb1 + i) : 0.f;
+        copy16_async(w1b, P, pk_w1_bytes(C, HP));
+        copy16_async(b1, P + pk_w1_bytes(C, HP) + pk_w2_bytes(C, HP), HP * 4);
+        async_wait_all();
         __syncthreads();
-        float acc[MT_PER_WARP][NT1][4];
+        float acc[MTW][NT1][4];
 #pragma unroll
-        for (int i = 0; i < MT_PER_WARP; ++i)
+        for (int i = 0; i < MTW; ++i)
 #pragma unroll
             for (int nt = 0; nt < NT1; ++nt)
             {
@@ -435,7 +426,7 @@ __global__ void __launch_bounds__(THREADS)
                     bf[nt][1] = ld32(wp + 8);
                 }
 #pragma unroll
-                for (int i = 0; i < MT_PER_WARP; ++i)
+                for (int i = 0; i < MTW; ++i)
                 {
                     const int row0 = 16 * (warp + WARPS * i) + shift + g;
                     const __nv_bfloat16 *ap = xb + row0 * XLD + 16 * kc + 2 * t;
@@ -448,7 +439,7 @@ __global__ void __launch_bounds__(THREADS)
         }
         float sa = 0.f, sb = 0.f;
 #pragma unroll
-        for (int i = 0; i < MT_PER_WARP; ++i)
+        for (int i = 0; i < MTW; ++i)
         {
             const int q0 = p0 + 16 * (warp + WARPS * i) + g, q1 = q0 + 8;
 #pragma unroll
@@ -488,27 +479,12 @@ __global__ void __launch_bounds__(THREADS)
     float *b1 = vec, *g1w = b1 + HP, *g1b = g1w + HP, *b2 = g1b + HP, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C,
           *scale = g2b + 2 * C;
     (void)b1;
-    for (int i = tid; i < 2 * C * HP; i += THREADS)
-    {
-        const int n = i / HP, k = i - n * HP;
-        w2b[n * W2LD + k] = __float2bfloat16(k < HID ? __ldg(PW2 + (size_t)n * HID + k) : 0.f);
-    }
-    for (int i = tid; i < HP; i += THREADS)
-    {
-        g1w[i] = i < HID ? __ldg(Pg1w + i) : 0.f;
-        g1b[i] = i < HID ? __ldg(Pg1b + i) : 0.f;
-    }
-    for (int i = tid; i < 2 * C; i += THREADS)
-    {
-        b2[i] = __ldg(Pb2 + i);
-        g2w[i] = __ldg(Pg2w + i);
-        g2b[i] = __ldg(Pg2b + i);
-    }
-    for (int i = tid; i < C; i += THREADS)
-        scale[i] = __ldg(Psc + i);
+    copy16_async(w2b, P + pk_w1_bytes(C, HP), pk_w2_bytes(C, HP));
+    copy16_async(vec, P + pk_w1_bytes(C, HP) + pk_w2_bytes(C, HP), pk_vec_bytes(C, HP));
+    async_wait_all();
     __syncthreads();
 
-    uint32_t af[MT_PER_WARP][NT1][2];
+    uint32_t af[MTW][NT1][2];
     {
         float mean, rstd;
         stats_to_mean_rstd(stats1 + 2 * b, (double)L * HID, 1e-5f, mean, rstd);
@@ -518,7 +494,7 @@ __global__ void __launch_bounds__(THREADS)
             const int j = 8 * nt + 2 * t;
             const float w0 = rstd * g1w[j], w1 = rstd * g1w[j + 1], o0 = g1b[j], o1 = g1b[j + 1];
 #pragma unroll
-            for (int i = 0; i < MT_PER_WARP; ++i)
+            for (int i = 0; i < MTW; ++i)
             {
                 const int q0 = p0 + 16 * (warp + WARPS * i) + g, q1 = q0 + 8;
                 float2 h0 = make_float2(0.f, 0.f), h1 = h0;
@@ -534,10 +510,10 @@ __global__ void __launch_bounds__(THREADS)
             }
         }
     }
-    auto conv2 = [&](int nt, float (&d)[MT_PER_WARP][4]) {
+    auto conv2 = [&](int nt, float (&d)[MTW][4]) {
         const float bb0 = b2[8 * nt + 2 * t], bb1 = b2[8 * nt + 2 * t + 1];
 #pragma unroll
-        for (int i = 0; i < MT_PER_WARP; ++i)
+        for (int i = 0; i < MTW; ++i)
         {
             d[i][0] = d[i][2] = bb0;
             d[i][1] = d[i][3] = bb1;
@@ -547,7 +523,7 @@ __global__ void __launch_bounds__(THREADS)
         {
             const uint32_t b0 = ld32(wp);
 #pragma unroll
-            for (int i = 0; i < MT_PER_WARP; ++i)
+            for (int i = 0; i < MTW; ++i)
                 mma_k8(d[i], af[i][0][0], af[i][0][1], b0);
         }
         else
@@ -557,15 +533,15 @@ __global__ void __launch_bounds__(THREADS)
             {
                 const uint32_t b0 = ld32(wp + 16 * s), b1v = ld32(wp + 16 * s + 8);
 #pragma unroll
-                for (int i = 0; i < MT_PER_WARP; ++i)
+                for (int i = 0; i < MTW; ++i)
                     mma_k16(d[i], af[i][(2 * s) % NT1][0], af[i][(2 * s) % NT1][1], af[i][(2 * s + 1) % NT1][0],
                             af[i][(2 * s + 1) % NT1][1], b0, b1v);
             }
         }
     };
-    bool v0[MT_PER_WARP], v1[MT_PER_WARP];
+    bool v0[MTW], v1[MTW];
 #pragma unroll
-    for (int i = 0; i < MT_PER_WARP; ++i)
+    for (int i = 0; i < MTW; ++i)
     {
         const int q0 = p0 + 16 * (warp + WARPS * i) + g;
         v0[i] = q0 < L;
@@ -577,10 +553,10 @@ __global__ void __launch_bounds__(THREADS)
 #pragma unroll 4
         for (int nt = 0; nt < NT2; ++nt)
         {
-            float d[MT_PER_WARP][4];
+            float d[MTW][4];
             conv2(nt, d);
 #pragma unroll
-            for (int i = 0; i < MT_PER_WARP; ++i)
+            for (int i = 0; i < MTW; ++i)
             {
                 if (v0[i])
                 {
@@ -609,7 +585,7 @@ __global__ void __launch_bounds__(THREADS)
 #pragma unroll 2
         for (int nt = 0; nt < C / 8; ++nt)
         {
-            float da[MT_PER_WARP][4], dg[MT_PER_WARP][4];
+            float da[MTW][4], dg[MTW][4];
             conv2(nt, da);
             conv2(nt + C / 8, dg);
             const int c = 8 * nt + 2 * t;
@@ -617,7 +593,7 @@ __global__ void __launch_bounds__(THREADS)
             const float gg0 = rstd * g2w[C + c], gg1 = rstd * g2w[C + c + 1], og0 = g2b[C + c], og1 = g2b[C + c + 1];
             const float sc0 = scale[c], sc1 = scale[c + 1];
 #pragma unroll
-            for (int i = 0; i < MT_PER_WARP; ++i)
+            for (int i = 0; i < MTW; ++i)
             {
                 // the residual goes straight to global memory in the fragment layout: per request 8 rows x 32
                 // contiguous bytes (whole sectors), no shared-memory copy of x and no block barrier in this phase
@@ -642,31 +618,38 @@ __global__ void __launch_bounds__(THREADS)
     }
 }
 
-__host__ __device__ constexpr size_t time_smem(int C, int hid, int phase)
+__host__ __device__ constexpr size_t time_smem(int C, int hid, int phase, int mtw)
 {
-    return phase == 0 ? (size_t)(T + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 + hid_pad(hid) * 4 + 16
+    return phase == 0 ? (size_t)(16 * WARPS * mtw + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 + hid_pad(hid) * 4 + 16
                       : (size_t)((nvec(C, hid_pad(hid)) + 3) & ~3) * 4 + (size_t)2 * C * w2ld(hid_pad(hid)) * 2 + 16;
 }
 
+// m-tiles per warp: 3 (336-position tiles) for the long 48- / 96-channel signals, 1 (112 positions) for the
+// 192-channel level, whose items are short (336 frames, 5375 samples): three times the CTAs to fill the SMs
+__host__ __device__ constexpr int time_mtw(int C) { return C >= 192 ? 1 : 3; }
+
 template <int C, int HID> static int time_set_attr()
 {
-    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 0)));
-    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 1)));
-    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 2)));
+    constexpr int M = time_mtw(C);
+    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 0, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 0, M)));
+    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 1, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 1, M)));
+    DMX_CUDA(cudaFuncSetAttribute(dconv_time_kernel<C, HID, 2, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)time_smem(C, HID, 2, M)));
     return 0;
 }
 
 template <int C, int HID>
-static int time_launch(float *x, float *hbuf, const float *params, int B, int L, int hs, double *const *stats, cudaStream_t st)
+static int time_launch(float *x, float *hbuf, const uint8_t *params, int B, int L, int hs, double *const *stats, cudaStream_t st)
 {
-    const dim3 grid((L + T - 1) / T, B);
+    constexpr int M = time_mtw(C);
+    constexpr int TT = 16 * WARPS * M;
+    const dim3 grid((L + TT - 1) / TT, B);
     for (int sub = 0; sub < 2; ++sub)
     {
-        const float *P = params + (size_t)sub * p_stride(C, HID);
+        const uint8_t *P = params + (size_t)sub * pk_sub_bytes(C, hid_pad(HID));
         double *s1 = stats[2 * sub], *s2 = stats[2 * sub + 1];
-        dconv_time_kernel<C, HID, 0><<<grid, THREADS, time_smem(C, HID, 0), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
-        dconv_time_kernel<C, HID, 1><<<grid, THREADS, time_smem(C, HID, 1), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
-        dconv_time_kernel<C, HID, 2><<<grid, THREADS, time_smem(C, HID, 2), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 0, M><<<grid, THREADS, time_smem(C, HID, 0, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 1, M><<<grid, THREADS, time_smem(C, HID, 1, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 2, M><<<grid, THREADS, time_smem(C, HID, 2, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
     }
     DMX_LAUNCH_CHECK();
     return 0;
@@ -678,7 +661,7 @@ template <int C, int HID> static int set_attr()
                                   (int)smem_bytes(C, HID)));
     return 0;
 }
-template <int C, int HID> static int launch(float *x, const float *params, int items, cudaStream_t st)
+template <int C, int HID> static int launch(float *x, const uint8_t *params, int items, cudaStream_t st)
 {
     dconv_mma_kernel<C, HID><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params);
     DMX_LAUNCH_CHECK();
@@ -706,12 +689,62 @@ bool dconv_time_mma_supported(int C, int hid, int hs)
            ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && (hid == 12 || hid == 24)) || (C == 192 && hid == 24));
 }
 
+// Floats (4-byte units) of the packed parameter block of one DConv (two sub-blocks); 0 = shape not handled here.
+int dconv_mma_pack_floats(int C, int hid)
+{
+    if (!dconv_mma_supported(C, hid, dm::T) && !dconv_time_mma_supported(C, hid, hid + (hid & 1)))
+        return 0;
+    return 2 * dm::pk_sub_bytes(C, dm::hid_pad(hid)) / 4;
+}
+
+// blk: the fp32 block of dconv_fused.cu (per sub-block W1[3][C][hid] | b1 g1w g1b | W2[2C][hid] | b2 g2w g2b | scale)
+// -> out: the shared-memory images of dconv_mma.cu, weights rounded to bf16 (round to nearest even)
+void dconv_mma_pack(int C, int hid, const float *blk, float *out)
+{
+    const int hp = dm::hid_pad(hid), K1 = dm::k1ld(C), W2 = dm::w2ld(hp);
+    const int sub = dm::pk_sub_bytes(C, hp);
+    uint8_t *o = reinterpret_cast<uint8_t *>(out);
+    memset(o, 0, (size_t)2 * sub);
+    for (int s = 0; s < 2; ++s)
+    {
+        const float *P = blk + (size_t)s * dm::p_stride(C, hid);
+        const float *Pb1 = P + 3 * C * hid, *Pg1w = Pb1 + hid, *Pg1b = Pg1w + hid, *PW2 = Pg1b + hid;
+        const float *Pb2 = PW2 + 2 * C * hid, *Pg2w = Pb2 + 2 * C, *Pg2b = Pg2w + 2 * C, *Psc = Pg2b + 2 * C;
+        __nv_bfloat16 *w1 = reinterpret_cast<__nv_bfloat16 *>(o + (size_t)s * sub);
+        __nv_bfloat16 *w2 = reinterpret_cast<__nv_bfloat16 *>(o + (size_t)s * sub + dm::pk_w1_bytes(C, hp));
+        float *vec = reinterpret_cast<float *>(o + (size_t)s * sub + dm::pk_w1_bytes(C, hp) + dm::pk_w2_bytes(C, hp));
+        for (int n = 0; n < hid; ++n)
+            for (int k = 0; k < 3 * C; ++k)
+                w1[n * K1 + k] = __float2bfloat16(P[(size_t)k * hid + n]);
+        for (int n = 0; n < 2 * C; ++n)
+            for (int k = 0; k < hid; ++k)
+                w2[n * W2 + k] = __float2bfloat16(PW2[(size_t)n * hid + k]);
+        float *b1 = vec, *g1w = b1 + hp, *g1b = g1w + hp, *b2 = g1b + hp, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C,
+              *scale = g2b + 2 * C;
+        for (int i = 0; i < hid; ++i)
+        {
+            b1[i] = Pb1[i];
+            g1w[i] = Pg1w[i];
+            g1b[i] = Pg1b[i];
+        }
+        for (int i = 0; i < 2 * C; ++i)
+        {
+            b2[i] = Pb2[i];
+            g2w[i] = Pg2w[i];
+            g2b[i] = Pg2b[i];
+        }
+        for (int i = 0; i < C; ++i)
+            scale[i] = Psc[i];
+    }
+}
+
 // Tiled form: x [B][L][C] in place (B GroupNorm items of L positions: batch elements of the time branch, or
 // frequency rows with L = 336), hbuf [B][L][hs] scratch, stats: four zeroed (sum, sumsq)[B] buffers (sub-block 0 GN1,
 // GN2, sub-block 1 GN1, GN2); six launches.
-int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int L, int C, int hid, int hs,
+int launch_dconv_time_mma(float *x, float *hbuf, const void *packed, int B, int L, int C, int hid, int hs,
                           double *const *stats, cudaStream_t st)
 {
+    const uint8_t *params = static_cast<const uint8_t *>(packed);
     if (C == 48 && hid == 6)
         return dm::time_launch<48, 6>(x, hbuf, params, B, L, hs, stats, st);
     if (C == 48 && hid == 12)
@@ -726,9 +759,10 @@ int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int
     return -1;
 }
 
-// x: [items][336][C] in place; items = B * F frequency rows; params: the fp32 block of dconv_fused.cu
-int launch_dconv_mma(float *x, const float *params, int items, int C, int hid, cudaStream_t st)
+// x: [items][336][C] in place; items = B * F frequency rows; packed: the block built by dconv_mma_pack
+int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st)
 {
+    const uint8_t *params = static_cast<const uint8_t *>(packed);
     if (C == 48 && hid == 6)
         return dm::launch<48, 6>(x, params, items, st);
     if (C == 48 && hid == 12)

@@ -111,9 +111,11 @@ int launch_dconv_fused(float *x, const float *params, int items, int C, int hid,
 // dconv_mma.cu: the same with both convolutions on tensor cores (mma.sync, bf16 operands); bf16 mode only
 bool dconv_mma_supported(int C, int hid, int V);
 int dconv_mma_init_device();
-int launch_dconv_mma(float *x, const float *params, int items, int C, int hid, cudaStream_t st);
+int dconv_mma_pack_floats(int C, int hid);
+void dconv_mma_pack(int C, int hid, const float *blk, float *out);
+int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st);
 bool dconv_time_mma_supported(int C, int hid, int hs);
-int launch_dconv_time_mma(float *x, float *hbuf, const float *params, int B, int L, int C, int hid, int hs,
+int launch_dconv_time_mma(float *x, float *hbuf, const void *packed, int B, int L, int C, int hid, int hs,
                           double *const *stats, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------

@@ -33,6 +33,7 @@ struct DConvW
     float *g1w[2], *g1b[2], *g2w[2], *g2b[2], *scale[2];
     int C = 0, hid = 0, hidp = 0;
     float *fused = nullptr; // parameter block of the fused shared-memory kernel (dconv_fused.cu), if the shape has one
+    float *fused_pk = nullptr; // the same pre-packed as bf16 shared-memory images for dconv_mma.cu
 };
 
 struct EncW

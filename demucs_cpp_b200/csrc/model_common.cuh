@@ -240,6 +240,13 @@ static int pack_dconv(dmx_model *m, DConvW &d, const std::string &prefix, int C,
         }
         if (upload(m, &d.fused, blk))
             return -1;
+        if (const int nf = dconv_mma_pack_floats(C, hid))
+        {
+            std::vector<float> pk((size_t)nf);
+            dconv_mma_pack(C, hid, blk.data(), pk.data());
+            if (upload(m, &d.fused_pk, pk))
+                return -1;
+        }
     }
     return 0;
 }
@@ -356,13 +363,13 @@ struct Fwd
             // one HBM read + one write of x; MACs: 2 sub-blocks x (k3 conv + the 1x1 conv evaluated twice)
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          (double)B * U * V * C * 8.0);
-            if (m->precision == DMX_PRECISION_BF16 && dconv_mma_supported(C, hid, V))
-                rc = launch_dconv_mma(x, w.fused, B * U, C, hid, st);
+            if (m->precision == DMX_PRECISION_BF16 && w.fused_pk && dconv_mma_supported(C, hid, V))
+                rc = launch_dconv_mma(x, w.fused_pk, B * U, C, hid, st);
             else
                 rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
             return;
         }
-        if ((per_u || U == 1) && w.fused && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
+        if ((per_u || U == 1) && w.fused_pk && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
         {
             if (rc)
                 return;
@@ -373,7 +380,7 @@ struct Fwd
             double *sl[4] = {stat_slots(items), stat_slots(items), stat_slots(items), stat_slots(items)};
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          2.0 * (double)B * U * V * (3.0 * C + 3.0 * hidp) * 4.0, 6);
-            rc = launch_dconv_time_mma(x, h, w.fused, items, V, C, hid, hidp, sl, st);
+            rc = launch_dconv_time_mma(x, h, w.fused_pk, items, V, C, hid, hidp, sl, st);
             return;
         }
         const size_t items = (size_t)B * (per_u ? U : 1);
