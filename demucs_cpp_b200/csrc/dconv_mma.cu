@@ -12,9 +12,9 @@
 //
 //     h = conv_k3_dil(x) ; g = GELU(GN1(h)) ; y = W2 g + b2 ; x += scale * GLU(GN2(y))
 // GroupNorm statistics: exact block reductions over the row in double, unbiased variance.  y is evaluated twice
-// (statistics, then normalise-GLU-residual) and never stored.  The residual stream x stays fp32 in shared memory;
-// only the MMA operands (x as the conv input, g, the weights) are rounded to bf16, like every other GEMM of the
-// bf16 mode.
+// (statistics, then normalise-GLU-residual) and never stored.  The residual stream x stays fp32 (updated in place in
+// global memory, in the accumulator-fragment layout, while the row is still L2 resident); only the MMA operands (x as
+// the conv input, g, the weights) are rounded to bf16, like every other GEMM of the bf16 mode.
 #include "kernels.cuh"
 
 #include <cuda_bf16.h>
@@ -41,7 +41,7 @@ __host__ __device__ constexpr int w2ld(int hp) { return hp == 8 ? 8 : hp + 8; } 
 __host__ __device__ constexpr int nvec(int C, int hp) { return 3 * hp + 7 * C; }  // b1 g1w g1b | b2 g2w g2b (2C each) | scale
 __host__ __device__ constexpr size_t smem_bytes(int C, int hid)
 {
-    return (size_t)T * (C + 1) * 4 + (size_t)(T + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 +
+    return (size_t)(T + 2 * HALO) * xld(C) * 2 + (size_t)hid_pad(hid) * k1ld(C) * 2 +
            (size_t)2 * C * w2ld(hid_pad(hid)) * 2 + (size_t)nvec(C, hid_pad(hid)) * 4 + 64;
 }
 // fp32 parameter block shared with dconv_fused.cu, per sub-block:
@@ -119,11 +119,9 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;       // n-tiles of the k3 conv
     constexpr int NT2 = 2 * C / 8;    // n-tiles of the 1x1 conv
-    constexpr int LD = C + 1;
     constexpr int XLD = xld(C), K1LD = k1ld(C), W2LD = w2ld(HP);
     extern __shared__ __align__(16) uint8_t smraw[];
-    float *xs = reinterpret_cast<float *>(smraw);                                 // [T][LD] fp32 residual stream
-    float *vec = xs + T * LD;                                                     // small fp32 vectors
+    float *vec = reinterpret_cast<float *>(smraw);                                // small fp32 vectors
     __nv_bfloat16 *xb = reinterpret_cast<__nv_bfloat16 *>(vec + ((nvec(C, HP) + 3) & ~3)); // [T + 4][XLD]
     __nv_bfloat16 *w1b = xb + (T + 2 * HALO) * XLD;                               // [HP][K1LD], k = tap*C + c
     __nv_bfloat16 *w2b = w1b + HP * K1LD;                                         // [2C][W2LD]
@@ -142,22 +140,17 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
         const int row = r < HALO ? r : T + r; // rows 0,1 and T+2,T+3
         reinterpret_cast<uint32_t *>(xb + row * XLD)[c2] = 0u;
     }
-    // fp32 rows by 4-byte async copies (the odd row stride rules out wider ones): all of a thread's copies are in
-    // flight at once instead of one exposed load latency per loop iteration; the bf16 copy is made from shared memory
-    for (int i = tid; i < T * C; i += THREADS)
+    // the conv operand copy: fp32 row -> bf16 (the fp32 residual itself stays in global memory / L2 and is updated
+    // there in the fragment layout, see pass B)
+#pragma unroll 6
+    for (int i = tid; i < T * C / 4; i += THREADS)
     {
-        const int tt = i / C, c = i - tt * C;
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(xs + tt * LD + c)),
-                     "l"(xg + i)
-                     : "memory");
-    }
-    asm volatile("cp.async.wait_all;" ::: "memory");
-    __syncthreads();
-    for (int i = tid; i < T * C / 2; i += THREADS)
-    {
-        const int tt = (2 * i) / C, c = (2 * i) % C;
-        const float *sr = xs + tt * LD + c;
-        *reinterpret_cast<uint32_t *>(xb + (tt + HALO) * XLD + c) = pack2(sr[0], sr[1]);
+        const float4 v = *reinterpret_cast<const float4 *>(xg + 4 * i);
+        const int tt = (4 * i) / C, c = (4 * i) % C;
+        uint2 pk;
+        pk.x = pack2(v.x, v.y);
+        pk.y = pack2(v.z, v.w);
+        *reinterpret_cast<uint2 *>(xb + (tt + HALO) * XLD + c) = pk;
     }
 
 #pragma unroll 1
@@ -322,33 +315,27 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
 #pragma unroll
                 for (int i = 0; i < MT_PER_WARP; ++i)
                 {
-                    float *r0 = xs + (16 * (warp + WARPS * i) + g) * LD + c;
-                    float *r1 = r0 + 8 * LD;
-                    r0[0] += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
-                    r0[1] += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
-                    r1[0] += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
-                    r1[1] += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
+                    // residual update straight on global memory (8 rows x 32 contiguous bytes per request: whole
+                    // sectors; the row was read moments ago, so it comes from L2) and, after the first sub-block, the
+                    // refreshed bf16 operand for the second one (nobody reads xb between the k3 conv and here)
+                    const int row = 16 * (warp + WARPS * i) + g;
+                    float2 *r0 = reinterpret_cast<float2 *>(xg + (size_t)row * C + c);
+                    float2 *r1 = reinterpret_cast<float2 *>(xg + (size_t)(row + 8) * C + c);
+                    float2 x0 = *r0, x1 = *r1;
+                    x0.x += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
+                    x0.y += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
+                    x1.x += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
+                    x1.y += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
+                    *r0 = x0;
+                    *r1 = x1;
+                    if (sub == 0)
+                    {
+                        *reinterpret_cast<uint32_t *>(xb + (row + HALO) * XLD + c) = pack2(x0.x, x0.y);
+                        *reinterpret_cast<uint32_t *>(xb + (row + 8 + HALO) * XLD + c) = pack2(x1.x, x1.y);
+                    }
                 }
             }
         }
-        if (sub == 0)
-        {
-            // the second sub-block convolves the updated row: refresh the bf16 operand copy
-            __syncthreads();
-            for (int i = tid; i < T * C / 2; i += THREADS)
-            {
-                const int tt = (2 * i) / C, c = (2 * i) % C;
-                const float *s = xs + tt * LD + c;
-                *reinterpret_cast<uint32_t *>(xb + (tt + HALO) * XLD + c) = pack2(s[0], s[1]);
-            }
-        }
-    }
-    __syncthreads();
-    for (int i = tid; i < T * C / 4; i += THREADS)
-    {
-        const int tt = (4 * i) / C, c = (4 * i) % C;
-        const float *s = xs + tt * LD + c;
-        *reinterpret_cast<float4 *>(xg + 4 * i) = make_float4(s[0], s[1], s[2], s[3]);
     }
 }
 
@@ -670,15 +657,15 @@ template <int C, int HID> static int launch(float *x, const uint8_t *params, int
 
 } // namespace dm
 
-// (96, 24) -- the v3 model's second level -- would need 238 KB of shared memory: it stays on the SIMT kernel
 bool dconv_mma_supported(int C, int hid, int V)
 {
-    return V == dm::T && ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && hid == 12));
+    return V == dm::T && ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && (hid == 12 || hid == 24)));
 }
 
 int dconv_mma_init_device()
 {
-    return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>() || dm::time_set_attr<48, 6>() ||
+    return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>() || dm::set_attr<96, 24>() ||
+           dm::time_set_attr<48, 6>() ||
            dm::time_set_attr<48, 12>() || dm::time_set_attr<96, 12>() || dm::time_set_attr<96, 24>() ||
            dm::time_set_attr<192, 24>();
 }
@@ -769,6 +756,8 @@ int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cu
         return dm::launch<48, 12>(x, params, items, st);
     if (C == 96 && hid == 12)
         return dm::launch<96, 12>(x, params, items, st);
+    if (C == 96 && hid == 24)
+        return dm::launch<96, 24>(x, params, items, st);
     set_error("dconv_mma: unsupported shape");
     return -1;
 }
