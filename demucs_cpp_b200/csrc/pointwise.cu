@@ -239,71 +239,91 @@ int launch_layer_norm(const float *x, float *y, int rows, int C, const float *w,
 
 // ------------------------------------------------------------------------------------------------
 // LayerNorm whose output is the tcgen05 GEMM's A-operand image: bf16, tile-packed [row/128][C/8][row%128][8].
-// One warp per row; lane l owns the 8-channel chunks l, l+32 (C <= 512).
+// One CTA = 32 consecutive rows (never straddling a 128-row tile).  Each warp normalises 4 rows (lane l owns the
+// 8-channel chunks l, l+32; C <= 512) into a shared tile [chunk][32 rows][16 B]; the tile is then written out one
+// chunk per warp pass, lane = row: 512 contiguous bytes per store instead of 32 scattered 16-byte pieces.
+constexpr int LNP_ROWS = 32;
+constexpr int LNP_CHS = LNP_ROWS * 16 + 16; // chunk stride in bytes, padded: conflict-free 16-byte stores by lane = chunk
 __global__ void __launch_bounds__(256) layer_norm_pack_kernel(const float *__restrict__ x, uint4 *__restrict__ ypk, int rows,
                                                               int C, const float *__restrict__ w, const float *__restrict__ b)
 {
-    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
-    if (row >= rows)
-        return;
+    __shared__ __align__(16) uint8_t tile[64 * LNP_CHS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row0 = blockIdx.x * LNP_ROWS;
     const int nch = C / 8;
-    const float *xr = x + (size_t)row * C;
-    float v[2][8];
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 2; ++i)
+#pragma unroll 1
+    for (int rr = 0; rr < 4; ++rr)
     {
-        const int ch = lane + 32 * i;
-        if (ch < nch)
+        const int rl = warp * 4 + rr, row = row0 + rl;
+        if (row >= rows)
+            break;
+        const float *xr = x + (size_t)row * C;
+        float v[2][8];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
         {
-            const float4 a = __ldg(reinterpret_cast<const float4 *>(xr + ch * 8));
-            const float4 c = __ldg(reinterpret_cast<const float4 *>(xr + ch * 8 + 4));
-            v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
-            v[i][4] = c.x; v[i][5] = c.y; v[i][6] = c.z; v[i][7] = c.w;
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-                s += v[i][e];
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1)
-        s += __shfl_xor_sync(0xffffffffu, s, o);
-    const float mean = s / (float)C;
-    float q = 0.f;
-#pragma unroll
-    for (int i = 0; i < 2; ++i)
-        if (lane + 32 * i < nch)
-        {
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
+            const int ch = lane + 32 * i;
+            if (ch < nch)
             {
-                const float d = v[i][e] - mean;
-                q += d * d;
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(xr + ch * 8));
+                const float4 c = __ldg(reinterpret_cast<const float4 *>(xr + ch * 8 + 4));
+                v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
+                v[i][4] = c.x; v[i][5] = c.y; v[i][6] = c.z; v[i][7] = c.w;
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    s += v[i][e];
             }
         }
-    for (int o = 16; o > 0; o >>= 1)
-        q += __shfl_xor_sync(0xffffffffu, q, o);
-    const float rstd = 1.0f / sqrtf(q / (float)(C - 1) + 1e-5f);
+        for (int o = 16; o > 0; o >>= 1)
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+        const float mean = s / (float)C;
+        float q = 0.f;
 #pragma unroll
-    for (int i = 0; i < 2; ++i)
-    {
-        const int ch = lane + 32 * i;
-        if (ch < nch)
+        for (int i = 0; i < 2; ++i)
+            if (lane + 32 * i < nch)
+            {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                {
+                    const float d = v[i][e] - mean;
+                    q += d * d;
+                }
+            }
+        for (int o = 16; o > 0; o >>= 1)
+            q += __shfl_xor_sync(0xffffffffu, q, o);
+        const float rstd = 1.0f / sqrtf(q / (float)(C - 1) + 1e-5f);
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
         {
-            float o8[8];
+            const int ch = lane + 32 * i;
+            if (ch < nch)
+            {
+                const float4 w0 = __ldg(reinterpret_cast<const float4 *>(w + ch * 8)), w1 = __ldg(reinterpret_cast<const float4 *>(w + ch * 8 + 4));
+                const float4 b0 = __ldg(reinterpret_cast<const float4 *>(b + ch * 8)), b1 = __ldg(reinterpret_cast<const float4 *>(b + ch * 8 + 4));
+                const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                float o8[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e)
-                o8[e] = (v[i][e] - mean) * rstd * __ldg(&w[ch * 8 + e]) + __ldg(&b[ch * 8 + e]);
-            uint4 pk;
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(o8[0], o8[1]), h1 = __floats2bfloat162_rn(o8[2], o8[3]),
-                           h2 = __floats2bfloat162_rn(o8[4], o8[5]), h3 = __floats2bfloat162_rn(o8[6], o8[7]);
-            pk.x = *reinterpret_cast<uint32_t *>(&h0);
-            pk.y = *reinterpret_cast<uint32_t *>(&h1);
-            pk.z = *reinterpret_cast<uint32_t *>(&h2);
-            pk.w = *reinterpret_cast<uint32_t *>(&h3);
-            ypk[((size_t)(row >> 7) * nch + ch) * 128 + (row & 127)] = pk;
+                for (int e = 0; e < 8; ++e)
+                    o8[e] = (v[i][e] - mean) * rstd * ww[e] + bb[e];
+                uint4 pk;
+                __nv_bfloat162 h0 = __floats2bfloat162_rn(o8[0], o8[1]), h1 = __floats2bfloat162_rn(o8[2], o8[3]),
+                               h2 = __floats2bfloat162_rn(o8[4], o8[5]), h3 = __floats2bfloat162_rn(o8[6], o8[7]);
+                pk.x = *reinterpret_cast<uint32_t *>(&h0);
+                pk.y = *reinterpret_cast<uint32_t *>(&h1);
+                pk.z = *reinterpret_cast<uint32_t *>(&h2);
+                pk.w = *reinterpret_cast<uint32_t *>(&h3);
+                *reinterpret_cast<uint4 *>(tile + ch * LNP_CHS + rl * 16) = pk;
+            }
         }
     }
+    __syncthreads();
+    // row0 is a multiple of 32: the 32 rows share one 128-row tile, at rows (row0 & 127) .. +31 of it
+    const int row = row0 + lane;
+    for (int ch = warp; ch < nch; ch += 8)
+        if (row < rows)
+            ypk[((size_t)(row0 >> 7) * nch + ch) * 128 + (row & 127)] = *reinterpret_cast<const uint4 *>(tile + ch * LNP_CHS + lane * 16);
 }
 
 int launch_layer_norm_pack(const float *x, void *ypk, int rows, int C, const float *w, const float *b, cudaStream_t st)
@@ -313,7 +333,7 @@ int launch_layer_norm_pack(const float *x, void *ypk, int rows, int C, const flo
         set_error("layer_norm_pack: C must be a multiple of 8 and <= 512");
         return -1;
     }
-    layer_norm_pack_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, (uint4 *)ypk, rows, C, w, b);
+    layer_norm_pack_kernel<<<(rows + LNP_ROWS - 1) / LNP_ROWS, 256, 0, st>>>(x, (uint4 *)ypk, rows, C, w, b);
     DMX_LAUNCH_CHECK();
     return 0;
 }
