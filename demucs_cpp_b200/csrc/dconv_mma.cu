@@ -58,6 +58,8 @@ __host__ __device__ constexpr int pk_w2_bytes(int C, int hp) { return 2 * C * w2
 __host__ __device__ constexpr int pk_vec_bytes(int C, int hp) { return ((nvec(C, hp) + 3) & ~3) * 4; }
 __host__ __device__ constexpr int pk_sub_bytes(int C, int hp) { return pk_w1_bytes(C, hp) + pk_w2_bytes(C, hp) + pk_vec_bytes(C, hp); }
 
+__host__ __device__ constexpr int rw_bytes(int C) { return 2 * C * xld(C) * 2 + 2 * C * 4; }
+
 __device__ __forceinline__ void copy16_async(void *sdst, const void *gsrc, int bytes)
 {
     for (int i = threadIdx.x * 16; i < bytes; i += THREADS * 16)
@@ -114,7 +116,13 @@ __device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
     b = sb;
 }
 
-template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_kernel(float *__restrict__ x, const uint8_t *__restrict__ params)
+// RW: the encoder's 1x1 "rewrite" conv + GLU (+ frequency embedding) that follows the DConv (src/encdec.cpp:118-164) runs
+// on the row while it is still here: out[row][c] = (Wa x + ba) * sigmoid(Wg x + bg) + rowadd[u][c]; the DConv result
+// itself is then not written back (nothing else reads it).  rw: Wr bf16 [2C][C + 8] | bias fp32 [2C].
+template <int C, int HID, bool RW>
+__global__ void __launch_bounds__(THREADS)
+    dconv_mma_kernel(float *__restrict__ x, const uint8_t *__restrict__ params, const uint8_t *__restrict__ rw,
+                     float *__restrict__ out, const float *__restrict__ rowadd, const int F)
 {
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;       // n-tiles of the k3 conv
@@ -125,6 +133,7 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
     __nv_bfloat16 *xb = reinterpret_cast<__nv_bfloat16 *>(vec + ((nvec(C, HP) + 3) & ~3)); // [T + 4][XLD]
     __nv_bfloat16 *w1b = xb + (T + 2 * HALO) * XLD;                               // [HP][K1LD], k = tap*C + c
     __nv_bfloat16 *w2b = w1b + HP * K1LD;                                         // [2C][W2LD]
+    __nv_bfloat16 *wr = w2b + 2 * C * W2LD;                                       // RW: [2C][XLD] | bias fp32 [2C]
     float *b1 = vec, *g1w = b1 + HP, *g1b = g1w + HP, *b2 = g1b + HP, *g2w = b2 + 2 * C, *g2b = g2w + 2 * C,
           *scale = g2b + 2 * C;
     __shared__ double red[2 * WARPS];
@@ -132,6 +141,8 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
     float *xg = x + (size_t)blockIdx.x * T * C;
+    if (RW)
+        copy16_async(wr, rw, rw_bytes(C)); // waited for together with the first sub-block's parameters
 
     // ---- load the row: fp32 copy + bf16 operand copy (halo rows zero) ----
     for (int i = tid; i < 2 * HALO * XLD / 2; i += THREADS)
@@ -326,14 +337,69 @@ template <int C, int HID> __global__ void __launch_bounds__(THREADS) dconv_mma_k
                     x0.y += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
                     x1.x += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
                     x1.y += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
-                    *r0 = x0;
-                    *r1 = x1;
-                    if (sub == 0)
+                    if (!RW || sub == 0)
+                    {
+                        *r0 = x0;
+                        *r1 = x1;
+                    }
+                    if (RW || sub == 0)
                     {
                         *reinterpret_cast<uint32_t *>(xb + (row + HALO) * XLD + c) = pack2(x0.x, x0.y);
                         *reinterpret_cast<uint32_t *>(xb + (row + 8 + HALO) * XLD + c) = pack2(x1.x, x1.y);
                     }
                 }
+            }
+        }
+    }
+    if (RW)
+    {
+        // ---- rewrite 1x1 + GLU on the finished row (bf16 copy in xb), straight to the encoder output ----
+        __syncthreads();
+        const float *rb = reinterpret_cast<const float *>(wr + 2 * C * XLD);
+        const int u = blockIdx.x % F;
+        float *og = out + (size_t)blockIdx.x * T * C;
+#pragma unroll 1
+        for (int nt = 0; nt < C / 8; ++nt)
+        {
+            const int c = 8 * nt + 2 * t;
+            float da[MT_PER_WARP][4], dg[MT_PER_WARP][4];
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+            {
+                da[i][0] = da[i][2] = rb[c];
+                da[i][1] = da[i][3] = rb[c + 1];
+                dg[i][0] = dg[i][2] = rb[C + c];
+                dg[i][1] = dg[i][3] = rb[C + c + 1];
+            }
+#pragma unroll
+            for (int kc = 0; kc < C / 16; ++kc)
+            {
+                const __nv_bfloat16 *wa = wr + (8 * nt + g) * XLD + 16 * kc + 2 * t;
+                const __nv_bfloat16 *wg = wa + C * XLD;
+                const uint32_t ba0 = ld32(wa), ba1 = ld32(wa + 8), bg0 = ld32(wg), bg1 = ld32(wg + 8);
+#pragma unroll
+                for (int i = 0; i < MT_PER_WARP; ++i)
+                {
+                    const __nv_bfloat16 *ap = xb + (16 * (warp + WARPS * i) + g + HALO) * XLD + 16 * kc + 2 * t;
+                    const uint32_t a0 = ld32(ap), a1 = ld32(ap + 8 * XLD), a2 = ld32(ap + 8), a3 = ld32(ap + 8 * XLD + 8);
+                    mma_k16(da[i], a0, a1, a2, a3, ba0, ba1);
+                    mma_k16(dg[i], a0, a1, a2, a3, bg0, bg1);
+                }
+            }
+            float e0 = 0.f, e1 = 0.f;
+            if (rowadd)
+            {
+                e0 = __ldg(rowadd + (size_t)u * C + c);
+                e1 = __ldg(rowadd + (size_t)u * C + c + 1);
+            }
+#pragma unroll
+            for (int i = 0; i < MT_PER_WARP; ++i)
+            {
+                const int row = 16 * (warp + WARPS * i) + g;
+                *reinterpret_cast<float2 *>(og + (size_t)row * C + c) =
+                    make_float2(da[i][0] * sigmoid_ref(dg[i][0]) + e0, da[i][1] * sigmoid_ref(dg[i][1]) + e1);
+                *reinterpret_cast<float2 *>(og + (size_t)(row + 8) * C + c) =
+                    make_float2(da[i][2] * sigmoid_ref(dg[i][2]) + e0, da[i][3] * sigmoid_ref(dg[i][3]) + e1);
             }
         }
     }
@@ -644,13 +710,27 @@ static int time_launch(float *x, float *hbuf, const uint8_t *params, int B, int 
 
 template <int C, int HID> static int set_attr()
 {
-    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem_bytes(C, HID)));
     return 0;
 }
 template <int C, int HID> static int launch(float *x, const uint8_t *params, int items, cudaStream_t st)
 {
-    dconv_mma_kernel<C, HID><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params);
+    dconv_mma_kernel<C, HID, false><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params, nullptr, nullptr, nullptr, 1);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+template <int C, int HID> static int set_attr_rw()
+{
+    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem_bytes(C, HID) + rw_bytes(C)));
+    return 0;
+}
+template <int C, int HID>
+static int launch_rw(float *x, const uint8_t *params, const uint8_t *rw, float *out, const float *rowadd, int F, int items,
+                     cudaStream_t st)
+{
+    dconv_mma_kernel<C, HID, true><<<items, THREADS, smem_bytes(C, HID) + rw_bytes(C), st>>>(x, params, rw, out, rowadd, F);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -664,7 +744,7 @@ bool dconv_mma_supported(int C, int hid, int V)
 
 int dconv_mma_init_device()
 {
-    return dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>() || dm::set_attr<96, 24>() ||
+    return dm::set_attr_rw<48, 6>() || dm::set_attr<48, 6>() || dm::set_attr<48, 12>() || dm::set_attr<96, 12>() || dm::set_attr<96, 24>() ||
            dm::time_set_attr<48, 6>() ||
            dm::time_set_attr<48, 12>() || dm::time_set_attr<96, 12>() || dm::time_set_attr<96, 24>() ||
            dm::time_set_attr<192, 24>();
@@ -674,6 +754,32 @@ bool dconv_time_mma_supported(int C, int hid, int hs)
 {
     return (hs % 2) == 0 && hs >= hid &&
            ((C == 48 && (hid == 6 || hid == 12)) || (C == 96 && (hid == 12 || hid == 24)) || (C == 192 && hid == 24));
+}
+
+// Encoder level with C = 48, hidden 6 (htdemucs encoder 0): DConv + the following 1x1 rewrite / GLU / frequency
+// embedding in one launch.  x [items][336][48] (DConv input, left holding the first sub-block's update only),
+// out [items][336][48]; rw = block built by dconv_mma_rw_pack; rowadd [F][48] or null, u = item % F.
+bool dconv_mma_rw_supported(int C, int hid, int V) { return V == dm::T && C == 48 && hid == 6; }
+int dconv_mma_rw_pack_floats(int C) { return dm::rw_bytes(C) / 4; }
+void dconv_mma_rw_pack(int C, const float *W, const float *bias, float *outp)
+{
+    uint8_t *o = reinterpret_cast<uint8_t *>(outp);
+    memset(o, 0, (size_t)dm::rw_bytes(C));
+    __nv_bfloat16 *w = reinterpret_cast<__nv_bfloat16 *>(o);
+    const int ld = dm::xld(C);
+    for (int n = 0; n < 2 * C; ++n)
+        for (int k = 0; k < C; ++k)
+            w[n * ld + k] = __float2bfloat16(W[(size_t)n * C + k]);
+    memcpy(o + (size_t)2 * C * ld * 2, bias, (size_t)2 * C * 4);
+}
+int launch_dconv_mma_rw(float *x, const void *packed, const void *rw, float *out, const float *rowadd, int F, int items,
+                        int C, int hid, cudaStream_t st)
+{
+    if (C == 48 && hid == 6)
+        return dm::launch_rw<48, 6>(x, static_cast<const uint8_t *>(packed), static_cast<const uint8_t *>(rw), out, rowadd, F,
+                                    items, st);
+    set_error("dconv_mma_rw: unsupported shape");
+    return -1;
 }
 
 // Floats (4-byte units) of the packed parameter block of one DConv (two sub-blocks); 0 = shape not handled here.

@@ -152,6 +152,16 @@ int model_finalize(dmx_model *m)
             pack_conv(m, m->tenc[i].rewrite, te + ".rewrite.weight", te + ".rewrite.bias", 2 * C, C, 1, true) ||
             pack_dconv(m, m->tenc[i].dc, te, C))
             return -1;
+        if (dconv_mma_rw_supported(C, m->enc[i].dc.hid, LE))
+        {
+            const HostTensor *rw = get(m, e + ".rewrite.weight", (size_t)2 * C * C), *rb = get(m, e + ".rewrite.bias", 2 * C);
+            if (!rw || !rb)
+                return -1;
+            std::vector<float> pk((size_t)dconv_mma_rw_pack_floats(C));
+            dconv_mma_rw_pack(C, rw->data.data(), rb->data.data(), pk.data());
+            if (upload(m, &m->enc[i].rw_pk, pk))
+                return -1;
+        }
     }
     for (int i = 0; i < 4; ++i)
     {
@@ -407,16 +417,32 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             }
             p.act = 1;
             f.gemm(p, PC_GEMM_CONV);
-            f.dconv(m->cA_f, FREQS[i + 1], T, fe.dc, m->h_f, m->y2_f, 1);
-            GemmParams r = f.base(m->cA_f, C, C, fe.rewrite, m->e[i], C, FREQS[i + 1], T, FREQS[i + 1], T);
-            r.glu = 1;
-            r.Nco = C;
-            if (i == 0)
+            if (m->precision == DMX_PRECISION_BF16 && fe.rw_pk && fe.dc.fused_pk && dconv_mma_rw_supported(C, fe.dc.hid, T))
             {
-                r.rowadd = m->freq_emb2;
-                r.rowadd_ld = 48;
+                // DConv + rewrite / GLU / frequency embedding of this level in one launch (row stays on the SM)
+                if (!f.rc)
+                {
+                    const int F = FREQS[i + 1], hid = fe.dc.hid;
+                    ProfScope ps(m, PC_DCONV_FUSED,
+                                 2.0 * (double)B * F * T * (2.0 * (3.0 * C * hid + 2.0 * 2.0 * C * hid) + 2.0 * C * C),
+                                 (double)B * F * T * C * 8.0);
+                    f.rc = launch_dconv_mma_rw(m->cA_f, fe.dc.fused_pk, fe.rw_pk, m->e[i], i == 0 ? m->freq_emb2 : nullptr, F,
+                                               B * F, C, hid, st);
+                }
             }
-            f.gemm(r, PC_GEMM_CONV);
+            else
+            {
+                f.dconv(m->cA_f, FREQS[i + 1], T, fe.dc, m->h_f, m->y2_f, 1);
+                GemmParams r = f.base(m->cA_f, C, C, fe.rewrite, m->e[i], C, FREQS[i + 1], T, FREQS[i + 1], T);
+                r.glu = 1;
+                r.Nco = C;
+                if (i == 0)
+                {
+                    r.rowadd = m->freq_emb2;
+                    r.rowadd_ld = 48;
+                }
+                f.gemm(r, PC_GEMM_CONV);
+            }
         }
         xin_t = m->te[i];
         xin_f = m->e[i];

@@ -40,6 +40,7 @@ struct EncW
 {
     Packed conv, rewrite;
     DConvW dc;
+    float *rw_pk = nullptr; // rewrite conv pre-packed for the fused DConv + rewrite kernel (dconv_mma.cu), if the shape has one
     int Cin = 0, C = 0;
 };
 
