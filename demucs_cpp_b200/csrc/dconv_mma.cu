@@ -59,6 +59,7 @@ __host__ __device__ constexpr int pk_vec_bytes(int C, int hp) { return ((nvec(C,
 __host__ __device__ constexpr int pk_sub_bytes(int C, int hp) { return pk_w1_bytes(C, hp) + pk_w2_bytes(C, hp) + pk_vec_bytes(C, hp); }
 
 __host__ __device__ constexpr int rw_bytes(int C) { return 2 * C * xld(C) * 2 + 2 * C * 4; }
+__host__ __device__ constexpr int cin_bytes(int C) { return C * 40 * 2 + C * 4; }
 
 __device__ __forceinline__ void copy16_async(void *sdst, const void *gsrc, int bytes)
 {
@@ -119,10 +120,15 @@ __device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
 // RW: the encoder's 1x1 "rewrite" conv + GLU (+ frequency embedding) that follows the DConv (src/encdec.cpp:118-164) runs
 // on the row while it is still here: out[row][c] = (Wa x + ba) * sigmoid(Wg x + bg) + rowadd[u][c]; the DConv result
 // itself is then not written back (nothing else reads it).  rw: Wr bf16 [2C][C + 8] | bias fp32 [2C].
-template <int C, int HID, bool RW>
+// CIN: the encoder's strided input conv (k8 s4 p2 along frequency, 4 CaC channels, + GELU; src/encdec.cpp:24-50) that
+// PRECEDES the DConv is computed here too: the row's A fragments are gathered straight from the spectrogram
+// [B][4F][336][4] (8 taps x 4 channels = K 32), so x is produced on the SM (written once for the residual updates)
+// instead of being written by a GEMM launch and read back.  cin: Wc bf16 [C][40] (k = tap*4 + ch) | bias fp32 [C].
+template <int C, int HID, bool RW, bool CIN>
 __global__ void __launch_bounds__(THREADS)
     dconv_mma_kernel(float *__restrict__ x, const uint8_t *__restrict__ params, const uint8_t *__restrict__ rw,
-                     float *__restrict__ out, const float *__restrict__ rowadd, const int F)
+                     float *__restrict__ out, const float *__restrict__ rowadd, const int F, const float *__restrict__ spec,
+                     const uint8_t *__restrict__ cin)
 {
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;       // n-tiles of the k3 conv
@@ -151,10 +157,70 @@ __global__ void __launch_bounds__(THREADS)
         const int row = r < HALO ? r : T + r; // rows 0,1 and T+2,T+3
         reinterpret_cast<uint32_t *>(xb + row * XLD)[c2] = 0u;
     }
+    if (CIN)
+    {
+        constexpr int CLD = 40; // 32 + 8: 20 words per row, conflict-free fragment loads
+        __nv_bfloat16 *wc = wr + (RW ? rw_bytes(C) / 2 : 0);
+        copy16_async(wc, cin, cin_bytes(C));
+        async_wait_all();
+        __syncthreads();
+        const float *cb = reinterpret_cast<const float *>(wc + C * CLD);
+        const int bi = blockIdx.x / F, u = blockIdx.x - bi * F;
+        const float *sb = spec + (size_t)bi * (4 * F) * T * 4;
+        // one m-tile at a time (24 accumulator registers): this stage must not set the kernel's register count
+#pragma unroll 1
+        for (int i = 0; i < MT_PER_WARP; ++i)
+        {
+            const int row = 16 * (warp + WARPS * i) + g;
+            float acc[C / 8][4];
+#pragma unroll
+            for (int nt = 0; nt < C / 8; ++nt)
+            {
+                acc[nt][0] = acc[nt][2] = cb[8 * nt + 2 * t];
+                acc[nt][1] = acc[nt][3] = cb[8 * nt + 2 * t + 1];
+            }
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks)
+            {
+                // k = tap*4 + ch: this lane's k pair (2t, 2t+1) is channels (t&1)*2, +1 of tap 4ks + (t>>1); k + 8 = two taps on
+                const int tap0 = 4 * ks + (t >> 1), ch0 = (t & 1) * 2;
+                const int f0 = 4 * u - 2 + tap0, f1 = f0 + 2;
+                float2 p0 = make_float2(0.f, 0.f), p1 = p0, p2 = p0, p3 = p0;
+                if (f0 >= 0 && f0 < 4 * F)
+                {
+                    p0 = __ldg(reinterpret_cast<const float2 *>(sb + ((size_t)f0 * T + row) * 4 + ch0));
+                    p1 = __ldg(reinterpret_cast<const float2 *>(sb + ((size_t)f0 * T + row + 8) * 4 + ch0));
+                }
+                if (f1 >= 0 && f1 < 4 * F)
+                {
+                    p2 = __ldg(reinterpret_cast<const float2 *>(sb + ((size_t)f1 * T + row) * 4 + ch0));
+                    p3 = __ldg(reinterpret_cast<const float2 *>(sb + ((size_t)f1 * T + row + 8) * 4 + ch0));
+                }
+                const uint32_t a0 = pack2(p0.x, p0.y), a1 = pack2(p1.x, p1.y), a2 = pack2(p2.x, p2.y), a3 = pack2(p3.x, p3.y);
+#pragma unroll
+                for (int nt = 0; nt < C / 8; ++nt)
+                {
+                    const __nv_bfloat16 *wp = wc + (8 * nt + g) * CLD + 16 * ks + 2 * t;
+                    mma_k16(acc[nt], a0, a1, a2, a3, ld32(wp), ld32(wp + 8));
+                }
+            }
+#pragma unroll
+            for (int nt = 0; nt < C / 8; ++nt)
+            {
+                const int c = 8 * nt + 2 * t;
+                const float2 x0 = make_float2(gelu_erf(acc[nt][0]), gelu_erf(acc[nt][1]));
+                const float2 x1 = make_float2(gelu_erf(acc[nt][2]), gelu_erf(acc[nt][3]));
+                *reinterpret_cast<float2 *>(xg + (size_t)row * C + c) = x0;
+                *reinterpret_cast<float2 *>(xg + (size_t)(row + 8) * C + c) = x1;
+                *reinterpret_cast<uint32_t *>(xb + (row + HALO) * XLD + c) = pack2(x0.x, x0.y);
+                *reinterpret_cast<uint32_t *>(xb + (row + 8 + HALO) * XLD + c) = pack2(x1.x, x1.y);
+            }
+        }
+    }
     // the conv operand copy: fp32 row -> bf16 (the fp32 residual itself stays in global memory / L2 and is updated
     // there in the fragment layout, see pass B)
 #pragma unroll 6
-    for (int i = tid; i < T * C / 4; i += THREADS)
+    for (int i = tid; i < (CIN ? 0 : T * C / 4); i += THREADS)
     {
         const float4 v = *reinterpret_cast<const float4 *>(xg + 4 * i);
         const int tt = (4 * i) / C, c = (4 * i) % C;
@@ -710,27 +776,35 @@ static int time_launch(float *x, float *hbuf, const uint8_t *params, int B, int 
 
 template <int C, int HID> static int set_attr()
 {
-    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem_bytes(C, HID)));
     return 0;
 }
 template <int C, int HID> static int launch(float *x, const uint8_t *params, int items, cudaStream_t st)
 {
-    dconv_mma_kernel<C, HID, false><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params, nullptr, nullptr, nullptr, 1);
+    dconv_mma_kernel<C, HID, false, false><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params, nullptr, nullptr, nullptr, 1,
+                                                                                    nullptr, nullptr);
     DMX_LAUNCH_CHECK();
     return 0;
 }
 template <int C, int HID> static int set_attr_rw()
 {
-    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem_bytes(C, HID) + rw_bytes(C)));
+    DMX_CUDA(cudaFuncSetAttribute(dconv_mma_kernel<C, HID, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem_bytes(C, HID) + rw_bytes(C) + cin_bytes(C)));
     return 0;
 }
 template <int C, int HID>
 static int launch_rw(float *x, const uint8_t *params, const uint8_t *rw, float *out, const float *rowadd, int F, int items,
-                     cudaStream_t st)
+                     const float *spec, const uint8_t *cin, cudaStream_t st)
 {
-    dconv_mma_kernel<C, HID, true><<<items, THREADS, smem_bytes(C, HID) + rw_bytes(C), st>>>(x, params, rw, out, rowadd, F);
+    if (spec)
+        dconv_mma_kernel<C, HID, true, true><<<items, THREADS, smem_bytes(C, HID) + rw_bytes(C) + cin_bytes(C), st>>>(
+            x, params, rw, out, rowadd, F, spec, cin);
+    else
+        dconv_mma_kernel<C, HID, true, false><<<items, THREADS, smem_bytes(C, HID) + rw_bytes(C), st>>>(x, params, rw, out, rowadd,
+                                                                                                  F, nullptr, nullptr);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -772,12 +846,26 @@ void dconv_mma_rw_pack(int C, const float *W, const float *bias, float *outp)
             w[n * ld + k] = __float2bfloat16(W[(size_t)n * C + k]);
     memcpy(o + (size_t)2 * C * ld * 2, bias, (size_t)2 * C * 4);
 }
+// Input conv block (Cin = 4, k8 along frequency): W [C][4][8] (PyTorch conv weight order) -> bf16 [C][40], k = tap*4 + ch
+int dconv_mma_cin_pack_floats(int C) { return dm::cin_bytes(C) / 4; }
+void dconv_mma_cin_pack(int C, const float *W, const float *bias, float *outp)
+{
+    uint8_t *o = reinterpret_cast<uint8_t *>(outp);
+    memset(o, 0, (size_t)dm::cin_bytes(C));
+    __nv_bfloat16 *w = reinterpret_cast<__nv_bfloat16 *>(o);
+    for (int n = 0; n < C; ++n)
+        for (int ch = 0; ch < 4; ++ch)
+            for (int tap = 0; tap < 8; ++tap)
+                w[n * 40 + tap * 4 + ch] = __float2bfloat16(W[((size_t)n * 4 + ch) * 8 + tap]);
+    memcpy(o + (size_t)C * 40 * 2, bias, (size_t)C * 4);
+}
+// spec / cin non-null: x is first computed from the spectrogram [B][4F][336][4] by the input conv + GELU
 int launch_dconv_mma_rw(float *x, const void *packed, const void *rw, float *out, const float *rowadd, int F, int items,
-                        int C, int hid, cudaStream_t st)
+                        int C, int hid, const float *spec, const void *cin, cudaStream_t st)
 {
     if (C == 48 && hid == 6)
         return dm::launch_rw<48, 6>(x, static_cast<const uint8_t *>(packed), static_cast<const uint8_t *>(rw), out, rowadd, F,
-                                    items, st);
+                                    items, spec, static_cast<const uint8_t *>(cin), st);
     set_error("dconv_mma_rw: unsupported shape");
     return -1;
 }

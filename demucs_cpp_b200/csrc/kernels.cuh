@@ -117,8 +117,10 @@ int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cu
 bool dconv_mma_rw_supported(int C, int hid, int V);
 int dconv_mma_rw_pack_floats(int C);
 void dconv_mma_rw_pack(int C, const float *W, const float *bias, float *out);
+int dconv_mma_cin_pack_floats(int C);
+void dconv_mma_cin_pack(int C, const float *W, const float *bias, float *out);
 int launch_dconv_mma_rw(float *x, const void *packed, const void *rw, float *out, const float *rowadd, int F, int items,
-                        int C, int hid, cudaStream_t st);
+                        int C, int hid, const float *spec, const void *cin, cudaStream_t st);
 bool dconv_time_mma_supported(int C, int hid, int hs);
 int launch_dconv_time_mma(float *x, float *hbuf, const void *packed, int B, int L, int C, int hid, int hs,
                           double *const *stats, cudaStream_t st);

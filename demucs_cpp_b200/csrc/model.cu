@@ -161,6 +161,16 @@ int model_finalize(dmx_model *m)
             dconv_mma_rw_pack(C, rw->data.data(), rb->data.data(), pk.data());
             if (upload(m, &m->enc[i].rw_pk, pk))
                 return -1;
+            if (cin_f == 4)
+            {
+                const HostTensor *cw = get(m, e + ".conv.weight", (size_t)C * 4 * 8), *cb = get(m, e + ".conv.bias", C);
+                if (!cw || !cb)
+                    return -1;
+                std::vector<float> ck((size_t)dconv_mma_cin_pack_floats(C));
+                dconv_mma_cin_pack(C, cw->data.data(), cb->data.data(), ck.data());
+                if (upload(m, &m->enc[i].cin_pk, ck))
+                    return -1;
+            }
         }
     }
     for (int i = 0; i < 4; ++i)
@@ -407,19 +417,25 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         // freq: conv k8 s4 p2 along frequency (+GELU), frames are independent
         f.st = st;
         {
-            GemmParams p = f.base(xin_f, fe.Cin, fe.Cin, fe.conv, m->cA_f, C, FREQS[i], T, FREQS[i + 1], T);
-            p.ntaps = 8;
-            p.su = 4;
-            for (int t = 0; t < 8; ++t)
+            const bool fused_rw =
+                m->precision == DMX_PRECISION_BF16 && fe.rw_pk && fe.dc.fused_pk && dconv_mma_rw_supported(C, fe.dc.hid, T);
+            const bool fused_cin = fused_rw && fe.cin_pk && fe.Cin == 4 && FREQS[i] == 4 * FREQS[i + 1];
+            if (!fused_cin)
             {
-                p.du[t] = t - 2;
-                p.dv[t] = 0;
+                GemmParams p = f.base(xin_f, fe.Cin, fe.Cin, fe.conv, m->cA_f, C, FREQS[i], T, FREQS[i + 1], T);
+                p.ntaps = 8;
+                p.su = 4;
+                for (int t = 0; t < 8; ++t)
+                {
+                    p.du[t] = t - 2;
+                    p.dv[t] = 0;
+                }
+                p.act = 1;
+                f.gemm(p, PC_GEMM_CONV);
             }
-            p.act = 1;
-            f.gemm(p, PC_GEMM_CONV);
-            if (m->precision == DMX_PRECISION_BF16 && fe.rw_pk && fe.dc.fused_pk && dconv_mma_rw_supported(C, fe.dc.hid, T))
+            if (fused_rw)
             {
-                // DConv + rewrite / GLU / frequency embedding of this level in one launch (row stays on the SM)
+                // (input conv +) DConv + rewrite / GLU / frequency embedding of this level in one launch (row stays on the SM)
                 if (!f.rc)
                 {
                     const int F = FREQS[i + 1], hid = fe.dc.hid;
@@ -427,7 +443,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
                                  2.0 * (double)B * F * T * (2.0 * (3.0 * C * hid + 2.0 * 2.0 * C * hid) + 2.0 * C * C),
                                  (double)B * F * T * C * 8.0);
                     f.rc = launch_dconv_mma_rw(m->cA_f, fe.dc.fused_pk, fe.rw_pk, m->e[i], i == 0 ? m->freq_emb2 : nullptr, F,
-                                               B * F, C, hid, st);
+                                               B * F, C, hid, fused_cin ? xin_f : nullptr, fe.cin_pk, st);
                 }
             }
             else

@@ -40,6 +40,7 @@ struct EncW
 {
     Packed conv, rewrite;
     DConvW dc;
+    float *cin_pk = nullptr; // input conv (4 CaC channels, k8) pre-packed for the same kernel (encoder 0)
     float *rw_pk = nullptr; // rewrite conv pre-packed for the fused DConv + rewrite kernel (dconv_mma.cu), if the shape has one
     int Cin = 0, C = 0;
 };
