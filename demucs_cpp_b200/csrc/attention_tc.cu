@@ -9,9 +9,12 @@
 //     exchange between them is needed: they are merged once at the end through shared memory.
 //     PV_h = P_h V_h  tcgen05.mma  M=128, N=dh, K=64 per half (V: MN-major canonical tile, i.e. stored as it lies
 //                                                      in memory, dh contiguous)      -> TMEM cols [128+h*dh, ...)
-//     O_h = O_h * exp2(m_old - m_new) + PV_h   in registers (fp32)
-// Q/K/V arrive as bf16 (the QKV projection's epilogue writes them that way); the output is fp32 because it
-// feeds the out-projection's fp32 A-gather.  The T x S score matrix never leaves the SM.
+//     O_h accumulates IN TMEM over all key tiles (the PV MMAs run with the accumulate flag).  The maximum used in the
+//     exponent may lag the true row maximum by up to 2^8; O_h and the row sum are rescaled (TMEM load / scale / store)
+//     only when it is raised -- the first tiles -- so a tile costs one pass over its scores and ONE commit: S of
+//     tile j+1 is issued right behind PV of tile j.
+// Q/K/V arrive tile-packed bf16 (the QKV projection's epilogue writes them that way, fetched by bulk copies); the
+// output is written tile-packed bf16 for the out-projection.  The T x S score matrix never leaves the SM.
 // Reference: src/layers.cpp:442-482 (heads = contiguous dh-wide column blocks, max-subtracted softmax).
 #include "kernels.cuh"
 
@@ -116,6 +119,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t *r)
                  : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
                    "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])::"memory");
 }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t *r)
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+                 "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+                 "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2f(float x)
 {
     float y;
@@ -157,7 +169,7 @@ __global__ void __launch_bounds__(THREADS, 2)
     constexpr int HK = BKEY / 2;                  // keys per thread per tile
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t *Qs = smem, *Ks = Qs + TILE, *Vs = Ks + 2 * TILE, *Ps = Vs + 2 * TILE;
-    __shared__ __align__(8) uint64_t mma_bar, q_full, kv_full[2], kv_empty[2];
+    __shared__ __align__(8) uint64_t mma_bar, q_full, kv_full[2];
     __shared__ uint32_t tmem_slot;
 
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -179,8 +191,6 @@ __global__ void __launch_bounds__(THREADS, 2)
         mbar_init(&q_full, 1);
         mbar_init(&kv_full[0], 1);
         mbar_init(&kv_full[1], 1);
-        mbar_init(&kv_empty[0], 1);
-        mbar_init(&kv_empty[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0)
@@ -207,111 +217,105 @@ __global__ void __launch_bounds__(THREADS, 2)
     const uint32_t idesc_s = make_idesc(BKEY, 0), idesc_pv = make_idesc(DH, 1);
     uint8_t *Prow = Ps + (half * (HK / 8)) * LBO + row * 16;
 
-    float o[DH];
-#pragma unroll
-    for (int i = 0; i < DH; ++i)
-        o[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f; // log2 domain
-    uint32_t phase = 0;
+    // The running output O_h stays in TMEM for the whole key loop (PV accumulates into it); the row maximum used in the
+    // exponent, m_use, is allowed to lag the true maximum by up to 2^8 (P <= 256 is harmless in bf16 / fp32) and O_h
+    // and the row sum are rescaled -- a TMEM load / scale / store by the whole warp -- only when it is raised, which
+    // happens in the first tiles only.  The result is the same softmax: P, the sum and O always share one m_use.
+    // One commit per tile: S(j+1) is issued right behind PV(j), and its completion implies PV(j)'s.
+    float m_use = -INFINITY, l_run = 0.f; // log2 domain
+    constexpr float LAG = 8.0f;
 
+    if (tid == 0)
+    {
+        mbar_wait(&q_full, 0);
+        mbar_wait(&kv_full[0], 0);
+        tc_fence_after();
+        const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks);
+#pragma unroll
+        for (int jj = 0; jj < DH / 16; ++jj)
+            umma(tmem_slot, make_desc(qa + jj * 2 * LBO, LBO, 128), make_desc(ka + jj * 2 * LBO, LBO, 128), idesc_s,
+                 jj > 0 ? 1u : 0u);
+        umma_commit(&mma_bar);
+    }
     for (int j = 0; j < ntiles; ++j)
     {
         const int buf = j & 1;
-        if (tid == 0)
-        {
-            // prefetch tile j+1 into the other buffer once the MMAs that read it (tile j-1) have completed
-            if (j + 1 < ntiles)
-            {
-                const int nb = (j + 1) & 1;
-                if (j + 1 >= 2)
-                    mbar_wait(&kv_empty[nb], (uint32_t)(((j + 1) / 2 - 1) & 1));
-                mbar_arrive_expect_tx(&kv_full[nb], 2 * TILE);
-                bulk_g2s(Ks + nb * TILE, tile_ptr(Kp, ldk8, kc8, Spad, j + 1), TILE, &kv_full[nb]);
-                bulk_g2s(Vs + nb * TILE, tile_ptr(Vp, ldv8, vc8, Spad, j + 1), TILE, &kv_full[nb]);
-            }
-            if (j == 0)
-                mbar_wait(&q_full, 0);
-            mbar_wait(&kv_full[buf], (uint32_t)((j / 2) & 1));
-            tc_fence_after();
-            const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks + buf * TILE);
-#pragma unroll
-            for (int jj = 0; jj < DH / 16; ++jj)
-                umma(tmem_slot, make_desc(qa + jj * 2 * LBO, LBO, 128), make_desc(ka + jj * 2 * LBO, LBO, 128), idesc_s,
-                     jj > 0 ? 1u : 0u);
-            umma_commit(&mma_bar);
-        }
-        mbar_wait(&mma_bar, phase);
-        phase ^= 1u;
+        mbar_wait(&mma_bar, (uint32_t)(j & 1)); // S(j) complete, and with it PV(j-1): the other K/V buffer is free
         tc_fence_after();
-        // ---- streaming softmax on this thread's half row: two passes over its 64 TMEM columns ----
-        // keys beyond S exist only in the last tile; nvalid = how many of this thread's 64 keys are real
-        const int nvalid = min(HK, max(0, S - j * BKEY - half * HK));
-        float corr;
+        if (tid == 0 && j + 1 < ntiles)
         {
-            float mx = -INFINITY;
-#pragma unroll
-            for (int c = 0; c < HK; c += 32)
-            {
-                uint32_t s[32];
-                tmem_ld32(tmem_S + (uint32_t)c, s);
-                if (nvalid == HK)
-                {
-#pragma unroll
-                    for (int jj = 0; jj < 32; ++jj)
-                        mx = fmaxf(mx, __uint_as_float(s[jj]));
-                }
-                else
-                {
-#pragma unroll
-                    for (int jj = 0; jj < 32; ++jj)
-                        if (c + jj < nvalid)
-                            mx = fmaxf(mx, __uint_as_float(s[jj]));
-                }
-            }
-            const float m_new = fmaxf(m_run, mx * scale_log2); // scale > 0: max commutes with it
-            corr = (m_run == -INFINITY) ? 0.f : ex2f(m_run - m_new);
-            // a half with no real key yet keeps m = -inf; give the exponent a finite offset (its p are forced to 0)
-            const float m_sub = (m_new == -INFINITY) ? 0.f : m_new;
-            float rs = 0.f;
-#pragma unroll
-            for (int c = 0; c < HK; c += 32)
-            {
-                uint32_t s[32];
-                tmem_ld32(tmem_S + (uint32_t)c, s);
-                float pv[32];
-                if (nvalid == HK)
-                {
-#pragma unroll
-                    for (int jj = 0; jj < 32; ++jj)
-                        pv[jj] = ex2f(fmaf(__uint_as_float(s[jj]), scale_log2, -m_sub));
-                }
-                else
-                {
-#pragma unroll
-                    for (int jj = 0; jj < 32; ++jj)
-                        pv[jj] = (c + jj < nvalid) ? ex2f(fmaf(__uint_as_float(s[jj]), scale_log2, -m_sub)) : 0.f;
-                }
-#pragma unroll
-                for (int jj = 0; jj < 32; ++jj)
-                    rs += pv[jj];
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                {
-                    uint4 pk;
-                    pk.x = pack_bf16x2(pv[8 * q], pv[8 * q + 1]);
-                    pk.y = pack_bf16x2(pv[8 * q + 2], pv[8 * q + 3]);
-                    pk.z = pack_bf16x2(pv[8 * q + 4], pv[8 * q + 5]);
-                    pk.w = pack_bf16x2(pv[8 * q + 6], pv[8 * q + 7]);
-                    *reinterpret_cast<uint4 *>(Prow + (c / 8 + q) * LBO) = pk;
-                }
-            }
-            l_run = l_run * corr + rs;
-            m_run = m_new;
+            const int nb = (j + 1) & 1;
+            mbar_arrive_expect_tx(&kv_full[nb], 2 * TILE);
+            bulk_g2s(Ks + nb * TILE, tile_ptr(Kp, ldk8, kc8, Spad, j + 1), TILE, &kv_full[nb]);
+            bulk_g2s(Vs + nb * TILE, tile_ptr(Vp, ldv8, vc8, Spad, j + 1), TILE, &kv_full[nb]);
         }
+        // ---- this thread's 64 scores of the tile, read once ----
+        const int nvalid = min(HK, max(0, S - j * BKEY - half * HK));
+        uint32_t s[HK];
+        tmem_ld32(tmem_S, s);
+        tmem_ld32(tmem_S + 32u, s + 32);
+        float mx = -INFINITY;
+        if (nvalid == HK)
+        {
+#pragma unroll
+            for (int jj = 0; jj < HK; ++jj)
+                mx = fmaxf(mx, __uint_as_float(s[jj]));
+        }
+        else
+        {
+#pragma unroll
+            for (int jj = 0; jj < HK; ++jj)
+                if (jj < nvalid)
+                    mx = fmaxf(mx, __uint_as_float(s[jj]));
+        }
+        mx *= scale_log2; // scale > 0: max commutes with it
+        const bool raise = mx > m_use + LAG || (m_use == -INFINITY && mx > -INFINITY);
+        if (__any_sync(0xffffffffu, raise))
+        {
+            const float f = raise ? ((m_use == -INFINITY) ? 0.f : ex2f(m_use - mx)) : 1.0f;
+            if (j > 0)
+            {
+#pragma unroll
+                for (int c = 0; c < DH; c += 16)
+                {
+                    uint32_t ov[16];
+                    tmem_ld16(tmem_PV + (uint32_t)c, ov);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        ov[i] = __float_as_uint(__uint_as_float(ov[i]) * f);
+                    tmem_st16(tmem_PV + (uint32_t)c, ov);
+                }
+                tmem_wait_st();
+            }
+            l_run *= f;
+            if (raise)
+                m_use = mx;
+        }
+        const float m_sub = (m_use == -INFINITY) ? 0.f : m_use; // no real key yet: the p below are all forced to 0
+        float rs = 0.f;
+#pragma unroll
+        for (int c = 0; c < HK; c += 8)
+        {
+            float pv[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+            {
+                const float p = ex2f(fmaf(__uint_as_float(s[c + e]), scale_log2, -m_sub));
+                pv[e] = (nvalid == HK || c + e < nvalid) ? p : 0.f;
+                rs += pv[e];
+            }
+            uint4 pk;
+            pk.x = pack_bf16x2(pv[0], pv[1]);
+            pk.y = pack_bf16x2(pv[2], pv[3]);
+            pk.z = pack_bf16x2(pv[4], pv[5]);
+            pk.w = pack_bf16x2(pv[6], pv[7]);
+            *reinterpret_cast<uint4 *>(Prow + (c / 8) * LBO) = pk;
+        }
+        l_run += rs;
         tc_fence_before();
         fence_proxy_async(); // P was written through the generic proxy
         __syncthreads();
-        // ---- PV_h = P_h V_h for both key halves ----
+        // ---- PV_h += P_h V_h for both key halves, then S of the next tile right behind it ----
         if (tid == 0)
         {
             tc_fence_after();
@@ -319,24 +323,35 @@ __global__ void __launch_bounds__(THREADS, 2)
 #pragma unroll
             for (int jj = 0; jj < BKEY / 16; ++jj)
                 umma(tmem_slot + 128u + (uint32_t)((jj / 4) * DH), make_desc(pa + jj * 2 * LBO, LBO, 128),
-                     make_desc(va + jj * 256, 128, LBO), idesc_pv, (jj & 3) ? 1u : 0u);
+                     make_desc(va + jj * 256, 128, LBO), idesc_pv, ((jj & 3) || j > 0) ? 1u : 0u);
+            if (j + 1 < ntiles)
+            {
+                const int nb = (j + 1) & 1;
+                mbar_wait(&kv_full[nb], (uint32_t)(((j + 1) / 2) & 1));
+                tc_fence_after();
+                const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks + nb * TILE);
+#pragma unroll
+                for (int jj = 0; jj < DH / 16; ++jj)
+                    umma(tmem_slot, make_desc(qa + jj * 2 * LBO, LBO, 128), make_desc(ka + jj * 2 * LBO, LBO, 128), idesc_s,
+                         jj > 0 ? 1u : 0u);
+            }
             umma_commit(&mma_bar);
-            umma_commit(&kv_empty[buf]); // K/V buffer reusable once everything issued so far has completed
         }
-        mbar_wait(&mma_bar, phase);
-        phase ^= 1u;
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < DH; c += 16)
-        {
-            uint32_t pv[16];
-            tmem_ld16(tmem_PV + (uint32_t)c, pv);
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-                o[c + i] = fmaf(o[c + i], corr, __uint_as_float(pv[i]));
-        }
-        tc_fence_before();
     }
+    mbar_wait(&mma_bar, (uint32_t)(ntiles & 1)); // the last PV
+    tc_fence_after();
+    float o[DH];
+#pragma unroll
+    for (int c = 0; c < DH; c += 16)
+    {
+        uint32_t ov[16];
+        tmem_ld16(tmem_PV + (uint32_t)c, ov);
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            o[c + i] = __uint_as_float(ov[i]);
+    }
+    tc_fence_before();
+    const float m_run = m_use;
     // ---- merge the two key halves of every row (all MMAs and copies have completed: operand smem is free) ----
     float *mg = reinterpret_cast<float *>(smem); // [DH + 2][128]
     __syncthreads();
