@@ -105,6 +105,9 @@ int model_v3_finalize(dmx_model *m)
         return 0;
     DMX_CUDA(cudaSetDevice(m->device));
     DMX_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+    DMX_CUDA(cudaStreamCreateWithFlags(&m->stream2, cudaStreamNonBlocking));
+    DMX_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
+    DMX_CUDA(cudaEventCreateWithFlags(&m->ev_join, cudaEventDisableTiming));
     DMX_CUDA(cudaEventCreate(&m->ev0));
     DMX_CUDA(cudaEventCreate(&m->ev1));
     DMX_CUDA(cudaEventCreate(&m->ev2));
@@ -370,6 +373,24 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             return -1;
     }
 
+    // time branch on a second stream through the branch-parallel parts (as in model.cu; one stream while profiling)
+    cudaStream_t st_t = m->prof.on ? st : m->stream2;
+    auto fork = [&]() -> int {
+        if (st_t == st)
+            return 0;
+        DMX_CUDA(cudaEventRecord(m->ev_fork, st));
+        DMX_CUDA(cudaStreamWaitEvent(st_t, m->ev_fork, 0));
+        return 0;
+    };
+    auto join = [&]() -> int {
+        if (st_t == st)
+            return 0;
+        DMX_CUDA(cudaEventRecord(m->ev_join, st_t));
+        DMX_CUDA(cudaStreamWaitEvent(st, m->ev_join, 0));
+        return 0;
+    };
+    if (fork())
+        return -1;
     // ---- encoders 0-3 (src/encdec.cpp:363-517) ----
     const float *xin_f = m->spec, *xin_t = m->xt_in;
     for (int i = 0; i < 4; ++i)
@@ -377,6 +398,7 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         const EncW &te = v->tenc[i];
         const EncW &fe = v->enc[i];
         const int C = fe.C;
+        f.st = st_t;
         {
             GemmParams p = f.base(xin_t, te.Cin, te.Cin, te.conv, m->cA_t, C, 1, TLENS[i], 1, TLENS[i + 1]);
             p.ntaps = 8;
@@ -405,6 +427,7 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             r.Nco = C;
             f.gemm(r, PC_GEMM_CONV);
         }
+        f.st = st;
         {
             GemmParams p = f.base(xin_f, fe.Cin, fe.Cin, fe.conv, m->cA_f, C, FREQS[i], T, FREQS[i + 1], T);
             p.ntaps = 8;
@@ -430,6 +453,9 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         xin_t = m->te[i];
         xin_f = m->e[i];
     }
+    f.st = st;
+    if (join())
+        return -1;
 
     // ---- time encoder 4: plain conv 384 -> 768, k8 s4 p2 (src/encdec.cpp:519-530) ----
     {
@@ -547,11 +573,14 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     }
     // ---- common decoders, no DConv (src/encdec.cpp:728-863) ----
     const float *dec_in_f = v->x3, *dec_in_t = v->xt3;
+    if (fork())
+        return -1;
     for (int i = 0; i < 4; ++i)
     {
         const DecW &fd = v->cdec[i];
         const DecW &td = v->ctdec[i];
         const int C = fd.C, F = FREQS[4 - i], Lin = TLENS[4 - i], Lout = TLENS[3 - i];
+        f.st = st;
         {
             GemmParams p = f.base(dec_in_f, C, C, fd.rewrite, m->cA_f, C, F, T, F, T);
             if (i == 0)
@@ -581,6 +610,7 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
                 q.addC = m->e[2 - i]; // the next decoder's skip (src/encdec.cpp:172), added once here
             f.gemm(q, PC_GEMM_CONV);
         }
+        f.st = st_t;
         {
             GemmParams p = f.base(dec_in_t, C, C, td.rewrite, m->cA_t, C, 1, Lin, 1, Lin);
             if (i == 0)
@@ -613,7 +643,8 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         dec_in_f = m->dx[i];
         dec_in_t = m->dxt[i];
     }
-    if (f.rc)
+    f.st = st;
+    if (f.rc || join())
         return -1;
     {
         ProfScope ps(m, PC_ISTFT_FRAMES, 0.0,
