@@ -1,4 +1,4 @@
-// STFT / iSTFT for the 7.8 s segment forward, as shared-memory radix-4 Stockham FFTs.
+// STFT / iSTFT for the 7.8 s segment forward, as shared-memory radix-16 Stockham FFTs.
 //
 // Reference semantics reproduced here (see oracle/demucs_oracle.py for the CPU restatement):
 //   * reflect_padding 1536/1620 with the edge sample included  (src/model_inference.cpp:22-46)
@@ -19,50 +19,123 @@ namespace dmx
 {
 
 constexpr int FFT_THREADS = 256;
-constexpr int FFT_SMEM = 2 * NFFT * (int)sizeof(float2); // ping-pong, 64 KB
+constexpr int FFT_YLEN = NFFT + NFFT / 16;                         // second buffer: padded layout of the first pass
+constexpr int FFT_SMEM = (NFFT + FFT_YLEN) * (int)sizeof(float2); // ping-pong, 66 KB
 
 __device__ __forceinline__ float2 cmul(float2 a, float2 b)
 {
     return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
 
-// In-place (ping-pong) 4096-point complex FFT over shared memory, 6 radix-4 Stockham passes.
-// tw[k] = exp(-2*pi*i*k/4096).  INV conjugates the twiddles and the +-i rotation (unscaled inverse).
-// Result ends in `x` (6 passes = even number of swaps).  Caller syncs before and after.
-template <bool INV>
-__device__ __forceinline__ void fft4096(float2 *x, float2 *y, const float2 *__restrict__ tw)
+// ------------------------------------------------------------------------------------------------
+// 4096-point complex FFT over shared memory: three radix-16 Stockham passes, one 16-point butterfly per thread per
+// pass, the butterfly in registers (4 x 4 decomposition), two block barriers.  tw[k] = exp(-2*pi*i*k/4096); INV
+// conjugates the twiddles and the +-i rotations (unscaled inverse).
+//   pass A: sub-length 4096, stride 1    x[p + 256 k]            -> y[pad(16 p + k)]      * w^(k p)
+//   pass B: sub-length  256, stride 16   y[pad(q + 16 p + 256 k)] -> x[q + 256 p + 16 k]   * w^(16 k p)
+//   pass C: sub-length   16, stride 256  x[q + 256 k]            -> y[q + 256 k]
+// pad(i) = i + i/16 keeps pass A's stride-16 stores conflict free.  The result ends in y (natural order, unpadded).
+__device__ __forceinline__ int fft_pad(int i) { return i + (i >> 4); }
+
+template <bool INV> __device__ __forceinline__ float2 mul_i(float2 a) // forward: -i a ; inverse: +i a
 {
-    int s = 1;
-#pragma unroll 1
-    for (int n = NFFT; n > 1; n >>= 2, s <<= 2)
+    return INV ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+
+// 4-point DFT: X1 = a0 -+ i a1 - a2 +- i a3 (upper sign forward)
+template <bool INV> __device__ __forceinline__ void dft4(float2 a0, float2 a1, float2 a2, float2 a3, float2 &X0, float2 &X1, float2 &X2, float2 &X3)
+{
+    const float2 s02 = cadd(a0, a2), d02 = csub(a0, a2), s13 = cadd(a1, a3), d13 = mul_i<INV>(csub(a1, a3));
+    X0 = cadd(s02, s13);
+    X2 = csub(s02, s13);
+    X1 = cadd(d02, d13);
+    X3 = csub(d02, d13);
+}
+
+template <bool INV> __device__ __forceinline__ void dft16(float2 (&v)[16])
+{
+    // w16^m = exp(-+ 2 pi i m / 16), m = j2 * k1
+    constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, C2 = 0.70710678118654752f;
+    float2 a[4][4];
+#pragma unroll
+    for (int j2 = 0; j2 < 4; ++j2)
+        dft4<INV>(v[j2], v[4 + j2], v[8 + j2], v[12 + j2], a[j2][0], a[j2][1], a[j2][2], a[j2][3]);
+    auto tw = [](float2 z, float c, float sn) { // z * (c - i sn) forward, z * (c + i sn) inverse
+        const float si = INV ? sn : -sn;
+        return make_float2(z.x * c - z.y * si, z.x * si + z.y * c);
+    };
+    a[1][1] = tw(a[1][1], C1, S1);
+    a[1][2] = tw(a[1][2], C2, C2);
+    a[1][3] = tw(a[1][3], S1, C1);
+    a[2][1] = tw(a[2][1], C2, C2);
+    a[2][2] = mul_i<INV>(a[2][2]);          // m = 4
+    a[2][3] = tw(a[2][3], -C2, C2);         // m = 6
+    a[3][1] = tw(a[3][1], S1, C1);          // m = 3
+    a[3][2] = tw(a[3][2], -C2, C2);         // m = 6
+    a[3][3] = tw(a[3][3], -C1, -S1);        // m = 9
+#pragma unroll
+    for (int k1 = 0; k1 < 4; ++k1)
+        dft4<INV>(a[0][k1], a[1][k1], a[2][k1], a[3][k1], v[k1], v[k1 + 4], v[k1 + 8], v[k1 + 12]);
+}
+
+// x: NFFT entries (input, natural order); y: FFT_YLEN entries; result in y[0..NFFT).  Caller syncs before and after.
+template <bool INV> __device__ __forceinline__ void fft4096_r16(float2 *x, float2 *y, const float2 *__restrict__ tw)
+{
+    static_assert(FFT_THREADS == NFFT / 16, "one radix-16 butterfly per thread per pass");
+    const int t = threadIdx.x;
+    float2 v[16];
+    // ---- pass A ----
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        v[k] = x[t + 256 * k];
+    dft16<INV>(v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
     {
-        const int n1 = n >> 2;
-        for (int t = threadIdx.x; t < NFFT / 4; t += FFT_THREADS)
+        float2 o = v[k];
+        if (k > 0)
         {
-            const int p = t / s, q = t - p * s;
-            float2 w1 = __ldg(&tw[p * s]), w2 = __ldg(&tw[2 * p * s]), w3 = __ldg(&tw[3 * p * s]);
+            float2 w = __ldg(&tw[k * t]);
             if (INV)
-            {
-                w1.y = -w1.y;
-                w2.y = -w2.y;
-                w3.y = -w3.y;
-            }
-            const float2 a = x[q + s * p], b = x[q + s * (p + n1)], c = x[q + s * (p + 2 * n1)],
-                         d = x[q + s * (p + 3 * n1)];
-            const float2 apc = make_float2(a.x + c.x, a.y + c.y), amc = make_float2(a.x - c.x, a.y - c.y);
-            const float2 bpd = make_float2(b.x + d.x, b.y + d.y), bmd = make_float2(b.x - d.x, b.y - d.y);
-            // j*(b-d): forward j = +i -> (-im, re); inverse j = -i -> (im, -re)
-            const float2 jb = INV ? make_float2(bmd.y, -bmd.x) : make_float2(-bmd.y, bmd.x);
-            y[q + s * (4 * p + 0)] = make_float2(apc.x + bpd.x, apc.y + bpd.y);
-            y[q + s * (4 * p + 1)] = cmul(w1, make_float2(amc.x - jb.x, amc.y - jb.y));
-            y[q + s * (4 * p + 2)] = cmul(w2, make_float2(apc.x - bpd.x, apc.y - bpd.y));
-            y[q + s * (4 * p + 3)] = cmul(w3, make_float2(amc.x + jb.x, amc.y + jb.y));
+                w.y = -w.y;
+            o = cmul(w, o);
         }
-        __syncthreads();
-        float2 *tmp = x;
-        x = y;
-        y = tmp;
+        y[fft_pad(16 * t + k)] = o;
     }
+    __syncthreads();
+    // ---- pass B ----
+    {
+        const int p = t >> 4, q = t & 15;
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            v[k] = y[fft_pad(q + 16 * p + 256 * k)];
+        dft16<INV>(v);
+        // x (pass A's input) may be overwritten now: every thread finished pass A before the barrier above
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+        {
+            float2 o = v[k];
+            if (k > 0 && p > 0)
+            {
+                float2 w = __ldg(&tw[16 * k * p]);
+                if (INV)
+                    w.y = -w.y;
+                o = cmul(w, o);
+            }
+            x[q + 256 * p + 16 * k] = o;
+        }
+    }
+    __syncthreads();
+    // ---- pass C ----
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        v[k] = x[t + 256 * k];
+    dft16<INV>(v);
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        y[t + 256 * k] = v[k];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -94,13 +167,14 @@ __global__ void __launch_bounds__(FFT_THREADS) stft_kernel(const float2 *__restr
         x[n] = make_float2(v.x * w, v.y * w);
     }
     __syncthreads();
-    fft4096<false>(x, y, tw);
+    fft4096_r16<false>(x, y, tw);
+    __syncthreads();
     const float sc = 1.0f / 64.0f; // 1/sqrt(4096)
     float s1 = 0.f, s2 = 0.f;
     for (int k = threadIdx.x; k < NBINS; k += FFT_THREADS)
     {
-        const float2 zk = x[k];
-        const float2 zm = x[(NFFT - k) & (NFFT - 1)];
+        const float2 zk = y[k];
+        const float2 zm = y[(NFFT - k) & (NFFT - 1)];
         // XL = (Z[k] + conj(Z[N-k]))/2 ; XR = (Z[k] - conj(Z[N-k]))/(2i)
         float4 o;
         o.x = 0.5f * (zk.x + zm.x) * sc;
@@ -181,13 +255,14 @@ __global__ void __launch_bounds__(FFT_THREADS) istft_frames_kernel(const float *
         }
     }
     __syncthreads();
-    fft4096<true>(x, y, tw);
+    fft4096_r16<true>(x, y, tw);
+    __syncthreads();
     float2 *dst = frames + (((size_t)b * S + s) * LE + t) * NFFT;
     const float sc = 64.0f / 4096.0f; // sqrt(4096) / 4096
     for (int n = threadIdx.x; n < NFFT; n += FFT_THREADS)
     {
         const float w = __ldg(&window[n]) * sc;
-        const float2 v = x[n];
+        const float2 v = y[n];
         dst[n] = make_float2(v.x * w, v.y * w);
     }
 }
