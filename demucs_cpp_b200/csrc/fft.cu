@@ -21,6 +21,7 @@ namespace dmx
 constexpr int FFT_THREADS = 256;
 constexpr int FFT_YLEN = NFFT + NFFT / 16;                         // second buffer: padded layout of the first pass
 constexpr int FFT_SMEM = (NFFT + FFT_YLEN) * (int)sizeof(float2); // ping-pong, 66 KB
+constexpr int ISTFT_SMEM = (2 * NFFT + FFT_YLEN) * (int)sizeof(float2); // two sources' spectra + the second buffer
 
 __device__ __forceinline__ float2 cmul(float2 a, float2 b)
 {
@@ -217,6 +218,9 @@ __global__ void __launch_bounds__(FFT_THREADS) stft_kernel(const float2 *__restr
 // xout[b][f][t][4*S] (channels s*4 + {ReL,ImL,ReR,ImR}), de-normalises with the per-item
 // (mean, std) of the input spectrogram, runs the inverse FFT and writes the windowed frame
 // (scaled by 64/4096, not yet divided by the window-sum-square) to frames[b][s][t][4096] (L,R).
+// A CTA handles a PAIR of sources: for one bin the pair's 8 values are one whole 32-byte sector of the
+// (bins x frames x channels) tensor, whose bins lie 21 KB apart -- the kernel is bound by the rate of those
+// scattered sector requests, and a single source would use only half of every sector it pulls.
 __global__ void __launch_bounds__(FFT_THREADS) istft_frames_kernel(const float *__restrict__ xout, int S,
                                                                    const float2 *__restrict__ meanstd, // [B] (mean,std)
                                                                    const float *__restrict__ window,
@@ -224,46 +228,60 @@ __global__ void __launch_bounds__(FFT_THREADS) istft_frames_kernel(const float *
                                                                    float2 *__restrict__ frames)
 {
     extern __shared__ float2 sm[];
-    float2 *x = sm, *y = sm + NFFT;
-    const int t = blockIdx.x, s = blockIdx.y, b = blockIdx.z;
+    float2 *xa = sm, *xb = sm + NFFT, *y = sm + 2 * NFFT;
+    const int t = blockIdx.x, s0 = 2 * blockIdx.y, b = blockIdx.z;
     const float2 ms = meanstd[b];
     const int C = 4 * S;
+    const bool pair = s0 + 1 < S; // an odd source count leaves the last CTA row with one source
     // the eight bins of a thread are 21 KB apart in memory: issue all loads before touching any of them
-    float4 vin[NBINS / FFT_THREADS];
+    float4 va[NBINS / FFT_THREADS], vb[NBINS / FFT_THREADS];
 #pragma unroll
     for (int i = 0; i < NBINS / FFT_THREADS; ++i)
-        vin[i] = __ldg(reinterpret_cast<const float4 *>(
-            xout + (((size_t)b * NBINS + threadIdx.x + i * FFT_THREADS) * LE + t) * C + 4 * s));
+    {
+        const float *src = xout + (((size_t)b * NBINS + threadIdx.x + i * FFT_THREADS) * LE + t) * C + 4 * s0;
+        va[i] = __ldg(reinterpret_cast<const float4 *>(src));
+        vb[i] = pair ? __ldg(reinterpret_cast<const float4 *>(src + 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
     for (int i = 0; i < NBINS / FFT_THREADS; ++i)
     {
         const int k = threadIdx.x + i * FFT_THREADS;
-        const float4 v = vin[i];
-        const float lr = v.x * ms.y + ms.x, li = v.y * ms.y + ms.x;
-        const float rr = v.z * ms.y + ms.x, ri = v.w * ms.y + ms.x;
-        if (k == 0)
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
         {
-            // real inverse ignores the imaginary part of DC; Nyquist bin is zero-padded
-            x[0] = make_float2(lr, rr);
-            x[NFFT / 2] = make_float2(0.f, 0.f);
-        }
-        else
-        {
-            // Z[k] = XL + i XR ; Z[N-k] = conj(XL) + i conj(XR)
-            x[k] = make_float2(lr - ri, li + rr);
-            x[NFFT - k] = make_float2(lr + ri, rr - li);
+            const float4 v = h ? vb[i] : va[i];
+            float2 *x = h ? xb : xa;
+            const float lr = v.x * ms.y + ms.x, li = v.y * ms.y + ms.x;
+            const float rr = v.z * ms.y + ms.x, ri = v.w * ms.y + ms.x;
+            if (k == 0)
+            {
+                // real inverse ignores the imaginary part of DC; Nyquist bin is zero-padded
+                x[0] = make_float2(lr, rr);
+                x[NFFT / 2] = make_float2(0.f, 0.f);
+            }
+            else
+            {
+                // Z[k] = XL + i XR ; Z[N-k] = conj(XL) + i conj(XR)
+                x[k] = make_float2(lr - ri, li + rr);
+                x[NFFT - k] = make_float2(lr + ri, rr - li);
+            }
         }
     }
     __syncthreads();
-    fft4096_r16<true>(x, y, tw);
-    __syncthreads();
-    float2 *dst = frames + (((size_t)b * S + s) * LE + t) * NFFT;
     const float sc = 64.0f / 4096.0f; // sqrt(4096) / 4096
-    for (int n = threadIdx.x; n < NFFT; n += FFT_THREADS)
+#pragma unroll 1
+    for (int h = 0; h < (pair ? 2 : 1); ++h)
     {
-        const float w = __ldg(&window[n]) * sc;
-        const float2 v = y[n];
-        dst[n] = make_float2(v.x * w, v.y * w);
+        fft4096_r16<true>(h ? xb : xa, y, tw);
+        __syncthreads();
+        float2 *dst = frames + (((size_t)b * S + s0 + h) * LE + t) * NFFT;
+        for (int n = threadIdx.x; n < NFFT; n += FFT_THREADS)
+        {
+            const float w = __ldg(&window[n]) * sc;
+            const float2 v = y[n];
+            dst[n] = make_float2(v.x * w, v.y * w);
+        }
+        __syncthreads(); // y is rewritten by the second transform
     }
 }
 
@@ -309,7 +327,7 @@ __global__ void __launch_bounds__(256) istft_ola_kernel(const float2 *__restrict
 int fft_init_device()
 {
     DMX_CUDA(cudaFuncSetAttribute(stft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FFT_SMEM));
-    DMX_CUDA(cudaFuncSetAttribute(istft_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FFT_SMEM));
+    DMX_CUDA(cudaFuncSetAttribute(istft_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ISTFT_SMEM));
     return 0;
 }
 
@@ -326,7 +344,7 @@ int launch_istft(const float *xout, int B, int S, const float *meanstd, const fl
                  const float *wss, const float *xt_out, const float *meanstd_t, float *frames_scratch,
                  float *out, cudaStream_t st)
 {
-    istft_frames_kernel<<<dim3(LE, S, B), FFT_THREADS, FFT_SMEM, st>>>(
+    istft_frames_kernel<<<dim3(LE, (S + 1) / 2, B), FFT_THREADS, ISTFT_SMEM, st>>>(
         xout, S, (const float2 *)meanstd, window, (const float2 *)tw, (float2 *)frames_scratch);
     DMX_LAUNCH_CHECK();
     istft_ola_kernel<<<dim3((SEG + 255) / 256, S, B), 256, 0, st>>>(
