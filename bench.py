@@ -210,7 +210,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=8, help="segments per launch")
+    ap.add_argument("--batch", type=int, default=16, help="segments per launch (8.4 GB of activations at 16)")
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
                     help="bf16: tcgen05 GEMMs/attention with bf16 operands, fp32 accumulate/residual/statistics (stems >= 40 dB "
                          "vs the reference); fp32: CUDA-core path (stems >= 80 dB)")

@@ -125,7 +125,7 @@ __device__ __forceinline__ void block_sum2(double &a, double &b, double *red)
 // [B][4F][336][4] (8 taps x 4 channels = K 32), so x is produced on the SM (written once for the residual updates)
 // instead of being written by a GEMM launch and read back.  cin: Wc bf16 [C][40] (k = tap*4 + ch) | bias fp32 [C].
 template <int C, int HID, bool RW, bool CIN>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, (C == 48 && HID == 6) ? 4 : 1)
     dconv_mma_kernel(float *__restrict__ x, const uint8_t *__restrict__ params, const uint8_t *__restrict__ rw,
                      float *__restrict__ out, const float *__restrict__ rowadd, const int F, const float *__restrict__ spec,
                      const uint8_t *__restrict__ cin)
