@@ -361,9 +361,20 @@ template <int H> static int lstm_cluster_launch(const float *pre, const float *w
 int launch_lstm_recurrent(const float *pre, const float *whh_fwd, const float *whh_bwd, const float *whh_t_fwd,
                           const float *whh_t_bwd, float *out, int B, int T, int H, cudaStream_t st)
 {
-    if ((H == 192 || H == 384) && B <= LSTM_BMAX)
-        return H == 192 ? lstm_cluster_launch<192>(pre, whh_fwd, whh_bwd, out, B, T, st)
-                        : lstm_cluster_launch<384>(pre, whh_fwd, whh_bwd, out, B, T, st);
+    if (H == 192 || H == 384)
+    {
+        // the cluster kernel keeps the hidden state of up to LSTM_BMAX items on chip: larger batches go in chunks
+        for (int b0 = 0; b0 < B; b0 += LSTM_BMAX)
+        {
+            const int nb = (B - b0) < LSTM_BMAX ? (B - b0) : LSTM_BMAX;
+            const float *pc = pre + (size_t)b0 * T * 2 * 4 * H;
+            float *oc = out + (size_t)b0 * T * 2 * H;
+            if (H == 192 ? lstm_cluster_launch<192>(pc, whh_fwd, whh_bwd, oc, nb, T, st)
+                         : lstm_cluster_launch<384>(pc, whh_fwd, whh_bwd, oc, nb, T, st))
+                return -1;
+        }
+        return 0;
+    }
     if (H > 1024)
     {
         set_error("lstm: hidden size > 1024");
