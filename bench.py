@@ -402,7 +402,13 @@ def main():
     roof["traffic"] = None
     if os.path.exists(tp):
         try:
-            roof["traffic"] = json.load(open(tp)).get(dom)
+            tj = json.load(open(tp))
+            roof["traffic"] = tj.get(dom)
+            if roof["traffic"] is not None and tj.get("_segments_per_launch"):
+                # the ncu capture profiled launches over 8 segments; a launch here covers args.batch of them
+                roof["traffic"] = roof["traffic"] * args.batch / tj["_segments_per_launch"]
+                roof["traffic_note"] = "ncu dram bytes per launch at %d segments per launch, scaled to %d" % (
+                    tj["_segments_per_launch"], args.batch)
         except Exception:
             pass
 

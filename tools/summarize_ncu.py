@@ -82,8 +82,9 @@ def main():
     for c, e in tr.items():
         e["dram_bytes_per_launch"] = e["dram_bytes_per_batch"] / e["launches_per_batch"]
     json.dump(tr, open(os.path.join(ROOT, "profiles", "%s_traffic.json" % tag), "w"), indent=1)
-    json.dump({c: e["dram_bytes_per_launch"] for c, e in tr.items()}, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"),
-              indent=1)
+    tj = {c: e["dram_bytes_per_launch"] for c, e in tr.items()}
+    tj["_segments_per_launch"] = 8  # tools/profile_step.py profiles one batch of 8 segments; bench.py rescales
+    json.dump(tj, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
     shutil.copy(traffic_csv, os.path.join(ROOT, "profiles", "%s_ncu_traffic.csv" % tag))
     print("\n".join(out[-14:]))
     print(json.dumps({c: round(e["dram_bytes_per_launch"] / 1e6, 1) for c, e in tr.items()}))
