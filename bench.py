@@ -7,8 +7,9 @@
 Workload = BASELINE.json configs[1]: htdemucs 4-source (random-init weights, seed 0) on a 3-minute synthetic
 stereo 44.1 kHz track = 31 overlapping 7.8 s segments.  One "step" = one full separation of that track
 (normalise, shift 4033, split, per-segment forward, weighted overlap-add).  Metric = audio-seconds separated
-per wall-second.  For N > 1 the segments of the ONE track are sharded round-robin over the ranks (strong
-scaling, as configs[1] says), each rank's stems are gathered to rank 0 over NCCL and rank 0 overlap-adds.
+per wall-second.  For N > 1 the segments of the ONE track are split into contiguous runs over the ranks (strong
+scaling, as configs[1] says): every rank reads its own window of the track, overlap-adds and writes its own stretch of
+the stems; between ranks travel a 16-byte all-reduce (track statistics) and one 2.75 MB tail per neighbour pair.
 
 `value`  : inputs resident in HBM, device time (CUDA events on the library's stream), max over ranks.
 `e2e`    : the same through the host-buffer entry point (pinned host audio in, host stems out, copies inside
@@ -153,6 +154,27 @@ def time_reference_segments(n_workers, omp_threads, steps, warmup, budget_s=200.
     return times, done_warm
 
 
+def time_reference_one_segment(omp_threads, seg, budget_s=75.0):
+    """cpu_baseline leg: one full 7.8 s segment through the reference's model_inference with all host cores in the
+    GEMMs; one warm-up run (first touch, OpenMP start-up), then at least two timed runs inside the budget.
+    Returns (times, stems of the last run)."""
+    os.environ["OMP_NUM_THREADS"] = str(omp_threads)
+    from demucs_cpp_b200 import weights
+    from oracle import ref
+    m = ref.RefModel(weights.cached_weights("htdemucs_4s", 0))
+    seg = np.ascontiguousarray(seg, dtype=np.float32)
+    t0 = time.perf_counter()
+    out = m.segment(seg)
+    first = time.perf_counter() - t0
+    times = []
+    while len(times) < 2 or (len(times) < 3 and first * (len(times) + 2) < budget_s):
+        t0 = time.perf_counter()
+        out = m.segment(seg)
+        times.append(time.perf_counter() - t0)
+    m.close()
+    return times, out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -199,11 +221,288 @@ def workload_config(args, world):
             "segments": 31, "segments_per_launch": args.batch, "precision": args.precision, "shift_offset": SHIFT,
             "l2": "inputs larger than L2: 63.5 MB track + %.1f GB of per-batch activations stream through the 126 MB L2 "
                   "every step" % (0.52 * args.batch),
-            "parallelism": "segments sharded round-robin over %d rank(s); NCCL gather of stems to rank 0; rank 0 "
-                           "overlap-adds" % world}
+            "parallelism": "contiguous runs of segments over %d rank(s); each rank reads its own window of the track and "
+                           "overlap-adds / writes its own stretch of the stems; between ranks: one 16-byte all-reduce "
+                           "(track statistics) and the 85995-frame tail of a rank's last segment to its neighbour "
+                           "(NCCL send/recv)" % world}
 
 
 # ------------------------------------------------------------------------------------------------ this repo's arm
+class SharedHostBuffer:
+    """The stems of the whole track in ONE host buffer that every rank's GPU can DMA into: rank 0 owns it (POSIX
+    shared memory), the other ranks map and page-lock the same pages, so each GPU copies its own stretch of the
+    output over its own PCIe link and nothing funnels through one device."""
+
+    def __init__(self, shape, rank, world, torch, dist):
+        import tempfile
+        self.torch = torch
+        n = int(np.prod(shape))
+        if world == 1:
+            self.t = torch.empty(shape, dtype=torch.float32).pin_memory()
+            self.path = None
+            return
+        obj = [None]
+        if rank == 0:
+            fd, path = tempfile.mkstemp(prefix="dmx_bench_out_", dir="/dev/shm")
+            os.ftruncate(fd, n * 4)
+            os.close(fd)
+            obj = [path]
+        dist.broadcast_object_list(obj, src=0)
+        self.path = obj[0]
+        self.mm = np.memmap(self.path, dtype=np.float32, mode="r+", shape=tuple(shape))
+        self.t = torch.from_numpy(self.mm)
+        self.registered = torch.cuda.cudart().cudaHostRegister(self.t.data_ptr(), n * 4, 0)
+        self.registered = int(self.registered) == 0
+        dist.barrier()
+        if rank == 0:
+            os.unlink(self.path)  # the mappings keep it alive
+
+    def close(self):
+        if self.path is not None and getattr(self, "registered", False):
+            self.torch.cuda.cudart().cudaHostUnregister(self.t.data_ptr())
+            self.registered = False
+
+
+class Workload:
+    """One BASELINE.json config on this rank: model(s), the track, device / host buffers, one step."""
+
+    def __init__(self, name, args, env):
+        torch, dist, api, weights = env["torch"], env["dist"], env["api"], env["weights"]
+        self.name, self.env = name, env
+        self.rank, self.world, dev = env["rank"], env["world"], env["dev"]
+        prec = api.PRECISION_BF16 if args.precision == "bf16" else api.PRECISION_FP32
+        if name == "htdemucs_ft":
+            # bag of four fine-tuned 4-source models, each with its own random shift (the successive rand() % 22050
+            # draws of a fresh process), stem i taken from model i (cli-apps/demucs_ft.cpp:221-241)
+            self.models = [api.DemucsModel(weights.cached_weights("htdemucs_4s", seed), device=env["local_rank"],
+                                           max_batch=args.batch, precision=prec) for seed in range(4)]
+            self.shifts = [4033, 12436, 5427, 6865]
+        else:
+            self.models = [api.DemucsModel(weights.cached_weights(name, 0), device=env["local_rank"], max_batch=args.batch,
+                                           precision=prec)]
+            self.shifts = [SHIFT]
+        self.S = S = self.models[0].nb_sources
+        self.L = L = TRACK_SECONDS * SR
+        self.nseg = api.num_segments(L, SHIFT)
+        self.h_audio = env["h_audio"]
+        self.h_out = SharedHostBuffer((L, 2, S), self.rank, self.world, torch, dist)
+        world = self.world
+        if world == 1:
+            self.d_audio = self.h_audio.to(dev)
+            self.d_out = torch.empty((L, 2, S), dtype=torch.float32, device=dev)
+        else:
+            # contiguous-block split: this rank's run of segments per bag member, its input window and output stretch
+            self.plans = [api.plan_block(L, sh, self.rank, world) for sh in self.shifts]
+            self.nxt_tail = [api.plan_block(L, sh, self.rank + 1, world).tail_frames > 0 if self.rank + 1 < world else False
+                             for sh in self.shifts]
+            lo = min(p.in_begin for p in self.plans)
+            hi = max(p.in_end for p in self.plans)
+            self.win_lo, self.win_hi = lo, hi
+            self.d_win = self.h_audio[lo:hi].to(dev)
+            nloc = max(p.seg_end - p.seg_begin for p in self.plans)
+            self.d_y = torch.zeros((max(nloc, 1), S, api.SEG, 2), dtype=torch.float32, device=dev)
+            self.d_sums = torch.zeros(2, dtype=torch.float64, device=dev)
+            self.d_tail_in = torch.zeros((S, api.TAIL_FRAMES, 2), dtype=torch.float32, device=dev)
+            self.d_tail_out = torch.zeros((S, api.TAIL_FRAMES, 2), dtype=torch.float32, device=dev)
+            self.olo = min(p.out_begin for p in self.plans)
+            self.ohi = max(p.out_end for p in self.plans)
+            self.d_out = torch.zeros((max(self.ohi - self.olo, 1), 2, S), dtype=torch.float32, device=dev)
+        self.h2d = 0
+        self.d2h = 0
+
+    def close(self):
+        for m in self.models:
+            m.close()
+        self.h_out.close()
+
+    def launches(self):
+        return sum(m.launch_count for m in self.models)
+
+    # ---- one separation with the inputs resident in HBM; returns device ms of this rank's work ----
+    def step_device(self):
+        torch, dist = self.env["torch"], self.env["dist"]
+        ms = 0.0
+        if self.world == 1:
+            if len(self.models) == 1:
+                self.models[0].demucs_inference_device(self.d_audio.data_ptr(), self.L, self.d_out.data_ptr(), self.shifts[0])
+                return self.models[0].last_device_ms
+            plan = None
+            for i, (mdl, shift) in enumerate(zip(self.models, self.shifts)):
+                # the bag through the block entry points with one worker: stem i of member i lands in d_out directly
+                api = self.env["api"]
+                plan = api.plan_block(self.L, shift, 0, 1)
+                if not hasattr(self, "d_y1"):
+                    self.d_y1 = torch.empty((plan.n_segments, self.S, api.SEG, 2), dtype=torch.float32, device=self.env["dev"])
+                    self.d_sums1 = torch.zeros(2, dtype=torch.float64, device=self.env["dev"])
+                self.d_sums1.zero_()
+                torch.cuda.current_stream().synchronize()
+                mdl.track_stats_device(self.d_audio.data_ptr(), self.L, self.d_sums1.data_ptr())
+                mdl.forward_block_device(self.d_audio.data_ptr(), self.L, shift, plan, self.d_sums1.data_ptr(), self.d_y1.data_ptr())
+                mdl.overlap_add_block_device(self.L, shift, plan, self.d_sums1.data_ptr(), self.d_y1.data_ptr(), 0,
+                                             self.d_out.data_ptr(), i, i + 1)
+                mdl.sync()
+                ms += mdl.last_device_ms
+            return ms
+        cur = torch.cuda.current_stream()
+        for i, (mdl, shift, pl) in enumerate(zip(self.models, self.shifts, self.plans)):
+            n = pl.seg_end - pl.seg_begin
+            self.d_sums.zero_()
+            cur.synchronize()
+            if pl.out_end > pl.out_begin:
+                mdl.track_stats_device(self.d_win[pl.out_begin - self.win_lo:].data_ptr(), pl.out_end - pl.out_begin,
+                                       self.d_sums.data_ptr())
+                mdl.sync()
+            dist.all_reduce(self.d_sums)                       # 16 bytes: the track's (sum, sum of squares)
+            cur.synchronize()
+            if n > 0:
+                mdl.forward_block_device(self.d_win[pl.in_begin - self.win_lo:].data_ptr(), self.L, shift, pl,
+                                         self.d_sums.data_ptr(), self.d_y.data_ptr())
+                mdl.sync()
+                ms += mdl.last_device_ms
+            # the one exchange of the data path: the 85995-frame tail of my last segment goes to the next rank
+            ops = []
+            if self.nxt_tail[i] and n > 0:
+                self.d_tail_out.copy_(self.d_y[n - 1, :, self.env["api"].SEG - self.env["api"].TAIL_FRAMES:, :])
+                ops.append(dist.P2POp(dist.isend, self.d_tail_out, self.rank + 1))
+            if pl.tail_frames > 0:
+                ops.append(dist.P2POp(dist.irecv, self.d_tail_in, self.rank - 1))
+            if ops:
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+                cur.synchronize()
+            if pl.out_end > pl.out_begin:
+                src = (i, i + 1) if len(self.models) > 1 else (0, self.S)
+                mdl.overlap_add_block_device(self.L, shift, pl, self.d_sums.data_ptr(), self.d_y.data_ptr(),
+                                             self.d_tail_in.data_ptr() if pl.tail_frames > 0 else 0,
+                                             self.d_out[pl.out_begin - self.olo:].data_ptr(), src[0], src[1])
+                mdl.sync()
+        if len(self.models) > 1:
+            self._bag_fixup()
+        return ms
+
+    def _bag_fixup(self):
+        """htdemucs_ft over several ranks: the members' shifts differ, so member i's natural stretch on this rank is
+        member 0's moved by (shift_0 - shift_i) frames.  Final ownership follows member 0; the sliver of stem i that
+        the neighbour computed (at most 0.5 s) crosses by one small send/recv per member."""
+        torch, dist = self.env["torch"], self.env["dist"]
+        p0 = self.plans[0]
+        for i in range(1, len(self.models)):
+            pi = self.plans[i]
+            ops, recv = [], []
+            # right edge: I own up to p0.out_end; stem i is mine only up to pi.out_end
+            if self.rank + 1 < self.world and p0.out_end > p0.out_begin:
+                if pi.out_end < p0.out_end:                                   # the next rank holds [pi.out_end, p0.out_end)
+                    buf = torch.empty((p0.out_end - pi.out_end, 2), dtype=torch.float32, device=self.env["dev"])
+                    ops.append(dist.P2POp(dist.irecv, buf, self.rank + 1))
+                    recv.append((buf, pi.out_end, p0.out_end))
+                elif pi.out_end > p0.out_end:                                 # I hold a sliver the next rank owns
+                    ops.append(dist.P2POp(dist.isend, self.d_out[p0.out_end - self.olo:pi.out_end - self.olo, :, i].contiguous(),
+                                          self.rank + 1))
+            if self.rank > 0 and p0.out_end > p0.out_begin:
+                if pi.out_begin > p0.out_begin:                               # the previous rank holds [p0.out_begin, pi.out_begin)
+                    buf = torch.empty((pi.out_begin - p0.out_begin, 2), dtype=torch.float32, device=self.env["dev"])
+                    ops.append(dist.P2POp(dist.irecv, buf, self.rank - 1))
+                    recv.append((buf, p0.out_begin, pi.out_begin))
+                elif pi.out_begin < p0.out_begin:
+                    ops.append(dist.P2POp(dist.isend, self.d_out[pi.out_begin - self.olo:p0.out_begin - self.olo, :, i].contiguous(),
+                                          self.rank - 1))
+            if ops:
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+            for buf, a, b in recv:
+                self.d_out[a - self.olo:b - self.olo, :, i] = buf
+        torch.cuda.current_stream().synchronize()
+
+    # ---- the same through host buffers: pinned host audio -> device, stems -> (shared) pinned host ----
+    def step_e2e(self):
+        torch, api = self.env["torch"], self.env["api"]
+        if self.world == 1 and len(self.models) == 1:
+            r = api.lib().dmx_separate(self.models[0]._h, self.h_audio.data_ptr(), self.L, self.shifts[0],
+                                       self.h_out.t.data_ptr(), api.ctypes.cast(None, api.PROGRESS_FN), None)
+            if r != 0:
+                raise RuntimeError(api.last_error())
+            self.h2d, self.d2h = self.L * 2 * 4, self.L * 2 * self.S * 4
+            return
+        if self.world == 1:
+            hs = (api.ctypes.c_void_p * len(self.models))(*[m._h for m in self.models])
+            sh = (api.ctypes.c_int * len(self.models))(*self.shifts)
+            r = api.lib().dmx_separate_bag(hs, len(self.models), self.h_audio.data_ptr(), self.L, sh, self.h_out.t.data_ptr(),
+                                           api.ctypes.cast(None, api.PROGRESS_FN), None)
+            if r != 0:
+                raise RuntimeError(api.last_error())
+            self.h2d, self.d2h = self.L * 2 * 4, self.L * 2 * self.S * 4
+            return
+        # N ranks: each copies in ONLY its window of the track and copies out ONLY its stretch of the stems
+        self.d_win.copy_(self.h_audio[self.win_lo:self.win_hi], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self.step_device()
+        p0 = self.plans[0]
+        if p0.out_end > p0.out_begin:
+            self.h_out.t[p0.out_begin:p0.out_end].copy_(self.d_out[p0.out_begin - self.olo:p0.out_end - self.olo], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        self.h2d = (self.win_hi - self.win_lo) * 2 * 4
+        self.d2h = (p0.out_end - p0.out_begin) * 2 * self.S * 4
+
+
+def time_workload(wl, steps, warmup, env, profile=False):
+    """-> dict(dev_ms, wall_ms, e2e_ms, launches, h2d, d2h, prof, prof_dev_ms) with times maxed / bytes summed over ranks."""
+    torch, dist = env["torch"], env["dist"]
+    world = env["world"]
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        wl.step_device()
+    sync_all()
+    launches0 = wl.launches()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(steps):
+        dev_ms += wl.step_device()
+    sync_all()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    launches = wl.launches() - launches0
+    prof, prof_dev_ms = None, 0.0
+    if profile:
+        # the same K steps again with per-class CUDA events (kernel classes, roofline): bracketing every launch with
+        # events serialises the two branch streams, so this pass is kept out of the timed region above
+        for mm in wl.models:
+            mm.profile_begin()
+        for _ in range(steps):
+            prof_dev_ms += wl.step_device()
+        sync_all()
+        for mm in wl.models:
+            pr = mm.profile_end()
+            if prof is None:
+                prof = pr
+            else:
+                for k in pr:
+                    for f in pr[k]:
+                        prof[k][f] += pr[k][f]
+    for _ in range(2):
+        wl.step_e2e()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        wl.step_e2e()
+    sync_all()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    h2d, d2h = float(wl.h2d), float(wl.d2h)
+    if world > 1:
+        t = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device=env["dev"])
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, wall_ms, e2e_ms = (float(x) for x in t)
+        u = torch.tensor([float(launches), h2d, d2h], dtype=torch.float64, device=env["dev"])
+        dist.all_reduce(u, op=dist.ReduceOp.SUM)
+        launches, h2d, d2h = int(u[0].item()), float(u[1]), float(u[2])
+    return {"dev_ms": dev_ms, "wall_ms": wall_ms, "e2e_ms": e2e_ms, "launches": int(launches), "h2d": int(h2d), "d2h": int(d2h),
+            "prof": prof, "prof_dev_ms": prof_dev_ms}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -215,6 +514,8 @@ def main():
                     help="bf16: tcgen05 GEMMs/attention with bf16 operands, fp32 accumulate/residual/statistics (stems >= 40 dB "
                          "vs the reference); fp32: CUDA-core path (stems >= 80 dB)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-configs", action="store_true",
+                    help="skip the short runs of BASELINE.json configs[2..4] that ride along in `extra_configs`")
     ap.add_argument("--model", default="htdemucs_4s", choices=["htdemucs_4s", "htdemucs_6s", "hdemucs_mmi", "htdemucs_ft"],
                     help="htdemucs_4s = BASELINE.json configs[1] (the headline); the others are configs[2..4]")
     args = ap.parse_args()
@@ -237,128 +538,51 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    prec = api.PRECISION_BF16 if args.precision == "bf16" else api.PRECISION_FP32
-    if args.model == "htdemucs_ft":
-        # bag of four fine-tuned 4-source models: four sequential passes, each with its own random shift (the
-        # successive rand() % 22050 draws of a fresh process), stem i taken from model i (cli-apps/demucs_ft.cpp:221-241)
-        models = [api.DemucsModel(weights.cached_weights("htdemucs_4s", seed), device=local_rank, max_batch=args.batch,
-                                  precision=prec) for seed in range(4)]
-        shifts = [4033, 12436, 5427, 6865]
-    else:
-        models = [api.DemucsModel(weights.cached_weights(args.model, 0), device=local_rank, max_batch=args.batch,
-                                  precision=prec)]
-        shifts = [SHIFT]
-    model = models[0]
-    S = model.nb_sources
     L = TRACK_SECONDS * SR
-    audio = synth_audio(L)                                           # (2, L)
-    nseg = api.num_segments(L, SHIFT)
-    cnt = (nseg + world - 1) // world
+    audio = synth_audio(L)                                                       # (2, L)
     h_audio = torch.from_numpy(np.ascontiguousarray(audio.T)).pin_memory()      # (L, 2) interleaved, pinned
-    h_out = torch.empty((L, 2, S), dtype=torch.float32).pin_memory()
-    d_audio = h_audio.to(dev)
-    d_out = torch.empty((L, 2, S), dtype=torch.float32, device=dev)
-    d_y = torch.zeros((cnt, S, api.SEG, 2), dtype=torch.float32, device=dev)
-    d_y_all = torch.zeros((world, cnt, S, api.SEG, 2), dtype=torch.float32, device=dev) if world > 1 else d_y
+    env = {"torch": torch, "dist": dist, "api": api, "weights": weights, "rank": rank, "local_rank": local_rank,
+           "world": world, "dev": dev, "h_audio": h_audio}
 
-    def sync_all():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    d_bag = torch.empty((L, 2, S), dtype=torch.float32, device=dev) if len(models) > 1 else None
-
-    def step_device():
-        """one separation (all bag members) with inputs resident in HBM; returns device ms of this rank's work"""
-        ms = 0.0
-        for i, (mdl, shift) in enumerate(zip(models, shifts)):
-            if world == 1:
-                mdl.demucs_inference_device(d_audio.data_ptr(), L, d_out.data_ptr(), shift)
-                ms += mdl.last_device_ms
-            else:
-                mdl.forward_shard_device(d_audio.data_ptr(), L, shift, rank, world, d_y.data_ptr())
-                ms += mdl.last_device_ms
-                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                ev0.record()
-                dist.gather(d_y, list(d_y_all.unbind(0)) if rank == 0 else None, dst=0)
-                ev1.record()
-                torch.cuda.synchronize()
-                ms += ev0.elapsed_time(ev1)
-                if rank == 0:
-                    mdl.overlap_add_device(d_audio.data_ptr(), L, shift, d_y_all.data_ptr(), world, d_out.data_ptr())
-                    ms += mdl.last_device_ms
-            if d_bag is not None and rank == 0:
-                d_bag[:, :, i].copy_(d_out[:, :, i])            # stem i from model i
-        return ms
-
-    def step_e2e():
-        """the same through host buffers: pinned host audio -> device, stems -> pinned host"""
-        if world == 1 and len(models) == 1:
-            r = api.lib().dmx_separate(model._h, h_audio.data_ptr(), L, SHIFT, h_out.data_ptr(),
-                                       api.ctypes.cast(None, api.PROGRESS_FN), None)
-            if r != 0:
-                raise RuntimeError(api.last_error())
-            return
-        d_audio.copy_(h_audio, non_blocking=True)
-        torch.cuda.synchronize()
-        step_device()
-        if rank == 0:
-            h_out.copy_(d_out if d_bag is None else d_bag, non_blocking=True)
-            torch.cuda.synchronize()
-
-    # ---- device-resident timing ----
-    for _ in range(args.warmup):
-        step_device()
-    sync_all()
+    wl = Workload(args.model, args, env)
+    S, nseg = wl.S, wl.nseg
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = sum(mm.launch_count for mm in models)
-    t0 = time.perf_counter()
-    dev_ms = 0.0
-    for _ in range(args.steps):
-        dev_ms += step_device()
-    sync_all()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    launches = sum(mm.launch_count for mm in models) - launches0
-    # ---- the same K steps again with per-class CUDA events (kernel classes, roofline): bracketing every launch
-    # with events serialises the two branch streams, so this pass is kept out of the timed region above ----
-    for mm in models:
-        mm.profile_begin()
-    prof_dev_ms = 0.0
-    for _ in range(args.steps):
-        prof_dev_ms += step_device()
-    sync_all()
-    prof = None
-    for mm in models:
-        pr = mm.profile_end()
-        if prof is None:
-            prof = pr
-        else:
-            for k in pr:
-                for f in pr[k]:
-                    prof[k][f] += pr[k][f]
+    r = time_workload(wl, args.steps, args.warmup, env, profile=True)
     clocks = sampler.stop() if rank == 0 else None
+    dev_ms, wall_ms, e2e_ms, launches, prof, prof_dev_ms = (r["dev_ms"], r["wall_ms"], r["e2e_ms"], r["launches"], r["prof"],
+                                                           r["prof_dev_ms"])
+    # ---- correctness guard on what was just timed: finite stems, and the host-buffer path equals the device path ----
+    check = {}
+    if rank == 0:
+        ho = wl.h_out.t.numpy()
+        check["finite"] = bool(np.isfinite(ho).all())
+        if world == 1:
+            do = wl.d_out.cpu().numpy()
+            num = float((do.astype(np.float64) ** 2).sum())
+            den = float(((do.astype(np.float64) - ho) ** 2).sum())
+            check["e2e_vs_device_snr_db"] = float(10 * np.log10(num / max(den, 1e-300)))
+        if not check["finite"]:
+            raise SystemExit("bench.py: non-finite stems")
+    seg_check = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and len(wl.models) == 1:
+        # the CUDA forward of the very segment the CPU baseline leg runs below (compared there)
+        seg_check = wl.models[0].model_inference(np.ascontiguousarray(audio[None, :, :api.SEG]))[0]
 
-    # ---- end-to-end timing ----
-    for _ in range(2):
-        step_e2e()
-    sync_all()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
-    sync_all()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
+    # ---- BASELINE.json configs[2..4]: short device / e2e runs of the other models, same track ----
+    extra = {}
+    if not args.no_extra_configs and args.model == "htdemucs_4s":
+        wl.close()
+        for name in ("htdemucs_6s", "htdemucs_ft", "hdemucs_mmi"):
+            w2 = Workload(name, args, env)
+            r2 = time_workload(w2, 3, 2, env)
+            ms2 = max(r2["dev_ms"], r2["wall_ms"]) / 3
+            extra[name] = {"value": TRACK_SECONDS / (ms2 * 1e-3), "unit": "audio-s/s", "ms_per_step": ms2,
+                           "e2e": TRACK_SECONDS / (r2["e2e_ms"] / 3 * 1e-3), "steps": 3, "warmup": 2,
+                           "workload": WORKLOADS[name]}
+            w2.close()
 
-    if world > 1:
-        t = torch.tensor([dev_ms, wall_ms, e2e_ms, float(launches)], dtype=torch.float64, device=dev)
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        dev_ms, wall_ms, e2e_ms = (float(x) for x in tmax[:3])
-        launches = int(tsum[3].item())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -367,8 +591,9 @@ def main():
     # whole-job time per step: the device-event time can miss host gaps between calls, the wall bracket
     # (sync + barrier on both sides) cannot -- report the larger (more conservative) of the two.
     ms_per_step = max(dev_ms, wall_ms) / args.steps
-    value = TRACK_SECONDS / (ms_per_step * 1e-3)
-    e2e_value = TRACK_SECONDS / (e2e_ms / args.steps * 1e-3)
+    units = TRACK_SECONDS
+    value = units / (ms_per_step * 1e-3)
+    e2e_value = units / (e2e_ms / args.steps * 1e-3)
 
     # ---- roofline of the dominant kernel class (rank 0's launches) ----
     peaks = read_peaks()
@@ -379,23 +604,27 @@ def main():
         e = {"ms_per_step": c["ms"] / args.steps, "launches_per_step": c["launches"] / args.steps}
         if c["flops"] > 0:
             e["tflops"] = c["flops"] / (c["ms"] * 1e-3) / 1e12
+            e["frac_of_tensor_peak"] = e["tflops"] / peaks["bf16_tflops_sustained"]
         if c["bytes"] > 0:
             e["gbs"] = c["bytes"] / (c["ms"] * 1e-3) / 1e9
+            e["frac_of_hbm_peak"] = e["gbs"] / peaks["hbm_gbs"]
         classes[name] = e
     dom = max(classes, key=lambda k: classes[k]["ms_per_step"])
     dc = prof[dom]
     tfl = dc["flops"] / (dc["ms"] * 1e-3) / 1e12 if dc["flops"] > 0 else 0.0
     gbs = dc["bytes"] / (dc["ms"] * 1e-3) / 1e9 if dc["bytes"] > 0 else 0.0
     f_t, f_h = tfl / peaks["bf16_tflops_sustained"], gbs / peaks["hbm_gbs"]
-    # the roofline that binds this class = the one it sits closer to (skinny-channel convs are HBM-bound)
-    if f_t >= f_h:
+    # GEMM-shaped classes are judged against the tensor pipe, the FFT / norm / elementwise ones against
+    # HBM; the other reading is carried along as `other_roofline_frac`
+    tensor_classes = ("gemm_conv", "gemm_dconv", "gemm_transformer", "attention", "lstm")
+    if dom in tensor_classes and args.precision == "bf16":
         roof = {"kernel": dom, "bound": "tensor", "achieved": tfl, "peak": peaks["bf16_tflops_sustained"],
-                "unit": "TFLOP/s", "frac": f_t,
+                "unit": "TFLOP/s", "frac": f_t, "other_roofline_frac": f_h, "other_roofline": "hbm",
                 "peak_source": peaks["src"] + " sustained bf16 (kernel timed inside a long step)"}
     else:
         roof = {"kernel": dom, "bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": f_h, "peak_source": peaks["src"] + " copy bandwidth"}
-    roof["other_roofline_frac"] = min(f_t, f_h)
+                "frac": f_h, "other_roofline_frac": f_t, "other_roofline": "tensor",
+                "peak_source": peaks["src"] + " copy bandwidth"}
     roof["avg_launch_ms"] = dc["ms"] / max(dc["launches"], 1)
     roof["share_of_step"] = dc["ms"] / prof_dev_ms  # share inside the event-bracketed (single-stream) pass
     tp = os.path.join(ROOT, "profiles", "traffic.json")
@@ -403,12 +632,9 @@ def main():
     if os.path.exists(tp):
         try:
             tj = json.load(open(tp))
-            roof["traffic"] = tj.get(dom)
-            if roof["traffic"] is not None and tj.get("_segments_per_launch"):
-                # the ncu capture profiled launches over 8 segments; a launch here covers args.batch of them
-                roof["traffic"] = roof["traffic"] * args.batch / tj["_segments_per_launch"]
-                roof["traffic_note"] = "ncu dram bytes per launch at %d segments per launch, scaled to %d" % (
-                    tj["_segments_per_launch"], args.batch)
+            if tj.get(dom) is not None and tj.get("_segments_per_launch") == args.batch:
+                roof["traffic"] = tj[dom]
+                roof["traffic_note"] = tj.get("_note", "ncu dram bytes per launch")
         except Exception:
             pass
 
@@ -421,26 +647,33 @@ def main():
         "device_ms_per_step": dev_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
         "profiled_pass_ms_per_step": prof_dev_ms / args.steps,
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "ms_per_step": e2e_ms / args.steps,
-                "h2d_bytes_per_step": int(L * 2 * 4 * world), "d2h_bytes_per_step": int(L * 2 * S * 4)},
+                "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"]},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roof,
         "kernel_classes": classes,
+        "check": check,
     }
+    if extra:
+        line["extra_configs"] = extra
 
     # ---- CPU baseline: the reference's own code on this box's host cores, bounded sample ----
     if world == 1 and not args.no_cpu_baseline:
         if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdemucs_ref.so")):
-            for mm in models:
-                mm.close()
+            wl.close()
             cores = os.cpu_count() or 1
             with quiet_stdout():
-                times, _ = time_reference_segments(1, cores, 1, 0, budget_s=60.0)
-            t = float(np.mean(times))
+                times, ref_out = time_reference_one_segment(cores, audio[:, :api.SEG])
+            t = float(min(times))
             line["cpu_baseline"] = {"value": SEG_STRIDE_S / t, "unit": "audio-s/s", "cores": cores, "kind": "reference",
-                                    "sample": "one 7.8 s segment through the reference's model_inference "
-                                              "(oracle/_ref, OMP_NUM_THREADS=%d): %.1f s; a segment advances the track by "
-                                              "5.85 s" % (cores, t)}
+                                    "sample": "one 7.8 s segment through the reference's model_inference (oracle/_ref, "
+                                              "OMP_NUM_THREADS=%d), 1 warm-up + %d timed runs: best %.1f s, mean %.1f s; a "
+                                              "segment advances the track by 5.85 s" % (cores, len(times), t,
+                                                                                      float(np.mean(times)))}
+            if seg_check is not None:
+                num = float((ref_out.astype(np.float64) ** 2).sum())
+                den = float(((ref_out.astype(np.float64) - seg_check) ** 2).sum())
+                line["check"]["segment_snr_db_vs_reference"] = float(10 * np.log10(num / max(den, 1e-300)))
         else:
             line["cpu_baseline"] = {"value": None, "unit": "audio-s/s", "cores": 0, "kind": "reference",
                                     "sample": "oracle/_ref not built on this box"}

@@ -31,8 +31,19 @@ EXPORTS = [
     "dmx_debug_tap", "dmx_launch_count", "dmx_stft_segment", "dmx_istft_segment", "dmx_profile_classes",
     "dmx_profile_class_name", "dmx_profile_begin", "dmx_profile_end", "dmx_forward_shard_device",
     "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
-    "dmx_debug_linear", "dmx_profile_sequence",
+    "dmx_debug_linear", "dmx_profile_sequence", "dmx_plan_block", "dmx_track_stats_device", "dmx_forward_block_device",
+    "dmx_overlap_add_block_device", "dmx_model_sync", "dmx_separate_multi", "dmx_separate_bag",
 ]
+
+
+class BlockPlan(ctypes.Structure):
+    """dmx_block_plan (include/demucs_b200.h): one worker's share of a track under the contiguous-block split."""
+    _fields_ = [("seg_begin", ctypes.c_int32), ("seg_end", ctypes.c_int32), ("n_segments", ctypes.c_int32),
+                ("tail_frames", ctypes.c_int32), ("in_begin", ctypes.c_int64), ("in_end", ctypes.c_int64),
+                ("out_begin", ctypes.c_int64), ("out_end", ctypes.c_int64)]
+
+
+TAIL_FRAMES = 85995
 
 _lib = None
 
@@ -80,6 +91,13 @@ def lib():
         L.dmx_profile_sequence.argtypes = [vp, vp, ci]
         L.dmx_stft_segment.argtypes = [vp, vp, vp]
         L.dmx_istft_segment.argtypes = [vp, vp, vp]
+        L.dmx_plan_block.argtypes = [i64, ci, ci, ci, ctypes.POINTER(BlockPlan)]
+        L.dmx_track_stats_device.argtypes = [vp, vp, i64, vp]
+        L.dmx_forward_block_device.argtypes = [vp, vp, i64, ci, ctypes.POINTER(BlockPlan), vp, vp]
+        L.dmx_overlap_add_block_device.argtypes = [vp, i64, ci, ctypes.POINTER(BlockPlan), vp, vp, vp, ci, ci, vp]
+        L.dmx_model_sync.argtypes = [vp]
+        L.dmx_separate_multi.argtypes = [vp, ci, vp, i64, ci, vp, PROGRESS_FN, vp]
+        L.dmx_separate_bag.argtypes = [vp, ci, vp, i64, vp, vp, PROGRESS_FN, vp]
         _lib = L
     return _lib
 
@@ -187,6 +205,27 @@ class DemucsModel:
                                             ctypes.c_void_p(d_y_all_ptr), world, ctypes.c_void_p(d_out_ptr)),
                "dmx_overlap_add_device")
 
+    # -- contiguous-block split (multi-GPU data path); raw device pointers, asynchronous on the model's stream
+    def track_stats_device(self, d_audio_ptr, n_frames, d_sums_ptr):
+        _check(lib().dmx_track_stats_device(self._h, ctypes.c_void_p(d_audio_ptr), n_frames, ctypes.c_void_p(d_sums_ptr)),
+               "dmx_track_stats_device")
+
+    def forward_block_device(self, d_win_ptr, n_frames, shift_offset, plan, d_sums_ptr, d_y_ptr):
+        _check(lib().dmx_forward_block_device(self._h, ctypes.c_void_p(d_win_ptr), n_frames, int(shift_offset),
+                                              ctypes.byref(plan), ctypes.c_void_p(d_sums_ptr), ctypes.c_void_p(d_y_ptr)),
+               "dmx_forward_block_device")
+
+    def overlap_add_block_device(self, n_frames, shift_offset, plan, d_sums_ptr, d_y_ptr, d_tail_ptr, d_out_ptr,
+                                 src_begin=0, src_end=None):
+        _check(lib().dmx_overlap_add_block_device(self._h, n_frames, int(shift_offset), ctypes.byref(plan),
+                                                  ctypes.c_void_p(d_sums_ptr), ctypes.c_void_p(d_y_ptr),
+                                                  ctypes.c_void_p(d_tail_ptr) if d_tail_ptr else None, src_begin,
+                                                  self.nb_sources if src_end is None else src_end,
+                                                  ctypes.c_void_p(d_out_ptr)), "dmx_overlap_add_block_device")
+
+    def sync(self):
+        _check(lib().dmx_model_sync(self._h), "dmx_model_sync")
+
     @property
     def last_device_ms(self):
         return float(lib().dmx_last_device_ms(self._h))
@@ -246,6 +285,43 @@ def debug_linear(A, W, bias=None, act=0, precision=PRECISION_FP32, device=0, ite
     _check(lib().dmx_debug_linear(device, precision, M, N, K, _p(A), _p(W), None if b is None else _p(b), act,
                                   _p(out), iters, ctypes.byref(ms)), "dmx_debug_linear")
     return (out, ms.value) if iters > 0 else out
+
+
+def plan_block(n_frames, shift_offset, rank, world):
+    """This worker's run of segments and its input / output stretches (dmx_plan_block)."""
+    pl = BlockPlan()
+    _check(lib().dmx_plan_block(n_frames, int(shift_offset), rank, world, ctypes.byref(pl)), "dmx_plan_block")
+    return pl
+
+
+def _track_io(audio, S):
+    audio = np.asarray(audio, dtype=np.float32)
+    if audio.ndim != 2 or audio.shape[0] != 2:
+        raise ValueError("audio must be (2, L)")
+    L = audio.shape[1]
+    return L, np.ascontiguousarray(audio.T), np.empty((L, 2, S), dtype=np.float32)
+
+
+def demucs_inference_multi(models, audio, cb=None, shift_offset=4033):
+    """demucs_inference over several GPUs of one process: `models` = one replica of the same model per GPU
+    (replaces the thread fan-out of cli-apps/threaded_inference.hpp:50-190).  (2, L) -> (S, 2, L)."""
+    L, inter, out = _track_io(audio, models[0].nb_sources)
+    hs = (ctypes.c_void_p * len(models))(*[m._h for m in models])
+    fn = PROGRESS_FN(lambda p, msg, _u: cb(p, msg.decode())) if cb is not None else ctypes.cast(None, PROGRESS_FN)
+    _check(lib().dmx_separate_multi(hs, len(models), _p(inter), L, int(shift_offset), _p(out), fn, None),
+           "dmx_separate_multi")
+    return np.ascontiguousarray(out.transpose(2, 1, 0))
+
+
+def demucs_ft_inference(models, audio, shift_offsets=(4033, 12436, 5427, 6865), cb=None):
+    """htdemucs_ft: four fine-tuned members, stem i from member i (cli-apps/demucs_ft.cpp:221-241); the default
+    shifts are the successive rand() % 22050 draws of a fresh process.  (2, L) -> (4, 2, L)."""
+    L, inter, out = _track_io(audio, models[0].nb_sources)
+    hs = (ctypes.c_void_p * len(models))(*[m._h for m in models])
+    sh = (ctypes.c_int * len(models))(*[int(x) for x in shift_offsets[:len(models)]])
+    fn = PROGRESS_FN(lambda p, msg, _u: cb(p, msg.decode())) if cb is not None else ctypes.cast(None, PROGRESS_FN)
+    _check(lib().dmx_separate_bag(hs, len(models), _p(inter), L, sh, _p(out), fn, None), "dmx_separate_bag")
+    return np.ascontiguousarray(out.transpose(2, 1, 0))
 
 
 def load_demucs_model(path, **kw):

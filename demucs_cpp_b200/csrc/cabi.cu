@@ -3,6 +3,9 @@
 
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <condition_variable>
+#include <thread>
 #include <vector>
 #include <cuda_fp16.h>
 
@@ -221,28 +224,29 @@ void dmx_model_free(dmx_model *m)
 {
     if (!m)
         return;
-    if (m->finalized || !m->allocs.empty())
+    if (m->finalized || !m->allocs.empty() || m->stream)
     {
+        int prev = -1;
+        cudaGetDevice(&prev);
         cudaSetDevice(m->device);
-        if (m->stream)
-            cudaStreamSynchronize(m->stream);
+        for (cudaStream_t s : {m->stream, m->stream2, m->stream_copy})
+            if (s)
+                cudaStreamSynchronize(s);
         for (void *p : m->allocs)
             cudaFree(p);
-        if (m->d_audio)
-            cudaFree(m->d_audio);
-        if (m->d_y)
-            cudaFree(m->d_y);
-        if (m->d_out)
-            cudaFree(m->d_out);
-        if (m->stream)
-            cudaStreamDestroy(m->stream);
-        if (m->stream2)
-            cudaStreamDestroy(m->stream2);
-        if (m->stream_copy)
-            cudaStreamDestroy(m->stream_copy);
-        for (cudaEvent_t e : {m->ev_fork, m->ev_join, m->ev_copy})
+        for (float *p : {m->d_audio, m->d_y, m->d_out, m->d_tail})
+            if (p)
+                cudaFree(p);
+        for (cudaStream_t s : {m->stream, m->stream2, m->stream_copy})
+            if (s)
+                cudaStreamDestroy(s);
+        for (cudaEvent_t e : {m->ev_fork, m->ev_join, m->ev_copy, m->ev0, m->ev1, m->ev2})
             if (e)
                 cudaEventDestroy(e);
+        for (cudaEvent_t e : m->prof.pool)
+            cudaEventDestroy(e);
+        if (prev >= 0)
+            cudaSetDevice(prev);
     }
     delete m->v3;
     delete m;
@@ -404,6 +408,85 @@ int dmx_overlap_add_device(dmx_model *m, const float *d_audio_lr, int64_t n_fram
     }
     DMX_CUDA(cudaSetDevice(m->device));
     return track_overlap_add(m, d_audio_lr, n_frames, shift_offset, d_y_all, world, d_out);
+}
+
+int dmx_plan_block(int64_t n_frames, int shift_offset, int rank, int world, dmx_block_plan *plan)
+{
+    if (!plan)
+    {
+        set_error("dmx_plan_block: null plan");
+        return -1;
+    }
+    return plan_block(n_frames, shift_offset, rank, world, plan);
+}
+
+static int check_ready(dmx_model *m, const char *who)
+{
+    if (!m)
+    {
+        set_error(std::string(who) + ": null model");
+        return -1;
+    }
+    if (!m->finalized)
+    {
+        set_error(std::string(who) + ": model not finalized");
+        return -1;
+    }
+    return 0;
+}
+
+int dmx_track_stats_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, double *d_sums)
+{
+    if (check_ready(m, "dmx_track_stats_device"))
+        return -1;
+    if (!d_sums || (n_frames > 0 && !d_audio_lr) || n_frames < 0)
+    {
+        set_error("dmx_track_stats_device: bad argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    DMX_CUDA(cudaSetDevice(m->device));
+    return track_stats_partial(m, d_audio_lr, n_frames, d_sums);
+}
+
+int dmx_forward_block_device(dmx_model *m, const float *d_audio_win, int64_t n_frames, int shift_offset,
+                             const dmx_block_plan *plan, const double *d_sums, float *d_y)
+{
+    if (check_ready(m, "dmx_forward_block_device"))
+        return -1;
+    if (!plan || !d_sums || (plan->seg_end > plan->seg_begin && (!d_audio_win || !d_y)))
+    {
+        set_error("dmx_forward_block_device: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    DMX_CUDA(cudaSetDevice(m->device));
+    return track_forward_block(m, d_audio_win, n_frames, shift_offset, *plan, d_sums, d_y);
+}
+
+int dmx_overlap_add_block_device(dmx_model *m, int64_t n_frames, int shift_offset, const dmx_block_plan *plan,
+                                 const double *d_sums, const float *d_y, const float *d_prev_tail, int src_begin, int src_end,
+                                 float *d_out_block)
+{
+    if (check_ready(m, "dmx_overlap_add_block_device"))
+        return -1;
+    if (!plan || !d_sums || (plan->out_end > plan->out_begin && (!d_y || !d_out_block)))
+    {
+        set_error("dmx_overlap_add_block_device: null argument");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    DMX_CUDA(cudaSetDevice(m->device));
+    return track_overlap_add_block(m, n_frames, shift_offset, *plan, d_sums, d_y, d_prev_tail, src_begin, src_end, d_out_block);
+}
+
+int dmx_model_sync(dmx_model *m)
+{
+    if (check_ready(m, "dmx_model_sync"))
+        return -1;
+    DMX_CUDA(cudaSetDevice(m->device));
+    DMX_CUDA(cudaStreamSynchronize(m->stream));
+    return 0;
 }
 
 double dmx_last_device_ms(dmx_model *m)
@@ -590,6 +673,264 @@ int dmx_istft_segment(dmx_model *m, const float *spec, float *seg_lr)
         return -1;
     DMX_CUDA(cudaMemcpyAsync(seg_lr, m->seg_out, (size_t)SEG * 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
     DMX_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// One process, several GPUs (dmx_separate_multi) and the htdemucs_ft bag (dmx_separate_bag).
+namespace
+{
+struct Rendezvous // reusable barrier for the worker threads (C++17: no std::barrier)
+{
+    std::mutex mu;
+    std::condition_variable cv;
+    int n, waiting = 0, gen = 0;
+    explicit Rendezvous(int n_) : n(n_) {}
+    void wait()
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        const int g = gen;
+        if (++waiting == n)
+        {
+            waiting = 0;
+            ++gen;
+            cv.notify_all();
+        }
+        else
+            cv.wait(lk, [&] { return gen != g; });
+    }
+};
+
+struct Flag
+{
+    std::mutex mu;
+    std::condition_variable cv;
+    bool set = false;
+    void raise()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            set = true;
+        }
+        cv.notify_all();
+    }
+    void wait()
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return set; });
+    }
+};
+} // namespace
+
+int dmx_separate_multi(dmx_model *const *models, int n_models, const float *audio_lr, int64_t n_frames, int shift_offset,
+                       float *out, dmx_progress_fn cb, void *user)
+{
+    if (!models || n_models < 1 || !audio_lr || !out)
+    {
+        set_error("dmx_separate_multi: bad argument");
+        return -1;
+    }
+    for (int r = 0; r < n_models; ++r)
+    {
+        if (check_ready(models[r], "dmx_separate_multi"))
+            return -1;
+        if (models[r]->arch != models[0]->arch)
+        {
+            set_error("dmx_separate_multi: the replicas must be the same model");
+            return -1;
+        }
+        for (int q = 0; q < r; ++q)
+            if (models[q] == models[r])
+            {
+                set_error("dmx_separate_multi: the same model handle was passed twice");
+                return -1;
+            }
+    }
+    if (n_models == 1)
+        return dmx_separate(models[0], audio_lr, n_frames, shift_offset, out, cb, user);
+    const int W = n_models, S = models[0]->S;
+    constexpr int TAIL = SEG - SEG_STRIDE;
+    std::vector<dmx_block_plan> plans(W);
+    for (int r = 0; r < W; ++r)
+        if (plan_block(n_frames, shift_offset, r, W, &plans[r]))
+            return -1;
+    // buffers the neighbours write into must exist before the workers start
+    for (int r = 0; r < W; ++r)
+    {
+        dmx_model *m = models[r];
+        DMX_CUDA(cudaSetDevice(m->device));
+        if (!m->d_tail)
+            DMX_CUDA(cudaMalloc(reinterpret_cast<void **>(&m->d_tail), (size_t)S * TAIL * 2 * sizeof(float)));
+        if (r + 1 < W && models[r + 1]->device != m->device)
+        {
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, m->device, models[r + 1]->device) == cudaSuccess && can)
+                if (cudaDeviceEnablePeerAccess(models[r + 1]->device, 0) != cudaSuccess)
+                    cudaGetLastError(); // already enabled
+        }
+    }
+    std::vector<double> part(2 * (size_t)W, 0.0);
+    std::vector<std::string> errs(W);
+    std::vector<Flag> tail_ready(W);
+    std::atomic<bool> failed{false};
+    Rendezvous rdv(W);
+    auto worker = [&](int r) {
+        dmx_model *m = models[r];
+        const dmx_block_plan &pl = plans[r];
+        std::lock_guard<std::mutex> lk(m->mtx);
+        const int nloc = pl.seg_end - pl.seg_begin;
+        const int64_t nin = pl.in_end - pl.in_begin, nout = pl.out_end - pl.out_begin;
+        auto step = [&](int rc) {
+            if (rc)
+            {
+                errs[r] = dmx_last_error();
+                failed = true;
+            }
+            return rc;
+        };
+        auto cuda = [&](cudaError_t e, const char *what) {
+            if (e != cudaSuccess)
+            {
+                set_error(std::string("dmx_separate_multi: ") + what + ": " + cudaGetErrorString(e));
+                return step(-1);
+            }
+            return 0;
+        };
+        cudaStream_t st = m->stream;
+        bool ok = !cuda(cudaSetDevice(m->device), "cudaSetDevice");
+        // ---- stage 1: own window in, partial statistics out ----
+        if (ok && nloc > 0)
+        {
+            ok = !step(grow(&m->d_audio, &m->cap_audio, (size_t)nin * 2)) && !step(grow(&m->d_y, &m->cap_y, (size_t)nloc * S * SEG * 2)) &&
+                 !step(grow(&m->d_out, &m->cap_out, (size_t)S * 2 * (size_t)nout));
+            ok = ok && !cuda(cudaEventRecord(m->ev2, st), "event");
+            ok = ok && !cuda(cudaMemcpyAsync(m->d_audio, audio_lr + 2 * pl.in_begin, (size_t)nin * 2 * sizeof(float),
+                                             cudaMemcpyHostToDevice, st), "copy in");
+            ok = ok && !cuda(cudaMemsetAsync(m->track_stats, 0, 2 * sizeof(double), st), "memset");
+            ok = ok && !step(track_stats_partial(m, m->d_audio + 2 * (pl.out_begin - pl.in_begin), nout, m->track_stats));
+            ok = ok && !cuda(cudaMemcpyAsync(&part[2 * r], m->track_stats, 2 * sizeof(double), cudaMemcpyDeviceToHost, st), "copy");
+            ok = ok && !cuda(cudaStreamSynchronize(st), "sync");
+        }
+        rdv.wait();
+        // ---- stage 2: whole-track statistics (same summation order on every worker), forward, tail to the neighbour ----
+        double tot[2] = {0.0, 0.0};
+        for (int q = 0; q < W; ++q)
+        {
+            tot[0] += part[2 * q];
+            tot[1] += part[2 * q + 1];
+        }
+        ok = ok && !failed;
+        if (ok && nloc > 0)
+        {
+            ok = !cuda(cudaMemcpyAsync(m->track_stats, tot, 2 * sizeof(double), cudaMemcpyHostToDevice, st), "copy");
+            ok = ok && !step(track_forward_block(m, m->d_audio, n_frames, shift_offset, pl, m->track_stats, m->d_y));
+            if (ok && r + 1 < W && plans[r + 1].tail_frames > 0)
+            {
+                const float *src = m->d_y + ((size_t)(nloc - 1) * S * SEG + SEG_STRIDE) * 2;
+                ok = !cuda(cudaMemcpy2DAsync(models[r + 1]->d_tail, (size_t)TAIL * 2 * sizeof(float), src,
+                                             (size_t)SEG * 2 * sizeof(float), (size_t)TAIL * 2 * sizeof(float), S,
+                                             cudaMemcpyDefault, st), "tail copy");
+                ok = ok && !cuda(cudaStreamSynchronize(st), "sync");
+            }
+        }
+        if (r + 1 < W)
+            tail_ready[r + 1].raise(); // also on failure: the neighbour must not wait for ever
+        // ---- stage 3: overlap-add of the own stretch, straight to the caller's buffer ----
+        if (pl.tail_frames > 0)
+            tail_ready[r].wait();
+        ok = ok && !failed;
+        if (ok && nloc > 0 && nout > 0)
+        {
+            ok = !step(track_overlap_add_block(m, n_frames, shift_offset, pl, m->track_stats, m->d_y, m->d_tail, 0, S, m->d_out));
+            ok = ok && !cuda(cudaMemcpyAsync(out + (size_t)S * 2 * pl.out_begin, m->d_out, (size_t)S * 2 * (size_t)nout * sizeof(float),
+                                             cudaMemcpyDeviceToHost, st), "copy out");
+            ok = ok && !cuda(cudaEventRecord(m->ev1, st), "event");
+            ok = ok && !cuda(cudaStreamSynchronize(st), "sync");
+            if (ok)
+                std::swap(m->ev0, m->ev2);
+        }
+    };
+    std::vector<std::thread> th;
+    for (int r = 1; r < W; ++r)
+        th.emplace_back(worker, r);
+    worker(0);
+    for (auto &t : th)
+        t.join();
+    if (failed)
+    {
+        for (int r = 0; r < W; ++r)
+            if (!errs[r].empty())
+            {
+                set_error("dmx_separate_multi (GPU " + std::to_string(models[r]->device) + "): " + errs[r]);
+                return -1;
+            }
+        set_error("dmx_separate_multi: a worker failed");
+        return -1;
+    }
+    track_fire_progress(models[0], plans[0].n_segments, cb, user);
+    return 0;
+}
+
+int dmx_separate_bag(dmx_model *const *models, int n_models, const float *audio_lr, int64_t n_frames,
+                     const int *shift_offsets, float *out, dmx_progress_fn cb, void *user)
+{
+    if (!models || !audio_lr || !out || !shift_offsets || n_models < 1)
+    {
+        set_error("dmx_separate_bag: bad argument");
+        return -1;
+    }
+    for (int i = 0; i < n_models; ++i)
+    {
+        if (check_ready(models[i], "dmx_separate_bag"))
+            return -1;
+        if (models[i]->device != models[0]->device || models[i]->S != models[0]->S)
+        {
+            set_error("dmx_separate_bag: the members must be on one GPU and have the same sources");
+            return -1;
+        }
+    }
+    if (n_models != models[0]->S)
+    {
+        set_error("dmx_separate_bag: needs one member per source (stem i is taken from member i)");
+        return -1;
+    }
+    dmx_model *m0 = models[0];
+    const int S = m0->S;
+    std::lock_guard<std::mutex> lk0(m0->mtx);
+    DMX_CUDA(cudaSetDevice(m0->device));
+    if (grow(&m0->d_audio, &m0->cap_audio, (size_t)n_frames * 2) || grow(&m0->d_out, &m0->cap_out, (size_t)S * 2 * (size_t)n_frames))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(m0->d_audio, audio_lr, (size_t)n_frames * 2 * sizeof(float), cudaMemcpyHostToDevice, m0->stream));
+    DMX_CUDA(cudaStreamSynchronize(m0->stream));
+    int nseg_total = 0;
+    for (int i = 0; i < n_models; ++i)
+    {
+        dmx_model *m = models[i];
+        std::unique_lock<std::mutex> lk(m->mtx, std::defer_lock);
+        if (i > 0)
+            lk.lock();
+        dmx_block_plan pl;
+        if (plan_block(n_frames, shift_offsets[i], 0, 1, &pl))
+            return -1;
+        nseg_total += pl.n_segments;
+        if (grow(&m->d_y, &m->cap_y, (size_t)pl.n_segments * S * SEG * 2))
+            return -1;
+        DMX_CUDA(cudaMemsetAsync(m->track_stats, 0, 2 * sizeof(double), m->stream));
+        if (track_stats_partial(m, m0->d_audio, n_frames, m->track_stats) ||
+            track_forward_block(m, m0->d_audio, n_frames, shift_offsets[i], pl, m->track_stats, m->d_y) ||
+            track_overlap_add_block(m, n_frames, shift_offsets[i], pl, m->track_stats, m->d_y, nullptr, i, i + 1, m0->d_out))
+            return -1;
+        DMX_CUDA(cudaStreamSynchronize(m->stream)); // members share m0's output buffer: one after the other
+        if (cb)
+        {
+            // the reference runs the members one after the other, each reporting its own 0..1 progress
+            // (cli-apps/demucs_ft.cpp:222-231)
+            track_fire_progress(m, pl.n_segments, cb, user);
+        }
+    }
+    (void)nseg_total;
+    DMX_CUDA(cudaMemcpyAsync(out, m0->d_out, (size_t)S * 2 * (size_t)n_frames * sizeof(float), cudaMemcpyDeviceToHost, m0->stream));
+    DMX_CUDA(cudaStreamSynchronize(m0->stream));
     return 0;
 }
 

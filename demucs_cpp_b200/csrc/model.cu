@@ -291,6 +291,8 @@ int model_finalize(dmx_model *m)
     m->stats_cap = B * 2 * (size_t)(2 * 2 * 2 * (512 + 128 + 32 + 8) * 2 + 16 * 2 * 2 + 64);
     if (dev_alloc_t(m, &m->stats, m->stats_cap) || dev_alloc_t(m, &m->track_stats, 2))
         return -1;
+    if (noalloc_warm_up(m->device))
+        return -1;
     m->finalized = true;
     return model_zero_attention_pads(m);
 }

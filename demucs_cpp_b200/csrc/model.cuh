@@ -169,6 +169,7 @@ struct dmx_model
     float *d_audio = nullptr, *d_y = nullptr, *d_out = nullptr;
     size_t cap_audio = 0, cap_y = 0, cap_out = 0;
     double *track_stats = nullptr;
+    float *d_tail = nullptr; // [S][SEG - SEG_STRIDE][2]: the previous worker's tail (dmx_separate_multi)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr; // device time of the last track-level call
 };
 
@@ -177,6 +178,7 @@ namespace dmx
 int model_finalize(dmx_model *m);
 int model_v3_finalize(dmx_model *m);
 int model_zero_attention_pads(dmx_model *m);
+int noalloc_warm_up(int device); // noalloc.cu
 int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out);
 int debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
                  int act, float *out, int iters, float *ms_out);
@@ -195,6 +197,13 @@ int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, 
                       float *d_out);
 int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
                    void *user);
+int plan_block(int64_t L, int shift, int rank, int world, dmx_block_plan *pl);
+int track_stats_partial(dmx_model *m, const float *d_audio, int64_t n, double *d_sums);
+int track_forward_block(dmx_model *m, const float *d_win, int64_t L, int shift, const dmx_block_plan &pl, const double *d_sums,
+                        float *d_y);
+int track_overlap_add_block(dmx_model *m, int64_t L, int shift, const dmx_block_plan &pl, const double *d_sums,
+                            const float *d_y, const float *d_tail, int s_begin, int s_end, float *d_out_block);
+void track_fire_progress(dmx_model *m, int nseg, dmx_progress_fn cb, void *user);
 int track_separate_host(dmx_model *m, const float *h_audio, int64_t L, int shift, float *h_out, dmx_progress_fn cb,
                         void *user);
 } // namespace dmx

@@ -260,6 +260,8 @@ int model_v3_finalize(dmx_model *m)
     m->stats_cap = B * 2 * (size_t)(2 * 2 * (512 + 128 + 32 + 8) * 2 + 512);
     if (dev_alloc_t(m, &m->stats, m->stats_cap) || dev_alloc_t(m, &m->track_stats, 2))
         return -1;
+    if (noalloc_warm_up(m->device))
+        return -1;
     m->finalized = true;
     return 0;
 }

@@ -17,8 +17,11 @@
 //     call zeroes the part it is going to use (cudaMemsetAsync on the stream, no allocation);
 //   * two calls whose GPU work overlaps (different streams, or different host threads) race on it;
 //     serialise them;
-//   * the very first call on a device looks up the array's device address (cudaGetSymbolAddress, with
-//     that device current).  Make that first call before starting any stream capture.
+//   * the array's device address is looked up once per device (cudaGetSymbolAddress, with that device
+//     current).  dmx_model_finalize does this for the model's device -- and touches the helper kernel so
+//     that the CUDA module is already loaded -- which keeps module loading (it may allocate and
+//     synchronise) out of the caller's no-allocation region.  Should a call still be the first one on its
+//     device, it does the look-up itself: make that call before starting any stream capture.
 #include "model.cuh"
 
 #include <mutex>
@@ -75,6 +78,18 @@ __global__ void noalloc_meanstd_kernel(int n, float2 *__restrict__ meanstd)
     meanstd[b] = make_float2((float)m, (float)sqrt(var));
 }
 
+// Called by model_finalize with the model's device current: resolves the workspace address and forces the
+// module that holds the helper kernel to load now, so that no later call has to.
+int noalloc_warm_up(int device)
+{
+    double *p = nullptr;
+    if (noalloc_setup(device, &p))
+        return -1;
+    cudaFuncAttributes attr;
+    DMX_CUDA(cudaFuncGetAttributes(&attr, noalloc_meanstd_kernel));
+    return 0;
+}
+
 } // namespace dmx
 
 using namespace dmx;
@@ -94,11 +109,23 @@ extern "C" int dmx_stft_segments_noalloc(dmx_model *m, const float *d_segs, int 
                   " (the static workspace is fixed at that size); split the batch");
         return -1;
     }
+    std::lock_guard<std::mutex> lk(m->mtx); // the model's tables and stream are shared with its other entry points
     if (!m->finalized)
     {
         set_error("dmx_stft_segments_noalloc: model not finalized");
         return -1;
     }
+    // the caller's current device is put back on every way out
+    struct DeviceGuard
+    {
+        int prev = -1;
+        DeviceGuard() { cudaGetDevice(&prev); }
+        ~DeviceGuard()
+        {
+            if (prev >= 0)
+                cudaSetDevice(prev);
+        }
+    } guard;
     DMX_CUDA(cudaSetDevice(m->device));
     double *stats = nullptr;
     if (noalloc_setup(m->device, &stats))

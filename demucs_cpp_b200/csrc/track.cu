@@ -282,6 +282,204 @@ int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, 
     return 0;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Contiguous-block split of a track over `world` workers (GPUs): worker r runs a run of consecutive
+// segments, overlap-adds and finalises the stretch of the track that starts at its first segment and
+// ends where the next worker's first segment starts.  The only data that crosses workers is the last
+// SEG - SEG_STRIDE frames of a worker's last segment (the part that overlaps the next worker's first
+// segment) and the two sums of the track statistics.  Replaces the chunk fan-out / merge of
+// cli-apps/threaded_inference.hpp:50-190 (which re-runs whole overlapping chunks on every thread).
+int plan_block(int64_t L, int shift, int rank, int world, dmx_block_plan *pl)
+{
+    if (check_track_args(L, shift, rank, world) || !pl)
+        return -1;
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    const int nseg = num_segments(L, shift);
+    const int base = nseg / world, rem = nseg % world;
+    const int k0 = rank * base + (rank < rem ? rank : rem);
+    const int k1 = k0 + base + (rank < rem ? 1 : 0);
+    const int64_t lead = MAX_SHIFT - shift; // shifted-track position of track frame 0
+    auto clampL = [&](int64_t t) { return t < 0 ? 0 : (t > L ? L : t); };
+    pl->seg_begin = k0;
+    pl->seg_end = k1;
+    pl->n_segments = nseg;
+    pl->tail_frames = (k1 > k0 && k0 > 0) ? SEG - SEG_STRIDE : 0;
+    if (k1 == k0) // more workers than segments: the idle ones are the trailing ranks
+    {
+        pl->in_begin = pl->in_end = pl->out_begin = pl->out_end = L;
+        return 0;
+    }
+    int64_t last_end = (int64_t)(k1 - 1) * SEG_STRIDE + SEG;
+    if (last_end > Ls)
+        last_end = Ls;
+    pl->in_begin = clampL((int64_t)k0 * SEG_STRIDE - lead);
+    pl->in_end = clampL(last_end - lead);
+    pl->out_begin = pl->in_begin;
+    pl->out_end = k1 >= nseg ? L : clampL((int64_t)k1 * SEG_STRIDE - lead);
+    return 0;
+}
+
+// (sum, sumsq) of the mono signal of `n` frames, ADDED to d_sums[0..1] (device doubles the caller zeroed):
+// the track statistics of demucs_inference (src/model_apply.cpp:72-80) are the sums over all workers' stretches.
+int track_stats_partial(dmx_model *m, const float *d_audio, int64_t n, double *d_sums)
+{
+    if (n <= 0)
+        return 0;
+    {
+        ProfScope ps(m, PC_TRACK, 0.0, (double)n * 8.0);
+        mono_stats_kernel<<<592, 256, 0, m->stream>>>((const float2 *)d_audio, n, d_sums);
+    }
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+// As extract_segments_kernel, but the audio pointer holds only track frames [w0, w1) and the statistics are given.
+__global__ void __launch_bounds__(256) extract_block_kernel(const float2 *__restrict__ win, int64_t w0, int64_t w1, int64_t L,
+                                                            int offset, int64_t Ls, const double *__restrict__ stats, int k0,
+                                                            float2 *__restrict__ segs)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= SEG)
+        return;
+    const int k = k0 + blockIdx.y;
+    float mean, stdv;
+    track_mean_std(stats, L, mean, stdv);
+    const int64_t off = (int64_t)k * SEG_STRIDE;
+    const int64_t nk = (Ls - off) < SEG ? (Ls - off) : SEG;
+    const int left = (int)((SEG - nk) / 2);
+    float2 v = make_float2(0.f, 0.f);
+    const int64_t j = i - left;
+    if (j >= 0 && j < nk)
+    {
+        const int64_t src = off + j + offset - MAX_SHIFT;
+        if (src >= 0 && src < L && src >= w0 && src < w1)
+        {
+            const float2 a = __ldg(&win[src - w0]);
+            v.x = (a.x - mean) / stdv;
+            v.y = (a.y - mean) / stdv;
+        }
+    }
+    segs[(size_t)blockIdx.y * SEG + i] = v;
+}
+
+int track_forward_block(dmx_model *m, const float *d_win, int64_t L, int shift, const dmx_block_plan &pl, const double *d_sums,
+                        float *d_y)
+{
+    if (check_track_args(L, shift, 0, 1))
+        return -1;
+    cudaStream_t st = m->stream;
+    const int S = m->S;
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    DMX_CUDA(cudaEventRecord(m->ev0, st));
+    const int nloc = pl.seg_end - pl.seg_begin;
+    for (int j0 = 0; j0 < nloc; j0 += m->maxB)
+    {
+        const int nb = (nloc - j0) < m->maxB ? (nloc - j0) : m->maxB;
+        {
+            ProfScope ps(m, PC_TRACK, 0.0, (double)nb * SEG * 16.0);
+            extract_block_kernel<<<dim3((SEG + 255) / 256, nb), 256, 0, st>>>((const float2 *)d_win, pl.in_begin, pl.in_end, L,
+                                                                              shift, Ls, d_sums, pl.seg_begin + j0,
+                                                                              (float2 *)m->mix);
+        }
+        DMX_LAUNCH_CHECK();
+        if (model_forward(m, m->mix, nb, d_y + (size_t)j0 * S * SEG * 2))
+            return -1;
+    }
+    DMX_CUDA(cudaEventRecord(m->ev1, st));
+    return 0;
+}
+
+// Overlap-add of one worker's block: y holds its segments [k0, k1) ([k1-k0][S][SEG]); tail ([S][SEG-SEG_STRIDE]) holds the
+// end of segment k0-1 (the previous worker's last one).  Writes track frames [t_begin, t_end) of sources
+// [s_begin, s_end) into out_block, whose frame 0 is track frame t_begin: index s + S*(ch + 2*(t - t_begin)).
+__global__ void __launch_bounds__(256)
+    overlap_add_block_kernel(const float2 *__restrict__ y, const float2 *__restrict__ tail, int S, int s_begin, int s_end,
+                             int nseg, int k0, int k1, int64_t L, int offset, int64_t Ls, const double *__restrict__ stats,
+                             float *__restrict__ out, int64_t t_begin, int64_t t_end)
+{
+    const int64_t t0 = t_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t0 >= t_end)
+        return;
+    float mean, stdv;
+    track_mean_std(stats, L, mean, stdv);
+    const int64_t t = t0 + MAX_SHIFT - offset;
+    const int khi = (int)(t / SEG_STRIDE);
+    const float h = (float)(SEG / 2);
+    constexpr int TAIL = SEG - SEG_STRIDE;
+    for (int s = s_begin; s < s_end; ++s)
+    {
+        float2 num = make_float2(0.f, 0.f);
+        float den = 0.f;
+        for (int k = khi - 1; k <= khi; ++k)
+        {
+            if (k < 0 || k >= nseg || k >= k1 || k < k0 - 1)
+                continue;
+            const int64_t off = (int64_t)k * SEG_STRIDE;
+            const int64_t nk = (Ls - off) < SEG ? (Ls - off) : SEG;
+            const int64_t i = t - off;
+            if (i < 0 || i >= nk)
+                continue;
+            const int left = (int)((SEG - nk) / 2);
+            const int ii = (int)i;
+            const float w = (float)(ii + 1 < SEG - ii ? ii + 1 : SEG - ii) / h;
+            float2 v;
+            if (k >= k0)
+                v = __ldg(&y[((size_t)(k - k0) * S + s) * SEG + left + ii]);
+            else
+                v = __ldg(&tail[(size_t)s * TAIL + (ii - SEG_STRIDE)]); // a previous segment is always a full one
+            num.x += w * v.x;
+            num.y += w * v.y;
+            den += w;
+        }
+        out[s + (size_t)S * (0 + 2 * (t0 - t_begin))] = (num.x / den) * stdv + mean;
+        out[s + (size_t)S * (1 + 2 * (t0 - t_begin))] = (num.y / den) * stdv + mean;
+    }
+}
+
+int track_overlap_add_block(dmx_model *m, int64_t L, int shift, const dmx_block_plan &pl, const double *d_sums,
+                            const float *d_y, const float *d_tail, int s_begin, int s_end, float *d_out_block)
+{
+    if (check_track_args(L, shift, 0, 1))
+        return -1;
+    if (s_begin < 0 || s_end > m->S || s_begin >= s_end)
+    {
+        set_error("overlap_add_block: bad source range");
+        return -1;
+    }
+    if (pl.tail_frames > 0 && !d_tail)
+    {
+        set_error("overlap_add_block: this block needs the previous block's tail");
+        return -1;
+    }
+    const int64_t n = pl.out_end - pl.out_begin;
+    if (n <= 0)
+        return 0;
+    cudaStream_t st = m->stream;
+    const int64_t Ls = L + MAX_SHIFT - shift;
+    {
+        ProfScope ps(m, PC_TRACK, 0.0, (double)n * (s_end - s_begin) * 8.0 * 2.3);
+        overlap_add_block_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(
+            (const float2 *)d_y, (const float2 *)d_tail, m->S, s_begin, s_end, pl.n_segments, pl.seg_begin, pl.seg_end, L, shift,
+            Ls, d_sums, d_out_block, pl.out_begin, pl.out_end);
+    }
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
+// The reference's numbered per-segment progress messages for all `nseg` segments, in order (used by the entry points
+// whose workers run off the calling thread: the callback may only be invoked on the caller's thread).
+void track_fire_progress(dmx_model *m, int nseg, dmx_progress_fn cb, void *user)
+{
+    if (!cb)
+        return;
+    const bool v3 = m->arch == DMX_ARCH_HDEMUCS_V3;
+    const int nmsg = v3 ? 22 : 26;
+    for (int j = 0; j < nseg; ++j)
+        for (int sidx = 0; sidx < nmsg; ++sidx)
+            cb(((float)j + (float)(sidx + 1) / (float)nmsg) / (float)nseg, v3 ? kStageMsgsV3[sidx] : kStageMsgs[sidx], user);
+}
+
 int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
                    void *user)
 {

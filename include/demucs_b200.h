@@ -80,8 +80,7 @@ extern "C"
                      dmx_progress_fn cb, void *user);
 
     /* Same with DEVICE-resident audio and output (cudaMalloc'd by the caller, e.g. a torch tensor's
-     * data_ptr); stream = 0 uses the model's own stream.  Asynchronous w.r.t. the host only up to the
-     * internal synchronisation at the end of the call. */
+     * data_ptr).  Runs on the model's own stream and returns after it has drained. */
     int dmx_separate_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset,
                             float *d_out);
 
@@ -94,6 +93,56 @@ extern "C"
                                  int world, float *d_y);
     int dmx_overlap_add_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, int shift_offset,
                                const float *d_y_all, int world, float *d_out);
+    /* ---- contiguous-block split (the multi-GPU data path; replaces the chunk fan-out and merge of
+     *      cli-apps/threaded_inference.hpp:50-190).  Worker `rank` of `world` runs a RUN OF CONSECUTIVE
+     *      segments and finalises the stretch of the track from its first segment's start to the next
+     *      worker's first segment's start, so every worker reads only its own window of the input and writes
+     *      only its own stretch of the output.  Between workers travel (1) two doubles, the partial sums of
+     *      the track statistics (src/model_apply.cpp:72-80), and (2) the last 85995 frames of a worker's last
+     *      segment, which overlap the next worker's first segment (2.75 MB for 4 sources).
+     *      All pointers are DEVICE memory of the model's GPU; the calls enqueue on the model's stream and
+     *      return without waiting (synchronise with dmx_model_sync). ---- */
+    typedef struct dmx_block_plan
+    {
+        int32_t seg_begin, seg_end; /* segments [seg_begin, seg_end) of the track belong to this worker */
+        int32_t n_segments;         /* segments of the whole track (src/model_apply.cpp:186,200) */
+        int32_t tail_frames;        /* frames of the previous worker's last segment this worker needs (0 or 85995) */
+        int64_t in_begin, in_end;   /* track frames this worker reads */
+        int64_t out_begin, out_end; /* track frames this worker finalises (a partition of [0, n_frames)) */
+    } dmx_block_plan;
+#define DMX_TAIL_FRAMES 85995 /* 343980 - 257985: overlap of consecutive segments (src/model_apply.cpp:145,162) */
+    int dmx_plan_block(int64_t n_frames, int shift_offset, int rank, int world, dmx_block_plan *plan);
+    /* Adds the (sum, sum of squares) of the mono mix of `n_frames` interleaved frames to d_sums[0..1] (device
+     * doubles, zeroed by the caller).  Summed over all workers' out-stretches they are the track statistics. */
+    int dmx_track_stats_device(dmx_model *m, const float *d_audio_lr, int64_t n_frames, double *d_sums);
+    /* Forward of the plan's segments.  d_audio_win holds track frames [in_begin, in_end); d_sums the statistics of
+     * the WHOLE track; d_y receives [seg_end - seg_begin][S][343980][2]. */
+    int dmx_forward_block_device(dmx_model *m, const float *d_audio_win, int64_t n_frames, int shift_offset,
+                                 const dmx_block_plan *plan, const double *d_sums, float *d_y);
+    /* Triangular-weighted overlap-add, trim and de-normalise (src/model_apply.cpp:171-246,129-135,88) of the
+     * worker's stretch: d_out_block (out_end - out_begin, 2, S) gets track frames [out_begin, out_end).
+     * d_prev_tail ([S][85995][2], the last tail_frames frames of segment seg_begin - 1, every source) is
+     * required when plan->tail_frames > 0.  Only sources [src_begin, src_end) are written -- the htdemucs_ft bag
+     * takes stem i from model i (cli-apps/demucs_ft.cpp:221-241), so member i calls this with (i, i + 1). */
+    int dmx_overlap_add_block_device(dmx_model *m, int64_t n_frames, int shift_offset, const dmx_block_plan *plan,
+                                     const double *d_sums, const float *d_y, const float *d_prev_tail, int src_begin,
+                                     int src_end, float *d_out_block);
+    int dmx_model_sync(dmx_model *m);
+
+    /* ---- one process, several GPUs: whole-track separation with HOST buffers over `n_models` replicas of the
+     *      same model, one per GPU (load the same file once per device).  One host thread per GPU runs the
+     *      block split above; tails cross GPUs by peer copies.  Same result as dmx_separate.  The callback is
+     *      invoked on the calling thread after the workers have finished. ---- */
+    int dmx_separate_multi(dmx_model *const *models, int n_models, const float *audio_lr, int64_t n_frames,
+                           int shift_offset, float *out, dmx_progress_fn cb, void *user);
+
+    /* ---- htdemucs_ft bag: replaces the four demucs_inference calls + stem pick of cli-apps/demucs_ft.cpp:
+     *      221-241.  models[i] (all on one GPU) is the member fine-tuned for source i; shift_offsets[i] its
+     *      own random shift (the reference draws rand() % 22050 once per member); out (S, 2, L) receives
+     *      stem i of member i. ---- */
+    int dmx_separate_bag(dmx_model *const *models, int n_models, const float *audio_lr, int64_t n_frames,
+                         const int *shift_offsets, float *out, dmx_progress_fn cb, void *user);
+
     /* Device milliseconds (CUDA events on the model's stream) of the last separate / shard / overlap-add call. */
     double dmx_last_device_ms(dmx_model *m);
 
@@ -155,8 +204,11 @@ extern "C"
      *        - the workspace (1 KiB) exists on every GPU that loads the library, until process exit;
      *        - all calls on a device share it: it is cleared at the start of each call, and calls
      *          whose GPU work overlaps race with each other -- serialise them;
-     *        - the first call on each device resolves the workspace's device address; make that first
-     *          call before beginning any stream capture;
+     *        - the workspace's device address is resolved once per device; dmx_model_finalize already does
+     *          it (and loads the CUDA module) for the model's device, so nothing of the kind is left for
+     *          the call itself.  If a call nevertheless is the first on its device it resolves the address
+     *          then: let that call happen before beginning any stream capture;
+     *        - the caller's current CUDA device is restored before returning;
      *        - `stream` is a cudaStream_t to enqueue on (the call then returns without waiting), or
      *          NULL to use the model's own stream and wait for completion. ---- */
 #define DMX_NOALLOC_MAX_SEGMENTS 64

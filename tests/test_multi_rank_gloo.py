@@ -1,7 +1,13 @@
-"""CPU test (gloo, world_size 2) of the multi-rank host logic bench.py uses on N GPUs: round-robin segment
-sharding, the rank-major gather layout and the slot mapping the device overlap-add assumes
-(slot(k) = (k % world) * ceil(nseg/world) + k // world, csrc/track.cu).  The per-segment forward is replaced
-by a deterministic stand-in so no GPU is needed; the real kernels are covered by the -m gpu tests."""
+"""CPU tests (gloo, world_size 2) of the multi-rank host logic bench.py uses on N GPUs.
+
+  * the contiguous-block split: the PRODUCT's planner (dmx_plan_block, pure host code in the C-ABI library) gives each
+    rank a run of segments, an input window and an output stretch; ranks exchange the two statistics sums
+    (all_reduce) and the 85995-frame tail of their last segment (send/recv) exactly as bench.py does over NCCL, and
+    the concatenated stretches must equal the oracle's demucs_inference pipeline.  The per-segment forward is a
+    deterministic stand-in (no GPU here); the device kernels of the same protocol are covered by
+    tests/test_gpu_configs.py::test_block_split_equals_single_worker;
+  * the older round-robin shard + gather layout (dmx_forward_shard_device / dmx_overlap_add_device), with its slot
+    mapping slot(k) = (k % world) * ceil(nseg/world) + k // world (csrc/track.cu)."""
 import os
 import socket
 
@@ -93,3 +99,108 @@ def test_shard_counts_cover_every_segment_once():
             cnt = (nseg + world - 1) // world
             slots = {(k % world) * cnt + k // world for k in range(nseg)}
             assert len(slots) == nseg and max(slots) < world * cnt
+
+
+# ------------------------------------------------------------------------------------------------ contiguous blocks
+def standin_forward(seg):
+    """(2, SEG) -> (3, 2, SEG): three "stems" that depend on the segment's content and on the position."""
+    ramp = torch.linspace(0.5, 1.5, seg.shape[1], dtype=seg.dtype)
+    return torch.stack([seg * ramp, -0.5 * seg.flip(0), seg * seg])
+
+
+def block_worker(rank, world, port, L, shift, ret):
+    from demucs_cpp_b200 import api
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    audio = torch.from_numpy(util.synth_audio(L, seed=5)).double()
+    pl = api.plan_block(L, shift, rank, world)
+    nxt = api.plan_block(L, shift, rank + 1, world) if rank + 1 < world else None
+    SEG, STRIDE, TAIL, lead = api.SEG, 257985, api.TAIL_FRAMES, 22050 - shift
+    Ls = L + lead
+    # (1) partial statistics over the OWN stretch, summed over ranks (src/model_apply.cpp:72-80)
+    mono = audio[:, pl.out_begin:pl.out_end].mean(0)
+    sums = torch.tensor([mono.sum(), (mono * mono).sum()], dtype=torch.float64)
+    dist.all_reduce(sums)
+    mean = sums[0] / L
+    std = torch.sqrt((sums[1] - sums[0] * mean) / (L - 1))
+    # (2) forward of the own run of segments, reading only the own window
+    win = audio[:, pl.in_begin:pl.in_end]
+    ys = []
+    for k in range(pl.seg_begin, pl.seg_end):
+        off = k * STRIDE
+        n = min(SEG, Ls - off)
+        left = (SEG - n) // 2
+        seg = torch.zeros(2, SEG, dtype=torch.float64)
+        src = torch.arange(off, off + n) - lead                 # track frames of the chunk (may fall outside [0, L))
+        ok = (src >= 0) & (src < L)
+        assert ((src[ok] >= pl.in_begin) & (src[ok] < pl.in_end)).all(), "the window does not cover the block"
+        seg[:, left:left + n][:, ok] = (win[:, src[ok] - pl.in_begin] - mean) / std
+        ys.append((standin_forward(seg), left, n))
+    # (3) the one exchange: my last segment's tail to the next rank
+    tail = torch.zeros(3, 2, TAIL, dtype=torch.float64)
+    reqs = []
+    if nxt is not None and nxt.tail_frames > 0:
+        reqs.append(dist.isend(ys[-1][0][:, :, SEG - TAIL:].contiguous(), rank + 1))
+    if pl.tail_frames > 0:
+        reqs.append(dist.irecv(tail, rank - 1))
+    for r in reqs:
+        r.wait()
+    # (4) overlap-add of the own stretch
+    w = torch.from_numpy(O.triangle_weight()).double()
+    out = torch.zeros(3, 2, pl.out_end - pl.out_begin, dtype=torch.float64)
+    den = torch.zeros(pl.out_end - pl.out_begin, dtype=torch.float64)
+
+    def add(y, w_seg, t_first):
+        """y (3,2,n) starts at shifted-track position t_first"""
+        a = max(t_first - lead, pl.out_begin)
+        b = min(t_first - lead + y.shape[2], pl.out_end)
+        if b > a:
+            sl = slice(a - (t_first - lead), b - (t_first - lead))
+            out[:, :, a - pl.out_begin:b - pl.out_begin] += w_seg[sl] * y[:, :, sl]
+            den[a - pl.out_begin:b - pl.out_begin] += w_seg[sl]
+
+    if pl.tail_frames > 0:
+        add(tail, w[SEG - TAIL:], (pl.seg_begin - 1) * STRIDE + SEG - TAIL)
+    for j, (y, left, n) in enumerate(ys):
+        add(y[:, :, left:left + n], w[:n], (pl.seg_begin + j) * STRIDE)
+    res = (out / den * std + mean) if out.shape[2] else out
+    ret.put((rank, pl.out_begin, pl.out_end, res.numpy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_contiguous_block_split_world2_matches_oracle_pipeline():
+    L, shift = 900000, 12436                                  # 4 segments, the last one short: 2 + 2
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=block_worker, args=(r, 2, port, L, shift, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    parts = sorted([ret.get(timeout=300) for _ in range(2)])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert parts[0][1] == 0 and parts[0][2] == parts[1][1] and parts[1][2] == L
+    got = np.concatenate([parts[0][3], parts[1][3]], axis=2)
+    W = type("W", (), {"dtype": torch.float64, "S": 3})()
+    ref = O.separate(W, util.synth_audio(L, seed=5).astype(np.float64), shift, forward=standin_forward).numpy()
+    np.testing.assert_allclose(got, ref, rtol=0, atol=1e-9)
+
+
+def test_block_plans_partition_the_track():
+    from demucs_cpp_b200 import api
+    for L, shift in [(7938000, 4033), (441000, 4033), (1000, 0), (600001, 22049)]:
+        nseg = api.num_segments(L, shift)
+        for world in (1, 2, 3, 4, 8, 40):
+            plans = [api.plan_block(L, shift, r, world) for r in range(world)]
+            segs = [k for p in plans for k in range(p.seg_begin, p.seg_end)]
+            assert segs == list(range(nseg)) and all(p.n_segments == nseg for p in plans)
+            sizes = [p.seg_end - p.seg_begin for p in plans]
+            assert max(sizes) - min(sizes) <= 1 and sizes == sorted(sizes, reverse=True)
+            edges = [plans[0].out_begin] + [p.out_end for p in plans]
+            assert edges[0] == 0 and edges[-1] == L and edges == sorted(edges)
+            for r, p in enumerate(plans):
+                assert (p.tail_frames == api.TAIL_FRAMES) == (r > 0 and p.seg_end > p.seg_begin)
+                assert p.in_begin <= p.out_begin and p.in_end >= p.out_end

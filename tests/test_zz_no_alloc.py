@@ -63,3 +63,33 @@ def test_noalloc_stft_matches_existing_entry_point_on_two_calls_in_a_row():
         assert rc != 0
     finally:
         m.close()
+
+
+def test_noalloc_stft_on_a_caller_stream_without_statistics():
+    """The asynchronous form: the caller passes its own stream (the call returns without waiting) and no
+    statistics buffer.  Two calls back to back on that stream, then one synchronisation; the caller's current
+    device must be what it was."""
+    m = api.DemucsModel(weights.cached_weights("htdemucs_6s", 0), max_batch=1)
+    L = api.lib()
+    try:
+        st = torch.cuda.Stream()
+        base = util.synth_audio(util.SEG + 3 * 5000, seed=78)
+        segs = np.stack([(b + 1) * base[:, b * 5000:b * 5000 + util.SEG] for b in range(3)]).astype(np.float32)
+        d_segs = torch.from_numpy(np.ascontiguousarray(segs.transpose(0, 2, 1))).cuda()
+        outs = [torch.full((n, 2048, 336, 4), float("nan"), dtype=torch.float32, device="cuda") for n in (3, 1)]
+        torch.cuda.synchronize()
+        dev_before = torch.cuda.current_device()
+        for d_spec in outs:
+            rc = L.dmx_stft_segments_noalloc(m._h, ctypes.c_void_p(d_segs.data_ptr()), d_spec.shape[0],
+                                             ctypes.c_void_p(d_spec.data_ptr()), None, ctypes.c_void_p(st.cuda_stream))
+            assert rc == 0, api.last_error()
+        st.synchronize()
+        assert torch.cuda.current_device() == dev_before
+        for d_spec in outs:
+            spec = d_spec.cpu().numpy()
+            for b in range(spec.shape[0]):
+                ref = m.stft(segs[b])
+                cac = np.stack([ref[0].real, ref[0].imag, ref[1].real, ref[1].imag], axis=-1)
+                assert util.max_rel_err(spec[b], cac) <= TOL_FP32
+    finally:
+        m.close()
