@@ -32,7 +32,7 @@ EXPORTS = [
     "dmx_profile_class_name", "dmx_profile_begin", "dmx_profile_end", "dmx_forward_shard_device",
     "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
     "dmx_debug_linear", "dmx_profile_sequence", "dmx_plan_block", "dmx_track_stats_device", "dmx_forward_block_device",
-    "dmx_overlap_add_block_device", "dmx_model_sync", "dmx_separate_multi", "dmx_separate_bag",
+    "dmx_overlap_add_block_device", "dmx_model_sync", "dmx_separate_multi", "dmx_separate_bag", "dmx_debug_conv",
 ]
 
 
@@ -98,6 +98,7 @@ def lib():
         L.dmx_model_sync.argtypes = [vp]
         L.dmx_separate_multi.argtypes = [vp, ci, vp, i64, ci, vp, PROGRESS_FN, vp]
         L.dmx_separate_bag.argtypes = [vp, ci, vp, i64, vp, vp, PROGRESS_FN, vp]
+        L.dmx_debug_conv.argtypes = [ci] * 7 + [vp] * 5 + [ci] * 3 + [vp, ci, vp]
         _lib = L
     return _lib
 
@@ -322,6 +323,23 @@ def demucs_ft_inference(models, audio, shift_offsets=(4033, 12436, 5427, 6865), 
     fn = PROGRESS_FN(lambda p, msg, _u: cb(p, msg.decode())) if cb is not None else ctypes.cast(None, PROGRESS_FN)
     _check(lib().dmx_separate_bag(hs, len(models), _p(inter), L, sh, _p(out), fn, None), "dmx_separate_bag")
     return np.ascontiguousarray(out.transpose(2, 1, 0))
+
+
+def debug_conv(img, W, taps, bias=None, act=0, glu=0, share_dv=1, device=0, iters=0):
+    """The TMA-fed convolution kernel alone (test hook): img (B, U, V, Cin), W (N, ntaps * Cin) with k = tap * Cin + c,
+    taps = [(du, dv), ...] -> (B, U, V, N or N / 2).  With iters > 0 returns (out, average kernel ms)."""
+    img = np.ascontiguousarray(img, dtype=np.float32)
+    W = np.ascontiguousarray(W, dtype=np.float32)
+    B, U, V, Cin = img.shape
+    N = W.shape[0]
+    du = (ctypes.c_int * len(taps))(*[int(t[0]) for t in taps])
+    dv = (ctypes.c_int * len(taps))(*[int(t[1]) for t in taps])
+    out = np.empty((B, U, V, N // 2 if glu else N), dtype=np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, dtype=np.float32)
+    ms = ctypes.c_float(0.0)
+    _check(lib().dmx_debug_conv(device, B, U, V, Cin, N, len(taps), du, dv, _p(img), _p(W), None if b is None else _p(b),
+                                act, glu, share_dv, _p(out), iters, ctypes.byref(ms)), "dmx_debug_conv")
+    return (out, ms.value) if iters > 0 else out
 
 
 def load_demucs_model(path, **kw):

@@ -623,6 +623,22 @@ int dmx_debug_linear(int device, int precision, int M, int N, int K, const float
     return debug_linear(device, precision, M, N, K, A, W, bias, act, out, iters, ms_out);
 }
 
+int dmx_debug_conv(int device, int B, int U, int V, int Cin, int N, int ntaps, const int *du, const int *dv, const float *img,
+                   const float *W, const float *bias, int act, int glu, int share_dv, float *out, int iters, float *ms_out)
+{
+    if (!img || !W || !out || !du || !dv || B < 1 || U < 1 || V < 1 || Cin < 1 || N < 1 || ntaps < 1 || (glu && (N & 1)))
+    {
+        set_error("dmx_debug_conv: bad argument");
+        return -1;
+    }
+    if (dmx_device_count() < 1)
+    {
+        set_error("dmx_debug_conv: no CUDA device (this library has no CPU fallback)");
+        return -1;
+    }
+    return debug_conv(device, B, U, V, Cin, N, ntaps, du, dv, img, W, bias, act, glu, share_dv, out, iters, ms_out);
+}
+
 int dmx_stft_segment(dmx_model *m, const float *seg_lr, float *spec)
 {
     if (!m || !seg_lr || !spec)

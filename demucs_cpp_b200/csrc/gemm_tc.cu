@@ -24,6 +24,7 @@
 // tensor).  Only the weights still stream through the k-block ring.
 #include "kernels.cuh"
 
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 #include <algorithm>
@@ -254,6 +255,13 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
             o[3] = old.w + g.w * o[3];
         }
         *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+        if (p.Cbf)
+        {
+            uint2 pk2;
+            pk2.x = pack_bf16x2(o[0], o[1]);
+            pk2.y = pack_bf16x2(o[2], o[3]);
+            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.Cbf) + (dst - p.C)) = pk2;
+        }
         rs = o[0] + o[1] + o[2] + o[3];
         rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
     }
@@ -498,7 +506,7 @@ __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.w
 
 __device__ __forceinline__ bool bulk_ok(const GemmParams &p, const int mode)
 {
-    return mode == 1 && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && (p.N % (p.glu ? 8 : 4)) == 0;
+    return mode == 1 && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && !p.Cbf && (p.N % (p.glu ? 8 : 4)) == 0;
 }
 
 // Epilogue for row-major fp32 outputs with the identity mapping (the convolutions and rewrites of the encoders /
@@ -770,7 +778,16 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams &p, const int bn,
                         *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.C) + ri.outoff + outc) = pk2;
                     }
                     else
+                    {
                         *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+                        if (p.Cbf)
+                        {
+                            uint2 pk2;
+                            pk2.x = pack_bf16x2(o[0], o[1]);
+                            pk2.y = pack_bf16x2(o[2], o[3]);
+                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.Cbf) + ri.outoff + outc) = pk2;
+                        }
+                    }
                     rs = o[0] + o[1] + o[2] + o[3];
                     rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
                 }
@@ -1413,6 +1430,262 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
     }
 }
 
+// =====================================================================================================================
+// TMA-fed persistent implicit-GEMM convolution.  The A operand is a bf16 channels-last IMAGE [B][U][V][Cin] in global
+// memory (written by the producing layer's epilogue) and reaches shared memory through a tensor map: one
+// cp.async.bulk.tensor per BOX = (plane u, rows v0 + dv0 .. + rows - 1, a chunk of cw channels), landed in the tensor
+// core's swizzled K-major layout (cw * 2 = 128 / 64 / 32-byte rows, SWIZZLE_128B / 64B / 32B), zero fill outside the
+// grid = the convolution's zero padding.  No thread touches the operand.  Every tap that reads the plane uses the SAME
+// box: its A descriptor starts dv - dv0 rows further down (start address + shift * row pitch), so a 3 x 3 convolution
+// moves each input row L2 -> SM three times less than nine separate tap loads would.  Boxes and 64-row weight blocks
+// travel through two independent mbarrier rings fed by two loader threads; one thread issues tcgen05.mma into one of
+// two TMEM accumulators while the epilogue warps drain the other (the epilogues above are reused unchanged).
+//   warps [0, ew)   epilogue (ew % 4 == 0, so warp % 4 == TMEM lane quadrant)
+//   warp ew         A loader (TMA boxes)      warp ew + 1   weight loader (bulk copies)      warp ew + 2   MMA issuer
+constexpr int T_MAX_ASLOTS = 12;
+constexpr int T_MAX_BSTAGES = 6;
+constexpr int T_MAX_EW = 16;
+
+__device__ __forceinline__ void tma_load_4d(void *smem_dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3)
+{
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+
+// Shared-memory matrix descriptor of a swizzled K-major operand whose rows are one swizzle span wide (pitch bytes):
+// 8-row groups lie SBO = 8 * pitch apart; the leading-dimension offset is not used.  layout: 2 = 128B, 4 = 64B, 6 = 32B.
+__device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr, uint32_t sbo, uint32_t layout)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)(layout & 7u) << 61;
+    return d;
+}
+
+__global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
+    gemm_tc_tma_kernel(const __grid_constant__ CUtensorMap tmA, const GemmParams p, const __nv_bfloat16 *__restrict__ Wt, const int bn,
+                       const int plain_out, const int a_slots, const int b_stages, const int mtiles, const int ntiles, const int ew)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t a_full[T_MAX_ASLOTS], a_empty[T_MAX_ASLOTS], b_full[T_MAX_BSTAGES], b_empty[T_MAX_BSTAGES];
+    __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_slot;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int nkb = (p.K + BK - 1) / BK;
+    const int total_tiles = mtiles * ntiles;
+    const uint32_t b_stage_bytes = (uint32_t)bn * BK * 2;
+    uint8_t *a_smem = smem;
+    uint8_t *b_smem = smem + (size_t)a_slots * p.t_box_bytes;
+    float *epi_smem = reinterpret_cast<float *>(b_smem + (size_t)b_stages * b_stage_bytes);
+    RowInfo *row_smem = reinterpret_cast<RowInfo *>(reinterpret_cast<uint8_t *>(epi_smem) + (size_t)ew * 32 * EPI_LD * 4);
+    uint32_t acc_cols = 32;
+    while ((int)acc_cols < bn)
+        acc_cols <<= 1;
+
+    if (tid == 0)
+    {
+        for (int s = 0; s < a_slots; ++s)
+        {
+            mbar_init(&a_full[s], 1);
+            mbar_init(&a_empty[s], 1);
+        }
+        for (int s = 0; s < b_stages; ++s)
+        {
+            mbar_init(&b_full[s], 1);
+            mbar_init(&b_empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a)
+        {
+            mbar_init(&acc_full[a], 1);
+            mbar_init(&acc_empty[a], (uint32_t)ew);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == ew + 2)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(2u * acc_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+
+    auto tile_coords = [&](int mt, int &hb, int &hu, int &hv0) {
+        const int bu = fast_div(mt, p.div_tpr);
+        hv0 = (mt - bu * p.halo_tpr) * BM;
+        hb = fast_div(bu, p.div_uo);
+        hu = bu - hb * p.Uo;
+    };
+
+    if (warp < ew)
+    {
+        // ================= epilogue =================
+        const int q = warp & 3;
+        const int csel = warp >> 2, nsel = ew >> 2;
+        float *stage = epi_smem + warp * (32 * EPI_LD);
+        RowInfo *rowinfo = row_smem + warp * 32 - q * 32;
+        const bool packed_direct = p.out_pack && plain_out == 1 && !p.glu && !p.gamma && !p.addC && !p.rowadd && !p.stats &&
+                                   (p.N % 8) == 0;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it)
+        {
+            const int mt = tile / ntiles, nt = tile - mt * ntiles;
+            {
+                const int row = q * 32 + lane;
+                int hb, hu, hv0;
+                tile_coords(mt, hb, hu, hv0);
+                const bool valid = hv0 + row < p.Vo;
+                RowCoord rc;
+                rc.b = hb;
+                rc.uo = hu;
+                rc.vo = valid ? hv0 + row : 0;
+                const int m = (hb * p.Uo + hu) * p.Vo + rc.vo;
+                RowInfo ri;
+                ri.uu0 = rc.uo * p.ous + p.ouo;
+                ri.vv0 = rc.vo * p.ovs + p.ovo;
+                ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
+                ri.uo = rc.uo;
+                ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
+                ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m;
+                ri.pad_ = 0;
+                rowinfo[row] = ri;
+            }
+            const int my_prow = rowinfo[q * 32 + lane].item >= 0 ? rowinfo[q * 32 + lane].prow : -1;
+            __syncwarp();
+            const int acc = it & 1;
+            mbar_wait(&acc_full[acc], (uint32_t)((it >> 1) & 1));
+            tc_fence_after();
+            const uint32_t lane_addr = tmem_base + (uint32_t)acc * acc_cols + ((uint32_t)(q * 32) << 16);
+            if (packed_direct)
+                epilogue_tile_packed(p, bn, nt * bn, lane_addr, my_prow, 32 * csel, 32 * nsel);
+            else if (bulk_ok(p, plain_out) && !p.no_bulk)
+                epilogue_tile_bulk(p, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], stage, 32 * csel, 32 * nsel, lane);
+            else
+                epilogue_tile(p, bn, plain_out, nt * bn, lane_addr, rowinfo, stage, q, 32 * csel, 32 * nsel, lane);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&acc_empty[acc]);
+        }
+    }
+    else if (warp == ew)
+    {
+        // ================= A loader: one tensor-map copy per box =================
+        if (lane == 0)
+        {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+            const uint32_t box_tx = (uint32_t)p.t_rows * (uint32_t)p.t_pitch;
+            int ga = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x)
+            {
+                const int mt = tile / ntiles;
+                int hb, hu, hv0;
+                tile_coords(mt, hb, hu, hv0);
+                for (int qc = 0; qc < p.t_nchunk; ++qc)
+                    for (int b = 0; b < p.t_nbox; ++b, ++ga)
+                    {
+                        const int slot = ga % a_slots;
+                        const uint32_t ph = (uint32_t)(ga / a_slots) & 1u;
+                        mbar_wait(&a_empty[slot], ph ^ 1u);
+                        mbar_arrive_expect_tx(&a_full[slot], box_tx);
+                        tma_load_4d(a_smem + (size_t)slot * p.t_box_bytes, &tmA, &a_full[slot], qc * p.t_cw, hv0 * p.sv + p.t_box_dv[b],
+                                    hu * p.su + p.t_box_du[b], hb);
+                    }
+            }
+        }
+    }
+    else if (warp == ew + 1)
+    {
+        // ================= weight loader: one bulk copy per 64-row block =================
+        if (lane == 0)
+        {
+            int gb = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x)
+            {
+                const int nt = tile % ntiles;
+                const uint8_t *src = reinterpret_cast<const uint8_t *>(Wt) + (size_t)nt * nkb * b_stage_bytes;
+                for (int kb = 0; kb < nkb; ++kb, ++gb)
+                {
+                    const int s = gb % b_stages;
+                    const uint32_t ph = (uint32_t)(gb / b_stages) & 1u;
+                    mbar_wait(&b_empty[s], ph ^ 1u);
+                    mbar_arrive_expect_tx(&b_full[s], b_stage_bytes);
+                    bulk_g2s(b_smem + (size_t)s * b_stage_bytes, src + (size_t)kb * b_stage_bytes, b_stage_bytes, &b_full[s]);
+                }
+            }
+        }
+    }
+    else
+    {
+        // ================= MMA issuer: a single thread =================
+        if (lane == 0)
+        {
+            const uint32_t idesc = make_idesc(bn);
+            const uint32_t b_lbo = (uint32_t)bn * 16, sbo = 128;
+            const uint32_t a_sbo = 8u * (uint32_t)p.t_pitch;
+            const int spc = p.t_cw >> 4;                 // K = 16 steps per tap and chunk
+            const int ksteps = p.K >> 4;                 // per tile
+            int ga = 0, gb0 = 0, it = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it)
+            {
+                const int acc = it & 1;
+                const uint32_t d_tmem = tmem_base + (uint32_t)acc * acc_cols;
+                mbar_wait(&acc_empty[acc], (uint32_t)((it >> 1) & 1) ^ 1u);
+                tc_fence_after();
+                int kstep = 0, bs = 0;
+                for (int qc = 0; qc < p.t_nchunk; ++qc)
+                {
+                    int j = 0;
+                    for (int b = 0; b < p.t_nbox; ++b, ++ga)
+                    {
+                        const int slot = ga % a_slots;
+                        mbar_wait(&a_full[slot], (uint32_t)(ga / a_slots) & 1u);
+                        tc_fence_after();
+                        const uint32_t a_base = smem_u32(a_smem + (size_t)slot * p.t_box_bytes);
+                        for (; j < p.t_ntap && p.t_tap_box[j] == b; ++j)
+                        {
+                            const uint32_t a_tap = a_base + (uint32_t)p.t_tap_shift[j] * (uint32_t)p.t_pitch;
+                            for (int s = 0; s < spc; ++s, ++kstep)
+                            {
+                                if ((kstep & 3) == 0)
+                                {
+                                    const int gb = gb0 + (kstep >> 2);
+                                    bs = gb % b_stages;
+                                    mbar_wait(&b_full[bs], (uint32_t)(gb / b_stages) & 1u);
+                                    tc_fence_after();
+                                }
+                                const uint32_t b_base = smem_u32(b_smem + (size_t)bs * b_stage_bytes);
+                                umma(d_tmem, make_desc_sw(a_tap + (uint32_t)s * 32u, a_sbo, (uint32_t)p.t_layout),
+                                     make_desc(b_base + (uint32_t)(kstep & 3) * 2u * b_lbo, b_lbo, sbo), idesc, kstep > 0 ? 1u : 0u);
+                                if ((kstep & 3) == 3 || kstep == ksteps - 1)
+                                    umma_commit(&b_empty[bs]);
+                            }
+                        }
+                        umma_commit(&a_empty[slot]);
+                    }
+                }
+                gb0 += nkb;
+                umma_commit(&acc_full[acc]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == ew + 2)
+    {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2u * acc_cols) : "memory");
+    }
+}
+
 } // namespace tc
 
 // Column-tile width for a layer with N output columns: N itself (rounded up to 16) when it fits one
@@ -1616,6 +1889,233 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
     if (nk == 2 || bn > 128)
         return tc_launch<2>(q, w, bn, vec, plain | vscat, st);
     return tc_launch<3>(q, w, bn, vec, plain | vscat, st);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// TMA-fed mode: plan, tensor map and launch
+int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv, TmaPlan *pl)
+{
+    if (ntaps < 1 || ntaps > 9 || Cin % 16)
+        return -1;
+    TmaPlan t;
+    t.cw = Cin % 64 == 0 ? 64 : (Cin % 32 == 0 ? 32 : 16);
+    t.nchunk = Cin / t.cw;
+    t.pitch = t.cw * 2;
+    t.layout = t.cw == 64 ? 2 : (t.cw == 32 ? 4 : 6);
+    int dvmin = dv[0], dvmax = dv[0];
+    for (int i = 1; i < ntaps; ++i)
+    {
+        dvmin = std::min(dvmin, dv[i]);
+        dvmax = std::max(dvmax, dv[i]);
+    }
+    t.nbox = 0;
+    t.ntap = 0;
+    if (share_dv)
+    {
+        t.rows = tc::BM + dvmax - dvmin;
+        // boxes = distinct du in order of first appearance; taps grouped by box, original order inside a box
+        for (int i = 0; i < ntaps; ++i)
+        {
+            int b = -1;
+            for (int k = 0; k < t.nbox; ++k)
+                if (t.box_du[k] == du[i])
+                    b = k;
+            if (b < 0)
+            {
+                t.box_du[t.nbox] = du[i];
+                t.box_dv[t.nbox] = dvmin;
+                ++t.nbox;
+            }
+        }
+        for (int b = 0; b < t.nbox; ++b)
+            for (int i = 0; i < ntaps; ++i)
+                if (du[i] == t.box_du[b])
+                {
+                    t.tap_id[t.ntap] = i;
+                    t.tap_box[t.ntap] = b;
+                    t.tap_shift[t.ntap] = dv[i] - dvmin;
+                    ++t.ntap;
+                }
+    }
+    else
+    {
+        t.rows = tc::BM;
+        for (int i = 0; i < ntaps; ++i)
+        {
+            t.box_du[i] = du[i];
+            t.box_dv[i] = dv[i];
+            t.tap_id[i] = i;
+            t.tap_box[i] = i;
+            t.tap_shift[i] = 0;
+        }
+        t.nbox = t.ntap = ntaps;
+    }
+    if (t.rows > 256)
+        return -1;
+    t.box_bytes = (t.rows * t.pitch + 1023) / 1024 * 1024;
+    *pl = t;
+    return 0;
+}
+
+int tc_tma_korig(const TmaPlan &pl, int Cin, int kp)
+{
+    const int cc = kp % pl.cw, r = kp / pl.cw;
+    const int j = r % pl.ntap, q = r / pl.ntap;
+    return pl.tap_id[j] * Cin + q * pl.cw + cc;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn tma_encoder()
+{
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried)
+    {
+        tried = true;
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(f);
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+bool tc_tma_available()
+{
+    static const bool off = getenv("DMX_NO_TMA") != nullptr;
+    return !off && tma_encoder() != nullptr;
+}
+
+static int tma_set_attr()
+{
+    DMX_CUDA(cudaFuncSetAttribute(tc::gemm_tc_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4 * 1024));
+    return 0;
+}
+
+// p: a stride-1 "same" convolution (Ui == Uo * 1, Vi == Vo, su == sv == 1) or any tap set without v shifts, Cin % 16 == 0,
+// K == ntaps * Cin, A given as the bf16 image p.Aimg, weights as p.Wt (K' order of tc_tma_plan with share_dv = true unless
+// the environment says otherwise).
+int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
+{
+    EncodeTiledFn enc = tma_encoder();
+    if (!enc)
+    {
+        set_error("launch_gemm_tma: cuTensorMapEncodeTiled is not available from this driver");
+        return -1;
+    }
+    if (!p.Aimg || !p.Wt || p.M <= 0 || p.N <= 0 || p.K != p.ntaps * p.Cin || p.Cin % 16 || p.pro || p.A2 || p.Apk)
+    {
+        set_error("launch_gemm_tma: unsupported problem");
+        return -1;
+    }
+    static const bool share_env = getenv("DMX_TMA_NO_SHARE") == nullptr;
+    const bool share = share_env && !p.t_noshare;
+    TmaPlan pl;
+    if (tc_tma_plan(p.ntaps, p.du, p.dv, p.Cin, share, &pl))
+    {
+        set_error("launch_gemm_tma: no plan for this tap set");
+        return -1;
+    }
+    const int bn = tc_tile_n(p.N);
+    const int nout = p.glu ? p.N / 2 : p.N;
+    GemmParams q = p;
+    auto recip = [](int d) { return d <= 1 ? 0ull : ~0ull / (unsigned long long)d + 1ull; };
+    q.div_per = recip(p.Uo * p.Vo);
+    q.div_vo = recip(p.Vo);
+    q.div_nco = recip(p.Nco);
+    q.halo_tpr = (p.Vo + tc::BM - 1) / tc::BM;
+    q.div_tpr = recip(q.halo_tpr);
+    q.div_uo = recip(p.Uo);
+    q.t_nbox = pl.nbox;
+    q.t_ntap = pl.ntap;
+    for (int i = 0; i < 9; ++i)
+    {
+        q.t_box_du[i] = i < pl.nbox ? pl.box_du[i] : 0;
+        q.t_box_dv[i] = i < pl.nbox ? pl.box_dv[i] : 0;
+        q.t_tap_box[i] = i < pl.ntap ? pl.tap_box[i] : -1;
+        q.t_tap_shift[i] = i < pl.ntap ? pl.tap_shift[i] : 0;
+    }
+    q.t_rows = pl.rows;
+    q.t_cw = pl.cw;
+    q.t_nchunk = pl.nchunk;
+    q.t_pitch = pl.pitch;
+    q.t_box_bytes = pl.box_bytes;
+    q.t_layout = pl.layout;
+    const int plain = (p.ous == 1 && p.ovs == 1 && p.our == 0 && p.ovr == 0 && p.ouo == 0 && p.ovo == 0 && p.Uout == p.Uo &&
+                       p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 &&
+                       (!p.rowadd || (p.rowadd_ld % 4) == 0) && (!p.addC || (reinterpret_cast<uintptr_t>(p.addC) & 15) == 0))
+                          ? 1
+                          : 0;
+    const int vscat = (!plain && (p.Nco % 4) == 0 && (nout % 4) == 0 && (p.ldc % 4) == 0 &&
+                       (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 && (!p.rowadd || (p.rowadd_ld % 4) == 0) &&
+                       (!p.gamma || (reinterpret_cast<uintptr_t>(p.gamma) & 15) == 0) &&
+                       (!p.addC || (reinterpret_cast<uintptr_t>(p.addC) & 15) == 0))
+                          ? 2
+                          : 0;
+    if (!plain && !vscat)
+    {
+        set_error("launch_gemm_tma: output mapping not supported");
+        return -1;
+    }
+    // tensor map over the image: dims (C, V, U, B), innermost first
+    const int items = p.M / (p.Uo * p.Vo);
+    CUtensorMap tm;
+    {
+        const cuuint64_t dims[4] = {(cuuint64_t)p.Cin, (cuuint64_t)p.Vi, (cuuint64_t)p.Ui, (cuuint64_t)items};
+        const cuuint64_t strides[3] = {(cuuint64_t)p.Cin * 2, (cuuint64_t)p.Vi * p.Cin * 2, (cuuint64_t)p.Ui * p.Vi * p.Cin * 2};
+        const cuuint32_t box[4] = {(cuuint32_t)pl.cw, (cuuint32_t)pl.rows, 1, 1};
+        const cuuint32_t es[4] = {1, 1, 1, 1};
+        const CUtensorMapSwizzle sw = pl.cw == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                                  : (pl.cw == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+        const CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(p.Aimg), dims, strides, box, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+        {
+            set_error("launch_gemm_tma: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+            return -1;
+        }
+    }
+    static int sms = 0;
+    if (!sms)
+    {
+        int dev = 0;
+        DMX_CUDA(cudaGetDevice(&dev));
+        DMX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        if (tma_set_attr())
+            return -1;
+    }
+    static const int ew_env = getenv("DMX_TMA_EW") ? atoi(getenv("DMX_TMA_EW")) : 0;
+    const int ew = (ew_env == 8 || ew_env == 16 || ew_env == 4 || ew_env == 12) ? ew_env : 8;
+    const size_t b_stage = (size_t)bn * tc::BK * 2;
+    const size_t fixed = (size_t)ew * 32 * tc::EPI_LD * 4 + (size_t)ew * 32 * sizeof(tc::RowInfo);
+    const size_t budget = 220 * 1024;
+    const int nkb = (p.K + tc::BK - 1) / tc::BK;
+    int b_stages = nkb < 3 ? (nkb < 2 ? 2 : nkb) : 3;
+    if (fixed + b_stages * b_stage + 2 * (size_t)pl.box_bytes > budget)
+    {
+        set_error("launch_gemm_tma: tile does not fit in shared memory");
+        return -1;
+    }
+    int a_slots = (int)((budget - fixed - b_stages * b_stage) / pl.box_bytes);
+    a_slots = std::min(a_slots, tc::T_MAX_ASLOTS);
+    // spare room goes to the weight ring
+    while (b_stages < tc::T_MAX_BSTAGES && b_stages < nkb * 2 &&
+           fixed + (size_t)(b_stages + 1) * b_stage + (size_t)a_slots * pl.box_bytes <= budget)
+        ++b_stages;
+    const size_t smem = fixed + (size_t)b_stages * b_stage + (size_t)a_slots * pl.box_bytes;
+    const int mtiles = items * p.Uo * q.halo_tpr, ntiles = (p.N + bn - 1) / bn;
+    const int total = mtiles * ntiles;
+    const int grid = total < sms ? total : sms;
+    tc::gemm_tc_tma_kernel<<<grid, (ew + 3) * 32, smem, st>>>(tm, q, static_cast<const __nv_bfloat16 *>(p.Wt), bn, plain | vscat,
+                                                             a_slots, b_stages, mtiles, ntiles, ew);
+    DMX_LAUNCH_CHECK();
+    return 0;
 }
 
 } // namespace dmx

@@ -63,7 +63,33 @@ struct GemmParams
     // halo mode of the tensor-core kernel (stride-1 multi-tap convolutions; see gemm_tc.cu), also set by the launcher
     int halo_nu = 0, halo_dumin = 0, halo_dvmin = 0, halo_rows = 0, halo_tpr = 0; // planes, first du / dv, patch rows, tiles per (b,u)
     unsigned long long div_tpr = 0, div_uo = 0, div_c8 = 0, div_rows = 0;
+    // optional bf16 copy of the output, same element indexing as C (identity or scatter mapping, not with bulk / packed
+    // outputs): the channels-last IMAGE the next convolution's TMA loads read
+    void *Cbf = nullptr;
+    // TMA-fed persistent mode (gemm_tc.cu: launch_gemm_tma): A is a bf16 channels-last image [B][Ui][Vi][Cin] read through a
+    // tensor map; Wt = the weights in that kernel's K order (TmaPlan); the t_* fields are filled in by the launcher
+    const void *Aimg = nullptr;
+    const void *Wt = nullptr;
+    int t_nbox = 0, t_box_du[9] = {0}, t_box_dv[9] = {0}, t_rows = 0, t_ntap = 0, t_tap_box[9] = {0}, t_tap_shift[9] = {0};
+    int t_cw = 0, t_nchunk = 0, t_pitch = 0, t_box_bytes = 0, t_layout = 0;
+    int t_noshare = 0; // set by the caller: one box per tap instead of one per plane (test hook)
 };
+
+// K order and operand boxes of the TMA-fed kernel for a stride-1 tap set: a BOX is a run of input rows of one plane
+// (one du) that TMA lands in shared memory once per tile; with share_dv all taps of a plane read the same box at
+// row offsets dv - dvmin, otherwise every tap has its own box.  K' = ((chunk * ntap + j) * cw + c % cw) for the j-th
+// tap in box order, chunk = c / cw, cw = 64 / 32 / 16 channels = one 128 / 64 / 32-byte swizzle row.
+struct TmaPlan
+{
+    int nbox = 0, box_du[9], box_dv[9], rows = 0;
+    int ntap = 0, tap_id[9], tap_box[9], tap_shift[9];
+    int cw = 0, nchunk = 0, pitch = 0, box_bytes = 0, layout = 0;
+};
+int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv, TmaPlan *pl);
+// original K index (tap * Cin + c) of K' index kp
+int tc_tma_korig(const TmaPlan &pl, int Cin, int kp);
+int launch_gemm_tma(const GemmParams &p, cudaStream_t st);
+bool tc_tma_available();
 
 int launch_gemm(const GemmParams &p, cudaStream_t st);
 

@@ -714,4 +714,115 @@ int debug_linear(int device, int precision, int M, int N, int K, const float *A,
     return rc;
 }
 
+// Test hook for the TMA-fed convolution kernel in isolation: a stride-1 "same" convolution with an arbitrary tap set over a
+// channels-last image, out = act / GLU(conv(img, W) + bias).  img (B, U, V, Cin) and W (N, ntaps * Cin) (k = tap * Cin + c)
+// are host fp32 (rounded to bf16 here, as the producing epilogue / the weight packer would); out (B, U, V, N or N / 2).
+int debug_conv(int device, int B, int U, int V, int Cin, int N, int ntaps, const int *du, const int *dv, const float *img,
+               const float *W, const float *bias, int act, int glu, int share_dv, float *out, int iters, float *ms_out)
+{
+    DMX_CUDA(cudaSetDevice(device));
+    if (!tc_tma_available())
+    {
+        set_error("debug_conv: the TMA path is not available");
+        return -1;
+    }
+    dmx_model tmp;
+    tmp.device = device;
+    int rc = 0;
+    void *dimg = nullptr;
+    float *dC = nullptr;
+    Packed pk;
+    const int K = ntaps * Cin, nout = glu ? N / 2 : N;
+    const size_t npos = (size_t)B * U * V;
+    do
+    {
+        TmaPlan pl;
+        if ((rc = tc_init_device()) || (rc = tc_tma_plan(ntaps, du, dv, Cin, share_dv != 0, &pl)))
+        {
+            if (rc)
+                set_error("debug_conv: bad tap set / channel count");
+            break;
+        }
+        rc = pack(
+            &tmp, pk, K, N, glu != 0, [=](int k, int n) { return W[(size_t)n * K + k]; }, [=](int n) { return bias ? bias[n] : 0.f; },
+            &pl, Cin);
+        if (rc)
+            break;
+        std::vector<uint16_t> hb(npos * Cin);
+        for (size_t i = 0; i < hb.size(); ++i)
+            hb[i] = f32_to_bf16_bits(img[i]);
+        if ((rc = dev_alloc(&tmp, &dimg, hb.size() * 2)) || (rc = dev_alloc_t(&tmp, &dC, npos * nout)))
+            break;
+        if (cudaMemcpy(dimg, hb.data(), hb.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess ||
+            cudaMemset(dC, 0, npos * nout * sizeof(float)) != cudaSuccess)
+        {
+            set_error("debug_conv: copy failed");
+            rc = -1;
+            break;
+        }
+        GemmParams p;
+        p.Aimg = dimg;
+        p.Wt = pk.Wt;
+        p.lda = Cin;
+        p.Cin = Cin;
+        p.K = K;
+        p.ntaps = ntaps;
+        for (int t = 0; t < ntaps; ++t)
+        {
+            p.du[t] = du[t];
+            p.dv[t] = dv[t];
+        }
+        p.bias = pk.bias;
+        p.N = N;
+        p.Ui = p.Uo = U;
+        p.Vi = p.Vo = V;
+        p.M = B * U * V;
+        p.C = dC;
+        p.ldc = nout;
+        p.Nco = nout;
+        p.Uout = U;
+        p.Vout = V;
+        p.act = act;
+        p.glu = glu;
+        p.t_noshare = share_dv ? 0 : 1;
+        if ((rc = launch_gemm_tma(p, 0)))
+            break;
+        if (iters > 0 && ms_out)
+        {
+            cudaEvent_t e0, e1;
+            cudaEventCreate(&e0);
+            cudaEventCreate(&e1);
+            cudaDeviceSynchronize();
+            cudaEventRecord(e0, 0);
+            for (int it = 0; it < iters && !rc; ++it)
+                rc = launch_gemm_tma(p, 0);
+            cudaEventRecord(e1, 0);
+            cudaEventSynchronize(e1);
+            float t = 0.f;
+            cudaEventElapsedTime(&t, e0, e1);
+            *ms_out = t / (float)iters;
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+            if (rc)
+                break;
+        }
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess)
+        {
+            set_error(std::string("debug_conv: kernel failed: ") + cudaGetErrorString(e));
+            rc = -1;
+            break;
+        }
+        if (cudaMemcpy(out, dC, npos * nout * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+        {
+            set_error("debug_conv: copy back failed");
+            rc = -1;
+        }
+    } while (0);
+    for (void *q : tmp.allocs)
+        cudaFree(q);
+    tmp.allocs.clear();
+    return rc;
+}
+
 } // namespace dmx

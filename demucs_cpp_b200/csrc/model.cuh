@@ -24,6 +24,7 @@ struct Packed
     float *W = nullptr;
     float *bias = nullptr;
     void *Wb = nullptr; // bf16 tensor-core image
+    void *Wt = nullptr; // the same in the K order of the TMA-fed kernel (layers that run on it)
     int K = 0, N = 0, ldw = 0;
 };
 
@@ -182,6 +183,8 @@ int noalloc_warm_up(int device); // noalloc.cu
 int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out);
 int debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W, const float *bias,
                  int act, float *out, int iters, float *ms_out);
+int debug_conv(int device, int B, int U, int V, int Cin, int N, int ntaps, const int *du, const int *dv, const float *img,
+               const float *W, const float *bias, int act, int glu, int share_dv, float *out, int iters, float *ms_out);
 int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out); // d_out: [B][S][SEG][2]
 // RAII: brackets the launches issued inside its scope with events when profiling is on
 struct ProfScope

@@ -4,6 +4,7 @@
 #include "model.cuh"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace dmx
@@ -76,7 +77,7 @@ static inline uint16_t f32_to_bf16_bits(float f)
 // Generic packer: element (k, n) of the GEMM B operand given by f(k, n); bias by fb(n).
 // If glu: output columns are interleaved so that packed 2j = original j, packed 2j+1 = original j + N/2.
 template <typename FW, typename FB>
-static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb)
+static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb, const TmaPlan *tp = nullptr, int tpCin = 0)
 {
     p.K = K;
     p.N = N;
@@ -102,12 +103,27 @@ static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb)
             return -1;
         DMX_CUDA(cudaMemcpy(p.Wb, wb.data(), wb.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
     }
+    if (tp)
+    {
+        // the same weights in the K order of the TMA-fed kernel (chunk, box, tap, channel): row k' of that image is
+        // row tc_tma_korig(k') of this one
+        std::vector<uint16_t> wt(tc_packed_elems(K, N), 0);
+        for (int kp = 0; kp < K; ++kp)
+        {
+            const int k = tc_tma_korig(*tp, tpCin, kp);
+            for (int n = 0; n < N; ++n)
+                wt[tc_packed_index(K, N, kp, n)] = f32_to_bf16_bits(w[(size_t)k * p.ldw + n]);
+        }
+        if (dev_alloc(m, &p.Wt, wt.size() * sizeof(uint16_t)))
+            return -1;
+        DMX_CUDA(cudaMemcpy(p.Wt, wt.data(), wt.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    }
     return 0;
 }
 
 // Conv weight (Cout, Cin, ntaps) row-major -> B[tap*Cin + c][cout]   (src/conv.hpp:97-110 equivalent)
 static int pack_conv(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cout, int Cin,
-                     int ntaps, bool glu)
+                     int ntaps, bool glu, const TmaPlan *tp = nullptr)
 {
     const HostTensor *w = get(m, wname, (size_t)Cout * Cin * ntaps);
     const HostTensor *b = get(m, bname, Cout);
@@ -121,7 +137,24 @@ static int pack_conv(dmx_model *m, Packed &p, const std::string &wname, const st
             const int tap = k / Cin, c = k % Cin;
             return wd[((size_t)n * Cin + c) * ntaps + tap];
         },
-        [=](int n) { return bd[n]; });
+        [=](int n) { return bd[n]; }, tp, Cin);
+}
+
+// The K order of the TMA-fed kernel for the decoders' "rewrite" convolutions: 3 x 3 over (frequency, frames), tap =
+// kh * 3 + kw (kh along frequency), or k3 along time (src/encdec.cpp:178-196,270-288)
+static TmaPlan rewrite_plan(int C, bool freq)
+{
+    int du[9], dv[9];
+    const int nt = freq ? 9 : 3;
+    for (int t = 0; t < nt; ++t)
+    {
+        du[t] = freq ? t / 3 - 1 : 0;
+        dv[t] = freq ? t % 3 - 1 : t - 1;
+    }
+    TmaPlan pl;
+    static const bool share = getenv("DMX_TMA_NO_SHARE") == nullptr;
+    tc_tma_plan(nt, du, dv, C, share, &pl);
+    return pl;
 }
 
 // ConvTranspose with kernel k = 2*stride (k8 s4, or v3's k4 s2): weight (Cin, Cout, k) -> two taps

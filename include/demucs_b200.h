@@ -169,6 +169,15 @@ extern "C"
     int dmx_debug_linear(int device, int precision, int M, int N, int K, const float *A, const float *W,
                          const float *bias, int act, float *out, int iters, float *ms_out);
 
+    /* Test hook for the TMA-fed convolution kernel in isolation (bf16 mode; stands in for the reference's conv tests,
+     * test/test_layers.cpp:856-1387, on conv2d / conv1d src/conv.hpp:13-262): a stride-1 zero-padded convolution with
+     * `ntaps` taps (du[j], dv[j]) over a channels-last image, out (B,U,V,N or N/2) = act / GLU(conv(img (B,U,V,Cin),
+     * W (N, ntaps*Cin), k = tap*Cin + c) + bias).  Host buffers; operands are rounded to bf16 as the producing layer's
+     * epilogue does.  share_dv = 1: taps of one plane share one staged box (production); 0: one box per tap. */
+    int dmx_debug_conv(int device, int B, int U, int V, int Cin, int N, int ntaps, const int *du, const int *dv,
+                       const float *img, const float *W, const float *bias, int act, int glu, int share_dv, float *out,
+                       int iters, float *ms_out);
+
     /* Kernel launches issued by this model's forward passes so far (for bench.py's gpu_launches). */
     int64_t dmx_launch_count(const dmx_model *m);
 
