@@ -29,6 +29,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 namespace dmx
 {
@@ -176,7 +177,7 @@ struct RowInfo
     long long outoff; // element offset in C of (b, uo*ous + ouo, vo*ovs + ovo), channel 0 (may be "virtual")
     int uu0, vv0;     // that output position (for the bounds checks of the scatter mapping)
     int uo, item;     // input-row frequency index (row-add table) and statistics item (-1: row invalid)
-    int prow, pad_;   // row index in the tile-packed output space (out_pack)
+    int prow, orow;   // row index in the tile-packed output space (out_pack); output position index outoff / ldc
 };
 
 constexpr int PROD_WARPS = 8;
@@ -260,7 +261,8 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
             uint2 pk2;
             pk2.x = pack_bf16x2(o[0], o[1]);
             pk2.y = pack_bf16x2(o[2], o[3]);
-            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.Cbf) + (dst - p.C)) = pk2;
+            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.Cbf) +
+                                       ((long long)ri.orow + (long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.Cbf_ld + co) = pk2;
         }
         rs = o[0] + o[1] + o[2] + o[3];
         rss = o[0] * o[0] + o[1] * o[1] + o[2] * o[2] + o[3] * o[3];
@@ -785,7 +787,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams &p, const int bn,
                             uint2 pk2;
                             pk2.x = pack_bf16x2(o[0], o[1]);
                             pk2.y = pack_bf16x2(o[2], o[3]);
-                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.Cbf) + ri.outoff + outc) = pk2;
+                            *reinterpret_cast<uint2 *>(reinterpret_cast<__nv_bfloat16 *>(p.Cbf) + (long long)ri.orow * p.Cbf_ld + outc) = pk2;
                         }
                     }
                     rs = o[0] + o[1] + o[2] + o[3];
@@ -908,7 +910,7 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         ri.uo = rc.uo;
         ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
         ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m; // per-item padding to whole 128-row tiles
-        ri.pad_ = 0;
+        ri.orow = (rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0;
         rowinfo[tid] = ri;
         float pmean = 0.f, prstd = 1.f;
         if (p.pro == 1 && valid)
@@ -1310,7 +1312,7 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
                 ri.uo = rc.uo;
                 ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
                 ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m;
-                ri.pad_ = 0;
+                ri.orow = (rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0;
                 rowinfo[row] = ri;
             }
             const int my_prow = rowinfo[q * 32 + lane].item >= 0 ? rowinfo[q * 32 + lane].prow : -1;
@@ -1437,14 +1439,22 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
 // core's swizzled K-major layout (cw * 2 = 128 / 64 / 32-byte rows, SWIZZLE_128B / 64B / 32B), zero fill outside the
 // grid = the convolution's zero padding.  No thread touches the operand.  Every tap that reads the plane uses the SAME
 // box: its A descriptor starts dv - dv0 rows further down (start address + shift * row pitch), so a 3 x 3 convolution
-// moves each input row L2 -> SM three times less than nine separate tap loads would.  Boxes and 64-row weight blocks
-// travel through two independent mbarrier rings fed by two loader threads; one thread issues tcgen05.mma into one of
-// two TMEM accumulators while the epilogue warps drain the other (the epilogues above are reused unchanged).
+// moves each input row L2 -> SM three times less than nine separate tap loads would.
+//
+// What bounds these layers (measured with dmx_debug_conv on B200): (1) the weights -- with one 128-row tile per pass every
+// tile re-streams the whole K x N weight image L2 -> SM at ~30 GB/s per SM; so G = 2 row tiles share every weight block
+// (two accumulators fed from one block), and a weight image that fits stays resident in shared memory for the whole
+// kernel; (2) the store side -- one cp.async.bulk per lane and 32-column piece (384 per tile) runs at the copy engine's
+// ~12 ns per operation, 4.5 us per tile; here a warp stages its 32 rows x 32 columns in a swizzled tile and ONE tensor-map
+// store (clipped at the line end by the map's bounds) moves it.
 //   warps [0, ew)   epilogue (ew % 4 == 0, so warp % 4 == TMEM lane quadrant)
 //   warp ew         A loader (TMA boxes)      warp ew + 1   weight loader (bulk copies)      warp ew + 2   MMA issuer
-constexpr int T_MAX_ASLOTS = 12;
-constexpr int T_MAX_BSTAGES = 6;
+// Rings: boxes (a_full / a_empty) and 64-row weight blocks (b_full / b_empty); accumulators acc_full / acc_empty.
+constexpr int T_MAX_ASLOTS = 16;
+constexpr int T_MAX_BSTAGES = 16;
 constexpr int T_MAX_EW = 16;
+constexpr int T_MAX_ACC = 4;
+constexpr int T_EPI_WARP_BYTES = 5120; // one 32 x 128-byte or two 32 x 64-byte store tiles (or the 32 x EPI_LD transposition buffer)
 
 __device__ __forceinline__ void tma_load_4d(void *smem_dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3)
 {
@@ -1452,6 +1462,14 @@ __device__ __forceinline__ void tma_load_4d(void *smem_dst, const CUtensorMap *t
                  ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                  : "memory");
 }
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *tm, const void *smem_src, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(tm)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 
 // Shared-memory matrix descriptor of a swizzled K-major operand whose rows are one swizzle span wide (pitch bytes):
 // 8-row groups lie SBO = 8 * pitch apart; the leading-dimension offset is not used.  layout: 2 = 128B, 4 = 64B, 6 = 32B.
@@ -1466,24 +1484,155 @@ __device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr, uint32_t sbo, u
     return d;
 }
 
-__global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
-    gemm_tc_tma_kernel(const __grid_constant__ CUtensorMap tmA, const GemmParams p, const __nv_bfloat16 *__restrict__ Wt, const int bn,
-                       const int plain_out, const int a_slots, const int b_stages, const int mtiles, const int ntiles, const int ew)
+// Epilogue for row-major fp32 outputs with the identity mapping and no read-modify-write: per 32 raw columns a lane applies
+// bias / GELU / GLU to its own row, the warp assembles the 32 x (32 | 16) tile in shared memory -- 16-byte pieces XOR-placed
+// as the tensor map's swizzle expects, so the stores do not collide on banks -- and lane 0 hands it to ONE tensor-map store;
+// rows past the end of the line (and columns past N) are clipped by the map.  Two tiles per warp alternate.
+__device__ __forceinline__ void epilogue_tile_tmast(const GemmParams &p, const CUtensorMap *tmC, const int bn, const int n0,
+                                                    const uint32_t lane_addr, const RowInfo &ri, uint8_t *stage, const int c_begin,
+                                                    const int c_step, const int lane, const int v_row0, const int line, int &parity)
+{
+    const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N;
+    const bool valid = ri.item >= 0;
+    double st_s = 0.0, st_ss = 0.0;
+    const int npc = p.glu ? 4 : 8;                         // 16-byte pieces per staged row
+    const int rowb = npc * 16;
+    const int sw = p.glu ? ((lane >> 1) & 3) : (lane & 7); // SWIZZLE_64B / SWIZZLE_128B phase of this lane's row
+    for (int c0 = c_begin; c0 < bn; c0 += c_step)
+    {
+        const int rawc0 = n0 + c0;
+        if (rawc0 >= ntile_end)
+            break;
+        float v[32];
+        tmem_ld32(lane_addr + (uint32_t)c0, v);
+        const int nraw = (ntile_end - rawc0) < 32 ? (ntile_end - rawc0) : 32;
+        if (p.bias)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < nraw)
+                {
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc0 + j));
+                    v[j] += b.x;
+                    v[j + 1] += b.y;
+                    v[j + 2] += b.z;
+                    v[j + 3] += b.w;
+                }
+        }
+        if (p.act == 1)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                v[j] = gelu_erf(v[j]);
+        }
+        int nout = nraw;
+        if (p.glu)
+        {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                v[j] = v[2 * j] * sigmoid_ref(v[2 * j + 1]);
+            nout = nraw >> 1;
+        }
+        // GLU tiles are 2 KB: two of them alternate; a plain 4 KB tile waits for its own previous store
+        uint8_t *buf = stage + (p.glu ? parity * 2048 : 0);
+        parity ^= 1;
+        if (lane == 0)
+        {
+            if (p.glu)
+                bulk_wait_read1();
+            else
+                bulk_wait_read();
+        }
+        __syncwarp();
+        float rs = 0.f, rss = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (j < npc)
+            {
+                *reinterpret_cast<float4 *>(buf + lane * rowb + ((j ^ sw) << 4)) =
+                    make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                if (4 * j < nout)
+                {
+                    rs += v[4 * j] + v[4 * j + 1] + v[4 * j + 2] + v[4 * j + 3];
+                    rss += v[4 * j] * v[4 * j] + v[4 * j + 1] * v[4 * j + 1] + v[4 * j + 2] * v[4 * j + 2] + v[4 * j + 3] * v[4 * j + 3];
+                }
+            }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0)
+        {
+            tma_store_3d(tmC, buf, p.glu ? (rawc0 >> 1) : rawc0, v_row0, line);
+            bulk_commit();
+        }
+        if (valid)
+        {
+            st_s += (double)rs;
+            st_ss += (double)rss;
+        }
+    }
+    if (p.stats)
+    {
+        const int item0 = __shfl_sync(0xffffffffu, ri.item, 0);
+        if (__all_sync(0xffffffffu, ri.item == item0))
+        {
+            for (int o = 16; o > 0; o >>= 1)
+            {
+                st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
+                st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
+            }
+            if (lane == 0 && item0 >= 0)
+            {
+                atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
+                atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
+            }
+        }
+        else if (valid)
+        {
+            atomicAdd(&p.stats[2 * (size_t)ri.item + 0], st_s);
+            atomicAdd(&p.stats[2 * (size_t)ri.item + 1], st_ss);
+        }
+    }
+}
+
+// umma with the descriptors given as (lo, hi) words: the issuing thread only adds to the lo words between instructions
+__device__ __forceinline__ void umma_lh(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                        uint32_t accum)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 ".reg .b64 da, db;\n"
+                 "mov.b64 da, {%1, %2};\n"
+                 "mov.b64 db, {%3, %4};\n"
+                 "setp.ne.b32 p, %6, 0;\n"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+                 "}\n" ::"r"(tmem_d),
+                 "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accum)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
+    gemm_tc_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmC, const GemmParams p,
+                       const __nv_bfloat16 *__restrict__ Wt, const int bn, const int plain_out, const int a_slots, const int b_stages,
+                       const int mtiles, const int ntiles, const int ew, const int G, const int nacc, const int b_resident,
+                       const int tma_store)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t a_full[T_MAX_ASLOTS], a_empty[T_MAX_ASLOTS], b_full[T_MAX_BSTAGES], b_empty[T_MAX_BSTAGES];
-    __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2];
+    __shared__ __align__(8) uint64_t acc_full[T_MAX_ACC], acc_empty[T_MAX_ACC];
     __shared__ uint32_t tmem_slot;
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int nkb = (p.K + BK - 1) / BK;
-    const int total_tiles = mtiles * ntiles;
+    const int npairs = (mtiles + G - 1) / G;
+    const int total_items = npairs * ntiles;
+    const int ewg = ew / G; // epilogue warps per tile of a pair
     const uint32_t b_stage_bytes = (uint32_t)bn * BK * 2;
     uint8_t *a_smem = smem;
-    uint8_t *b_smem = smem + (size_t)a_slots * p.t_box_bytes;
-    float *epi_smem = reinterpret_cast<float *>(b_smem + (size_t)b_stages * b_stage_bytes);
-    RowInfo *row_smem = reinterpret_cast<RowInfo *>(reinterpret_cast<uint8_t *>(epi_smem) + (size_t)ew * 32 * EPI_LD * 4);
+    const uint32_t slot_bytes = (uint32_t)p.t_cps * (uint32_t)p.t_box_bytes; // a ring slot holds the cps chunk boxes of a plane
+    uint8_t *epi_smem = smem + (size_t)a_slots * slot_bytes;                          // 1024-aligned: ew x T_EPI_WARP_BYTES
+    uint8_t *b_smem = epi_smem + (size_t)ew * T_EPI_WARP_BYTES;
+    RowInfo *row_smem = reinterpret_cast<RowInfo *>(b_smem + (size_t)b_stages * b_stage_bytes);
     uint32_t acc_cols = 32;
     while ((int)acc_cols < bn)
         acc_cols <<= 1;
@@ -1498,18 +1647,19 @@ __global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
         for (int s = 0; s < b_stages; ++s)
         {
             mbar_init(&b_full[s], 1);
-            mbar_init(&b_empty[s], 1);
+            mbar_init(&b_empty[s], (uint32_t)G); // every MMA issuer of a pair releases the block
         }
-        for (int a = 0; a < 2; ++a)
+        for (int a = 0; a < nacc; ++a)
         {
             mbar_init(&acc_full[a], 1);
-            mbar_init(&acc_empty[a], (uint32_t)ew);
+            mbar_init(&acc_empty[a], (uint32_t)ewg);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == ew + 2)
     {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(2u * acc_cols)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                     "r"((uint32_t)nacc * acc_cols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -1527,21 +1677,27 @@ __global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
 
     if (warp < ew)
     {
-        // ================= epilogue =================
-        const int q = warp & 3;
-        const int csel = warp >> 2, nsel = ew >> 2;
-        float *stage = epi_smem + warp * (32 * EPI_LD);
+        // ================= epilogue: warp group g = warp / ewg drains tile g of every pair =================
+        const int g = warp / ewg, wg = warp - g * ewg;
+        const int q = warp & 3; // ewg % 4 == 0, so this is also wg & 3: the TMEM lane quadrant this warp may read
+        const int csel = wg >> 2, nsel = ewg >> 2;
+        uint8_t *stage = epi_smem + (size_t)warp * T_EPI_WARP_BYTES;
         RowInfo *rowinfo = row_smem + warp * 32 - q * 32;
         const bool packed_direct = p.out_pack && plain_out == 1 && !p.glu && !p.gamma && !p.addC && !p.rowadd && !p.stats &&
                                    (p.N % 8) == 0;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it)
+        const bool use_tmast = tma_store && bulk_ok(p, plain_out) && !p.gamma;
+        int parity = 0, itm = 0;
+        for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++itm)
         {
-            const int mt = tile / ntiles, nt = tile - mt * ntiles;
+            const int pr = item / ntiles, nt = item - pr * ntiles;
+            const int mt = pr * G + g;
+            if (mt >= mtiles)
+                break;
+            const int tl = itm * G + g;
+            int hb, hu, hv0;
+            tile_coords(mt, hb, hu, hv0);
             {
                 const int row = q * 32 + lane;
-                int hb, hu, hv0;
-                tile_coords(mt, hb, hu, hv0);
                 const bool valid = hv0 + row < p.Vo;
                 RowCoord rc;
                 rc.b = hb;
@@ -1555,26 +1711,33 @@ __global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
                 ri.uo = rc.uo;
                 ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
                 ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m;
-                ri.pad_ = 0;
+                ri.orow = (rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0;
                 rowinfo[row] = ri;
             }
             const int my_prow = rowinfo[q * 32 + lane].item >= 0 ? rowinfo[q * 32 + lane].prow : -1;
             __syncwarp();
-            const int acc = it & 1;
-            mbar_wait(&acc_full[acc], (uint32_t)((it >> 1) & 1));
+            const int acc = tl % nacc;
+            mbar_wait(&acc_full[acc], (uint32_t)(tl / nacc) & 1u);
             tc_fence_after();
             const uint32_t lane_addr = tmem_base + (uint32_t)acc * acc_cols + ((uint32_t)(q * 32) << 16);
-            if (packed_direct)
+            if (use_tmast)
+                epilogue_tile_tmast(p, &tmC, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], stage, 32 * csel, 32 * nsel, lane,
+                                    hv0 + q * 32, hb * p.Uo + hu, parity);
+            else if (packed_direct)
                 epilogue_tile_packed(p, bn, nt * bn, lane_addr, my_prow, 32 * csel, 32 * nsel);
             else if (bulk_ok(p, plain_out) && !p.no_bulk)
-                epilogue_tile_bulk(p, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], stage, 32 * csel, 32 * nsel, lane);
+                epilogue_tile_bulk(p, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], reinterpret_cast<float *>(stage), 32 * csel,
+                                   32 * nsel, lane);
             else
-                epilogue_tile(p, bn, plain_out, nt * bn, lane_addr, rowinfo, stage, q, 32 * csel, 32 * nsel, lane);
+                epilogue_tile(p, bn, plain_out, nt * bn, lane_addr, rowinfo, reinterpret_cast<float *>(stage), q, 32 * csel, 32 * nsel,
+                              lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0)
                 mbar_arrive(&acc_empty[acc]);
         }
+        if (use_tmast && lane == 0)
+            bulk_wait_read(); // the store tiles live in this CTA's shared memory: drain before exit
     }
     else if (warp == ew)
     {
@@ -1582,97 +1745,176 @@ __global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
         if (lane == 0)
         {
             asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
-            const uint32_t box_tx = (uint32_t)p.t_rows * (uint32_t)p.t_pitch;
-            int ga = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x)
+            const uint32_t box_tx = (uint32_t)p.t_rows * (uint32_t)p.t_pitch * (uint32_t)p.t_cps;
+            const int ngrp = p.t_nchunk / p.t_cps;
+            int slot = 0;
+            uint32_t ph = 0;
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x)
             {
-                const int mt = tile / ntiles;
-                int hb, hu, hv0;
-                tile_coords(mt, hb, hu, hv0);
-                for (int qc = 0; qc < p.t_nchunk; ++qc)
-                    for (int b = 0; b < p.t_nbox; ++b, ++ga)
-                    {
-                        const int slot = ga % a_slots;
-                        const uint32_t ph = (uint32_t)(ga / a_slots) & 1u;
-                        mbar_wait(&a_empty[slot], ph ^ 1u);
-                        mbar_arrive_expect_tx(&a_full[slot], box_tx);
-                        tma_load_4d(a_smem + (size_t)slot * p.t_box_bytes, &tmA, &a_full[slot], qc * p.t_cw, hv0 * p.sv + p.t_box_dv[b],
-                                    hu * p.su + p.t_box_du[b], hb);
-                    }
+                const int pr = item / ntiles;
+                int hb[2], hu[2], hv0[2], ng = 0;
+                for (int g = 0; g < G && pr * G + g < mtiles; ++g, ++ng)
+                    tile_coords(pr * G + g, hb[g], hu[g], hv0[g]);
+                for (int qg = 0; qg < ngrp; ++qg)
+                    for (int b = 0; b < p.t_nbox; ++b)
+                        for (int g = 0; g < ng; ++g)
+                        {
+                            mbar_wait(&a_empty[slot], ph ^ 1u);
+                            mbar_arrive_expect_tx(&a_full[slot], box_tx);
+                            for (int qi = 0; qi < p.t_cps; ++qi)
+                                tma_load_4d(a_smem + (size_t)slot * slot_bytes + (size_t)qi * p.t_box_bytes, &tmA, &a_full[slot],
+                                            (qg * p.t_cps + qi) * p.t_cw, hv0[g] * p.sv + p.t_box_dv[b], hu[g] * p.su + p.t_box_du[b],
+                                            hb[g]);
+                            if (++slot == a_slots)
+                            {
+                                slot = 0;
+                                ph ^= 1u;
+                            }
+                        }
             }
         }
     }
     else if (warp == ew + 1)
     {
-        // ================= weight loader: one bulk copy per 64-row block =================
+        // ================= weight loader: one bulk copy per 64-row block (once only when the image is resident) =================
         if (lane == 0)
         {
-            int gb = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x)
+            int s = 0;
+            uint32_t ph = 0;
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x)
             {
-                const int nt = tile % ntiles;
+                const int nt = item % ntiles;
                 const uint8_t *src = reinterpret_cast<const uint8_t *>(Wt) + (size_t)nt * nkb * b_stage_bytes;
-                for (int kb = 0; kb < nkb; ++kb, ++gb)
+                for (int kb = 0; kb < nkb; ++kb)
                 {
-                    const int s = gb % b_stages;
-                    const uint32_t ph = (uint32_t)(gb / b_stages) & 1u;
-                    mbar_wait(&b_empty[s], ph ^ 1u);
+                    if (!b_resident)
+                        mbar_wait(&b_empty[s], ph ^ 1u);
                     mbar_arrive_expect_tx(&b_full[s], b_stage_bytes);
                     bulk_g2s(b_smem + (size_t)s * b_stage_bytes, src + (size_t)kb * b_stage_bytes, b_stage_bytes, &b_full[s]);
+                    if (++s == b_stages)
+                    {
+                        s = 0;
+                        ph ^= 1u;
+                    }
                 }
+                if (b_resident)
+                    break;
             }
         }
     }
     else
     {
-        // ================= MMA issuer: a single thread =================
-        if (lane == 0)
+        // ================= MMA issuers: one thread per tile of the pair.  The loop between two tcgen05.mma is a handful of
+        // integer instructions (descriptor lo-word adds, ring counters): a lone thread issues a dependent instruction every
+        // few cycles, and at N = 96 an MMA is only 48 cycles long. =================
+        const int g = warp - (ew + 2);
+        if (lane == 0 && g < G)
         {
             const uint32_t idesc = make_idesc(bn);
-            const uint32_t b_lbo = (uint32_t)bn * 16, sbo = 128;
-            const uint32_t a_sbo = 8u * (uint32_t)p.t_pitch;
-            const int spc = p.t_cw >> 4;                 // K = 16 steps per tap and chunk
-            const int ksteps = p.K >> 4;                 // per tile
-            int ga = 0, gb0 = 0, it = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it)
+            const uint32_t b_lbo16 = (uint32_t)bn;                                  // (bn * 16 bytes) >> 4
+            const uint64_t a_proto = make_desc_sw(0, 8u * (uint32_t)p.t_pitch, (uint32_t)p.t_layout);
+            const uint64_t b_proto = make_desc(0, (uint32_t)bn * 16, 128);
+            const uint32_t a_hi = (uint32_t)(a_proto >> 32), a_lo0 = (uint32_t)a_proto;
+            const uint32_t b_hi = (uint32_t)(b_proto >> 32), b_lo0 = (uint32_t)b_proto;
+            const uint32_t a_smem16 = smem_u32(a_smem) >> 4, box16 = (uint32_t)p.t_box_bytes >> 4, slot16 = slot_bytes >> 4;
+            const uint32_t b_smem16 = smem_u32(b_smem) >> 4, bstage16 = b_stage_bytes >> 4;
+            const int spc = p.t_kw >> 4, cps = p.t_cps, tpb = p.t_tpb, nbox = p.t_nbox, ngrp = p.t_nchunk / p.t_cps;
+            const uint32_t shift16 = (uint32_t)p.t_shift16;
+            const int slots_per_item = ngrp * nbox * G;
+            int itm = 0;
+            for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++itm)
             {
-                const int acc = it & 1;
-                const uint32_t d_tmem = tmem_base + (uint32_t)acc * acc_cols;
-                mbar_wait(&acc_empty[acc], (uint32_t)((it >> 1) & 1) ^ 1u);
-                tc_fence_after();
-                int kstep = 0, bs = 0;
-                for (int qc = 0; qc < p.t_nchunk; ++qc)
+                const int pr = item / ntiles;
+                const int ng = (mtiles - pr * G) < G ? (mtiles - pr * G) : G;
+                if (g >= ng)
                 {
-                    int j = 0;
-                    for (int b = 0; b < p.t_nbox; ++b, ++ga)
+                    // the last, incomplete pair (always this CTA's last item): no tile for this issuer, but the weight
+                    // blocks still need its release
+                    if (!b_resident)
                     {
-                        const int slot = ga % a_slots;
-                        mbar_wait(&a_full[slot], (uint32_t)(ga / a_slots) & 1u);
-                        tc_fence_after();
-                        const uint32_t a_base = smem_u32(a_smem + (size_t)slot * p.t_box_bytes);
-                        for (; j < p.t_ntap && p.t_tap_box[j] == b; ++j)
+                        const int gb = itm * nkb;
+                        int bs = gb % b_stages;
+                        uint32_t bph = (uint32_t)(gb / b_stages) & 1u;
+                        for (int kb = 0; kb < nkb; ++kb)
                         {
-                            const uint32_t a_tap = a_base + (uint32_t)p.t_tap_shift[j] * (uint32_t)p.t_pitch;
-                            for (int s = 0; s < spc; ++s, ++kstep)
+                            mbar_wait(&b_full[bs], bph);
+                            mbar_arrive(&b_empty[bs]);
+                            if (++bs == b_stages)
                             {
-                                if ((kstep & 3) == 0)
+                                bs = 0;
+                                bph ^= 1u;
+                            }
+                        }
+                    }
+                    break;
+                }
+                const int tl = itm * G + g, acc = tl % nacc;
+                const uint32_t d_tmem = tmem_base + (uint32_t)acc * acc_cols;
+                // ring positions at the start of this item (all earlier items of this CTA were full pairs)
+                const int ga = itm * slots_per_item + g;
+                int slot = ga % a_slots;
+                uint32_t aph = (uint32_t)(ga / a_slots) & 1u;
+                int bs = 0;
+                uint32_t bph = 0;
+                if (!b_resident)
+                {
+                    const int gb = itm * nkb;
+                    bs = gb % b_stages;
+                    bph = (uint32_t)(gb / b_stages) & 1u;
+                }
+                mbar_wait(&acc_empty[acc], ((uint32_t)(tl / nacc) & 1u) ^ 1u);
+                tc_fence_after();
+                uint32_t accum = 0, bstep = 0, b_lo = 0;
+                for (int qg = 0; qg < ngrp; ++qg)
+                    for (int b = 0; b < nbox; ++b)
+                    {
+                        mbar_wait(&a_full[slot], aph);
+                        tc_fence_after();
+                        uint32_t a_chunk = a_lo0 + a_smem16 + (uint32_t)slot * slot16;
+                        for (int qi = 0; qi < cps; ++qi, a_chunk += box16)
+                        {
+                            uint32_t a_tap = a_chunk;
+                            for (int t = 0; t < tpb; ++t, a_tap += shift16)
+                            {
+                                uint32_t a_lo = a_tap;
+                                for (int s = 0; s < spc; ++s, a_lo += 2)
                                 {
-                                    const int gb = gb0 + (kstep >> 2);
-                                    bs = gb % b_stages;
-                                    mbar_wait(&b_full[bs], (uint32_t)(gb / b_stages) & 1u);
-                                    tc_fence_after();
+                                    if (bstep == 0)
+                                    {
+                                        if (!b_resident || itm == 0)
+                                        {
+                                            mbar_wait(&b_full[bs], bph);
+                                            tc_fence_after();
+                                        }
+                                        b_lo = b_lo0 + b_smem16 + (uint32_t)bs * bstage16;
+                                    }
+                                    umma_lh(d_tmem, a_lo, a_hi, b_lo, b_hi, idesc, accum);
+                                    accum = 1;
+                                    b_lo += 2 * b_lbo16;
+                                    if (++bstep == 4)
+                                    {
+                                        bstep = 0;
+                                        if (!b_resident)
+                                            umma_commit(&b_empty[bs]);
+                                        if (++bs == b_stages)
+                                        {
+                                            bs = 0;
+                                            bph ^= 1u;
+                                        }
+                                    }
                                 }
-                                const uint32_t b_base = smem_u32(b_smem + (size_t)bs * b_stage_bytes);
-                                umma(d_tmem, make_desc_sw(a_tap + (uint32_t)s * 32u, a_sbo, (uint32_t)p.t_layout),
-                                     make_desc(b_base + (uint32_t)(kstep & 3) * 2u * b_lbo, b_lbo, sbo), idesc, kstep > 0 ? 1u : 0u);
-                                if ((kstep & 3) == 3 || kstep == ksteps - 1)
-                                    umma_commit(&b_empty[bs]);
                             }
                         }
                         umma_commit(&a_empty[slot]);
+                        slot += ng;
+                        if (slot >= a_slots)
+                        {
+                            slot -= a_slots;
+                            aph ^= 1u;
+                        }
                     }
-                }
-                gb0 += nkb;
+                if (bstep != 0 && !b_resident)
+                    umma_commit(&b_empty[bs]); // the last, partial weight block of the tile
                 umma_commit(&acc_full[acc]);
             }
         }
@@ -1682,7 +1924,8 @@ __global__ void __launch_bounds__((T_MAX_EW + 3) * 32, 1)
     if (warp == ew + 2)
     {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2u * acc_cols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)nacc * acc_cols)
+                     : "memory");
     }
 }
 
@@ -1899,7 +2142,14 @@ int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv,
         return -1;
     TmaPlan t;
     t.cw = Cin % 64 == 0 ? 64 : (Cin % 32 == 0 ? 32 : 16);
-    t.nchunk = Cin / t.cw;
+    t.kw = t.cw;
+    t.cpitch = tc_tma_cpitch(Cin);
+    if (t.cpitch != Cin)
+    {
+        t.cw = 64; // one 128-byte row per position, 48 of its 64 channels used
+        t.kw = Cin;
+    }
+    t.nchunk = Cin / t.kw;
     t.pitch = t.cw * 2;
     t.layout = t.cw == 64 ? 2 : (t.cw == 32 ? 4 : 6);
     int dvmin = dv[0], dvmax = dv[0];
@@ -1913,29 +2163,35 @@ int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv,
     if (share_dv)
     {
         t.rows = tc::BM + dvmax - dvmin;
-        // boxes = distinct du in order of first appearance; taps grouped by box, original order inside a box
+        // boxes = distinct du in order of first appearance; taps grouped by box, increasing dv inside a box
         for (int i = 0; i < ntaps; ++i)
         {
-            int b = -1;
+            bool seen = false;
             for (int k = 0; k < t.nbox; ++k)
-                if (t.box_du[k] == du[i])
-                    b = k;
-            if (b < 0)
+                seen = seen || t.box_du[k] == du[i];
+            if (!seen)
             {
                 t.box_du[t.nbox] = du[i];
                 t.box_dv[t.nbox] = dvmin;
                 ++t.nbox;
             }
         }
+        if (ntaps % t.nbox)
+            return -1;
+        t.tpb = ntaps / t.nbox;
+        t.shift = t.tpb > 1 ? (dvmax - dvmin) / (t.tpb - 1) : 0;
         for (int b = 0; b < t.nbox; ++b)
-            for (int i = 0; i < ntaps; ++i)
-                if (du[i] == t.box_du[b])
-                {
-                    t.tap_id[t.ntap] = i;
-                    t.tap_box[t.ntap] = b;
-                    t.tap_shift[t.ntap] = dv[i] - dvmin;
-                    ++t.ntap;
-                }
+            for (int k = 0; k < t.tpb; ++k)
+            {
+                // the tap of this plane at row shift k * shift
+                int found = -1;
+                for (int i = 0; i < ntaps; ++i)
+                    if (du[i] == t.box_du[b] && dv[i] - dvmin == k * t.shift)
+                        found = i;
+                if (found < 0)
+                    return -1; // not a regular tap grid
+                t.tap_id[t.ntap++] = found;
+            }
     }
     else
     {
@@ -1945,23 +2201,32 @@ int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv,
             t.box_du[i] = du[i];
             t.box_dv[i] = dv[i];
             t.tap_id[i] = i;
-            t.tap_box[i] = i;
-            t.tap_shift[i] = 0;
         }
         t.nbox = t.ntap = ntaps;
+        t.tpb = 1;
+        t.shift = 0;
     }
     if (t.rows > 256)
         return -1;
     t.box_bytes = (t.rows * t.pitch + 1023) / 1024 * 1024;
+    // narrow chunks: all chunks of a plane travel together (one ring slot, one barrier) when that stays small
+    t.cps = (t.nchunk > 1 && t.nchunk * t.box_bytes <= 18 * 1024) ? t.nchunk : 1;
     *pl = t;
     return 0;
 }
 
+int tc_tma_cpitch(int C) { return C == 48 ? 64 : C; }
+
 int tc_tma_korig(const TmaPlan &pl, int Cin, int kp)
 {
-    const int cc = kp % pl.cw, r = kp / pl.cw;
-    const int j = r % pl.ntap, q = r / pl.ntap;
-    return pl.tap_id[j] * Cin + q * pl.cw + cc;
+    const int cc = kp % pl.kw;
+    int r = kp / pl.kw;
+    const int k = r % pl.tpb;
+    r /= pl.tpb;
+    const int qi = r % pl.cps;
+    r /= pl.cps;
+    const int b = r % pl.nbox, qg = r / pl.nbox;
+    return pl.tap_id[b * pl.tpb + k] * Cin + (qg * pl.cps + qi) * pl.kw + cc;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -2032,20 +2297,22 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
     q.div_tpr = recip(q.halo_tpr);
     q.div_uo = recip(p.Uo);
     q.t_nbox = pl.nbox;
-    q.t_ntap = pl.ntap;
     for (int i = 0; i < 9; ++i)
     {
         q.t_box_du[i] = i < pl.nbox ? pl.box_du[i] : 0;
         q.t_box_dv[i] = i < pl.nbox ? pl.box_dv[i] : 0;
-        q.t_tap_box[i] = i < pl.ntap ? pl.tap_box[i] : -1;
-        q.t_tap_shift[i] = i < pl.ntap ? pl.tap_shift[i] : 0;
     }
+    q.t_tpb = pl.tpb;
+    q.t_shift16 = pl.shift * pl.pitch / 16;
+    q.t_cps = pl.cps;
     q.t_rows = pl.rows;
     q.t_cw = pl.cw;
+    q.t_kw = pl.kw;
     q.t_nchunk = pl.nchunk;
     q.t_pitch = pl.pitch;
     q.t_box_bytes = pl.box_bytes;
     q.t_layout = pl.layout;
+    const size_t slot_bytes = (size_t)pl.cps * pl.box_bytes; // one ring slot = the cps chunk boxes of a plane
     const int plain = (p.ous == 1 && p.ovs == 1 && p.our == 0 && p.ovr == 0 && p.ouo == 0 && p.ovo == 0 && p.Uout == p.Uo &&
                        p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 &&
                        (!p.rowadd || (p.rowadd_ld % 4) == 0) && (!p.addC || (reinterpret_cast<uintptr_t>(p.addC) & 15) == 0))
@@ -2066,8 +2333,14 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
     const int items = p.M / (p.Uo * p.Vo);
     CUtensorMap tm;
     {
-        const cuuint64_t dims[4] = {(cuuint64_t)p.Cin, (cuuint64_t)p.Vi, (cuuint64_t)p.Ui, (cuuint64_t)items};
-        const cuuint64_t strides[3] = {(cuuint64_t)p.Cin * 2, (cuuint64_t)p.Vi * p.Cin * 2, (cuuint64_t)p.Ui * p.Vi * p.Cin * 2};
+        const cuuint64_t cp = (cuuint64_t)(p.Aimg_ld ? p.Aimg_ld : p.Cin);
+        if ((int)cp != pl.cpitch)
+        {
+            set_error("launch_gemm_tma: the image's row pitch does not match the plan");
+            return -1;
+        }
+        const cuuint64_t dims[4] = {cp, (cuuint64_t)p.Vi, (cuuint64_t)p.Ui, (cuuint64_t)items};
+        const cuuint64_t strides[3] = {cp * 2, (cuuint64_t)p.Vi * cp * 2, (cuuint64_t)p.Ui * p.Vi * cp * 2};
         const cuuint32_t box[4] = {(cuuint32_t)pl.cw, (cuuint32_t)pl.rows, 1, 1};
         const cuuint32_t es[4] = {1, 1, 1, 1};
         const CUtensorMapSwizzle sw = pl.cw == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
@@ -2091,29 +2364,111 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
             return -1;
     }
     static const int ew_env = getenv("DMX_TMA_EW") ? atoi(getenv("DMX_TMA_EW")) : 0;
-    const int ew = (ew_env == 8 || ew_env == 16 || ew_env == 4 || ew_env == 12) ? ew_env : 8;
+    static const int g_env = getenv("DMX_TMA_G") ? atoi(getenv("DMX_TMA_G")) : 0;
+    static const bool no_res = getenv("DMX_TMA_NO_RESIDENT") != nullptr;
+    static const bool no_tmast = getenv("DMX_TMA_NO_STORE") != nullptr;
     const size_t b_stage = (size_t)bn * tc::BK * 2;
-    const size_t fixed = (size_t)ew * 32 * tc::EPI_LD * 4 + (size_t)ew * 32 * sizeof(tc::RowInfo);
     const size_t budget = 220 * 1024;
     const int nkb = (p.K + tc::BK - 1) / tc::BK;
-    int b_stages = nkb < 3 ? (nkb < 2 ? 2 : nkb) : 3;
-    if (fixed + b_stages * b_stage + 2 * (size_t)pl.box_bytes > budget)
+    const int mtiles = items * p.Uo * q.halo_tpr, ntiles = (p.N + bn - 1) / bn;
+    int acc_cols = 32;
+    while (acc_cols < bn)
+        acc_cols <<= 1;
+    // G = 2 row tiles share every weight block (one MMA issuer and one group of epilogue warps per tile); four accumulators
+    // (one pair draining while the next fills) when they fit in TMEM
+    int G = (g_env == 1 || g_env == 2) ? g_env : 2;
+    if (mtiles < 2 * sms && !g_env)
+        G = 1; // too few tiles to pair without idling SMs
+    const int nacc = (2 * G * acc_cols <= 512) ? 2 * G : G;
+    if (nacc * acc_cols > 512)
     {
-        set_error("launch_gemm_tma: tile does not fit in shared memory");
+        set_error("launch_gemm_tma: accumulators do not fit in TMEM");
         return -1;
     }
-    int a_slots = (int)((budget - fixed - b_stages * b_stage) / pl.box_bytes);
-    a_slots = std::min(a_slots, tc::T_MAX_ASLOTS);
-    // spare room goes to the weight ring
-    while (b_stages < tc::T_MAX_BSTAGES && b_stages < nkb * 2 &&
-           fixed + (size_t)(b_stages + 1) * b_stage + (size_t)a_slots * pl.box_bytes <= budget)
+    auto fixed_for = [&](int e) { return (size_t)e * tc::T_EPI_WARP_BYTES + (size_t)e * 32 * sizeof(tc::RowInfo); };
+    // epilogue warps: 8 per tile when shared memory allows (the epilogue is a chain of TMEM load -> math -> store tile ->
+    // tensor-map store per 32 columns: more warps = more chains in flight), else 4 per tile
+    int ew = 8 * G;
+    int b_resident = 0, b_stages = 0;
+    {
+        // preference order: resident weights with 8 then 4 epilogue warps per tile; streamed weights with (8, 3 stages),
+        // (4, 3 stages), (4, 2 stages); every variant needs at least 2 boxes per tile of the pair in the ring
+        const int min_boxes = 2 * G;
+        bool found = false;
+        const bool can_res = !no_res && ntiles == 1 && nkb <= tc::T_MAX_BSTAGES;
+        for (int e = 8; e >= 4 && !found && can_res; e -= 4)
+            if (fixed_for(e * G) + (size_t)nkb * b_stage + (size_t)(min_boxes + 1) * slot_bytes <= budget)
+            {
+                ew = e * G;
+                b_resident = 1;
+                b_stages = nkb;
+                found = true;
+            }
+        const int tries[3][2] = {{8, 3}, {4, 3}, {4, 2}};
+        for (int t = 0; t < 3 && !found; ++t)
+        {
+            const int st = std::min(tries[t][1], std::max(nkb, 2));
+            if (fixed_for(tries[t][0] * G) + (size_t)st * b_stage + (size_t)(min_boxes + (t < 2 ? G : 0)) * slot_bytes <= budget)
+            {
+                ew = tries[t][0] * G;
+                b_stages = st;
+                found = true;
+            }
+        }
+        if (!found)
+        {
+            set_error("launch_gemm_tma: tile does not fit in shared memory");
+            return -1;
+        }
+    }
+    if (ew_env == 4 * G || ew_env == 8 * G)
+        ew = ew_env;
+    const size_t fixed = fixed_for(ew);
+    // Ring depths.  Streamed weights are what these layers wait for: a stage is refilled only after the MMAs that read it
+    // have completed and the copy has crossed L2 -> SM (~1.5 us), so the bytes in flight bound the rate.  Boxes first get a
+    // modest ring (4 per tile of the pair), then the weight ring takes what is left, then the boxes the remainder.
+    const int slots_per_item = G * pl.nbox * (pl.nchunk / pl.cps);
+    int a_max = (int)((budget - fixed - b_stages * b_stage) / slot_bytes);
+    a_max = std::min(a_max, tc::T_MAX_ASLOTS);
+    if (a_max < 2 * G)
+    {
+        set_error("launch_gemm_tma: box ring does not fit in shared memory");
+        return -1;
+    }
+    int a_slots = std::min(a_max, std::max(2 * G, std::min(4 * G, slots_per_item)));
+    while (!b_resident && b_stages < tc::T_MAX_BSTAGES && b_stages < nkb &&
+           fixed + (size_t)(b_stages + 1) * b_stage + (size_t)a_slots * slot_bytes <= budget)
         ++b_stages;
-    const size_t smem = fixed + (size_t)b_stages * b_stage + (size_t)a_slots * pl.box_bytes;
-    const int mtiles = items * p.Uo * q.halo_tpr, ntiles = (p.N + bn - 1) / bn;
-    const int total = mtiles * ntiles;
+    while (a_slots < tc::T_MAX_ASLOTS && a_slots < 2 * slots_per_item &&
+           fixed + (size_t)b_stages * b_stage + (size_t)(a_slots + 1) * slot_bytes <= budget)
+        ++a_slots;
+    const size_t smem = fixed + (size_t)b_stages * b_stage + (size_t)a_slots * slot_bytes;
+    // tensor map of the output for the store epilogue: (columns, positions of a line, lines)
+    CUtensorMap tmc;
+    memset(&tmc, 0, sizeof tmc);
+    int tma_store = 0;
+    if (plain == 1 && !no_tmast && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && !p.Cbf && !p.gamma &&
+        (p.N % (p.glu ? 8 : 4)) == 0)
+    {
+        const cuuint64_t dims[3] = {(cuuint64_t)nout, (cuuint64_t)p.Vout, (cuuint64_t)items * p.Uout};
+        const cuuint64_t strides[2] = {(cuuint64_t)p.ldc * 4, (cuuint64_t)p.Vout * p.ldc * 4};
+        const cuuint32_t box[3] = {(cuuint32_t)(p.glu ? 16 : 32), 32, 1};
+        const cuuint32_t es[3] = {1, 1, 1};
+        const CUresult r = enc(&tmc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, p.C, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               p.glu ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+        {
+            set_error("launch_gemm_tma: cuTensorMapEncodeTiled (output) failed (" + std::to_string((int)r) + ")");
+            return -1;
+        }
+        tma_store = 1;
+    }
+    const int npairs = (mtiles + G - 1) / G;
+    const int total = npairs * ntiles;
     const int grid = total < sms ? total : sms;
-    tc::gemm_tc_tma_kernel<<<grid, (ew + 3) * 32, smem, st>>>(tm, q, static_cast<const __nv_bfloat16 *>(p.Wt), bn, plain | vscat,
-                                                             a_slots, b_stages, mtiles, ntiles, ew);
+    tc::gemm_tc_tma_kernel<<<grid, (ew + 2 + G) * 32, smem, st>>>(tm, tmc, q, static_cast<const __nv_bfloat16 *>(p.Wt), bn, plain | vscat,
+                                                             a_slots, b_stages, mtiles, ntiles, ew, G, nacc, b_resident, tma_store);
     DMX_LAUNCH_CHECK();
     return 0;
 }

@@ -66,26 +66,34 @@ struct GemmParams
     // optional bf16 copy of the output, same element indexing as C (identity or scatter mapping, not with bulk / packed
     // outputs): the channels-last IMAGE the next convolution's TMA loads read
     void *Cbf = nullptr;
+    int Cbf_ld = 0; // channels per image row (>= Nco; 48-channel images are stored with a 64-channel pitch, see TmaPlan)
     // TMA-fed persistent mode (gemm_tc.cu: launch_gemm_tma): A is a bf16 channels-last image [B][Ui][Vi][Cin] read through a
     // tensor map; Wt = the weights in that kernel's K order (TmaPlan); the t_* fields are filled in by the launcher
     const void *Aimg = nullptr;
     const void *Wt = nullptr;
-    int t_nbox = 0, t_box_du[9] = {0}, t_box_dv[9] = {0}, t_rows = 0, t_ntap = 0, t_tap_box[9] = {0}, t_tap_shift[9] = {0};
-    int t_cw = 0, t_nchunk = 0, t_pitch = 0, t_box_bytes = 0, t_layout = 0;
+    int t_nbox = 0, t_box_du[9] = {0}, t_box_dv[9] = {0}, t_rows = 0;
+    int t_tpb = 0, t_shift16 = 0; // taps per box; descriptor offset (16-byte units) between consecutive taps of a box
+    int t_cw = 0, t_kw = 0, t_nchunk = 0, t_cps = 1, t_pitch = 0, t_box_bytes = 0, t_layout = 0;
+    int Aimg_ld = 0; // channels per image row of Aimg (0: Cin)
     int t_noshare = 0; // set by the caller: one box per tap instead of one per plane (test hook)
 };
 
 // K order and operand boxes of the TMA-fed kernel for a stride-1 tap set: a BOX is a run of input rows of one plane
 // (one du) that TMA lands in shared memory once per tile; with share_dv all taps of a plane read the same box at
-// row offsets dv - dvmin, otherwise every tap has its own box.  K' = ((chunk * ntap + j) * cw + c % cw) for the j-th
-// tap in box order, chunk = c / cw, cw = 64 / 32 / 16 channels = one 128 / 64 / 32-byte swizzle row.
+// row offsets dv - dvmin (equally spaced), otherwise every tap has its own box.  cw = 64 / 32 / 16 channels = one
+// 128 / 64 / 32-byte swizzle row; K' runs over (chunk group, box, chunk in group, tap in box, channel in chunk).
 struct TmaPlan
 {
     int nbox = 0, box_du[9], box_dv[9], rows = 0;
-    int ntap = 0, tap_id[9], tap_box[9], tap_shift[9];
-    int cw = 0, nchunk = 0, pitch = 0, box_bytes = 0, layout = 0;
+    int ntap = 0, tap_id[9]; // taps in box order: box b holds taps tap_id[b * tpb .. + tpb)
+    int tpb = 0, shift = 0;  // taps per box (the same for every box) and the row shift between consecutive taps of a box
+    int cw = 0, nchunk = 0, cps = 1, pitch = 0, box_bytes = 0, layout = 0; // cps: chunks that share one ring slot / barrier
+    int kw = 0;     // channels of a chunk that enter the GEMM (= cw, except 48-channel images: cw 64, kw 48)
+    int cpitch = 0; // channels per image row the producer must write (Cin, or 64 for 48-channel images: a tensor-map copy
+                    // costs per ROW whatever its width, so one 128-byte row beats three 32-byte ones)
 };
 int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv, TmaPlan *pl);
+int tc_tma_cpitch(int C); // image row pitch in channels for a C-channel tensor
 // original K index (tap * Cin + c) of K' index kp
 int tc_tma_korig(const TmaPlan &pl, int Cin, int kp);
 int launch_gemm_tma(const GemmParams &p, cudaStream_t st);

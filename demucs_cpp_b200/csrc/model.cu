@@ -183,10 +183,11 @@ int model_finalize(dmx_model *m)
         m->tdec[i].C = C;
         m->tdec[i].Cout = cout_t;
         // 3x3 rewrite weight (2C, C, 3, 3): tap = kh*3 + kw with kh along frequency, kw along frames
-        if (pack_conv(m, m->dec[i].rewrite, dn + ".rewrite.weight", dn + ".rewrite.bias", 2 * C, C, 9, true) ||
+        const TmaPlan plf = rewrite_plan(C, true), plt = rewrite_plan(C, false);
+        if (pack_conv(m, m->dec[i].rewrite, dn + ".rewrite.weight", dn + ".rewrite.bias", 2 * C, C, 9, true, &plf) ||
             pack_dconv(m, m->dec[i].dc, dn, C) ||
             pack_convtr(m, m->dec[i].convtr, dn + ".conv_tr.weight", dn + ".conv_tr.bias", C, cout_f) ||
-            pack_conv(m, m->tdec[i].rewrite, tn + ".rewrite.weight", tn + ".rewrite.bias", 2 * C, C, 3, true) ||
+            pack_conv(m, m->tdec[i].rewrite, tn + ".rewrite.weight", tn + ".rewrite.bias", 2 * C, C, 3, true, &plt) ||
             pack_dconv(m, m->tdec[i].dc, tn, C) ||
             pack_convtr(m, m->tdec[i].convtr, tn + ".conv_tr.weight", tn + ".conv_tr.bias", C, cout_t))
             return -1;
@@ -282,6 +283,14 @@ int model_finalize(dmx_model *m)
     rc |= A(&m->seg_out, (size_t)S * SEG * 2);
     rc |= A(&m->meanstd_x, 2);
     rc |= A(&m->meanstd_t, 2);
+    m->use_tma = tc_tma_available();
+    if (m->use_tma)
+        for (int i = 0; i < 4 && !rc; ++i)
+        {
+            // decoder i reads [B][FREQS[4-i]][T][CH[4-i]] / [B][TLENS[4-i]][CH[4-i]] as bf16
+            rc |= dev_alloc(m, &m->dimg_f[i], B * (size_t)FREQS[4 - i] * T * tc_tma_cpitch(CH[4 - i]) * 2);
+            rc |= dev_alloc(m, &m->dimg_t[i], B * (size_t)TLENS[4 - i] * tc_tma_cpitch(CH[4 - i]) * 2);
+        }
     if (rc)
         return -1;
     // pad channels of the DConv hidden tensors are never written: they must hold finite values
@@ -499,10 +508,25 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         }
     }
     const float *dec_in_f = m->xq, *dec_in_t = m->tq;
+    // bf16 mode: the decoders' rewrite convolutions run on the TMA-fed kernel whenever the (x + skip) image exists
+    const bool tma = m->use_tma && m->precision == DMX_PRECISION_BF16;
+    const void *img_f = nullptr, *img_t = nullptr;
     if (m->arch == DMX_ARCH_HTDEMUCS_4S)
     {
-        f.gemm(f.linear(m->xq, d, m->down, m->x3d, 384, TF), PC_GEMM_XFMR);
-        f.gemm(f.linear(m->tq, d, m->down_t, m->xt3d, 384, TT), PC_GEMM_XFMR);
+        GemmParams pd = f.linear(m->xq, d, m->down, m->x3d, 384, TF), pdt = f.linear(m->tq, d, m->down_t, m->xt3d, 384, TT);
+        if (tma)
+        {
+            // decoder 0's skip is added here and the sum also leaves as the bf16 image its rewrite conv reads
+            pd.addC = m->e[3];
+            pd.Cbf = m->dimg_f[0];
+            pdt.addC = m->te[3];
+            pdt.Cbf = m->dimg_t[0];
+            pd.Cbf_ld = pdt.Cbf_ld = tc_tma_cpitch(384);
+            img_f = m->dimg_f[0];
+            img_t = m->dimg_t[0];
+        }
+        f.gemm(pd, PC_GEMM_XFMR);
+        f.gemm(pdt, PC_GEMM_XFMR);
         dec_in_f = m->x3d;
         dec_in_t = m->xt3d;
     }
@@ -519,8 +543,14 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         {
             // (x + skip) -> 3x3 conv -> GLU
             GemmParams p = f.base(dec_in_f, C, C, fd.rewrite, m->cA_f, C, F, T, F, T);
-            if (i == 0)
+            if (i == 0 && !img_f)
                 p.A2 = m->e[3]; // later decoders find their skip already added by the previous convT's epilogue
+            if (img_f && fd.rewrite.Wt)
+            {
+                p.Aimg = img_f;
+                p.Aimg_ld = tc_tma_cpitch(C);
+                p.Wt = fd.rewrite.Wt;
+            }
             p.ntaps = 9;
             for (int kh = 0; kh < 3; ++kh)
                 for (int kw = 0; kw < 3; ++kw)
@@ -547,13 +577,26 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.act = i < 3 ? 1 : 0;
             if (i < 3)
                 q.addC = m->e[2 - i]; // the next decoder's skip (src/encdec.cpp:172), added once here
+            img_f = nullptr;
+            if (tma && i < 3)
+            {
+                q.Cbf = m->dimg_f[i + 1];
+                q.Cbf_ld = tc_tma_cpitch(fd.Cout);
+                img_f = m->dimg_f[i + 1];
+            }
             f.gemm(q, PC_GEMM_CONV);
         }
         f.st = st_t;
         {
             GemmParams p = f.base(dec_in_t, C, C, td.rewrite, m->cA_t, C, 1, Lin, 1, Lin);
-            if (i == 0)
+            if (i == 0 && !img_t)
                 p.A2 = m->te[3];
+            if (img_t && td.rewrite.Wt)
+            {
+                p.Aimg = img_t;
+                p.Aimg_ld = tc_tma_cpitch(C);
+                p.Wt = td.rewrite.Wt;
+            }
             p.ntaps = 3;
             for (int t = 0; t < 3; ++t)
             {
@@ -579,6 +622,13 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.act = i < 3 ? 1 : 0;
             if (i < 3)
                 q.addC = m->te[2 - i];
+            img_t = nullptr;
+            if (tma && i < 3)
+            {
+                q.Cbf = m->dimg_t[i + 1];
+                q.Cbf_ld = tc_tma_cpitch(td.Cout);
+                img_t = m->dimg_t[i + 1];
+            }
             f.gemm(q, PC_GEMM_CONV);
         }
         dec_in_f = m->dx[i];
@@ -609,10 +659,11 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     }
     set_tap(m, "x_3_up", m->xq, 8, T, d);
     set_tap(m, "xt_3_up", m->tq, 1, TLEN3, d);
+    const bool pre3 = tma && m->arch == DMX_ARCH_HTDEMUCS_4S; // x3d / xt3d hold value + skip (see above)
     set_tap(m, "x_3", const_cast<float *>(m->arch == DMX_ARCH_HTDEMUCS_4S ? m->x3d : m->xq), 8, T,
-            m->arch == DMX_ARCH_HTDEMUCS_4S ? 384 : d);
+            m->arch == DMX_ARCH_HTDEMUCS_4S ? 384 : d, pre3 ? m->e[3] : nullptr);
     set_tap(m, "xt_3", const_cast<float *>(m->arch == DMX_ARCH_HTDEMUCS_4S ? m->xt3d : m->tq), 1, TLEN3,
-            m->arch == DMX_ARCH_HTDEMUCS_4S ? 384 : d);
+            m->arch == DMX_ARCH_HTDEMUCS_4S ? 384 : d, pre3 ? m->te[3] : nullptr);
     const char *fn[4] = {"x_2", "x_1", "x_0", "x_out"};
     const char *tn[4] = {"xt_2", "xt_1", "xt_0", "xt_out"};
     for (int i = 0; i < 4; ++i)
@@ -748,9 +799,11 @@ int debug_conv(int device, int B, int U, int V, int Cin, int N, int ntaps, const
             &pl, Cin);
         if (rc)
             break;
-        std::vector<uint16_t> hb(npos * Cin);
-        for (size_t i = 0; i < hb.size(); ++i)
-            hb[i] = f32_to_bf16_bits(img[i]);
+        const int cp = tc_tma_cpitch(Cin);
+        std::vector<uint16_t> hb(npos * cp, 0x7fc0); // pad channels hold NaN: they must never reach the GEMM
+        for (size_t i = 0; i < npos; ++i)
+            for (int c = 0; c < Cin; ++c)
+                hb[i * cp + c] = f32_to_bf16_bits(img[i * Cin + c]);
         if ((rc = dev_alloc(&tmp, &dimg, hb.size() * 2)) || (rc = dev_alloc_t(&tmp, &dC, npos * nout)))
             break;
         if (cudaMemcpy(dimg, hb.data(), hb.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess ||
@@ -762,6 +815,7 @@ int debug_conv(int device, int B, int U, int V, int Cin, int N, int ntaps, const
         }
         GemmParams p;
         p.Aimg = dimg;
+        p.Aimg_ld = cp;
         p.Wt = pk.Wt;
         p.lda = Cin;
         p.Cin = Cin;

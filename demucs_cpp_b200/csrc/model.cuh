@@ -156,6 +156,10 @@ struct dmx_model
 
     // workspace (all sized for maxB)
     float *mix, *spec, *xt_in, *cA_f, *cA_t, *e[4], *te[4], *dx[4], *dxt[4];
+    // bf16 channels-last images of the decoder inputs (x + skip), written by the producing epilogue and read by the
+    // TMA-fed rewrite convolutions: [0] = bottleneck + skip, [i] = output of transposed conv i-1 + skip
+    void *dimg_f[4] = {nullptr, nullptr, nullptr, nullptr}, *dimg_t[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool use_tma = false;
     float *h_f, *y2_f, *h_t, *y2_t;
     float *up_f, *up_tt, *xq, *tq, *ln_f, *ln_t, *kn_f, *kn_t, *qkv_f, *qkv_t, *kv_f, *kv_t, *ao_f, *ao_t, *ff_f,
         *ff_t, *x3d, *xt3d;

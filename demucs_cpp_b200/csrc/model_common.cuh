@@ -349,10 +349,16 @@ struct Fwd
         const double nout = p.glu ? p.N / 2 : p.N;
         const double esz_out = p.out_bf16 ? 2.0 : 4.0;
         double bytes = (double)B * p.Ui * p.Vi * p.Cin * 4.0 * (p.A2 ? 2.0 : 1.0) + (double)p.M * nout * esz_out;
+        if (p.Aimg && p.Wt && m->precision == DMX_PRECISION_BF16)
+            bytes = (double)B * p.Ui * p.Vi * p.Cin * 2.0 + (double)p.M * nout * esz_out;
+        if (p.Cbf)
+            bytes += (double)B * p.Uout * p.Vout * p.Nco * 2.0;
         if (p.gamma)
             bytes += (double)p.M * nout * 4.0;
         ProfScope ps(m, cls, 2.0 * (double)p.M * (double)p.N * (double)p.K, bytes);
-        if (m->precision == DMX_PRECISION_BF16 && p.Wb)
+        if (m->precision == DMX_PRECISION_BF16 && p.Aimg && p.Wt)
+            rc = launch_gemm_tma(p, st);
+        else if (m->precision == DMX_PRECISION_BF16 && p.Wb)
             rc = launch_gemm_tc(p, p.Wb, st);
         else
             rc = launch_gemm(p, st);
