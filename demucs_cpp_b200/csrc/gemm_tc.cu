@@ -186,7 +186,8 @@ constexpr int THREADS = PROD_THREADS + 64;      // + warp 8 (B loader) + warp 9 
 constexpr int A_LBO = BM * 16 + 16;             // 2064 B: +16 B pad makes the producers' 16-byte stores conflict free
 constexpr int A_STAGE = 8 * A_LBO;              // 16512 B per stage
 constexpr int EPI_LD = 36;                      // floats per staged row (32 + 4 pad)
-constexpr int EPI_BYTES = PROD_WARPS * 32 * EPI_LD * 4;
+constexpr int EPI_WARP = 5120;                   // per-warp epilogue buffer: 32 x EPI_LD floats, or two 2 KB store tiles (1 KB aligned)
+constexpr int EPI_BYTES = PROD_WARPS * EPI_WARP;
 
 // Store 4 consecutive OUTPUT columns nc0..nc0+3 of one row (general mapping: transposed-conv scatter).
 __device__ __forceinline__ void store_group4_scatter(const GemmParams &p, const RowInfo &ri, int nc0, int nlimit,
@@ -839,9 +840,164 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams &p, const int bn,
     }
 }
 
+__device__ __forceinline__ void tma_load_4d(void *smem_dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3)
+{
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *tm, const void *smem_src, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(tm)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+
+// Shared-memory matrix descriptor of a swizzled K-major operand whose rows are one swizzle span wide (pitch bytes):
+// 8-row groups lie SBO = 8 * pitch apart; the leading-dimension offset is not used.  layout: 2 = 128B, 4 = 64B, 6 = 32B.
+__device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr, uint32_t sbo, uint32_t layout)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)(layout & 7u) << 61;
+    return d;
+}
+
+// Epilogue for row-major fp32 outputs with the identity mapping: per 32 raw columns a lane applies bias / GELU / GLU (and the
+// LayerScale residual, reading the old piece of its own row) to its own row, the warp assembles 32 rows x 16 columns in
+// shared memory -- 16-byte pieces XOR-placed as the tensor map's SWIZZLE_64B expects, so the stores do not collide on
+// banks -- and lane 0 hands the tile to ONE tensor-map store; rows past the end of the line (and columns past N) are
+// clipped by the map.  Two 2 KB tiles per warp alternate.  (One cp.async.bulk per lane and piece, as epilogue_tile_bulk
+// does, runs at the copy engine's ~12 ns per operation: 4.5 us for a 128 x 96 tile.)
+__device__ __forceinline__ void epilogue_tile_tmast(const GemmParams &p, const CUtensorMap *tmC, const int bn, const int n0,
+                                                    const uint32_t lane_addr, const RowInfo &ri, uint8_t *stage, const int c_begin,
+                                                    const int c_step, const int lane, const int v_row0, const int line, int &parity)
+{
+    const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N;
+    const bool valid = ri.item >= 0;
+    double st_s = 0.0, st_ss = 0.0;
+    const int sw = (lane >> 1) & 3; // SWIZZLE_64B phase of this lane's 64-byte row
+    const float *crow = p.C + ri.outoff;
+    for (int c0 = c_begin; c0 < bn; c0 += c_step)
+    {
+        const int rawc0 = n0 + c0;
+        if (rawc0 >= ntile_end)
+            break;
+        float v[32];
+        tmem_ld32(lane_addr + (uint32_t)c0, v);
+        const int nraw = (ntile_end - rawc0) < 32 ? (ntile_end - rawc0) : 32;
+        if (p.bias)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < nraw)
+                {
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc0 + j));
+                    v[j] += b.x;
+                    v[j + 1] += b.y;
+                    v[j + 2] += b.z;
+                    v[j + 3] += b.w;
+                }
+        }
+        if (p.act == 1)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                v[j] = gelu_erf(v[j]);
+        }
+        int nout = nraw;
+        if (p.glu)
+        {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                v[j] = v[2 * j] * sigmoid_ref(v[2 * j + 1]);
+            nout = nraw >> 1;
+        }
+        const int outc0 = p.glu ? (rawc0 >> 1) : rawc0;
+        if (p.gamma && valid)
+        {
+            const float *orow = crow + outc0;
+            const float *grow = p.gamma + outc0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < nout)
+                {
+                    const float4 o = *reinterpret_cast<const float4 *>(orow + j);
+                    const float4 gm = __ldg(reinterpret_cast<const float4 *>(grow + j));
+                    v[j] = o.x + gm.x * v[j];
+                    v[j + 1] = o.y + gm.y * v[j + 1];
+                    v[j + 2] = o.z + gm.z * v[j + 2];
+                    v[j + 3] = o.w + gm.w * v[j + 3];
+                }
+        }
+        float rs = 0.f, rss = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (16 * h < nout)
+            {
+                uint8_t *buf = stage + parity * 2048;
+                parity ^= 1;
+                if (lane == 0)
+                    bulk_wait_read1(); // the store issued two tiles ago has drained this buffer
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    const int e = 16 * h + 4 * j;
+                    *reinterpret_cast<float4 *>(buf + lane * 64 + ((j ^ sw) << 4)) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+                    if (e < nout)
+                    {
+                        rs += v[e] + v[e + 1] + v[e + 2] + v[e + 3];
+                        rss += v[e] * v[e] + v[e + 1] * v[e + 1] + v[e + 2] * v[e + 2] + v[e + 3] * v[e + 3];
+                    }
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0)
+                {
+                    tma_store_3d(tmC, buf, outc0 + 16 * h, v_row0, line);
+                    bulk_commit();
+                }
+            }
+        if (valid)
+        {
+            st_s += (double)rs;
+            st_ss += (double)rss;
+        }
+    }
+    if (p.stats)
+    {
+        const int item0 = __shfl_sync(0xffffffffu, ri.item, 0);
+        if (__all_sync(0xffffffffu, ri.item == item0))
+        {
+            for (int o = 16; o > 0; o >>= 1)
+            {
+                st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
+                st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
+            }
+            if (lane == 0 && item0 >= 0)
+            {
+                atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
+                atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
+            }
+        }
+        else if (valid)
+        {
+            atomicAdd(&p.stats[2 * (size_t)ri.item + 0], st_s);
+            atomicAdd(&p.stats[2 * (size_t)ri.item + 1], st_ss);
+        }
+    }
+}
+
 template <int STAGES, bool VECA, bool HALO>
-__global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
-                                                          const int bn, const int plain_out)
+__global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmC, const GemmParams p,
+                                                          const __nv_bfloat16 *__restrict__ Wb, const int bn,
+                                                          const int plain_out, const int tma_store)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[STAGES];
@@ -980,12 +1136,22 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const GemmParams p,
         tc_fence_after();
         const int q = warp & 3, hsel = warp >> 2;
         static_assert((EPI_LD * 4) % 16 == 0, "bulk copies need 16-byte aligned row slots");
-        if (bulk_ok(p, plain_out) && !p.no_bulk)
+        if (tma_store && bulk_ok(p, plain_out) && !p.no_bulk)
+        {
+            // tensor-map store: flat rows (line 0), or one (item, u) line per tile in HALO mode
+            int parity = 0;
+            epilogue_tile_tmast(p, &tmC, bn, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo[q * 32 + lane],
+                                smem + warp * EPI_WARP, 32 * hsel, 64, lane, (HALO ? hv0 : m0) + q * 32, HALO ? hb * p.Uo + hu : 0,
+                                parity);
+            if (lane == 0)
+                bulk_wait_read();
+        }
+        else if (bulk_ok(p, plain_out) && !p.no_bulk)
             epilogue_tile_bulk(p, bn, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo[q * 32 + lane],
-                               reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD), 32 * hsel, 64, lane);
+                               reinterpret_cast<float *>(smem + warp * EPI_WARP), 32 * hsel, 64, lane);
         else
             epilogue_tile(p, bn, plain_out, n0, tmem_base + ((uint32_t)(q * 32) << 16), rowinfo,
-                          reinterpret_cast<float *>(smem) + warp * (32 * EPI_LD), q, 32 * hsel, 64, lane);
+                          reinterpret_cast<float *>(smem + warp * EPI_WARP), q, 32 * hsel, 64, lane);
         tc_fence_before();
     }
     else if (warp == PROD_WARPS)
@@ -1143,14 +1309,16 @@ __device__ __forceinline__ void epilogue_tile_packed(const GemmParams &p, const 
 // acc_full/acc_empty per accumulator, patch_full/patch_empty per HALO patch buffer.
 constexpr int P_EPI_WARPS = 16;
 constexpr int P_MAX_STAGES = 6;
-constexpr int P_EPI_BYTES = P_EPI_WARPS * 32 * EPI_LD * 4;          // private transposition buffers
+constexpr int P_EPI_WARP = 5120;                                    // per warp: 32 x EPI_LD transposition buffer / two 2 KB store tiles
+constexpr int P_EPI_BYTES = P_EPI_WARPS * P_EPI_WARP + 1024;        // + alignment slack
 constexpr int P_ROW_BYTES = P_EPI_WARPS * 32 * (int)sizeof(RowInfo); // private row tables
 __host__ __device__ constexpr int p_threads(bool prod) { return ((prod ? PROD_WARPS : 0) + P_EPI_WARPS + 2) * 32; }
 
 template <bool VECA, bool HALO, bool PROD>
 __global__ void __launch_bounds__(p_threads(PROD), 1)
-    gemm_tc_persist_kernel(const GemmParams p, const __nv_bfloat16 *__restrict__ Wb, const int bn, const int plain_out,
-                           const int stages, const int mtiles, const int ntiles)
+    gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmC, const GemmParams p, const __nv_bfloat16 *__restrict__ Wb,
+                           const int bn, const int plain_out, const int stages, const int mtiles, const int ntiles,
+                           const int tma_store)
 {
     constexpr int PW = PROD ? PROD_WARPS : 0; // first epilogue warp; PW % 4 == 0 keeps warp % 4 == lane quadrant
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -1170,8 +1338,11 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
     const uint32_t a_bytes = HALO ? 2u * patch_bytes : (uint32_t)(stages * A_STAGE);
     uint8_t *a_smem = smem;
     uint8_t *b_smem = smem + a_bytes;
-    float *epi_smem = reinterpret_cast<float *>(b_smem + (size_t)stages * b_stage_bytes);
-    RowInfo *row_smem = reinterpret_cast<RowInfo *>(reinterpret_cast<uint8_t *>(epi_smem) + P_EPI_BYTES);
+    // epilogue buffers: 1024-byte aligned (the tensor-map store tiles are swizzled), P_EPI_WARP bytes per warp
+    uint8_t *epi_base = b_smem + (size_t)stages * b_stage_bytes;
+    epi_base += (1024u - (smem_u32(epi_base) & 1023u)) & 1023u;
+    float *epi_smem = reinterpret_cast<float *>(epi_base);
+    RowInfo *row_smem = reinterpret_cast<RowInfo *>(epi_base + P_EPI_WARPS * P_EPI_WARP);
     uint32_t acc_cols = 32;
     while ((int)acc_cols < bn)
         acc_cols <<= 1;
@@ -1280,8 +1451,10 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
         const int e = warp - PW;
         const int q = e & 3;      // == warp % 4: the TMEM lane quadrant this warp may read
         const int csel = e >> 2;  // which of every four 32-column chunks
-        float *stage = epi_smem + e * (32 * EPI_LD);
+        float *stage = epi_smem + e * (P_EPI_WARP / 4);
         RowInfo *rowinfo = row_smem + e * 32 - q * 32; // private table, indexed by tile row q*32 + r like the shared one
+        const bool use_tmast = tma_store && !HALO && bulk_ok(p, plain_out) && !p.no_bulk;
+        int st_parity = 0;
         const bool packed_direct = p.out_pack && plain_out == 1 && !p.glu && !p.gamma && !p.addC && !p.rowadd && !p.stats &&
                                    (p.N % 8) == 0;
         int it = 0;
@@ -1323,6 +1496,9 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
             const uint32_t lane_addr = tmem_base + (uint32_t)acc * acc_cols + ((uint32_t)(q * 32) << 16);
             if (packed_direct)
                 epilogue_tile_packed(p, bn, nt * bn, lane_addr, my_prow, 32 * csel, 32 * (P_EPI_WARPS / 4));
+            else if (use_tmast)
+                epilogue_tile_tmast(p, &tmC, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], reinterpret_cast<uint8_t *>(stage),
+                                    32 * csel, 32 * (P_EPI_WARPS / 4), lane, mt * BM + q * 32, 0, st_parity);
             else if (bulk_ok(p, plain_out) && !p.no_bulk)
                 epilogue_tile_bulk(p, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], stage, 32 * csel,
                                    32 * (P_EPI_WARPS / 4), lane);
@@ -1333,6 +1509,8 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
             if (lane == 0)
                 mbar_arrive(&acc_empty[acc]);
         }
+        if (use_tmast && lane == 0)
+            bulk_wait_read(); // the store tiles live in this CTA's shared memory: drain before exit
     }
     else if (warp == PW + P_EPI_WARPS)
     {
@@ -1456,144 +1634,6 @@ constexpr int T_MAX_EW = 16;
 constexpr int T_MAX_ACC = 4;
 constexpr int T_EPI_WARP_BYTES = 5120; // one 32 x 128-byte or two 32 x 64-byte store tiles (or the 32 x EPI_LD transposition buffer)
 
-__device__ __forceinline__ void tma_load_4d(void *smem_dst, const CUtensorMap *tm, uint64_t *bar, int c0, int c1, int c2, int c3)
-{
-    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-                 ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-                 : "memory");
-}
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap *tm, const void *smem_src, int c0, int c1, int c2)
-{
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                     reinterpret_cast<uint64_t>(tm)),
-                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
-
-// Shared-memory matrix descriptor of a swizzled K-major operand whose rows are one swizzle span wide (pitch bytes):
-// 8-row groups lie SBO = 8 * pitch apart; the leading-dimension offset is not used.  layout: 2 = 128B, 4 = 64B, 6 = 32B.
-__device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr, uint32_t sbo, uint32_t layout)
-{
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3fff);
-    d |= (uint64_t)1 << 16;
-    d |= (uint64_t)((sbo >> 4) & 0x3fff) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)(layout & 7u) << 61;
-    return d;
-}
-
-// Epilogue for row-major fp32 outputs with the identity mapping and no read-modify-write: per 32 raw columns a lane applies
-// bias / GELU / GLU to its own row, the warp assembles the 32 x (32 | 16) tile in shared memory -- 16-byte pieces XOR-placed
-// as the tensor map's swizzle expects, so the stores do not collide on banks -- and lane 0 hands it to ONE tensor-map store;
-// rows past the end of the line (and columns past N) are clipped by the map.  Two tiles per warp alternate.
-__device__ __forceinline__ void epilogue_tile_tmast(const GemmParams &p, const CUtensorMap *tmC, const int bn, const int n0,
-                                                    const uint32_t lane_addr, const RowInfo &ri, uint8_t *stage, const int c_begin,
-                                                    const int c_step, const int lane, const int v_row0, const int line, int &parity)
-{
-    const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N;
-    const bool valid = ri.item >= 0;
-    double st_s = 0.0, st_ss = 0.0;
-    const int npc = p.glu ? 4 : 8;                         // 16-byte pieces per staged row
-    const int rowb = npc * 16;
-    const int sw = p.glu ? ((lane >> 1) & 3) : (lane & 7); // SWIZZLE_64B / SWIZZLE_128B phase of this lane's row
-    for (int c0 = c_begin; c0 < bn; c0 += c_step)
-    {
-        const int rawc0 = n0 + c0;
-        if (rawc0 >= ntile_end)
-            break;
-        float v[32];
-        tmem_ld32(lane_addr + (uint32_t)c0, v);
-        const int nraw = (ntile_end - rawc0) < 32 ? (ntile_end - rawc0) : 32;
-        if (p.bias)
-        {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-                if (j < nraw)
-                {
-                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc0 + j));
-                    v[j] += b.x;
-                    v[j + 1] += b.y;
-                    v[j + 2] += b.z;
-                    v[j + 3] += b.w;
-                }
-        }
-        if (p.act == 1)
-        {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                v[j] = gelu_erf(v[j]);
-        }
-        int nout = nraw;
-        if (p.glu)
-        {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-                v[j] = v[2 * j] * sigmoid_ref(v[2 * j + 1]);
-            nout = nraw >> 1;
-        }
-        // GLU tiles are 2 KB: two of them alternate; a plain 4 KB tile waits for its own previous store
-        uint8_t *buf = stage + (p.glu ? parity * 2048 : 0);
-        parity ^= 1;
-        if (lane == 0)
-        {
-            if (p.glu)
-                bulk_wait_read1();
-            else
-                bulk_wait_read();
-        }
-        __syncwarp();
-        float rs = 0.f, rss = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-            if (j < npc)
-            {
-                *reinterpret_cast<float4 *>(buf + lane * rowb + ((j ^ sw) << 4)) =
-                    make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                if (4 * j < nout)
-                {
-                    rs += v[4 * j] + v[4 * j + 1] + v[4 * j + 2] + v[4 * j + 3];
-                    rss += v[4 * j] * v[4 * j] + v[4 * j + 1] * v[4 * j + 1] + v[4 * j + 2] * v[4 * j + 2] + v[4 * j + 3] * v[4 * j + 3];
-                }
-            }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0)
-        {
-            tma_store_3d(tmC, buf, p.glu ? (rawc0 >> 1) : rawc0, v_row0, line);
-            bulk_commit();
-        }
-        if (valid)
-        {
-            st_s += (double)rs;
-            st_ss += (double)rss;
-        }
-    }
-    if (p.stats)
-    {
-        const int item0 = __shfl_sync(0xffffffffu, ri.item, 0);
-        if (__all_sync(0xffffffffu, ri.item == item0))
-        {
-            for (int o = 16; o > 0; o >>= 1)
-            {
-                st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
-                st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
-            }
-            if (lane == 0 && item0 >= 0)
-            {
-                atomicAdd(&p.stats[2 * (size_t)item0 + 0], st_s);
-                atomicAdd(&p.stats[2 * (size_t)item0 + 1], st_ss);
-            }
-        }
-        else if (valid)
-        {
-            atomicAdd(&p.stats[2 * (size_t)ri.item + 0], st_s);
-            atomicAdd(&p.stats[2 * (size_t)ri.item + 1], st_ss);
-        }
-    }
-}
-
 // umma with the descriptors given as (lo, hi) words: the issuing thread only adds to the lo words between instructions
 __device__ __forceinline__ void umma_lh(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
                                         uint32_t accum)
@@ -1685,7 +1725,7 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
         RowInfo *rowinfo = row_smem + warp * 32 - q * 32;
         const bool packed_direct = p.out_pack && plain_out == 1 && !p.glu && !p.gamma && !p.addC && !p.rowadd && !p.stats &&
                                    (p.N % 8) == 0;
-        const bool use_tmast = tma_store && bulk_ok(p, plain_out) && !p.gamma;
+        const bool use_tmast = tma_store && bulk_ok(p, plain_out);
         int parity = 0, itm = 0;
         for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++itm)
         {
@@ -1960,6 +2000,35 @@ size_t tc_packed_index(int K, int N, int k, int n)
     return (((size_t)nt * nkb + kb) * 8 + kr / 8) * ((size_t)bn * 8) + (size_t)nn * 8 + (kr % 8);
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn tma_encoder();
+// Tensor map of a row-major fp32 output for the store epilogue: (columns, positions of a line, lines), tiles of 32 rows x 16
+// columns, SWIZZLE_64B.  Returns 0 and sets *ok when the mapping qualifies.
+static int make_store_map(const GemmParams &p, int nout, int vout, long long lines, CUtensorMap *tm, int *ok)
+{
+    *ok = 0;
+    memset(tm, 0, sizeof *tm);
+    static const bool off = getenv("DMX_TMA_NO_STORE") != nullptr;
+    EncodeTiledFn enc = tma_encoder();
+    if (off || !enc || p.addC || p.rowadd || p.out_pack || p.out_bf16 || p.Cbf || (p.N % (p.glu ? 8 : 4)) != 0 || (p.ldc % 4) != 0)
+        return 0;
+    const cuuint64_t dims[3] = {(cuuint64_t)nout, (cuuint64_t)vout, (cuuint64_t)lines};
+    const cuuint64_t strides[2] = {(cuuint64_t)p.ldc * 4, (cuuint64_t)vout * p.ldc * 4};
+    const cuuint32_t box[3] = {16, 32, 1};
+    const cuuint32_t es[3] = {1, 1, 1};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, p.C, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+    {
+        set_error("cuTensorMapEncodeTiled (output) failed (" + std::to_string((int)r) + ")");
+        return -1;
+    }
+    *ok = 1;
+    return 0;
+}
+
 template <int STAGES> static int tc_set_attr()
 {
     const int max_smem = 227 * 1024 - 8 * 1024;
@@ -2004,8 +2073,17 @@ static int tc_launch_persist(const GemmParams &q, const __nv_bfloat16 *w, int bn
     const int smem = (int)(fixed + (size_t)stages * stage_bytes);
     const int total = mtiles * ntiles;
     const int grid = total < sms ? total : sms;
+    CUtensorMap tmc;
+    int tma_store = 0;
+    if (plain == 1 && !HALO)
+    {
+        if (make_store_map(q, q.glu ? q.N / 2 : q.N, q.M, 1, &tmc, &tma_store))
+            return -1;
+    }
+    else
+        memset(&tmc, 0, sizeof tmc);
     tc::gemm_tc_persist_kernel<VECA, HALO, PROD>
-        <<<grid, tc::p_threads(PROD), smem, st>>>(q, w, bn, plain, stages, mtiles, ntiles);
+        <<<grid, tc::p_threads(PROD), smem, st>>>(tmc, q, w, bn, plain, stages, mtiles, ntiles, tma_store);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -2017,10 +2095,19 @@ static int tc_launch(const GemmParams &p, const __nv_bfloat16 *w, int bn, bool v
     int smem = STAGES * (tc::A_STAGE + bn * tc::BK * 2);
     if (smem < tc::EPI_BYTES)
         smem = tc::EPI_BYTES; // the epilogue stages its transposition in the pipeline buffers
-    if (vec)
-        tc::gemm_tc_kernel<STAGES, true, false><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
+    CUtensorMap tmc;
+    int tma_store = 0;
+    if (plain == 1)
+    {
+        if (make_store_map(p, p.glu ? p.N / 2 : p.N, p.M, 1, &tmc, &tma_store))
+            return -1;
+    }
     else
-        tc::gemm_tc_kernel<STAGES, false, false><<<grid, tc::THREADS, smem, st>>>(p, w, bn, plain);
+        memset(&tmc, 0, sizeof tmc);
+    if (vec)
+        tc::gemm_tc_kernel<STAGES, true, false><<<grid, tc::THREADS, smem, st>>>(tmc, p, w, bn, plain, tma_store);
+    else
+        tc::gemm_tc_kernel<STAGES, false, false><<<grid, tc::THREADS, smem, st>>>(tmc, p, w, bn, plain, tma_store);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -2108,7 +2195,16 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
             const int items = p.M / (p.Uo * p.Vo);
             dim3 grid(items * p.Uo * q.halo_tpr, (p.N + bn - 1) / bn);
             const int smem = (int)std::max(total, (size_t)tc::EPI_BYTES);
-            tc::gemm_tc_kernel<2, true, true><<<grid, tc::THREADS, smem, st>>>(q, w, bn, plain | vscat);
+            CUtensorMap tmc;
+            int tma_store = 0;
+            if (plain == 1)
+            {
+                if (make_store_map(q, nout, p.Vo, (long long)items * p.Uo, &tmc, &tma_store))
+                    return -1;
+            }
+            else
+                memset(&tmc, 0, sizeof tmc);
+            tc::gemm_tc_kernel<2, true, true><<<grid, tc::THREADS, smem, st>>>(tmc, q, w, bn, plain | vscat, tma_store);
             DMX_LAUNCH_CHECK();
             return 0;
         }
@@ -2229,9 +2325,6 @@ int tc_tma_korig(const TmaPlan &pl, int Cin, int kp)
     return pl.tap_id[b * pl.tpb + k] * Cin + (qg * pl.cps + qi) * pl.kw + cc;
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn tma_encoder()
 {
     static EncodeTiledFn fn = nullptr;
@@ -2445,25 +2538,14 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
     const size_t smem = fixed + (size_t)b_stages * b_stage + (size_t)a_slots * slot_bytes;
     // tensor map of the output for the store epilogue: (columns, positions of a line, lines)
     CUtensorMap tmc;
-    memset(&tmc, 0, sizeof tmc);
     int tma_store = 0;
-    if (plain == 1 && !no_tmast && !p.addC && !p.rowadd && !p.out_pack && !p.out_bf16 && !p.Cbf && !p.gamma &&
-        (p.N % (p.glu ? 8 : 4)) == 0)
+    if (plain == 1 && !no_tmast)
     {
-        const cuuint64_t dims[3] = {(cuuint64_t)nout, (cuuint64_t)p.Vout, (cuuint64_t)items * p.Uout};
-        const cuuint64_t strides[2] = {(cuuint64_t)p.ldc * 4, (cuuint64_t)p.Vout * p.ldc * 4};
-        const cuuint32_t box[3] = {(cuuint32_t)(p.glu ? 16 : 32), 32, 1};
-        const cuuint32_t es[3] = {1, 1, 1};
-        const CUresult r = enc(&tmc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, p.C, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                               p.glu ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS)
-        {
-            set_error("launch_gemm_tma: cuTensorMapEncodeTiled (output) failed (" + std::to_string((int)r) + ")");
+        if (make_store_map(p, nout, p.Vout, (long long)items * p.Uout, &tmc, &tma_store))
             return -1;
-        }
-        tma_store = 1;
     }
+    else
+        memset(&tmc, 0, sizeof tmc);
     const int npairs = (mtiles + G - 1) / G;
     const int total = npairs * ntiles;
     const int grid = total < sms ? total : sms;
