@@ -126,7 +126,8 @@ int launch_normalize_input(float *x, int B, size_t n_per_item, const double *sta
                            cudaStream_t st);
 // DConv tail: x[r][c] += scale[c] * GN(y)[r][c] * sigmoid(GN(y)[r][c+C])  (src/layers.cpp:240-253)
 int launch_gn_glu_residual(const float *y, float *x, int B, int U, int V, int C, const double *stats,
-                           int per_u, const float *gw, const float *gb, const float *scale, cudaStream_t st);
+                           int per_u, const float *gw, const float *gb, const float *scale, cudaStream_t st,
+                           void *img = nullptr, int img_ld = 0);
 // LayerNorm writing TILE-PACKED bf16 (the tcgen05 GEMM's A image, see GemmParams::Apk) instead of fp32 rows
 int launch_layer_norm_pack(const float *x, void *ypk, int rows, int C, const float *w, const float *b, cudaStream_t st);
 // LayerNorm over the last dim (unbiased var), optional additive table add[row % add_rows][c]
@@ -147,7 +148,9 @@ bool dconv_mma_supported(int C, int hid, int V);
 int dconv_mma_init_device();
 int dconv_mma_pack_floats(int C, int hid);
 void dconv_mma_pack(int C, int hid, const float *blk, float *out);
-int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st);
+// img (optional, bf16 mode): the finished x also leaves as a bf16 channels-last image with img_ld channels per row
+int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st, void *img = nullptr,
+                     int img_ld = 0);
 bool dconv_mma_rw_supported(int C, int hid, int V);
 int dconv_mma_rw_pack_floats(int C);
 void dconv_mma_rw_pack(int C, const float *W, const float *bias, float *out);
@@ -157,7 +160,7 @@ int launch_dconv_mma_rw(float *x, const void *packed, const void *rw, float *out
                         int C, int hid, const float *spec, const void *cin, cudaStream_t st);
 bool dconv_time_mma_supported(int C, int hid, int hs);
 int launch_dconv_time_mma(float *x, float *hbuf, const void *packed, int B, int L, int C, int hid, int hs,
-                          double *const *stats, cudaStream_t st);
+                          double *const *stats, cudaStream_t st, void *img = nullptr, int img_ld = 0);
 
 // ---------------------------------------------------------------------------------------------
 // v3_kernels.cu (hdemucs_mmi)

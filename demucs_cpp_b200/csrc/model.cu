@@ -184,12 +184,13 @@ int model_finalize(dmx_model *m)
         m->tdec[i].Cout = cout_t;
         // 3x3 rewrite weight (2C, C, 3, 3): tap = kh*3 + kw with kh along frequency, kw along frames
         const TmaPlan plf = rewrite_plan(C, true), plt = rewrite_plan(C, false);
+        const TmaPlan pcf = convtr_plan(C, true), pct = convtr_plan(C, false);
         if (pack_conv(m, m->dec[i].rewrite, dn + ".rewrite.weight", dn + ".rewrite.bias", 2 * C, C, 9, true, &plf) ||
             pack_dconv(m, m->dec[i].dc, dn, C) ||
-            pack_convtr(m, m->dec[i].convtr, dn + ".conv_tr.weight", dn + ".conv_tr.bias", C, cout_f) ||
+            pack_convtr(m, m->dec[i].convtr, dn + ".conv_tr.weight", dn + ".conv_tr.bias", C, cout_f, 8, &pcf) ||
             pack_conv(m, m->tdec[i].rewrite, tn + ".rewrite.weight", tn + ".rewrite.bias", 2 * C, C, 3, true, &plt) ||
             pack_dconv(m, m->tdec[i].dc, tn, C) ||
-            pack_convtr(m, m->tdec[i].convtr, tn + ".conv_tr.weight", tn + ".conv_tr.bias", C, cout_t))
+            pack_convtr(m, m->tdec[i].convtr, tn + ".conv_tr.weight", tn + ".conv_tr.bias", C, cout_t, 8, &pct))
             return -1;
     }
     {
@@ -284,6 +285,11 @@ int model_finalize(dmx_model *m)
     rc |= A(&m->meanstd_x, 2);
     rc |= A(&m->meanstd_t, 2);
     m->use_tma = tc_tma_available();
+    if (m->use_tma)
+    {
+        rc |= dev_alloc(m, &m->cimg_f, B * (size_t)512 * T * 64 * 2);
+        rc |= dev_alloc(m, &m->cimg_t, B * (size_t)TLEN0 * 64 * 2);
+    }
     if (m->use_tma)
         for (int i = 0; i < 4 && !rc; ++i)
         {
@@ -511,6 +517,8 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     // bf16 mode: the decoders' rewrite convolutions run on the TMA-fed kernel whenever the (x + skip) image exists
     const bool tma = m->use_tma && m->precision == DMX_PRECISION_BF16;
     const void *img_f = nullptr, *img_t = nullptr;
+    static const bool tma_ct_env = getenv("DMX_TMA_CONVTR") != nullptr;
+    const bool tma_ct = tma && tma_ct_env;
     if (m->arch == DMX_ARCH_HTDEMUCS_4S)
     {
         GemmParams pd = f.linear(m->xq, d, m->down, m->x3d, 384, TF), pdt = f.linear(m->tq, d, m->down_t, m->xt3d, 384, TT);
@@ -561,9 +569,17 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             p.glu = 1;
             p.Nco = C;
             f.gemm(p, PC_GEMM_CONV);
-            f.dconv(m->cA_f, F, T, fd.dc, m->h_f, m->y2_f, 1);
+            // (the transposed convolutions can run on the TMA-fed kernel too, but they are bound by their scatter epilogue and
+            // the DConv kernels' extra bf16 image stores cost more than the operand path saves: 41.3 -> 42.4 ms/step; off)
+            const bool cimg = f.dconv(m->cA_f, F, T, fd.dc, m->h_f, m->y2_f, 1, tma_ct ? m->cimg_f : nullptr, tc_tma_cpitch(C));
             // ConvTranspose k(8,1) s(4,1) along frequency as a 2-tap GEMM, crop [2, 2+4F)
             GemmParams q = f.base(m->cA_f, C, C, fd.convtr, m->dx[i], fd.Cout, F, T, F + 1, T);
+            if (cimg && fd.convtr.Wt)
+            {
+                q.Aimg = m->cimg_f;
+                q.Aimg_ld = tc_tma_cpitch(C);
+                q.Wt = fd.convtr.Wt;
+            }
             q.ntaps = 2;
             q.du[0] = -1;
             q.du[1] = 0;
@@ -606,8 +622,14 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             p.glu = 1;
             p.Nco = C;
             f.gemm(p, PC_GEMM_CONV);
-            f.dconv(m->cA_t, 1, Lin, td.dc, m->h_t, m->y2_t, 0);
+            const bool cimg = f.dconv(m->cA_t, 1, Lin, td.dc, m->h_t, m->y2_t, 0, tma_ct ? m->cimg_t : nullptr, tc_tma_cpitch(C));
             GemmParams q = f.base(m->cA_t, C, C, td.convtr, m->dxt[i], td.Cout, 1, Lin, 1, Lin + 1);
+            if (cimg && td.convtr.Wt)
+            {
+                q.Aimg = m->cimg_t;
+                q.Aimg_ld = tc_tma_cpitch(C);
+                q.Wt = td.convtr.Wt;
+            }
             q.ntaps = 2;
             q.dv[0] = -1;
             q.dv[1] = 0;

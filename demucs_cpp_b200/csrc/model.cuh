@@ -159,6 +159,7 @@ struct dmx_model
     // bf16 channels-last images of the decoder inputs (x + skip), written by the producing epilogue and read by the
     // TMA-fed rewrite convolutions: [0] = bottleneck + skip, [i] = output of transposed conv i-1 + skip
     void *dimg_f[4] = {nullptr, nullptr, nullptr, nullptr}, *dimg_t[4] = {nullptr, nullptr, nullptr, nullptr};
+    void *cimg_f = nullptr, *cimg_t = nullptr; // ... of the DConv results that feed the transposed convolutions
     bool use_tma = false;
     float *h_f, *y2_f, *h_t, *y2_t;
     float *up_f, *up_tt, *xq, *tq, *ln_f, *ln_t, *kn_f, *kn_t, *qkv_f, *qkv_t, *kv_f, *kv_t, *ao_f, *ao_t, *ff_f,

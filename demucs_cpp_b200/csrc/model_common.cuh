@@ -161,7 +161,7 @@ static TmaPlan rewrite_plan(int C, bool freq)
 // (x[i-1] with kernel index r+stride, x[i] with kernel index r), N = stride*Cout columns n = r*Cout + co
 // (src/conv.hpp:264-474 equivalent)
 static int pack_convtr(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cin, int Cout,
-                       int ksize = 8)
+                       int ksize = 8, const TmaPlan *tp = nullptr)
 {
     const HostTensor *w = get(m, wname, (size_t)Cin * Cout * ksize);
     const HostTensor *b = get(m, bname, Cout);
@@ -178,7 +178,18 @@ static int pack_convtr(dmx_model *m, Packed &p, const std::string &wname, const 
             const int kk = tap == 0 ? r + stride : r;
             return wd[((size_t)c * Cout + co) * ksize + kk];
         },
-        [=](int n) { return bd[n % Cout]; });
+        [=](int n) { return bd[n % Cout]; }, tp, Cin);
+}
+
+// The K order of the TMA-fed kernel for a transposed convolution as a two-tap GEMM: x[i - 1], x[i] along frequency
+// (two planes) or along time (one box, rows shifted by one)
+static TmaPlan convtr_plan(int C, bool freq)
+{
+    const int du[2] = {freq ? -1 : 0, 0}, dv[2] = {freq ? 0 : -1, 0};
+    TmaPlan pl;
+    static const bool share = getenv("DMX_TMA_NO_SHARE") == nullptr;
+    tc_tma_plan(2, du, dv, C, share, &pl);
+    return pl;
 }
 
 // Linear weight rows [row0, row0+N) of an (out, in) matrix -> B[in][n]
@@ -392,26 +403,30 @@ struct Fwd
 
     // DConv residual branch (src/layers.cpp:152-375) in place on x [B][U][V][C]; GroupNorm items are
     // frequency rows (per_u = 1) or whole batch elements (time branch, U = 1).
-    void dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u)
+    // img (bf16 mode): the result is also written as a bf16 channels-last image with img_ld channels per row (what the
+    // TMA-fed convolution that follows reads); returns whether the path taken wrote it.
+    bool dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u, void *img = nullptr, int img_ld = 0)
     {
         const int C = w.C, hid = w.hid, hidp = w.hidp;
         if (per_u && w.fused && dconv_fused_supported(C, hid, V))
         {
             if (rc)
-                return;
+                return false;
             // one HBM read + one write of x; MACs: 2 sub-blocks x (k3 conv + the 1x1 conv evaluated twice)
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          (double)B * U * V * C * 8.0);
             if (m->precision == DMX_PRECISION_BF16 && w.fused_pk && dconv_mma_supported(C, hid, V))
-                rc = launch_dconv_mma(x, w.fused_pk, B * U, C, hid, st);
-            else
-                rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
-            return;
+            {
+                rc = launch_dconv_mma(x, w.fused_pk, B * U, C, hid, st, img, img_ld);
+                return img != nullptr;
+            }
+            rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
+            return false;
         }
         if ((per_u || U == 1) && w.fused_pk && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
         {
             if (rc)
-                return;
+                return false;
             // bf16 mode, tiled form: three tensor-core launches per sub-block, y never stored.  GroupNorm items are
             // the batch elements (time branch) or the B*U frequency rows (the 192-channel level, too wide for the
             // row-resident kernel above)
@@ -419,8 +434,8 @@ struct Fwd
             double *sl[4] = {stat_slots(items), stat_slots(items), stat_slots(items), stat_slots(items)};
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          2.0 * (double)B * U * V * (3.0 * C + 3.0 * hidp) * 4.0, 6);
-            rc = launch_dconv_time_mma(x, h, w.fused_pk, items, V, C, hid, hidp, sl, st);
-            return;
+            rc = launch_dconv_time_mma(x, h, w.fused_pk, items, V, C, hid, hidp, sl, st, img, img_ld);
+            return img != nullptr;
         }
         const size_t items = (size_t)B * (per_u ? U : 1);
         for (int j = 0; j < 2; ++j)
@@ -450,9 +465,11 @@ struct Fwd
             if (!rc)
             {
                 ProfScope ps(m, PC_POINTWISE, 0.0, (double)B * U * V * C * 4.0 * 4.0);
-                rc = launch_gn_glu_residual(y2, x, B, U, V, C, s2, per_u, w.g2w[j], w.g2b[j], w.scale[j], st);
+                rc = launch_gn_glu_residual(y2, x, B, U, V, C, s2, per_u, w.g2w[j], w.g2b[j], w.scale[j], st, j == 1 ? img : nullptr,
+                                            img_ld);
             }
         }
+        return img != nullptr && m->precision == DMX_PRECISION_BF16;
     }
 
     void layer_norm(const float *x, float *y, int rows, int C, const float *w, const float *b, const float *add = nullptr,

@@ -128,7 +128,8 @@ __global__ void __launch_bounds__(256) gn_glu_residual_kernel(const float *__res
                                                               const double *__restrict__ stats, double count,
                                                               int per_u, const float *__restrict__ gw,
                                                               const float *__restrict__ gb,
-                                                              const float *__restrict__ scale, size_t total4)
+                                                              const float *__restrict__ scale, size_t total4,
+                                                              __nv_bfloat16 *__restrict__ img, int img_ld)
 {
     const int c4n = C / 4;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x)
@@ -151,11 +152,20 @@ __global__ void __launch_bounds__(256) gn_glu_residual_kernel(const float *__res
         xv.z += sc.z * (((a.z - mean) * rstd * wa.z + ba.z) * sigmoid_ref((g.z - mean) * rstd * wg.z + bg.z));
         xv.w += sc.w * (((a.w - mean) * rstd * wa.w + ba.w) * sigmoid_ref((g.w - mean) * rstd * wg.w + bg.w));
         *reinterpret_cast<float4 *>(x + row * (size_t)C + c) = xv;
+        if (img)
+        {
+            // the finished values also leave as the bf16 channels-last image the next convolution's tensor-map loads read
+            __nv_bfloat162 lo = __floats2bfloat162_rn(xv.x, xv.y), hi = __floats2bfloat162_rn(xv.z, xv.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t *>(&lo);
+            pk.y = *reinterpret_cast<uint32_t *>(&hi);
+            *reinterpret_cast<uint2 *>(img + row * (size_t)img_ld + c) = pk;
+        }
     }
 }
 
 int launch_gn_glu_residual(const float *y, float *x, int B, int U, int V, int C, const double *stats, int per_u,
-                           const float *gw, const float *gb, const float *scale, cudaStream_t st)
+                           const float *gw, const float *gb, const float *scale, cudaStream_t st, void *img, int img_ld)
 {
     if (C % 4)
     {
@@ -169,7 +179,7 @@ int launch_gn_glu_residual(const float *y, float *x, int B, int U, int V, int C,
     if (blocks > 148 * 16)
         blocks = 148 * 16;
     gn_glu_residual_kernel<<<(unsigned)blocks, 256, 0, st>>>(y, x, U * V, V, C, U, stats, count, per_u, gw, gb, scale,
-                                                             total4);
+                                                             total4, static_cast<__nv_bfloat16 *>(img), img_ld);
     DMX_LAUNCH_CHECK();
     return 0;
 }
