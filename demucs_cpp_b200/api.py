@@ -33,6 +33,7 @@ EXPORTS = [
     "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
     "dmx_debug_linear", "dmx_profile_sequence", "dmx_plan_block", "dmx_track_stats_device", "dmx_forward_block_device",
     "dmx_overlap_add_block_device", "dmx_model_sync", "dmx_separate_multi", "dmx_separate_bag", "dmx_debug_conv",
+    "dmx_separate_shifts", "dmx_model_set_layer_taps",
 ]
 
 
@@ -99,6 +100,8 @@ def lib():
         L.dmx_separate_multi.argtypes = [vp, ci, vp, i64, ci, vp, PROGRESS_FN, vp]
         L.dmx_separate_bag.argtypes = [vp, ci, vp, i64, vp, vp, PROGRESS_FN, vp]
         L.dmx_debug_conv.argtypes = [ci] * 7 + [vp] * 5 + [ci] * 3 + [vp, ci, vp]
+        L.dmx_separate_shifts.argtypes = [vp, vp, i64, vp, ci, vp, PROGRESS_FN, vp]
+        L.dmx_model_set_layer_taps.argtypes = [vp, ci]
         _lib = L
     return _lib
 
@@ -147,6 +150,10 @@ class DemucsModel:
         except Exception:
             pass
 
+    def set_layer_taps(self, on=True):
+        """Keep the transformer's token streams after norm_in and after every layer (taps x_ct_* / xt_ct_*)."""
+        _check(lib().dmx_model_set_layer_taps(self._h, 1 if on else 0), "dmx_model_set_layer_taps")
+
     def set_precision(self, precision):
         _check(lib().dmx_model_set_precision(self._h, precision), "dmx_model_set_precision")
 
@@ -189,6 +196,16 @@ class DemucsModel:
         else:
             fn = ctypes.cast(None, PROGRESS_FN)
         _check(lib().dmx_separate(self._h, _p(inter), L, int(shift_offset), _p(out), fn, None), "dmx_separate")
+        return np.ascontiguousarray(out.transpose(2, 1, 0))
+
+    def demucs_inference_shifts(self, audio, shift_offsets, cb=None):
+        """Upstream's `shifts > 1` mode (vendor/demucs/demucs/apply.py:187-199): the mean of demucs_inference over the given
+        shift offsets.  (2, L) -> (S, 2, L)."""
+        L, inter, out = _track_io(audio, self.nb_sources)
+        sh = (ctypes.c_int * len(shift_offsets))(*[int(x) for x in shift_offsets])
+        fn = PROGRESS_FN(lambda p, msg, _u: cb(p, msg.decode())) if cb is not None else ctypes.cast(None, PROGRESS_FN)
+        _check(lib().dmx_separate_shifts(self._h, _p(inter), L, sh, len(shift_offsets), _p(out), fn, None),
+               "dmx_separate_shifts")
         return np.ascontiguousarray(out.transpose(2, 1, 0))
 
     def demucs_inference_device(self, d_audio_ptr, n_frames, d_out_ptr, shift_offset=4033):

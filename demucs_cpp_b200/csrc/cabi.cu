@@ -232,9 +232,11 @@ void dmx_model_free(dmx_model *m)
         for (cudaStream_t s : {m->stream, m->stream2, m->stream_copy})
             if (s)
                 cudaStreamSynchronize(s);
+        if (m->stager)
+            stager_free(m->stager);
         for (void *p : m->allocs)
             cudaFree(p);
-        for (float *p : {m->d_audio, m->d_y, m->d_out, m->d_tail})
+        for (float *p : {m->d_audio, m->d_y, m->d_out, m->d_tail, m->d_acc})
             if (p)
                 cudaFree(p);
         for (cudaStream_t s : {m->stream, m->stream2, m->stream_copy})
@@ -340,6 +342,18 @@ int dmx_model_set_precision(dmx_model *m, int precision)
     std::lock_guard<std::mutex> lk(m->mtx);
     m->precision = precision;
     return model_zero_attention_pads(m);
+}
+
+int dmx_model_set_layer_taps(dmx_model *m, int on)
+{
+    if (!m)
+    {
+        set_error("dmx_model_set_layer_taps: null model");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(m->mtx);
+    m->layer_taps = on != 0;
+    return 0;
 }
 
 int dmx_num_segments(int64_t n_frames, int shift_offset) { return num_segments(n_frames, shift_offset); }
@@ -884,6 +898,37 @@ int dmx_separate_multi(dmx_model *const *models, int n_models, const float *audi
         return -1;
     }
     track_fire_progress(models[0], plans[0].n_segments, cb, user);
+    return 0;
+}
+
+int dmx_separate_shifts(dmx_model *m, const float *audio_lr, int64_t n_frames, const int *shift_offsets, int n_shifts, float *out,
+                        dmx_progress_fn cb, void *user)
+{
+    if (check_ready(m, "dmx_separate_shifts"))
+        return -1;
+    if (!audio_lr || !out || !shift_offsets || n_shifts < 1)
+    {
+        set_error("dmx_separate_shifts: bad argument");
+        return -1;
+    }
+    if (n_shifts == 1)
+        return dmx_separate(m, audio_lr, n_frames, shift_offsets[0], out, cb, user);
+    std::lock_guard<std::mutex> lk(m->mtx);
+    DMX_CUDA(cudaSetDevice(m->device));
+    const size_t n = (size_t)m->S * 2 * (size_t)n_frames;
+    if (grow(&m->d_audio, &m->cap_audio, (size_t)n_frames * 2) || grow(&m->d_out, &m->cap_out, n) ||
+        grow(&m->d_acc, &m->cap_acc, (n + 3) / 4 * 4))
+        return -1;
+    DMX_CUDA(cudaMemcpyAsync(m->d_audio, audio_lr, (size_t)n_frames * 2 * sizeof(float), cudaMemcpyHostToDevice, m->stream));
+    for (int k = 0; k < n_shifts; ++k)
+    {
+        // each pass reports its own 0..1 progress, like successive demucs_inference calls would
+        if (track_separate(m, m->d_audio, n_frames, shift_offsets[k], m->d_out, cb, user) ||
+            track_accumulate(m, m->d_acc, m->d_out, 1.0f / (float)n_shifts, (n + 3) / 4 * 4, k == 0))
+            return -1;
+    }
+    DMX_CUDA(cudaMemcpyAsync(out, m->d_acc, n * sizeof(float), cudaMemcpyDeviceToHost, m->stream));
+    DMX_CUDA(cudaStreamSynchronize(m->stream));
     return 0;
 }
 

@@ -496,6 +496,20 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     }
     f.layer_norm(tok_f, m->xq, B * TF, d, m->nin_w, m->nin_b, m->pe2d, TF);
     f.layer_norm(tok_t, m->tq, B * TT, d, m->nint_w, m->nint_b, m->pe1d, TT);
+    // per-layer test tier (the reference tests common_encoder_layer in isolation, test/test_layers.cpp:1973-2157): keep
+    // the token streams after norm_in and after every layer
+    auto keep_layer = [&](int slot) -> int {
+        if (!m->layer_taps)
+            return 0;
+        const size_t nf = (size_t)m->maxB * TF * d, nt = (size_t)m->maxB * TT * d;
+        if (!m->lt_f[slot] && (dev_alloc_t(m, &m->lt_f[slot], nf) || dev_alloc_t(m, &m->lt_t[slot], nt)))
+            return -1;
+        DMX_CUDA(cudaMemcpyAsync(m->lt_f[slot], m->xq, (size_t)B * TF * d * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        DMX_CUDA(cudaMemcpyAsync(m->lt_t[slot], m->tq, (size_t)B * TT * d * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        return 0;
+    };
+    if (keep_layer(0))
+        return -1;
     for (int i = 0; i < 5; ++i)
     {
         if (i % 2 == 0)
@@ -512,6 +526,8 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             f.tlayer(m->lay[i], m->xq, TF, m->kn_f, TT, m->ln_f, m->qkv_f, m->kv_f, m->ao_f, m->ff_f);
             f.tlayer(m->lay_t[i], m->tq, TT, m->kn_t, TF, m->ln_t, m->qkv_t, m->kv_t, m->ao_t, m->ff_t);
         }
+        if (f.rc || keep_layer(i + 1))
+            return -1;
     }
     const float *dec_in_f = m->xq, *dec_in_t = m->tq;
     // bf16 mode: the decoders' rewrite convolutions run on the TMA-fed kernel whenever the (x + skip) image exists
@@ -679,6 +695,13 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         set_tap(m, ("saved_" + si).c_str(), m->e[i], FREQS[i + 1], T, CH[i + 1]);
         set_tap(m, ("savedt_" + si).c_str(), m->te[i], 1, TLENS[i + 1], CH[i + 1]);
     }
+    if (m->layer_taps)
+        for (int i = 0; i < 6; ++i)
+        {
+            const std::string tag = i == 0 ? "in" : std::to_string(i - 1);
+            set_tap(m, ("x_ct_" + tag).c_str(), m->lt_f[i], 8, T, d);
+            set_tap(m, ("xt_ct_" + tag).c_str(), m->lt_t[i], 1, TLEN3, d);
+        }
     set_tap(m, "x_3_up", m->xq, 8, T, d);
     set_tap(m, "xt_3_up", m->tq, 1, TLEN3, d);
     const bool pre3 = tma && m->arch == DMX_ARCH_HTDEMUCS_4S; // x3d / xt3d hold value + skip (see above)

@@ -129,6 +129,12 @@ struct Tap
 
 } // namespace dmx
 
+namespace dmx
+{
+struct HostStager;              // track.cu: pinned ring + worker thread for pageable caller buffers
+void stager_free(HostStager *s);
+} // namespace dmx
+
 struct dmx_model
 {
     int arch = 0, S = 4, d_model = 512, device = 0, maxB = 1, precision = 0;
@@ -161,6 +167,9 @@ struct dmx_model
     void *dimg_f[4] = {nullptr, nullptr, nullptr, nullptr}, *dimg_t[4] = {nullptr, nullptr, nullptr, nullptr};
     void *cimg_f = nullptr, *cimg_t = nullptr; // ... of the DConv results that feed the transposed convolutions
     bool use_tma = false;
+    // test tier (dmx_model_set_layer_taps): copies of the token streams after norm_in and after every transformer layer
+    bool layer_taps = false;
+    float *lt_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, *lt_t[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     float *h_f, *y2_f, *h_t, *y2_t;
     float *up_f, *up_tt, *xq, *tq, *ln_f, *ln_t, *kn_f, *kn_t, *qkv_f, *qkv_t, *kv_f, *kv_t, *ao_f, *ao_t, *ff_f,
         *ff_t, *x3d, *xt3d;
@@ -172,10 +181,11 @@ struct dmx_model
     std::map<std::string, dmx::Tap> taps;
 
     // track-level buffers (grow only)
-    float *d_audio = nullptr, *d_y = nullptr, *d_out = nullptr;
-    size_t cap_audio = 0, cap_y = 0, cap_out = 0;
+    float *d_audio = nullptr, *d_y = nullptr, *d_out = nullptr, *d_acc = nullptr;
+    size_t cap_audio = 0, cap_y = 0, cap_out = 0, cap_acc = 0;
     double *track_stats = nullptr;
     float *d_tail = nullptr; // [S][SEG - SEG_STRIDE][2]: the previous worker's tail (dmx_separate_multi)
+    dmx::HostStager *stager = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr; // device time of the last track-level call
 };
 
@@ -212,6 +222,7 @@ int track_forward_block(dmx_model *m, const float *d_win, int64_t L, int shift, 
 int track_overlap_add_block(dmx_model *m, int64_t L, int shift, const dmx_block_plan &pl, const double *d_sums,
                             const float *d_y, const float *d_tail, int s_begin, int s_end, float *d_out_block);
 void track_fire_progress(dmx_model *m, int nseg, dmx_progress_fn cb, void *user);
+int track_accumulate(dmx_model *m, float *d_acc, const float *d_x, float scale, size_t n, int first);
 int track_separate_host(dmx_model *m, const float *h_audio, int64_t L, int shift, float *h_out, dmx_progress_fn cb,
                         void *user);
 } // namespace dmx

@@ -143,6 +143,14 @@ extern "C"
     int dmx_separate_bag(dmx_model *const *models, int n_models, const float *audio_lr, int64_t n_frames,
                          const int *shift_offsets, float *out, dmx_progress_fn cb, void *user);
 
+    /* ---- shift averaging ("shifts > 1"): the reference's shift_inference draws ONE random offset
+     *      (src/model_apply.cpp:93-138); upstream's apply_model averages several
+     *      (vendor/demucs/demucs/apply.py:187-199: out = mean over k of shift-k, separate, un-shift).  This entry
+     *      point is that opt-in mode: the mean over `n_shifts` passes of dmx_separate with the given offsets
+     *      (n_shifts = 1 is dmx_separate).  It also multiplies the independent work units of a track by n_shifts. ---- */
+    int dmx_separate_shifts(dmx_model *m, const float *audio_lr, int64_t n_frames, const int *shift_offsets, int n_shifts,
+                            float *out, dmx_progress_fn cb, void *user);
+
     /* Device milliseconds (CUDA events on the model's stream) of the last separate / shard / overlap-add call. */
     double dmx_last_device_ms(dmx_model *m);
 
@@ -160,6 +168,12 @@ extern "C"
      * dmx_forward_segments call to the host.  dims[4] receives (B, d1, d2, C) of the channels-last
      * device layout; returns the element count, or -1.  With dst == NULL only dims are filled. */
     int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capacity, int64_t dims[4]);
+
+    /* Per-layer test tier (the reference tests one transformer layer at a time, common_encoder_layer src/layers.cpp:377-531
+     * in test/test_layers.cpp:1973-2157): when switched on, every forward also keeps the token streams after norm_in +
+     * positional embedding (taps "x_ct_in", "xt_ct_in") and after each of the five layers ("x_ct_0" .. "x_ct_4",
+     * "xt_ct_0" .. "xt_ct_4") for dmx_debug_tap.  htdemucs only; costs device copies, so it is off by default. */
+    int dmx_model_set_layer_taps(dmx_model *m, int on);
 
     /* Test hook for the GEMM kernels in isolation (stands in for the reference's GemmConv* tests,
      * test/test_layers.cpp:856-1387): out (M,N) = act(A (M,K) x W (N,K)^T + bias) through the production

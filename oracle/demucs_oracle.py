@@ -275,10 +275,12 @@ def transformer_layer(W, p, q, k, cross):
     return (q - m) / torch.sqrt(v + 1e-5) * W[p + "norm_out.weight"] + W[p + "norm_out.bias"]
 
 
-def crosstransformer(W, x, xt):
+def crosstransformer(W, x, xt, taps=None):
     """demucscpp::apply_crosstransformer (src/crosstransformer.cpp:205-339).
     x: (C, Fr, T1) freq branch, xt: (C, T2) time branch; returns same shapes.
-    Freq tokens are ordered t*Fr + f (:227-238)."""
+    Freq tokens are ordered t*Fr + f (:227-238).  With `taps`, the token streams after norm_in + positional
+    embedding ("x_ct_in", "xt_ct_in") and after each of the five layers ("x_ct_<i>", "xt_ct_<i>": the output of
+    common_encoder_layer, src/layers.cpp:377-531) are kept, freq as (C, Fr, T1), time as (1, C, T2)."""
     C, Fr, T1 = x.shape
     dt = x.dtype
     pe2 = sin_embedding_2d(C, Fr, T1, dt).permute(2, 1, 0).reshape(T1 * Fr, C)
@@ -287,6 +289,13 @@ def crosstransformer(W, x, xt):
     tq = xt.T
     tq = layer_norm(tq, W["crosstransformer.norm_in_t.weight"], W["crosstransformer.norm_in_t.bias"]) \
         + sin_embedding_1d(tq.shape[0], C, dt)
+
+    def keep(tag):
+        if taps is not None:
+            taps["x_ct_" + tag] = xq.reshape(T1, Fr, C).permute(2, 1, 0).clone()
+            taps["xt_ct_" + tag] = tq.T[None].clone()
+
+    keep("in")
     for idx in range(5):
         pf = "crosstransformer.layers.%d." % idx
         pt = "crosstransformer.layers_t.%d." % idx
@@ -297,6 +306,7 @@ def crosstransformer(W, x, xt):
             old = xq
             xq = transformer_layer(W, pf, xq, tq, True)
             tq = transformer_layer(W, pt, tq, old, True)
+        keep(str(idx))
     return xq.reshape(T1, Fr, C).permute(2, 1, 0), tq.T
 
 
@@ -335,7 +345,7 @@ def segment_forward(W, mix, taps=None):
     if W.is_4s:                                                          # :214-287
         x = torch.einsum("oc,cft->oft", W["channel_upsampler.weight"], x) + W["channel_upsampler.bias"][:, None, None]
         xt = W["channel_upsampler_t.weight"] @ xt + W["channel_upsampler_t.bias"][:, None]
-    x, xt = crosstransformer(W, x, xt)
+    x, xt = crosstransformer(W, x, xt, taps)
     if W.is_4s:
         tp["x_3_up"], tp["xt_3_up"] = x, xt[None]
         x = torch.einsum("oc,cft->oft", W["channel_downsampler.weight"], x) + W["channel_downsampler.bias"][:, None, None]

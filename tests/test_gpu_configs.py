@@ -209,3 +209,62 @@ def test_separate_multi_one_process():
         out = api.demucs_inference_multi(reps, audio, cb=lambda p, msg: calls.append(p), shift_offset=4033)
         assert util.max_rel_err(out, ref) <= 1e-5 and util.snr_db(out, ref) >= 100.0
         assert len(calls) == api.num_segments(60 * SR, 4033) * 26 and abs(calls[-1] - 1.0) < 1e-6
+
+
+# ------------------------------------------------------------------------------ per-layer tier (transformer)
+@pytest.mark.parametrize("arch,precision", [("htdemucs_4s", api.PRECISION_FP32), ("htdemucs_6s", api.PRECISION_FP32),
+                                            ("htdemucs_4s", api.PRECISION_BF16)])
+def test_transformer_layer_by_layer(arch, precision):
+    """The reference tests one transformer layer at a time (common_encoder_layer, src/layers.cpp:377-531, in
+    test/test_layers.cpp:1973-2157; norms :2159-2234).  Here: the token streams after norm_in + positional embedding and
+    after EACH of the five self / cross layers of both branches, for 4s (d = 512, with up / down-samplers) and 6s (d = 384),
+    stress weights (LayerScale 0.3, so attention and FFN branches count), against the oracle's per-layer values."""
+    m = model(arch, True, 1, precision)
+    m.set_layer_taps(True)
+    seg = util.synth_audio(util.SEG, seed=23)
+    m.model_inference(seg[None])
+    ot = {}
+    with torch.no_grad():
+        O.segment_forward(oracle_weights(arch, 0, True), torch.from_numpy(seg), ot)
+    tol = TOL_FP32 if precision == api.PRECISION_FP32 else TOL_BF16
+    for tag in ["in"] + [str(i) for i in range(5)]:
+        for name in ("x_ct_" + tag, "xt_ct_" + tag):
+            got = util.tap_to_cfirst(m.tap(name))[0]
+            ref = util.oracle_tap_to_cfirst(name, ot[name].numpy())
+            err = util.max_rel_err(got, ref)
+            assert err <= tol, "%s: max rel err %.3e" % (name, err)
+    m.set_layer_taps(False)
+    drop_models()
+
+
+# ------------------------------------------------------------------------------ shifts > 1, host buffer kinds
+def test_shift_averaging_matches_oracle():
+    """dmx_separate_shifts = upstream's `shifts` option (vendor/demucs/demucs/apply.py:187-199): the mean of the
+    single-shift separations.  Against the mean of the oracle's demucs_inference over the same offsets."""
+    shifts = (4033, 12436, 7)
+    audio = util.synth_audio(300000, seed=29)
+    m = model(max_batch=4)
+    out = m.demucs_inference_shifts(audio, shifts)
+    own = np.mean([m.demucs_inference(audio, shift_offset=s) for s in shifts], axis=0)
+    assert util.max_rel_err(out, own) <= 1e-6
+    W = oracle_weights("htdemucs_4s")
+    with torch.no_grad():
+        ref = np.mean([O.separate(W, audio, s).numpy() for s in shifts], axis=0)
+    assert util.snr_db(out, ref) >= SNR_FP32 and util.max_rel_err(out, ref) <= TOL_FP32
+
+
+def test_pageable_and_pinned_host_buffers_agree():
+    """dmx_separate copies pinned caller buffers directly and stages ordinary (pageable) ones -- what the reference's CLIs
+    hold, cli-apps/demucs.cpp:162-230 -- through its pinned ring and worker thread: same bytes either way."""
+    import ctypes
+    L = 45 * SR
+    audio = util.synth_audio(L, seed=31)
+    m = model(max_batch=4)
+    ref = m.demucs_inference(audio, shift_offset=4033)                  # numpy buffers: the staged path
+    h_in = torch.from_numpy(np.ascontiguousarray(audio.T)).pin_memory()
+    h_out = torch.empty((L, 2, 4), dtype=torch.float32).pin_memory()
+    rc = api.lib().dmx_separate(m._h, ctypes.c_void_p(h_in.data_ptr()), L, 4033, ctypes.c_void_p(h_out.data_ptr()),
+                                ctypes.cast(None, api.PROGRESS_FN), None)
+    assert rc == 0, api.last_error()
+    got = h_out.numpy().transpose(2, 1, 0)
+    assert util.max_rel_err(got, ref) <= 1e-6 and np.isfinite(got).all()
