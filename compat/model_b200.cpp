@@ -18,8 +18,9 @@ int env_int(const char *name, int dflt)
 
 std::shared_ptr<void> load(const std::string &path, int want_v3, bool *is4)
 {
-    // DEMUCS_DEVICE / DEMUCS_MAX_BATCH / DEMUCS_PRECISION (fp32 | bf16): the CLIs take positional arguments only
-    dmx_model *h = dmx_model_load_file(path.c_str(), env_int("DEMUCS_DEVICE", 0), env_int("DEMUCS_MAX_BATCH", 8));
+    // DEMUCS_DEVICE / DEMUCS_MAX_BATCH / DEMUCS_PRECISION (bf16 | fp32): the CLIs take positional arguments only.  Defaults
+    // are the benchmarked configuration: bf16 tensor-core mode (stems >= 40 dB vs the reference), 16 segments per launch.
+    dmx_model *h = dmx_model_load_file(path.c_str(), env_int("DEMUCS_DEVICE", 0), env_int("DEMUCS_MAX_BATCH", 16));
     if (!h)
     {
         std::cerr << "load_demucs_model: " << dmx_last_error() << std::endl;
@@ -33,7 +34,7 @@ std::shared_ptr<void> load(const std::string &path, int want_v3, bool *is4)
         return nullptr;
     }
     const char *prec = std::getenv("DEMUCS_PRECISION");
-    if (prec && std::string(prec) == "bf16")
+    if (!prec || std::string(prec) != "fp32")
         dmx_model_set_precision(h, DMX_PRECISION_BF16);
     if (is4)
         *is4 = dmx_model_sources(h) == 4;
