@@ -5,8 +5,10 @@
 
 #include "demucs_b200.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <iostream>
+#include <vector>
 
 namespace
 {
@@ -15,6 +17,18 @@ int env_int(const char *name, int dflt)
     const char *v = std::getenv(name);
     return v ? std::atoi(v) : dflt;
 }
+
+// The device-side state behind a demucs_model: the model on GPU DEMUCS_DEVICE and, with DEMUCS_NGPU = n > 1, replicas on the
+// next n - 1 GPUs; demucs_inference then splits every track over them (dmx_separate_multi).
+struct Handle
+{
+    std::vector<dmx_model *> reps;
+    ~Handle()
+    {
+        for (dmx_model *h : reps)
+            dmx_model_free(h);
+    }
+};
 
 std::shared_ptr<void> load(const std::string &path, int want_v3, bool *is4)
 {
@@ -38,7 +52,24 @@ std::shared_ptr<void> load(const std::string &path, int want_v3, bool *is4)
         dmx_model_set_precision(h, DMX_PRECISION_BF16);
     if (is4)
         *is4 = dmx_model_sources(h) == 4;
-    return std::shared_ptr<void>(h, [](void *p) { dmx_model_free(static_cast<dmx_model *>(p)); });
+    Handle *hd = new Handle();
+    hd->reps.push_back(h);
+    const int ngpu = std::min(env_int("DEMUCS_NGPU", 1), dmx_device_count());
+    for (int r = 1; r < ngpu; ++r)
+    {
+        dmx_model *rep = dmx_model_load_file(path.c_str(), (env_int("DEMUCS_DEVICE", 0) + r) % dmx_device_count(),
+                                             env_int("DEMUCS_MAX_BATCH", 16));
+        if (!rep)
+        {
+            std::cerr << "load_demucs_model (replica " << r << "): " << dmx_last_error() << std::endl;
+            delete hd;
+            return nullptr;
+        }
+        if (!prec || std::string(prec) != "fp32")
+            dmx_model_set_precision(rep, DMX_PRECISION_BF16);
+        hd->reps.push_back(rep);
+    }
+    return std::shared_ptr<void>(hd, [](void *p) { delete static_cast<Handle *>(p); });
 }
 
 void trampoline(float p, const char *msg, void *user)
@@ -48,7 +79,8 @@ void trampoline(float p, const char *msg, void *user)
 
 Eigen::Tensor3dXf separate(void *handle, const Eigen::MatrixXf &audio, demucscpp::ProgressCallback cb)
 {
-    dmx_model *h = static_cast<dmx_model *>(handle);
+    Handle *hd = static_cast<Handle *>(handle);
+    dmx_model *h = hd ? hd->reps[0] : nullptr;
     if (!h || audio.rows() != 2)
     {
         std::cerr << "demucs_inference: model not loaded or audio is not (2, L)" << std::endl;
@@ -58,7 +90,8 @@ Eigen::Tensor3dXf separate(void *handle, const Eigen::MatrixXf &audio, demucscpp
     Eigen::Tensor3dXf out(S, 2, audio.cols());
     const int offset = rand() % 22050; // src/model_apply.cpp:114 (unseeded glibc rand, like the reference)
     std::cout << "1., apply model w/ shift, offset: " << offset << std::endl;
-    if (dmx_separate(h, audio.data(), (int64_t)audio.cols(), offset, out.data(), cb ? trampoline : nullptr, &cb) != 0)
+    if (dmx_separate_multi(hd->reps.data(), (int)hd->reps.size(), audio.data(), (int64_t)audio.cols(), offset, out.data(),
+                           cb ? trampoline : nullptr, &cb) != 0)
     {
         std::cerr << "demucs_inference: " << dmx_last_error() << std::endl;
         std::exit(1);

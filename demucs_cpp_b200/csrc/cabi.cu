@@ -778,6 +778,9 @@ int dmx_separate_multi(dmx_model *const *models, int n_models, const float *audi
     }
     if (n_models == 1)
         return dmx_separate(models[0], audio_lr, n_frames, shift_offset, out, cb, user);
+    // one multi-GPU separation at a time: two calls' workers would otherwise take the replicas' locks in different orders
+    static std::mutex multi_mtx;
+    std::lock_guard<std::mutex> multi_lock(multi_mtx);
     const int W = n_models, S = models[0]->S;
     constexpr int TAIL = SEG - SEG_STRIDE;
     std::vector<dmx_block_plan> plans(W);

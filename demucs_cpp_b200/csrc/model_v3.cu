@@ -176,9 +176,10 @@ int model_v3_finalize(dmx_model *m)
         v->cdec[l].Cout = cout_f;
         v->ctdec[l].C = C;
         v->ctdec[l].Cout = cout_t;
-        if (pack_conv(m, v->cdec[l].rewrite, dn + ".rewrite.weight", dn + ".rewrite.bias", 2 * C, C, 9, true) ||
+        const TmaPlan plf = rewrite_plan(C, true), plt = rewrite_plan(C, false);
+        if (pack_conv(m, v->cdec[l].rewrite, dn + ".rewrite.weight", dn + ".rewrite.bias", 2 * C, C, 9, true, &plf) ||
             pack_convtr(m, v->cdec[l].convtr, dn + ".conv_tr.weight", dn + ".conv_tr.bias", C, cout_f) ||
-            pack_conv(m, v->ctdec[l].rewrite, tn + ".rewrite.weight", tn + ".rewrite.bias", 2 * C, C, 3, true) ||
+            pack_conv(m, v->ctdec[l].rewrite, tn + ".rewrite.weight", tn + ".rewrite.bias", 2 * C, C, 3, true, &plt) ||
             pack_convtr(m, v->ctdec[l].convtr, tn + ".conv_tr.weight", tn + ".conv_tr.bias", C, cout_t))
             return -1;
     }
@@ -216,6 +217,13 @@ int model_v3_finalize(dmx_model *m)
         rc |= A(&m->te[i], (size_t)TLENS[i + 1] * CH[i + 1]);
         rc |= A(&m->dx[i], (size_t)FREQS[3 - i] * T * v->cdec[i].Cout);
         rc |= A(&m->dxt[i], (size_t)TLENS[3 - i] * v->ctdec[i].Cout);
+        if (i > 0 && tc_tma_available())
+        {
+            // bf16 images of the common decoders' inputs (transposed conv i-1 + skip), read by the TMA-fed rewrite convolutions
+            m->use_tma = true;
+            rc |= dev_alloc(m, &m->dimg_f[i], B * (size_t)FREQS[4 - i] * T * tc_tma_cpitch(CH[4 - i]) * 2);
+            rc |= dev_alloc(m, &m->dimg_t[i], B * (size_t)TLENS[4 - i] * tc_tma_cpitch(CH[4 - i]) * 2);
+        }
     }
     rc |= A(&m->h_f, (size_t)512 * T * 12);
     rc |= A(&m->y2_f, (size_t)512 * T * 96);
@@ -575,6 +583,8 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     }
     // ---- common decoders, no DConv (src/encdec.cpp:728-863) ----
     const float *dec_in_f = v->x3, *dec_in_t = v->xt3;
+    const bool tma = m->use_tma && m->precision == DMX_PRECISION_BF16;
+    const void *img_f = nullptr, *img_t = nullptr;
     if (fork())
         return -1;
     for (int i = 0; i < 4; ++i)
@@ -587,6 +597,12 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             GemmParams p = f.base(dec_in_f, C, C, fd.rewrite, m->cA_f, C, F, T, F, T);
             if (i == 0)
                 p.A2 = m->e[3]; // later decoders find their skip already added by the previous convT's epilogue
+            if (img_f && fd.rewrite.Wt)
+            {
+                p.Aimg = img_f;
+                p.Aimg_ld = tc_tma_cpitch(C);
+                p.Wt = fd.rewrite.Wt;
+            }
             p.ntaps = 9;
             for (int kh = 0; kh < 3; ++kh)
                 for (int kw = 0; kw < 3; ++kw)
@@ -610,6 +626,13 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.act = i < 3 ? 1 : 0;
             if (i < 3)
                 q.addC = m->e[2 - i]; // the next decoder's skip (src/encdec.cpp:172), added once here
+            img_f = nullptr;
+            if (tma && i < 3 && m->dimg_f[i + 1])
+            {
+                q.Cbf = m->dimg_f[i + 1];
+                q.Cbf_ld = tc_tma_cpitch(fd.Cout);
+                img_f = m->dimg_f[i + 1];
+            }
             f.gemm(q, PC_GEMM_CONV);
         }
         f.st = st_t;
@@ -617,6 +640,12 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             GemmParams p = f.base(dec_in_t, C, C, td.rewrite, m->cA_t, C, 1, Lin, 1, Lin);
             if (i == 0)
                 p.A2 = m->te[3];
+            if (img_t && td.rewrite.Wt)
+            {
+                p.Aimg = img_t;
+                p.Aimg_ld = tc_tma_cpitch(C);
+                p.Wt = td.rewrite.Wt;
+            }
             p.ntaps = 3;
             for (int t = 0; t < 3; ++t)
             {
@@ -640,6 +669,13 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.act = i < 3 ? 1 : 0;
             if (i < 3)
                 q.addC = m->te[2 - i];
+            img_t = nullptr;
+            if (tma && i < 3 && m->dimg_t[i + 1])
+            {
+                q.Cbf = m->dimg_t[i + 1];
+                q.Cbf_ld = tc_tma_cpitch(td.Cout);
+                img_t = m->dimg_t[i + 1];
+            }
             f.gemm(q, PC_GEMM_CONV);
         }
         dec_in_f = m->dx[i];

@@ -2,6 +2,8 @@
 // and LocalState attention.  All tensors channels-last fp32: [B][rows][C].
 #include "kernels.cuh"
 
+#include <cstdlib>
+
 #include <cooperative_groups.h>
 
 namespace dmx
@@ -199,13 +201,20 @@ constexpr int LSTM_BMAX = 8;
 template <int H>
 __global__ void __launch_bounds__(LSTM_THREADS, 1)
     lstm_cluster_kernel(const float *__restrict__ pre, const float *__restrict__ whh_fwd,
-                        const float *__restrict__ whh_bwd, float *__restrict__ out, int B, int T)
+                        const float *__restrict__ whh_bwd, float *__restrict__ out, int Btot, int T, int chunk)
 {
     constexpr int NC = H / LSTM_UNITS; // cluster size
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     const int crank = (int)cluster.block_rank();
-    const int dir = blockIdx.x / NC;
+    // cluster ci = (direction, chunk of `chunk` batch items): all chunks of the batch run at the same time on their
+    // own clusters instead of one after the other
+    const int ci = blockIdx.x / NC;
+    const int dir = ci & 1;
+    const int b0 = (ci >> 1) * chunk;
+    const int B = (Btot - b0) < chunk ? (Btot - b0) : chunk;
+    pre += (size_t)b0 * T * 2 * 4 * H;
+    out += (size_t)b0 * T * 2 * H;
     const float *W = dir == 0 ? whh_fwd : whh_bwd;
 
     __shared__ __align__(16) float hbuf[2][LSTM_BMAX][H];       // full hidden state of every batch item, double buffered
@@ -330,7 +339,7 @@ __global__ void __launch_bounds__(LSTM_THREADS, 1)
 }
 
 template <int H> static int lstm_cluster_launch(const float *pre, const float *whh_fwd, const float *whh_bwd, float *out,
-                                                int B, int T, cudaStream_t st)
+                                                int B, int T, int chunk, cudaStream_t st)
 {
     constexpr int NC = H / LSTM_UNITS;
     static bool attr_done = false; // per process; the attribute is per function, harmless to repeat per device
@@ -342,7 +351,7 @@ template <int H> static int lstm_cluster_launch(const float *pre, const float *w
     if (NC > 8)
         DMX_CUDA(cudaFuncSetAttribute(lstm_cluster_kernel<H>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * NC);
+    cfg.gridDim = dim3(2 * NC * ((B + chunk - 1) / chunk));
     cfg.blockDim = dim3(LSTM_THREADS);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = st;
@@ -353,7 +362,7 @@ template <int H> static int lstm_cluster_launch(const float *pre, const float *w
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    DMX_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<H>, pre, whh_fwd, whh_bwd, out, B, T));
+    DMX_CUDA(cudaLaunchKernelEx(&cfg, lstm_cluster_kernel<H>, pre, whh_fwd, whh_bwd, out, B, T, chunk));
     return 0;
 }
 
@@ -363,17 +372,15 @@ int launch_lstm_recurrent(const float *pre, const float *whh_fwd, const float *w
 {
     if (H == 192 || H == 384)
     {
-        // the cluster kernel keeps the hidden state of up to LSTM_BMAX items on chip: larger batches go in chunks
-        for (int b0 = 0; b0 < B; b0 += LSTM_BMAX)
-        {
-            const int nb = (B - b0) < LSTM_BMAX ? (B - b0) : LSTM_BMAX;
-            const float *pc = pre + (size_t)b0 * T * 2 * 4 * H;
-            float *oc = out + (size_t)b0 * T * 2 * H;
-            if (H == 192 ? lstm_cluster_launch<192>(pc, whh_fwd, whh_bwd, oc, nb, T, st)
-                         : lstm_cluster_launch<384>(pc, whh_fwd, whh_bwd, oc, nb, T, st))
-                return -1;
-        }
-        return 0;
+        // a cluster keeps the hidden state of up to LSTM_BMAX items on chip; the recurrence is a latency chain (one
+        // cluster barrier per step) that occupies 8 / 16 SMs per cluster, so the batch is cut into chunks of 4 items that
+        // all run AT THE SAME TIME on their own clusters (16 items: 8 clusters) rather than one after the other
+        static const int chunk_env = getenv("DMX_LSTM_CHUNK") ? atoi(getenv("DMX_LSTM_CHUNK")) : 0;
+        int chunk = (chunk_env >= 1 && chunk_env <= LSTM_BMAX) ? chunk_env : 4;
+        if (B < chunk)
+            chunk = B;
+        return H == 192 ? lstm_cluster_launch<192>(pre, whh_fwd, whh_bwd, out, B, T, chunk, st)
+                        : lstm_cluster_launch<384>(pre, whh_fwd, whh_bwd, out, B, T, chunk, st);
     }
     if (H > 1024)
     {
