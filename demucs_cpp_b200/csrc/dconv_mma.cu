@@ -128,7 +128,7 @@ template <int C, int HID, bool RW, bool CIN>
 __global__ void __launch_bounds__(THREADS, (C == 48 && HID == 6) ? 4 : 1)
     dconv_mma_kernel(float *__restrict__ x, const uint8_t *__restrict__ params, const uint8_t *__restrict__ rw,
                      float *__restrict__ out, const float *__restrict__ rowadd, const int F, const float *__restrict__ spec,
-                     const uint8_t *__restrict__ cin, __nv_bfloat16 *__restrict__ img, const int img_ld)
+                     const uint8_t *__restrict__ cin)
 {
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;       // n-tiles of the k3 conv
@@ -408,14 +408,6 @@ __global__ void __launch_bounds__(THREADS, (C == 48 && HID == 6) ? 4 : 1)
                         *r0 = x0;
                         *r1 = x1;
                     }
-                    if (!RW && img != nullptr && sub == 1)
-                    {
-                        // the finished row also leaves as bf16: the channels-last image the next convolution's tensor-map
-                        // loads read (row pitch img_ld channels)
-                        __nv_bfloat16 *ib = img + ((size_t)blockIdx.x * T + row) * img_ld + c;
-                        *reinterpret_cast<uint32_t *>(ib) = pack2(x0.x, x0.y);
-                        *reinterpret_cast<uint32_t *>(ib + (size_t)8 * img_ld) = pack2(x1.x, x1.y);
-                    }
                     if (RW || sub == 0)
                     {
                         *reinterpret_cast<uint32_t *>(xb + (row + HALO) * XLD + c) = pack2(x0.x, x0.y);
@@ -490,8 +482,7 @@ __global__ void __launch_bounds__(THREADS, (C == 48 && HID == 6) ? 4 : 1)
 template <int C, int HID, int PHASE, int MTW>
 __global__ void __launch_bounds__(THREADS)
     dconv_time_kernel(float *__restrict__ x, float *__restrict__ hbuf, const uint8_t *__restrict__ P, const int L, const int hs,
-                      const int dil, double *__restrict__ stats1, double *__restrict__ stats2, __nv_bfloat16 *__restrict__ img,
-                      const int img_ld)
+                      const int dil, double *__restrict__ stats1, double *__restrict__ stats2)
 {
     constexpr int HP = hid_pad(HID);
     constexpr int NT1 = HP / 8;
@@ -727,17 +718,12 @@ __global__ void __launch_bounds__(THREADS)
                 // contiguous bytes (whole sectors), no shared-memory copy of x and no block barrier in this phase
                 float2 *r0 = reinterpret_cast<float2 *>(xg + (size_t)(p0 + 16 * (warp + WARPS * i) + g) * C + c);
                 float2 *r1 = reinterpret_cast<float2 *>(reinterpret_cast<float *>(r0) + 8 * C);
-                // img (last sub-block only): the finished values also leave as the bf16 channels-last image that the next
-                // convolution's tensor-map loads read
-                const size_t ipos = (size_t)b * L + (size_t)(p0 + 16 * (warp + WARPS * i) + g);
                 if (v0[i])
                 {
                     float2 xv = *r0;
                     xv.x += sc0 * (((da[i][0] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][0] - mean) * gg0 + og0));
                     xv.y += sc1 * (((da[i][1] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][1] - mean) * gg1 + og1));
                     *r0 = xv;
-                    if (img)
-                        *reinterpret_cast<uint32_t *>(img + ipos * img_ld + c) = pack2(xv.x, xv.y);
                 }
                 if (v1[i])
                 {
@@ -745,8 +731,6 @@ __global__ void __launch_bounds__(THREADS)
                     xv.x += sc0 * (((da[i][2] - mean) * ga0 + oa0) * sigmoid_ref((dg[i][2] - mean) * gg0 + og0));
                     xv.y += sc1 * (((da[i][3] - mean) * ga1 + oa1) * sigmoid_ref((dg[i][3] - mean) * gg1 + og1));
                     *r1 = xv;
-                    if (img)
-                        *reinterpret_cast<uint32_t *>(img + (ipos + 8) * img_ld + c) = pack2(xv.x, xv.y);
                 }
             }
         }
@@ -773,8 +757,7 @@ template <int C, int HID> static int time_set_attr()
 }
 
 template <int C, int HID>
-static int time_launch(float *x, float *hbuf, const uint8_t *params, int B, int L, int hs, double *const *stats, void *img,
-                       int img_ld, cudaStream_t st)
+static int time_launch(float *x, float *hbuf, const uint8_t *params, int B, int L, int hs, double *const *stats, cudaStream_t st)
 {
     constexpr int M = time_mtw(C);
     constexpr int TT = 16 * WARPS * M;
@@ -783,10 +766,9 @@ static int time_launch(float *x, float *hbuf, const uint8_t *params, int B, int 
     {
         const uint8_t *P = params + (size_t)sub * pk_sub_bytes(C, hid_pad(HID));
         double *s1 = stats[2 * sub], *s2 = stats[2 * sub + 1];
-        __nv_bfloat16 *im = sub == 1 ? static_cast<__nv_bfloat16 *>(img) : nullptr;
-        dconv_time_kernel<C, HID, 0, M><<<grid, THREADS, time_smem(C, HID, 0, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2, nullptr, 0);
-        dconv_time_kernel<C, HID, 1, M><<<grid, THREADS, time_smem(C, HID, 1, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2, nullptr, 0);
-        dconv_time_kernel<C, HID, 2, M><<<grid, THREADS, time_smem(C, HID, 2, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2, im, img_ld);
+        dconv_time_kernel<C, HID, 0, M><<<grid, THREADS, time_smem(C, HID, 0, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 1, M><<<grid, THREADS, time_smem(C, HID, 1, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
+        dconv_time_kernel<C, HID, 2, M><<<grid, THREADS, time_smem(C, HID, 2, M), st>>>(x, hbuf, P, L, hs, 1 << sub, s1, s2);
     }
     DMX_LAUNCH_CHECK();
     return 0;
@@ -798,10 +780,10 @@ template <int C, int HID> static int set_attr()
                                   (int)smem_bytes(C, HID)));
     return 0;
 }
-template <int C, int HID> static int launch(float *x, const uint8_t *params, int items, void *img, int img_ld, cudaStream_t st)
+template <int C, int HID> static int launch(float *x, const uint8_t *params, int items, cudaStream_t st)
 {
-    dconv_mma_kernel<C, HID, false, false><<<items, THREADS, smem_bytes(C, HID), st>>>(
-        x, params, nullptr, nullptr, nullptr, 1, nullptr, nullptr, static_cast<__nv_bfloat16 *>(img), img_ld);
+    dconv_mma_kernel<C, HID, false, false><<<items, THREADS, smem_bytes(C, HID), st>>>(x, params, nullptr, nullptr, nullptr, 1,
+                                                                                    nullptr, nullptr);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -819,10 +801,10 @@ static int launch_rw(float *x, const uint8_t *params, const uint8_t *rw, float *
 {
     if (spec)
         dconv_mma_kernel<C, HID, true, true><<<items, THREADS, smem_bytes(C, HID) + rw_bytes(C) + cin_bytes(C), st>>>(
-            x, params, rw, out, rowadd, F, spec, cin, nullptr, 0);
+            x, params, rw, out, rowadd, F, spec, cin);
     else
         dconv_mma_kernel<C, HID, true, false><<<items, THREADS, smem_bytes(C, HID) + rw_bytes(C), st>>>(x, params, rw, out, rowadd,
-                                                                                                  F, nullptr, nullptr, nullptr, 0);
+                                                                                                  F, nullptr, nullptr);
     DMX_LAUNCH_CHECK();
     return 0;
 }
@@ -941,35 +923,35 @@ void dconv_mma_pack(int C, int hid, const float *blk, float *out)
 // frequency rows with L = 336), hbuf [B][L][hs] scratch, stats: four zeroed (sum, sumsq)[B] buffers (sub-block 0 GN1,
 // GN2, sub-block 1 GN1, GN2); six launches.
 int launch_dconv_time_mma(float *x, float *hbuf, const void *packed, int B, int L, int C, int hid, int hs,
-                          double *const *stats, cudaStream_t st, void *img, int img_ld)
+                          double *const *stats, cudaStream_t st)
 {
     const uint8_t *params = static_cast<const uint8_t *>(packed);
     if (C == 48 && hid == 6)
-        return dm::time_launch<48, 6>(x, hbuf, params, B, L, hs, stats, img, img_ld, st);
+        return dm::time_launch<48, 6>(x, hbuf, params, B, L, hs, stats, st);
     if (C == 48 && hid == 12)
-        return dm::time_launch<48, 12>(x, hbuf, params, B, L, hs, stats, img, img_ld, st);
+        return dm::time_launch<48, 12>(x, hbuf, params, B, L, hs, stats, st);
     if (C == 96 && hid == 12)
-        return dm::time_launch<96, 12>(x, hbuf, params, B, L, hs, stats, img, img_ld, st);
+        return dm::time_launch<96, 12>(x, hbuf, params, B, L, hs, stats, st);
     if (C == 96 && hid == 24)
-        return dm::time_launch<96, 24>(x, hbuf, params, B, L, hs, stats, img, img_ld, st);
+        return dm::time_launch<96, 24>(x, hbuf, params, B, L, hs, stats, st);
     if (C == 192 && hid == 24)
-        return dm::time_launch<192, 24>(x, hbuf, params, B, L, hs, stats, img, img_ld, st);
+        return dm::time_launch<192, 24>(x, hbuf, params, B, L, hs, stats, st);
     set_error("dconv_time_mma: unsupported shape");
     return -1;
 }
 
 // x: [items][336][C] in place; items = B * F frequency rows; packed: the block built by dconv_mma_pack
-int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st, void *img, int img_ld)
+int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st)
 {
     const uint8_t *params = static_cast<const uint8_t *>(packed);
     if (C == 48 && hid == 6)
-        return dm::launch<48, 6>(x, params, items, img, img_ld, st);
+        return dm::launch<48, 6>(x, params, items, st);
     if (C == 48 && hid == 12)
-        return dm::launch<48, 12>(x, params, items, img, img_ld, st);
+        return dm::launch<48, 12>(x, params, items, st);
     if (C == 96 && hid == 12)
-        return dm::launch<96, 12>(x, params, items, img, img_ld, st);
+        return dm::launch<96, 12>(x, params, items, st);
     if (C == 96 && hid == 24)
-        return dm::launch<96, 24>(x, params, items, img, img_ld, st);
+        return dm::launch<96, 24>(x, params, items, st);
     set_error("dconv_mma: unsupported shape");
     return -1;
 }

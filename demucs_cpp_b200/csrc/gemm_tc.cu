@@ -1654,7 +1654,7 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
     gemm_tc_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmC, const GemmParams p,
                        const __nv_bfloat16 *__restrict__ Wt, const int bn, const int plain_out, const int a_slots, const int b_stages,
                        const int mtiles, const int ntiles, const int ew, const int G, const int nacc, const int b_resident,
-                       const int tma_store)
+                       const int tma_store, const int epi_warp_bytes)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t a_full[T_MAX_ASLOTS], a_empty[T_MAX_ASLOTS], b_full[T_MAX_BSTAGES], b_empty[T_MAX_BSTAGES];
@@ -1670,9 +1670,11 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
     const uint32_t b_stage_bytes = (uint32_t)bn * BK * 2;
     uint8_t *a_smem = smem;
     const uint32_t slot_bytes = (uint32_t)p.t_cps * (uint32_t)p.t_box_bytes; // a ring slot holds the cps chunk boxes of a plane
-    uint8_t *epi_smem = smem + (size_t)a_slots * slot_bytes;                          // 1024-aligned: ew x T_EPI_WARP_BYTES
-    uint8_t *b_smem = epi_smem + (size_t)ew * T_EPI_WARP_BYTES;
-    RowInfo *row_smem = reinterpret_cast<RowInfo *>(b_smem + (size_t)b_stages * b_stage_bytes);
+    // per-warp epilogue buffers (1024-aligned): nothing for the direct tile-packed epilogue, 4 KB of store tiles for the
+    // tensor-map store, T_EPI_WARP_BYTES + a 32-row table for the transposing epilogue
+    uint8_t *epi_smem = smem + (size_t)a_slots * slot_bytes;
+    uint8_t *b_smem = epi_smem + (size_t)ew * epi_warp_bytes;
+    const bool flat = p.Apk != nullptr; // tile-packed A: tiles are 128 consecutive GEMM rows, no line structure
     uint32_t acc_cols = 32;
     while ((int)acc_cols < bn)
         acc_cols <<= 1;
@@ -1721,11 +1723,12 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
         const int g = warp / ewg, wg = warp - g * ewg;
         const int q = warp & 3; // ewg % 4 == 0, so this is also wg & 3: the TMEM lane quadrant this warp may read
         const int csel = wg >> 2, nsel = ewg >> 2;
-        uint8_t *stage = epi_smem + (size_t)warp * T_EPI_WARP_BYTES;
-        RowInfo *rowinfo = row_smem + warp * 32 - q * 32;
+        uint8_t *stage = epi_smem + (size_t)warp * epi_warp_bytes;
+        RowInfo *rowinfo = reinterpret_cast<RowInfo *>(stage + T_EPI_WARP_BYTES) - q * 32; // transposing epilogue only
         const bool packed_direct = p.out_pack && plain_out == 1 && !p.glu && !p.gamma && !p.addC && !p.rowadd && !p.stats &&
                                    (p.N % 8) == 0;
         const bool use_tmast = tma_store && bulk_ok(p, plain_out);
+        const bool need_table = !packed_direct && !use_tmast && !(bulk_ok(p, plain_out) && !p.no_bulk);
         int parity = 0, itm = 0;
         for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++itm)
         {
@@ -1734,17 +1737,28 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
             if (mt >= mtiles)
                 break;
             const int tl = itm * G + g;
-            int hb, hu, hv0;
-            tile_coords(mt, hb, hu, hv0);
+            int hb = 0, hu = 0, hv0 = 0;
+            RowInfo ri;
             {
                 const int row = q * 32 + lane;
-                const bool valid = hv0 + row < p.Vo;
                 RowCoord rc;
-                rc.b = hb;
-                rc.uo = hu;
-                rc.vo = valid ? hv0 + row : 0;
-                const int m = (hb * p.Uo + hu) * p.Vo + rc.vo;
-                RowInfo ri;
+                bool valid;
+                int m;
+                if (flat)
+                {
+                    m = mt * BM + row;
+                    valid = m < p.M;
+                    rc = decode_row(valid ? m : 0, p);
+                }
+                else
+                {
+                    tile_coords(mt, hb, hu, hv0);
+                    valid = hv0 + row < p.Vo;
+                    rc.b = hb;
+                    rc.uo = hu;
+                    rc.vo = valid ? hv0 + row : 0;
+                    m = (hb * p.Uo + hu) * p.Vo + rc.vo;
+                }
                 ri.uu0 = rc.uo * p.ous + p.ouo;
                 ri.vv0 = rc.vo * p.ovs + p.ovo;
                 ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
@@ -1752,22 +1766,22 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
                 ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
                 ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m;
                 ri.orow = (rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0;
-                rowinfo[row] = ri;
+                if (need_table)
+                    rowinfo[row] = ri;
             }
-            const int my_prow = rowinfo[q * 32 + lane].item >= 0 ? rowinfo[q * 32 + lane].prow : -1;
+            const int my_prow = ri.item >= 0 ? ri.prow : -1;
             __syncwarp();
             const int acc = tl % nacc;
             mbar_wait(&acc_full[acc], (uint32_t)(tl / nacc) & 1u);
             tc_fence_after();
             const uint32_t lane_addr = tmem_base + (uint32_t)acc * acc_cols + ((uint32_t)(q * 32) << 16);
             if (use_tmast)
-                epilogue_tile_tmast(p, &tmC, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], stage, 32 * csel, 32 * nsel, lane,
-                                    hv0 + q * 32, hb * p.Uo + hu, parity);
+                epilogue_tile_tmast(p, &tmC, bn, nt * bn, lane_addr, ri, stage, 32 * csel, 32 * nsel, lane,
+                                    flat ? mt * BM + q * 32 : hv0 + q * 32, flat ? 0 : hb * p.Uo + hu, parity);
             else if (packed_direct)
                 epilogue_tile_packed(p, bn, nt * bn, lane_addr, my_prow, 32 * csel, 32 * nsel);
             else if (bulk_ok(p, plain_out) && !p.no_bulk)
-                epilogue_tile_bulk(p, bn, nt * bn, lane_addr, rowinfo[q * 32 + lane], reinterpret_cast<float *>(stage), 32 * csel,
-                                   32 * nsel, lane);
+                epilogue_tile_bulk(p, bn, nt * bn, lane_addr, ri, reinterpret_cast<float *>(stage), 32 * csel, 32 * nsel, lane);
             else
                 epilogue_tile(p, bn, plain_out, nt * bn, lane_addr, rowinfo, reinterpret_cast<float *>(stage), q, 32 * csel, 32 * nsel,
                               lane);
@@ -1792,14 +1806,29 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
             for (int item = blockIdx.x; item < total_items; item += gridDim.x)
             {
                 const int pr = item / ntiles;
-                int hb[2], hu[2], hv0[2], ng = 0;
+                int hb[2] = {0, 0}, hu[2] = {0, 0}, hv0[2] = {0, 0}, ng = 0;
                 for (int g = 0; g < G && pr * G + g < mtiles; ++g, ++ng)
-                    tile_coords(pr * G + g, hb[g], hu[g], hv0[g]);
+                    if (!flat)
+                        tile_coords(pr * G + g, hb[g], hu[g], hv0[g]);
                 for (int qg = 0; qg < ngrp; ++qg)
                     for (int b = 0; b < p.t_nbox; ++b)
                         for (int g = 0; g < ng; ++g)
                         {
                             mbar_wait(&a_empty[slot], ph ^ 1u);
+                            if (flat)
+                            {
+                                // tile-packed activations: the k-block's A operand is one contiguous 16 KB image
+                                const uint8_t *asrc = reinterpret_cast<const uint8_t *>(p.Apk) +
+                                                      ((size_t)(pr * G + g) * ngrp + qg) * (size_t)(BM * BK * 2);
+                                mbar_arrive_expect_tx(&a_full[slot], BM * BK * 2);
+                                bulk_g2s(a_smem + (size_t)slot * slot_bytes, asrc, BM * BK * 2, &a_full[slot]);
+                                if (++slot == a_slots)
+                                {
+                                    slot = 0;
+                                    ph ^= 1u;
+                                }
+                                continue;
+                            }
                             mbar_arrive_expect_tx(&a_full[slot], box_tx);
                             for (int qi = 0; qi < p.t_cps; ++qi)
                                 tma_load_4d(a_smem + (size_t)slot * slot_bytes + (size_t)qi * p.t_box_bytes, &tmA, &a_full[slot],
@@ -1852,7 +1881,10 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
         {
             const uint32_t idesc = make_idesc(bn);
             const uint32_t b_lbo16 = (uint32_t)bn;                                  // (bn * 16 bytes) >> 4
-            const uint64_t a_proto = make_desc_sw(0, 8u * (uint32_t)p.t_pitch, (uint32_t)p.t_layout);
+            // A descriptors: swizzled K-major boxes (32 bytes per K = 16 step), or the canonical no-swizzle image of tile-packed
+            // activations (two 2 KB core-matrix columns per step)
+            const uint64_t a_proto = flat ? make_desc(0, (uint32_t)(BM * 16), 128) : make_desc_sw(0, 8u * (uint32_t)p.t_pitch, (uint32_t)p.t_layout);
+            const uint32_t a_step16 = flat ? (uint32_t)(2 * BM) : 2u;
             const uint64_t b_proto = make_desc(0, (uint32_t)bn * 16, 128);
             const uint32_t a_hi = (uint32_t)(a_proto >> 32), a_lo0 = (uint32_t)a_proto;
             const uint32_t b_hi = (uint32_t)(b_proto >> 32), b_lo0 = (uint32_t)b_proto;
@@ -1917,7 +1949,7 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
                             for (int t = 0; t < tpb; ++t, a_tap += shift16)
                             {
                                 uint32_t a_lo = a_tap;
-                                for (int s = 0; s < spc; ++s, a_lo += 2)
+                                for (int s = 0; s < spc; ++s, a_lo += a_step16)
                                 {
                                     if (bstep == 0)
                                     {
@@ -2112,6 +2144,9 @@ static int tc_launch(const GemmParams &p, const __nv_bfloat16 *w, int bn, bool v
     return 0;
 }
 
+int launch_gemm_tma_packed(const GemmParams &p, const void *Wb, cudaStream_t st);
+bool tc_tma_available();
+
 int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
 {
     if (p.M <= 0 || p.N <= 0 || p.K <= 0 || !Wb)
@@ -2213,6 +2248,11 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
         // tile-packed A (the transformer's linear layers): persistent kernel.  The gather / halo layers stay on the
         // one-tile-per-CTA kernel: they are bound by producer + epilogue instruction issue, which three co-resident
         // CTAs (24 producer warps) serve better than one persistent CTA (measured: 20.3 -> 25.2 ms/step persistent).
+        // (the paired kernel can take tile-packed A too -- DMX_TMA_PACKED=1 -- but measured 1.5x slower than the persistent
+        // kernel below on every transformer GEMM, 7.3 -> 10.2 ms/step; not understood yet, so it stays off)
+        static const bool packed_tma = getenv("DMX_TMA_PACKED") != nullptr;
+        if (p.Apk && plain && packed_tma && tc_tma_available())
+            return launch_gemm_tma_packed(p, Wb, st);
         if (p.Apk)
         {
             const int mt = (p.M + tc::BM - 1) / tc::BM, nt = (p.N + bn - 1) / bn;
@@ -2355,6 +2395,129 @@ static int tma_set_attr()
     return 0;
 }
 
+static int mtiles_of_lines(int items, int Uo, int tpr) { return items * Uo * tpr; }
+
+// Shared-memory budget, ring depths, pairing and launch of gemm_tc_tma_kernel.  slots_per_tile = ring slots one row tile
+// consumes; (store_v, store_lines) = the output viewed as lines of store_v rows for the tensor-map store.
+static int tma_launch_core(const GemmParams &q, const CUtensorMap &tm, const __nv_bfloat16 *W, int bn, int plain_out, int nout,
+                           int mtiles, size_t slot_bytes, int slots_per_tile, long long store_v, long long store_lines,
+                           cudaStream_t st, int g_want = 0)
+{
+    static int sms = 0;
+    if (!sms)
+    {
+        int dev = 0;
+        DMX_CUDA(cudaGetDevice(&dev));
+        DMX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        if (tma_set_attr())
+            return -1;
+    }
+    static const int ew_env = getenv("DMX_TMA_EW") ? atoi(getenv("DMX_TMA_EW")) : 0;
+    static const int g_env = getenv("DMX_TMA_G") ? atoi(getenv("DMX_TMA_G")) : 0;
+    static const bool no_res = getenv("DMX_TMA_NO_RESIDENT") != nullptr;
+    static const bool no_tmast = getenv("DMX_TMA_NO_STORE") != nullptr;
+    const size_t b_stage = (size_t)bn * tc::BK * 2;
+    const size_t budget = 220 * 1024;
+    const int nkb = (q.K + tc::BK - 1) / tc::BK;
+    const int ntiles = (q.N + bn - 1) / bn;
+    int acc_cols = 32;
+    while (acc_cols < bn)
+        acc_cols <<= 1;
+    // tensor map of the output for the store epilogue
+    CUtensorMap tmc;
+    int tma_store = 0;
+    if (plain_out == 1 && !no_tmast)
+    {
+        if (make_store_map(q, nout, (int)store_v, store_lines, &tmc, &tma_store))
+            return -1;
+    }
+    else
+        memset(&tmc, 0, sizeof tmc);
+    // per-warp epilogue shared memory by epilogue kind (see the kernel)
+    const bool packed_direct = q.out_pack && plain_out == 1 && !q.glu && !q.gamma && !q.addC && !q.rowadd && !q.stats && (q.N % 8) == 0;
+    const bool tmast = tma_store && plain_out == 1 && !q.addC && !q.rowadd && !q.out_pack && !q.out_bf16 && !q.Cbf &&
+                       (q.N % (q.glu ? 8 : 4)) == 0;
+    const int epi_warp = packed_direct ? 0 : (tmast ? 4096 : tc::T_EPI_WARP_BYTES + 32 * (int)sizeof(tc::RowInfo));
+    // G = 2 row tiles share every weight block (one MMA issuer and one group of epilogue warps per tile); four accumulators
+    // (one pair draining while the next fills) when they fit in TMEM
+    int G = (g_env == 1 || g_env == 2) ? g_env : (g_want ? g_want : 2);
+    if (mtiles < 2 * sms && !g_env)
+        G = 1; // too few tiles to pair without idling SMs
+    const int nacc = (2 * G * acc_cols <= 512) ? 2 * G : G;
+    if (nacc * acc_cols > 512)
+    {
+        set_error("launch_gemm_tma: accumulators do not fit in TMEM");
+        return -1;
+    }
+    auto fixed_for = [&](int e) { return ((size_t)e * epi_warp + 1023) / 1024 * 1024; };
+    // epilogue warps: 8 per tile when shared memory allows (the epilogue is a chain of TMEM load -> math -> store tile ->
+    // tensor-map store per 32 columns: more warps = more chains in flight), else 4 per tile
+    int ew = 8 * G;
+    int b_resident = 0, b_stages = 0;
+    {
+        // preference order: resident weights with 8 then 4 epilogue warps per tile; streamed weights with (8, 3 stages),
+        // (4, 3 stages), (4, 2 stages); every variant needs at least 2 boxes per tile of the pair in the ring
+        const int min_boxes = 2 * G;
+        bool found = false;
+        const bool can_res = !no_res && ntiles == 1 && nkb <= tc::T_MAX_BSTAGES;
+        // total epilogue warps: 16 (8 per tile of a pair, 16 for a single tile), 8, or 4 per tile
+        const int ews[3] = {16, 8, 4 * G};
+        for (int i = 0; i < 3 && !found && can_res; ++i)
+            if (fixed_for(ews[i]) + (size_t)nkb * b_stage + (size_t)(min_boxes + 1) * slot_bytes <= budget)
+            {
+                ew = ews[i];
+                b_resident = 1;
+                b_stages = nkb;
+                found = true;
+            }
+        const int tries[4][2] = {{16, 3}, {8, 3}, {4 * G, 3}, {4 * G, 2}};
+        for (int t = 0; t < 4 && !found; ++t)
+        {
+            const int stg = std::min(tries[t][1], std::max(nkb, 2));
+            if (fixed_for(tries[t][0]) + (size_t)stg * b_stage + (size_t)min_boxes * slot_bytes <= budget)
+            {
+                ew = tries[t][0];
+                b_stages = stg;
+                found = true;
+            }
+        }
+        if (!found)
+        {
+            set_error("launch_gemm_tma: tile does not fit in shared memory");
+            return -1;
+        }
+    }
+    if (ew_env == 4 * G || ew_env == 8 || ew_env == 16)
+        ew = ew_env;
+    const size_t fixed = fixed_for(ew);
+    // Ring depths.  Streamed weights are what these layers wait for: a stage is refilled only after the MMAs that read it
+    // have completed and the copy has crossed L2 -> SM (~1.5 us), so the bytes in flight bound the rate.  Boxes first get a
+    // modest ring (4 per tile of the pair), then the weight ring takes what is left, then the boxes the remainder.
+    const int slots_per_item = G * slots_per_tile;
+    int a_max = (int)((budget - fixed - b_stages * b_stage) / slot_bytes);
+    a_max = std::min(a_max, tc::T_MAX_ASLOTS);
+    if (a_max < 2 * G)
+    {
+        set_error("launch_gemm_tma: box ring does not fit in shared memory");
+        return -1;
+    }
+    int a_slots = std::min(a_max, std::max(2 * G, std::min(4 * G, slots_per_item)));
+    while (!b_resident && b_stages < tc::T_MAX_BSTAGES && b_stages < nkb &&
+           fixed + (size_t)(b_stages + 1) * b_stage + (size_t)a_slots * slot_bytes <= budget)
+        ++b_stages;
+    while (a_slots < tc::T_MAX_ASLOTS && a_slots < 2 * slots_per_item &&
+           fixed + (size_t)b_stages * b_stage + (size_t)(a_slots + 1) * slot_bytes <= budget)
+        ++a_slots;
+    const size_t smem = fixed + (size_t)b_stages * b_stage + (size_t)a_slots * slot_bytes;
+    const int npairs = (mtiles + G - 1) / G;
+    const int total = npairs * ntiles;
+    const int grid = total < sms ? total : sms;
+    tc::gemm_tc_tma_kernel<<<grid, (ew + 2 + G) * 32, smem, st>>>(tm, tmc, q, W, bn, plain_out, a_slots, b_stages, mtiles, ntiles, ew,
+                                                             G, nacc, b_resident, tma_store, epi_warp);
+    DMX_LAUNCH_CHECK();
+    return 0;
+}
+
 // p: a stride-1 "same" convolution (Ui == Uo * 1, Vi == Vo, su == sv == 1) or any tap set without v shifts, Cin % 16 == 0,
 // K == ntaps * Cin, A given as the bf16 image p.Aimg, weights as p.Wt (K' order of tc_tma_plan with share_dv = true unless
 // the environment says otherwise).
@@ -2447,112 +2610,63 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
             return -1;
         }
     }
-    static int sms = 0;
-    if (!sms)
+    return tma_launch_core(q, tm, static_cast<const __nv_bfloat16 *>(p.Wt), bn, plain | vscat, nout, mtiles_of_lines(items, p.Uo, q.halo_tpr),
+                           slot_bytes, pl.nbox * (pl.nchunk / pl.cps), p.Vout, (long long)items * p.Uout, st);
+}
+
+// The transformer's linear layers on the same kernel: A arrives tile-packed ([row/128][K/8][row%128][8] bf16, written by
+// LayerNorm / attention / the previous GEMM), i.e. one contiguous 16 KB image per (row tile, 64-wide k-block), fetched by
+// bulk copies into the box ring; W = the ordinary packed weight image.  Same rings, pairing and epilogues as above.
+int launch_gemm_tma_packed(const GemmParams &p, const void *Wb, cudaStream_t st)
+{
+    if (!p.Apk || !Wb || p.M <= 0 || p.N <= 0 || p.K % tc::BK || p.ntaps != 1 || p.pro || p.A2)
     {
-        int dev = 0;
-        DMX_CUDA(cudaGetDevice(&dev));
-        DMX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        if (tma_set_attr())
-            return -1;
+        set_error("launch_gemm_tma_packed: unsupported problem");
+        return -1;
     }
-    static const int ew_env = getenv("DMX_TMA_EW") ? atoi(getenv("DMX_TMA_EW")) : 0;
-    static const int g_env = getenv("DMX_TMA_G") ? atoi(getenv("DMX_TMA_G")) : 0;
-    static const bool no_res = getenv("DMX_TMA_NO_RESIDENT") != nullptr;
-    static const bool no_tmast = getenv("DMX_TMA_NO_STORE") != nullptr;
-    const size_t b_stage = (size_t)bn * tc::BK * 2;
-    const size_t budget = 220 * 1024;
-    const int nkb = (p.K + tc::BK - 1) / tc::BK;
-    const int mtiles = items * p.Uo * q.halo_tpr, ntiles = (p.N + bn - 1) / bn;
+    const int bn = tc_tile_n(p.N);
+    const int nout = p.glu ? p.N / 2 : p.N;
+    GemmParams q = p;
+    auto recip = [](int d) { return d <= 1 ? 0ull : ~0ull / (unsigned long long)d + 1ull; };
+    q.div_per = recip(p.Uo * p.Vo);
+    q.div_vo = recip(p.Vo);
+    q.div_nco = recip(p.Nco);
+    q.t_nbox = 1;
+    q.t_tpb = 1;
+    q.t_shift16 = 0;
+    q.t_cps = 1;
+    q.t_cw = q.t_kw = tc::BK;
+    q.t_nchunk = p.K / tc::BK;
+    q.t_pitch = 128;
+    q.t_rows = tc::BM;
+    q.t_box_bytes = tc::BM * tc::BK * 2;
+    q.t_layout = 0;
+    const int plain = (p.ous == 1 && p.ovs == 1 && p.our == 0 && p.ovr == 0 && p.ouo == 0 && p.ovo == 0 && p.Uout == p.Uo &&
+                       p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 &&
+                       (!p.rowadd || (p.rowadd_ld % 4) == 0) && (!p.addC || (reinterpret_cast<uintptr_t>(p.addC) & 15) == 0))
+                          ? 1
+                          : 0;
+    if (!plain)
+    {
+        set_error("launch_gemm_tma_packed: output mapping not supported");
+        return -1;
+    }
+    if ((p.out_bf16 || p.out_pack) && (p.gamma || p.addC || (nout % 4) || (p.out_pack && (p.ldc % 8))))
+    {
+        set_error("launch_gemm_tma_packed: bf16 / packed output needs no residual and N % 4 == 0");
+        return -1;
+    }
+    CUtensorMap tm;
+    memset(&tm, 0, sizeof tm);
+    // pairing needs both accumulators of a 256-wide tile pair at once (512 TMEM columns), so a pair's MMAs and epilogues
+    // alternate instead of overlapping: worth it only when the MMA phase is long (K >= 1024: FFN down-projection)
+    static const int pg_env = getenv("DMX_TMA_PACKED_G") ? atoi(getenv("DMX_TMA_PACKED_G")) : 0;
     int acc_cols = 32;
     while (acc_cols < bn)
         acc_cols <<= 1;
-    // G = 2 row tiles share every weight block (one MMA issuer and one group of epilogue warps per tile); four accumulators
-    // (one pair draining while the next fills) when they fit in TMEM
-    int G = (g_env == 1 || g_env == 2) ? g_env : 2;
-    if (mtiles < 2 * sms && !g_env)
-        G = 1; // too few tiles to pair without idling SMs
-    const int nacc = (2 * G * acc_cols <= 512) ? 2 * G : G;
-    if (nacc * acc_cols > 512)
-    {
-        set_error("launch_gemm_tma: accumulators do not fit in TMEM");
-        return -1;
-    }
-    auto fixed_for = [&](int e) { return (size_t)e * tc::T_EPI_WARP_BYTES + (size_t)e * 32 * sizeof(tc::RowInfo); };
-    // epilogue warps: 8 per tile when shared memory allows (the epilogue is a chain of TMEM load -> math -> store tile ->
-    // tensor-map store per 32 columns: more warps = more chains in flight), else 4 per tile
-    int ew = 8 * G;
-    int b_resident = 0, b_stages = 0;
-    {
-        // preference order: resident weights with 8 then 4 epilogue warps per tile; streamed weights with (8, 3 stages),
-        // (4, 3 stages), (4, 2 stages); every variant needs at least 2 boxes per tile of the pair in the ring
-        const int min_boxes = 2 * G;
-        bool found = false;
-        const bool can_res = !no_res && ntiles == 1 && nkb <= tc::T_MAX_BSTAGES;
-        for (int e = 8; e >= 4 && !found && can_res; e -= 4)
-            if (fixed_for(e * G) + (size_t)nkb * b_stage + (size_t)(min_boxes + 1) * slot_bytes <= budget)
-            {
-                ew = e * G;
-                b_resident = 1;
-                b_stages = nkb;
-                found = true;
-            }
-        const int tries[3][2] = {{8, 3}, {4, 3}, {4, 2}};
-        for (int t = 0; t < 3 && !found; ++t)
-        {
-            const int st = std::min(tries[t][1], std::max(nkb, 2));
-            if (fixed_for(tries[t][0] * G) + (size_t)st * b_stage + (size_t)(min_boxes + (t < 2 ? G : 0)) * slot_bytes <= budget)
-            {
-                ew = tries[t][0] * G;
-                b_stages = st;
-                found = true;
-            }
-        }
-        if (!found)
-        {
-            set_error("launch_gemm_tma: tile does not fit in shared memory");
-            return -1;
-        }
-    }
-    if (ew_env == 4 * G || ew_env == 8 * G)
-        ew = ew_env;
-    const size_t fixed = fixed_for(ew);
-    // Ring depths.  Streamed weights are what these layers wait for: a stage is refilled only after the MMAs that read it
-    // have completed and the copy has crossed L2 -> SM (~1.5 us), so the bytes in flight bound the rate.  Boxes first get a
-    // modest ring (4 per tile of the pair), then the weight ring takes what is left, then the boxes the remainder.
-    const int slots_per_item = G * pl.nbox * (pl.nchunk / pl.cps);
-    int a_max = (int)((budget - fixed - b_stages * b_stage) / slot_bytes);
-    a_max = std::min(a_max, tc::T_MAX_ASLOTS);
-    if (a_max < 2 * G)
-    {
-        set_error("launch_gemm_tma: box ring does not fit in shared memory");
-        return -1;
-    }
-    int a_slots = std::min(a_max, std::max(2 * G, std::min(4 * G, slots_per_item)));
-    while (!b_resident && b_stages < tc::T_MAX_BSTAGES && b_stages < nkb &&
-           fixed + (size_t)(b_stages + 1) * b_stage + (size_t)a_slots * slot_bytes <= budget)
-        ++b_stages;
-    while (a_slots < tc::T_MAX_ASLOTS && a_slots < 2 * slots_per_item &&
-           fixed + (size_t)b_stages * b_stage + (size_t)(a_slots + 1) * slot_bytes <= budget)
-        ++a_slots;
-    const size_t smem = fixed + (size_t)b_stages * b_stage + (size_t)a_slots * slot_bytes;
-    // tensor map of the output for the store epilogue: (columns, positions of a line, lines)
-    CUtensorMap tmc;
-    int tma_store = 0;
-    if (plain == 1 && !no_tmast)
-    {
-        if (make_store_map(p, nout, p.Vout, (long long)items * p.Uout, &tmc, &tma_store))
-            return -1;
-    }
-    else
-        memset(&tmc, 0, sizeof tmc);
-    const int npairs = (mtiles + G - 1) / G;
-    const int total = npairs * ntiles;
-    const int grid = total < sms ? total : sms;
-    tc::gemm_tc_tma_kernel<<<grid, (ew + 2 + G) * 32, smem, st>>>(tm, tmc, q, static_cast<const __nv_bfloat16 *>(p.Wt), bn, plain | vscat,
-                                                             a_slots, b_stages, mtiles, ntiles, ew, G, nacc, b_resident, tma_store);
-    DMX_LAUNCH_CHECK();
-    return 0;
+    const int g_want = pg_env ? pg_env : ((4 * acc_cols <= 512 || p.K >= 1024) ? 2 : 1);
+    return tma_launch_core(q, tm, static_cast<const __nv_bfloat16 *>(Wb), bn, plain, nout, (p.M + tc::BM - 1) / tc::BM,
+                           (size_t)tc::BM * tc::BK * 2, p.K / tc::BK, p.M, 1, st, g_want);
 }
 
 } // namespace dmx

@@ -148,9 +148,7 @@ bool dconv_mma_supported(int C, int hid, int V);
 int dconv_mma_init_device();
 int dconv_mma_pack_floats(int C, int hid);
 void dconv_mma_pack(int C, int hid, const float *blk, float *out);
-// img (optional, bf16 mode): the finished x also leaves as a bf16 channels-last image with img_ld channels per row
-int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st, void *img = nullptr,
-                     int img_ld = 0);
+int launch_dconv_mma(float *x, const void *packed, int items, int C, int hid, cudaStream_t st);
 bool dconv_mma_rw_supported(int C, int hid, int V);
 int dconv_mma_rw_pack_floats(int C);
 void dconv_mma_rw_pack(int C, const float *W, const float *bias, float *out);
@@ -160,7 +158,7 @@ int launch_dconv_mma_rw(float *x, const void *packed, const void *rw, float *out
                         int C, int hid, const float *spec, const void *cin, cudaStream_t st);
 bool dconv_time_mma_supported(int C, int hid, int hs);
 int launch_dconv_time_mma(float *x, float *hbuf, const void *packed, int B, int L, int C, int hid, int hs,
-                          double *const *stats, cudaStream_t st, void *img = nullptr, int img_ld = 0);
+                          double *const *stats, cudaStream_t st);
 
 // ---------------------------------------------------------------------------------------------
 // v3_kernels.cu (hdemucs_mmi)

@@ -585,8 +585,9 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             p.glu = 1;
             p.Nco = C;
             f.gemm(p, PC_GEMM_CONV);
-            // (the transposed convolutions can run on the TMA-fed kernel too, but they are bound by their scatter epilogue and
-            // the DConv kernels' extra bf16 image stores cost more than the operand path saves: 41.3 -> 42.4 ms/step; off)
+            // (the transposed convolutions can run on the TMA-fed kernel too -- DMX_TMA_CONVTR, 384-channel level only -- but they
+            // are bound by their scatter epilogue, and bf16 image stores in the fused DConv kernels cost more than the operand
+            // path saved: 41.3 -> 42.4 ms/step with all four levels on it)
             const bool cimg = f.dconv(m->cA_f, F, T, fd.dc, m->h_f, m->y2_f, 1, tma_ct ? m->cimg_f : nullptr, tc_tma_cpitch(C));
             // ConvTranspose k(8,1) s(4,1) along frequency as a 2-tap GEMM, crop [2, 2+4F)
             GemmParams q = f.base(m->cA_f, C, C, fd.convtr, m->dx[i], fd.Cout, F, T, F + 1, T);

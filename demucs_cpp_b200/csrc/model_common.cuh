@@ -403,8 +403,9 @@ struct Fwd
 
     // DConv residual branch (src/layers.cpp:152-375) in place on x [B][U][V][C]; GroupNorm items are
     // frequency rows (per_u = 1) or whole batch elements (time branch, U = 1).
-    // img (bf16 mode): the result is also written as a bf16 channels-last image with img_ld channels per row (what the
-    // TMA-fed convolution that follows reads); returns whether the path taken wrote it.
+    // img (bf16 mode): the result is also written as a bf16 channels-last image with img_ld channels per row (what a
+    // TMA-fed convolution that follows would read); returns whether the path taken wrote it -- only the GEMM +
+    // gn_glu_residual form (the 384-channel level) does: the image stores measurably slowed the fused mma.sync kernels.
     bool dconv(float *x, int U, int V, const DConvW &w, float *h, float *y2, int per_u, void *img = nullptr, int img_ld = 0)
     {
         const int C = w.C, hid = w.hid, hidp = w.hidp;
@@ -416,11 +417,9 @@ struct Fwd
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          (double)B * U * V * C * 8.0);
             if (m->precision == DMX_PRECISION_BF16 && w.fused_pk && dconv_mma_supported(C, hid, V))
-            {
-                rc = launch_dconv_mma(x, w.fused_pk, B * U, C, hid, st, img, img_ld);
-                return img != nullptr;
-            }
-            rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
+                rc = launch_dconv_mma(x, w.fused_pk, B * U, C, hid, st);
+            else
+                rc = launch_dconv_fused(x, w.fused, B * U, C, hid, st);
             return false;
         }
         if ((per_u || U == 1) && w.fused_pk && m->precision == DMX_PRECISION_BF16 && dconv_time_mma_supported(C, hid, hidp))
@@ -434,8 +433,8 @@ struct Fwd
             double *sl[4] = {stat_slots(items), stat_slots(items), stat_slots(items), stat_slots(items)};
             ProfScope ps(m, PC_DCONV_FUSED, 2.0 * 2.0 * (double)B * U * V * (3.0 * C * hid + 2.0 * 2.0 * C * hid),
                          2.0 * (double)B * U * V * (3.0 * C + 3.0 * hidp) * 4.0, 6);
-            rc = launch_dconv_time_mma(x, h, w.fused_pk, items, V, C, hid, hidp, sl, st, img, img_ld);
-            return img != nullptr;
+            rc = launch_dconv_time_mma(x, h, w.fused_pk, items, V, C, hid, hidp, sl, st);
+            return false;
         }
         const size_t items = (size_t)B * (per_u ? U : 1);
         for (int j = 0; j < 2; ++j)

@@ -1,4 +1,4 @@
-"""One batch of 8 segments of the bench workload, bracketed by cudaProfilerStart/Stop, for ncu:
+"""One batch of --batch segments (default 16, what bench.py launches) of the bench workload, bracketed by cudaProfilerStart/Stop, for ncu:
   ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file X python tools/profile_step.py
 Same model, precision and segments-per-launch as bench.py; the track is cut to exactly 8 segments."""
 import argparse
@@ -15,11 +15,11 @@ from demucs_cpp_b200.synth import synth_audio  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--precision", default="bf16")
-ap.add_argument("--batch", type=int, default=8)
+ap.add_argument("--batch", type=int, default=16)
 ap.add_argument("--arch", default="htdemucs_4s")
 args = ap.parse_args()
-L = 8 * 257985 - 22050 + 4033 - 1000          # -> exactly 8 segments at shift 4033
-assert api.num_segments(L, 4033) == 8
+L = args.batch * 257985 - 22050 + 4033 - 1000          # -> exactly --batch segments at shift 4033
+assert api.num_segments(L, 4033) == args.batch
 m = api.DemucsModel(weights.cached_weights(args.arch, 0), max_batch=args.batch,
                     precision=api.PRECISION_BF16 if args.precision == "bf16" else api.PRECISION_FP32)
 d_audio = torch.from_numpy(np.ascontiguousarray(synth_audio(L).T)).cuda()
@@ -38,4 +38,4 @@ import json
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 with open(os.path.join(ROOT, "gpurun_out", "profile_step_classes.json"), "w") as f:
     json.dump({"sequence": seq, "classes": prof}, f)
-print("device ms for 8 segments: %.2f" % m.last_device_ms)
+print("device ms for %d segments: %.2f" % (args.batch, m.last_device_ms))

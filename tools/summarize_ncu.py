@@ -43,10 +43,10 @@ def main():
         by_class[seq[i] if i < len(seq) else "?"] += us
         total += us
     out = []
-    out.append("# ncu launch list, %s: one batch of 8 segments (htdemucs 4s, bf16 mode)\n" % tag)
+    out.append("# ncu launch list, %s: one batch of 16 segments (htdemucs 4s, bf16 mode)\n" % tag)
     out.append("Command (B200, `gpurun`): `ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none "
                "--csv --log-file X python tools/profile_step.py` (the plain run of the same command exited 0 first: %s ms "
-               "device time for the 8 segments).  Per-launch times under ncu are serialised and cold-cache, and the second "
+               "device time for the 16 segments).  Per-launch times under ncu are serialised and cold-cache, and the second "
                "stream of the time branch cannot overlap: compare SHARES.\n" % plain_ms)
     out.append("%d kernel launches, %.1f ms summed.\n" % (len(rows), total / 1000.0))
     out.append("| kernel | launches | total us | share |\n|---|---:|---:|---:|")
@@ -54,7 +54,7 @@ def main():
         out.append("| `%s` | %d | %.1f | %.1f %% |" % (name, n, us, 100.0 * us / total))
     out.append("\nBy kernel class (the classes of bench.py's `kernel_classes`; class of each launch from "
                "`dmx_profile_sequence`):\n")
-    out.append("| class | ncu us (batch of 8) | ncu share | bench.py live CUDA-event ms / step (31 segments) | live share |\n|---|---:|---:|---:|---:|")
+    out.append("| class | ncu us (batch of 16) | ncu share | bench.py live CUDA-event ms / step (31 segments) | live share |\n|---|---:|---:|---:|---:|")
     live_total = sum(v["ms"] for v in cls_ms.values())
     for c, us in by_class.most_common():
         lm = cls_ms.get(c, {}).get("ms", 0.0)
@@ -83,7 +83,7 @@ def main():
         e["dram_bytes_per_launch"] = e["dram_bytes_per_batch"] / e["launches_per_batch"]
     json.dump(tr, open(os.path.join(ROOT, "profiles", "%s_traffic.json" % tag), "w"), indent=1)
     tj = {c: e["dram_bytes_per_launch"] for c, e in tr.items()}
-    tj["_segments_per_launch"] = 8  # tools/profile_step.py profiles one batch of 8 segments; bench.py rescales
+    tj["_segments_per_launch"] = 16  # tools/profile_step.py profiles one batch of 16 segments, what bench.py launches
     json.dump(tj, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
     shutil.copy(traffic_csv, os.path.join(ROOT, "profiles", "%s_ncu_traffic.csv" % tag))
     print("\n".join(out[-14:]))
