@@ -1688,8 +1688,8 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
         }
         for (int s = 0; s < b_stages; ++s)
         {
-            mbar_init(&b_full[s], 1);
-            mbar_init(&b_empty[s], (uint32_t)G); // every MMA issuer of a pair releases the block
+            mbar_init(&b_full[s], p.Apk ? 2u : 1u); // tile-packed A travels in the weight ring's stages (both loaders arrive)
+            mbar_init(&b_empty[s], (uint32_t)G);   // every MMA issuer of a pair releases the block
         }
         for (int a = 0; a < nacc; ++a)
         {
@@ -1810,25 +1810,31 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
                 for (int g = 0; g < G && pr * G + g < mtiles; ++g, ++ng)
                     if (!flat)
                         tile_coords(pr * G + g, hb[g], hu[g], hv0[g]);
+                if (flat)
+                {
+                    // tile-packed activations: a k-block of A is one contiguous 16 KB image per row tile; it rides in the weight
+                    // ring's stage for the same k-block (one full / empty barrier pair per k-block for the MMA issuers)
+                    for (int kb = 0; kb < ngrp; ++kb)
+                    {
+                        mbar_wait(&b_empty[slot], ph ^ 1u);
+                        mbar_arrive_expect_tx(&b_full[slot], (uint32_t)ng * BM * BK * 2);
+                        for (int g = 0; g < ng; ++g)
+                            bulk_g2s(a_smem + ((size_t)slot * G + g) * (BM * BK * 2),
+                                     reinterpret_cast<const uint8_t *>(p.Apk) + ((size_t)(pr * G + g) * ngrp + kb) * (size_t)(BM * BK * 2),
+                                     BM * BK * 2, &b_full[slot]);
+                        if (++slot == b_stages)
+                        {
+                            slot = 0;
+                            ph ^= 1u;
+                        }
+                    }
+                    continue;
+                }
                 for (int qg = 0; qg < ngrp; ++qg)
                     for (int b = 0; b < p.t_nbox; ++b)
                         for (int g = 0; g < ng; ++g)
                         {
                             mbar_wait(&a_empty[slot], ph ^ 1u);
-                            if (flat)
-                            {
-                                // tile-packed activations: the k-block's A operand is one contiguous 16 KB image
-                                const uint8_t *asrc = reinterpret_cast<const uint8_t *>(p.Apk) +
-                                                      ((size_t)(pr * G + g) * ngrp + qg) * (size_t)(BM * BK * 2);
-                                mbar_arrive_expect_tx(&a_full[slot], BM * BK * 2);
-                                bulk_g2s(a_smem + (size_t)slot * slot_bytes, asrc, BM * BK * 2, &a_full[slot]);
-                                if (++slot == a_slots)
-                                {
-                                    slot = 0;
-                                    ph ^= 1u;
-                                }
-                                continue;
-                            }
                             mbar_arrive_expect_tx(&a_full[slot], box_tx);
                             for (int qi = 0; qi < p.t_cps; ++qi)
                                 tma_load_4d(a_smem + (size_t)slot * slot_bytes + (size_t)qi * p.t_box_bytes, &tmA, &a_full[slot],
@@ -1937,6 +1943,31 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
                 mbar_wait(&acc_empty[acc], ((uint32_t)(tl / nacc) & 1u) ^ 1u);
                 tc_fence_after();
                 uint32_t accum = 0, bstep = 0, b_lo = 0;
+                if (flat)
+                {
+                    // one stage = this k-block's weights + the pair's A images: one wait, four MMAs, one release
+                    for (int kb = 0; kb < nkb; ++kb)
+                    {
+                        mbar_wait(&b_full[bs], bph);
+                        tc_fence_after();
+                        const uint32_t a_lo = a_lo0 + a_smem16 + (uint32_t)(bs * G + g) * (uint32_t)(BM * BK * 2 / 16);
+                        b_lo = b_lo0 + b_smem16 + (uint32_t)bs * bstage16;
+#pragma unroll
+                        for (int j = 0; j < BK / 16; ++j)
+                        {
+                            umma_lh(d_tmem, a_lo + (uint32_t)j * a_step16, a_hi, b_lo + (uint32_t)j * 2u * b_lbo16, b_hi, idesc, accum);
+                            accum = 1;
+                        }
+                        umma_commit(&b_empty[bs]);
+                        if (++bs == b_stages)
+                        {
+                            bs = 0;
+                            bph ^= 1u;
+                        }
+                    }
+                    umma_commit(&acc_full[acc]);
+                    continue;
+                }
                 for (int qg = 0; qg < ngrp; ++qg)
                     for (int b = 0; b < nbox; ++b)
                     {
@@ -2248,9 +2279,10 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st)
         // tile-packed A (the transformer's linear layers): persistent kernel.  The gather / halo layers stay on the
         // one-tile-per-CTA kernel: they are bound by producer + epilogue instruction issue, which three co-resident
         // CTAs (24 producer warps) serve better than one persistent CTA (measured: 20.3 -> 25.2 ms/step persistent).
-        // (the paired kernel can take tile-packed A too -- DMX_TMA_PACKED=1 -- but measured 1.5x slower than the persistent
-        // kernel below on every transformer GEMM, 7.3 -> 10.2 ms/step; not understood yet, so it stays off)
-        static const bool packed_tma = getenv("DMX_TMA_PACKED") != nullptr;
+        // tile-packed A (the transformer's linear layers): the ring kernel with A riding in the weight ring's stages, one
+        // tile per pass, 16 epilogue warps -- 4 stages of 48 KB in flight against the 2 of the persistent kernel below
+        // (7.30 -> 6.87 ms/step); DMX_NO_TMA_PACKED=1 goes back to it
+        static const bool packed_tma = getenv("DMX_NO_TMA_PACKED") == nullptr;
         if (p.Apk && plain && packed_tma && tc_tma_available())
             return launch_gemm_tma_packed(p, Wb, st);
         if (p.Apk)
@@ -2490,6 +2522,25 @@ static int tma_launch_core(const GemmParams &q, const CUtensorMap &tm, const __n
     if (ew_env == 4 * G || ew_env == 8 || ew_env == 16)
         ew = ew_env;
     const size_t fixed = fixed_for(ew);
+    if (q.Apk)
+    {
+        // tile-packed A: a stage holds the k-block's weights and the pair's A images
+        const size_t stage_total = b_stage + (size_t)G * slot_bytes;
+        int stages = (int)((budget - fixed) / stage_total);
+        stages = std::min(stages, std::min(8, std::max(nkb, 2)));
+        if (stages < 2)
+        {
+            set_error("launch_gemm_tma: tile does not fit in shared memory");
+            return -1;
+        }
+        const size_t smem_f = fixed + (size_t)stages * stage_total;
+        const int npairs_f = (mtiles + G - 1) / G;
+        const int total_f = npairs_f * ntiles;
+        tc::gemm_tc_tma_kernel<<<total_f < sms ? total_f : sms, (ew + 2 + G) * 32, smem_f, st>>>(
+            tm, tmc, q, W, bn, plain_out, stages * G, stages, mtiles, ntiles, ew, G, nacc, 0, tma_store, epi_warp);
+        DMX_LAUNCH_CHECK();
+        return 0;
+    }
     // Ring depths.  Streamed weights are what these layers wait for: a stage is refilled only after the MMAs that read it
     // have completed and the copy has crossed L2 -> SM (~1.5 us), so the bytes in flight bound the rate.  Boxes first get a
     // modest ring (4 per tile of the pair), then the weight ring takes what is left, then the boxes the remainder.
@@ -2664,7 +2715,8 @@ int launch_gemm_tma_packed(const GemmParams &p, const void *Wb, cudaStream_t st)
     int acc_cols = 32;
     while (acc_cols < bn)
         acc_cols <<= 1;
-    const int g_want = pg_env ? pg_env : ((4 * acc_cols <= 512 || p.K >= 1024) ? 2 : 1);
+    // measured (transformer GEMMs, ms/step): one tile per pass 6.87, pairs for K >= 1024 only 7.46, pairs everywhere 8.18
+    const int g_want = pg_env ? pg_env : ((4 * acc_cols <= 512) ? 2 : 1);
     return tma_launch_core(q, tm, static_cast<const __nv_bfloat16 *>(Wb), bn, plain, nout, (p.M + tc::BM - 1) / tc::BM,
                            (size_t)tc::BM * tc::BK * 2, p.K / tc::BK, p.M, 1, st, g_want);
 }
