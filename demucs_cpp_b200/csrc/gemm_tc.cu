@@ -994,6 +994,114 @@ __device__ __forceinline__ void epilogue_tile_tmast(const GemmParams &p, const C
     }
 }
 
+// Epilogue for row-major fp32 outputs with the identity mapping whose tile rows are CONSECUTIVE output rows (flat GEMM rows, or
+// positions of one line): per 32 raw columns a lane finishes its own row in registers (bias / GELU / GLU, statistics), the
+// warp turns the 32 x 32 (or 32 x 16) piece around through its private buffer, and every store instruction then writes whole
+// 128-byte (64-byte) row segments -- with the LayerScale residual read the same coalesced way.  No row table, no per-row
+// address arithmetic.  (The tensor-map store above moves such a piece with one instruction, but the copy engine handles a
+// tile row by row: for outputs with a 2 KB row pitch -- the transformer's 512-wide residual stream -- it sustained only
+// ~9 ns per 64-byte row, 17 us per 128 x 256 tile against 2 us of MMAs.)
+__device__ __forceinline__ void epilogue_tile_direct(const GemmParams &p, const int bn, const int n0, const uint32_t lane_addr,
+                                                     const int item, float *crow0, const int nvalid, float *stage, const int c_begin,
+                                                     const int c_step, const int lane)
+{
+    // crow0: output row of tile row q*32 (this warp's first row); nvalid: how many of the warp's 32 rows exist
+    const int ntile_end = (n0 + bn) < p.N ? (n0 + bn) : p.N;
+    const bool valid = lane < nvalid;
+    double st_s = 0.0, st_ss = 0.0;
+    const int gpr = p.glu ? 4 : 8;       // 4-column groups per row of a piece
+    const int rpi = 32 / gpr;            // rows per store instruction
+    const int g = lane % gpr, rsub = lane / gpr;
+    for (int c0 = c_begin; c0 < bn; c0 += c_step)
+    {
+        const int rawc0 = n0 + c0;
+        if (rawc0 >= ntile_end)
+            break;
+        float v[32];
+        tmem_ld32(lane_addr + (uint32_t)c0, v);
+        const int nraw = (ntile_end - rawc0) < 32 ? (ntile_end - rawc0) : 32;
+        if (p.bias)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < nraw)
+                {
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias + rawc0 + j));
+                    v[j] += b.x;
+                    v[j + 1] += b.y;
+                    v[j + 2] += b.z;
+                    v[j + 3] += b.w;
+                }
+        }
+        if (p.act == 1)
+        {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                v[j] = gelu_erf(v[j]);
+        }
+        int nout = nraw;
+        if (p.glu)
+        {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                v[j] = v[2 * j] * sigmoid_ref(v[2 * j + 1]);
+            nout = nraw >> 1;
+        }
+        const int outc0 = p.glu ? (rawc0 >> 1) : rawc0;
+        __syncwarp(); // the previous piece has been read back
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (j < gpr)
+                *reinterpret_cast<float4 *>(&stage[lane * EPI_LD + 4 * j]) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        const int col = outc0 + 4 * g;
+        const bool colok = 4 * g < nout;
+        float4 gam = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.gamma && colok)
+            gam = __ldg(reinterpret_cast<const float4 *>(p.gamma + col));
+        float rs = 0.f, rss = 0.f;
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+            if (it < gpr)
+            {
+                const int r = it * rpi + rsub;
+                if (r < nvalid && colok)
+                {
+                    float4 o = *reinterpret_cast<const float4 *>(&stage[r * EPI_LD + 4 * g]);
+                    float *dst = crow0 + (size_t)r * p.ldc + col;
+                    if (p.gamma)
+                    {
+                        const float4 old = *reinterpret_cast<const float4 *>(dst);
+                        o.x = old.x + gam.x * o.x;
+                        o.y = old.y + gam.y * o.y;
+                        o.z = old.z + gam.z * o.z;
+                        o.w = old.w + gam.w * o.w;
+                    }
+                    *reinterpret_cast<float4 *>(dst) = o;
+                    rs += o.x + o.y + o.z + o.w;
+                    rss += o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
+                }
+            }
+        st_s += (double)rs;
+        st_ss += (double)rss;
+    }
+    (void)valid;
+    if (p.stats)
+    {
+        // the warp's rows belong to one statistics item in the common case (checked by the caller: item >= 0), else -1
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            st_s += __shfl_xor_sync(0xffffffffu, st_s, o);
+            st_ss += __shfl_xor_sync(0xffffffffu, st_ss, o);
+        }
+        if (lane == 0 && item >= 0)
+        {
+            atomicAdd(&p.stats[2 * (size_t)item + 0], st_s);
+            atomicAdd(&p.stats[2 * (size_t)item + 1], st_ss);
+        }
+    }
+}
+
 template <int STAGES, bool VECA, bool HALO>
 __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmC, const GemmParams p,
                                                           const __nv_bfloat16 *__restrict__ Wb, const int bn,
@@ -1728,6 +1836,8 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
         const bool packed_direct = p.out_pack && plain_out == 1 && !p.glu && !p.gamma && !p.addC && !p.rowadd && !p.stats &&
                                    (p.N % 8) == 0;
         const bool use_tmast = tma_store && bulk_ok(p, plain_out);
+        // coalesced direct stores where the output rows are far apart (row pitch >= 1 KB: the tensor-map store is slow there)
+        const bool use_direct = (tma_store & 2) && bulk_ok(p, plain_out);
         const bool need_table = !packed_direct && !use_tmast && !(bulk_ok(p, plain_out) && !p.no_bulk);
         int parity = 0, itm = 0;
         for (int item = blockIdx.x; item < total_items; item += gridDim.x, ++itm)
@@ -1775,7 +1885,15 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
             mbar_wait(&acc_full[acc], (uint32_t)(tl / nacc) & 1u);
             tc_fence_after();
             const uint32_t lane_addr = tmem_base + (uint32_t)acc * acc_cols + ((uint32_t)(q * 32) << 16);
-            if (use_tmast)
+            // rows of this warp: consecutive output rows?  (always within a line; flat rows only while they stay in one item)
+            const int item0 = __shfl_sync(0xffffffffu, ri.item, 0);
+            const int nvalid = __popc(__ballot_sync(0xffffffffu, ri.item >= 0));
+            const bool one_item = __all_sync(0xffffffffu, ri.item < 0 || ri.item == item0);
+            const long long off0 = __shfl_sync(0xffffffffu, ri.outoff, 0);
+            if (use_direct && (one_item || !p.stats) && nvalid > 0)
+                epilogue_tile_direct(p, bn, nt * bn, lane_addr, one_item ? item0 : -1, p.C + off0, nvalid,
+                                     reinterpret_cast<float *>(stage), 32 * csel, 32 * nsel, lane);
+            else if (use_tmast)
                 epilogue_tile_tmast(p, &tmC, bn, nt * bn, lane_addr, ri, stage, 32 * csel, 32 * nsel, lane,
                                     flat ? mt * BM + q * 32 : hv0 + q * 32, flat ? 0 : hb * p.Uo + hu, parity);
             else if (packed_direct)
@@ -2469,7 +2587,13 @@ static int tma_launch_core(const GemmParams &q, const CUtensorMap &tm, const __n
     const bool packed_direct = q.out_pack && plain_out == 1 && !q.glu && !q.gamma && !q.addC && !q.rowadd && !q.stats && (q.N % 8) == 0;
     const bool tmast = tma_store && plain_out == 1 && !q.addC && !q.rowadd && !q.out_pack && !q.out_bf16 && !q.Cbf &&
                        (q.N % (q.glu ? 8 : 4)) == 0;
-    const int epi_warp = packed_direct ? 0 : (tmast ? 4096 : tc::T_EPI_WARP_BYTES + 32 * (int)sizeof(tc::RowInfo));
+    // coalesced direct stores instead of the tensor-map store: measured no better (transformer GEMMs 7.04 -> 7.39 ms/step
+    // when used for the 512-wide residual outputs, conv GEMMs 13.3 -> 13.7 when used everywhere), so only on request
+    static const bool direct_env = getenv("DMX_TMA_DIRECT") != nullptr && atoi(getenv("DMX_TMA_DIRECT")) == 1;
+    const bool direct = tmast && direct_env;
+    if (direct)
+        tma_store |= 2;
+    const int epi_warp = packed_direct ? 0 : (direct ? tc::T_EPI_WARP_BYTES : (tmast ? 4096 : tc::T_EPI_WARP_BYTES + 32 * (int)sizeof(tc::RowInfo)));
     // G = 2 row tiles share every weight block (one MMA issuer and one group of epilogue warps per tile); four accumulators
     // (one pair draining while the next fills) when they fit in TMEM
     int G = (g_env == 1 || g_env == 2) ? g_env : (g_want ? g_want : 2);

@@ -17,7 +17,7 @@ COLS = [("us", "gpu__time_duration.sum", 1e-3, "%.1f"),
         ("regs", "launch__registers_per_thread", 1, "%d"),
         ("smem KB", "launch__shared_mem_per_block_dynamic", None, "%.0f"),
         ("grid x block", None, None, None)]
-UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "ns": 1.0, "us": 1e3, "ms": 1e6, "s": 1e9,
+UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "ns": 1.0, "us": 1e3, "ms": 1e6, "Kbyte/block": 1e3, "byte/block": 1.0, "s": 1e9,
         "usecond": 1e3, "nsecond": 1.0, "msecond": 1e6, "second": 1e9}
 
 
