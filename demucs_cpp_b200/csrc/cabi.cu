@@ -607,6 +607,16 @@ int64_t dmx_debug_tap(dmx_model *m, const char *name, float *dst, int64_t capaci
         set_error("dmx_debug_tap: copy failed");
         return -1;
     }
+    if (t.swapped)
+    {
+        // stored [b][d2][d1][C]; reported [b][d1][d2][C]
+        std::vector<float> tmp(dst, dst + n);
+        for (int64_t b = 0; b < m->lastB; ++b)
+            for (int64_t i2 = 0; i2 < t.d2; ++i2)
+                for (int64_t i1 = 0; i1 < t.d1; ++i1)
+                    memcpy(dst + ((b * t.d1 + i1) * t.d2 + i2) * t.C, tmp.data() + ((b * t.d2 + i2) * t.d1 + i1) * t.C,
+                           (size_t)t.C * sizeof(float));
+    }
     if (t.minus)
     {
         std::vector<float> sk((size_t)n);

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(FFT_THREADS) istft_frames_kernel(const float *
                                                                    const float2 *__restrict__ meanstd, // [B] (mean,std)
                                                                    const float *__restrict__ window,
                                                                    const float2 *__restrict__ tw,
-                                                                   float2 *__restrict__ frames)
+                                                                   float2 *__restrict__ frames, const size_t sk, const size_t st_)
 {
     extern __shared__ float2 sm[];
     float2 *xa = sm, *xb = sm + NFFT, *y = sm + 2 * NFFT;
@@ -238,7 +238,9 @@ __global__ void __launch_bounds__(FFT_THREADS) istft_frames_kernel(const float *
 #pragma unroll
     for (int i = 0; i < NBINS / FFT_THREADS; ++i)
     {
-        const float *src = xout + (((size_t)b * NBINS + threadIdx.x + i * FFT_THREADS) * LE + t) * C + 4 * s0;
+        // frame-major input (production): the bins of frame t are 64 contiguous bytes apart, a warp reads 2 KB in one piece;
+        // bin-major (the stand-alone dmx_istft_segment): 21 KB apart
+        const float *src = xout + (size_t)b * NBINS * LE * C + (size_t)(threadIdx.x + i * FFT_THREADS) * sk + (size_t)t * st_ + 4 * s0;
         va[i] = __ldg(reinterpret_cast<const float4 *>(src));
         vb[i] = pair ? __ldg(reinterpret_cast<const float4 *>(src + 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
@@ -342,10 +344,12 @@ int launch_stft(const float *mix, int B, const float *window, const float *tw, f
 
 int launch_istft(const float *xout, int B, int S, const float *meanstd, const float *window, const float *tw,
                  const float *wss, const float *xt_out, const float *meanstd_t, float *frames_scratch,
-                 float *out, cudaStream_t st)
+                 float *out, cudaStream_t st, int frame_major)
 {
+    const size_t C = 4 * (size_t)S;
     istft_frames_kernel<<<dim3(LE, (S + 1) / 2, B), FFT_THREADS, ISTFT_SMEM, st>>>(
-        xout, S, (const float2 *)meanstd, window, (const float2 *)tw, (float2 *)frames_scratch);
+        xout, S, (const float2 *)meanstd, window, (const float2 *)tw, (float2 *)frames_scratch, frame_major ? C : (size_t)LE * C,
+        frame_major ? (size_t)NBINS * C : C);
     DMX_LAUNCH_CHECK();
     istft_ola_kernel<<<dim3((SEG + 255) / 256, S, B), 256, 0, st>>>(
         (const float2 *)frames_scratch, S, wss, xt_out, (const float2 *)meanstd_t, (float2 *)out);

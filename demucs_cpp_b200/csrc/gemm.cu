@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(G_THREADS) gemm_kernel(const GemmParams p)
                     done = true; // whole group shares one destination pixel
                     if (uu >= 0 && uu < p.Uout && vv >= 0 && vv < p.Vout)
                     {
-                        float *dst = p.C + (((size_t)rc.b * p.Uout + uu) * p.Vout + vv) * p.ldc + co0;
+                        float *dst = p.C + (p.out_vu ? ((size_t)rc.b * p.Vout + vv) * p.Uout + uu : ((size_t)rc.b * p.Uout + uu) * p.Vout + vv) * p.ldc + co0;
                         float o[4];
 #pragma unroll
                         for (int e = 0; e < 4; ++e)
@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(G_THREADS) gemm_kernel(const GemmParams p)
                             const int v2 = rc.vo * p.ovs + r2 * p.ovr + p.ovo;
                             if (u2 >= 0 && u2 < p.Uout && v2 >= 0 && v2 < p.Vout)
                             {
-                                float *dst = p.C + (((size_t)rc.b * p.Uout + u2) * p.Vout + v2) * p.ldc + co;
+                                float *dst = p.C + (p.out_vu ? ((size_t)rc.b * p.Vout + v2) * p.Uout + u2 : ((size_t)rc.b * p.Uout + u2) * p.Vout + v2) * p.ldc + co;
                                 float o = val[j0 + e];
                                 if (p.rowadd)
                                     o += __ldg(p.rowadd + (size_t)rc.uo * p.rowadd_ld + co);

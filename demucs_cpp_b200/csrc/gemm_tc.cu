@@ -204,7 +204,9 @@ __device__ __forceinline__ void store_group4_scatter(const GemmParams &p, const 
             const int uu = ri.uu0 + r * p.our, vv = ri.vv0 + r * p.ovr;
             if (uu >= 0 && uu < p.Uout && vv >= 0 && vv < p.Vout)
             {
-                float *dst = p.C + ri.outoff + ((long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.ldc + co;
+                float *dst = p.C + ri.outoff +
+                             (p.out_vu ? (long long)r * p.our + (long long)r * p.ovr * p.Uout
+                                       : (long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.ldc + co;
                 float v = o[e];
                 if (p.rowadd)
                     v += __ldg(p.rowadd + (size_t)ri.uo * p.rowadd_ld + co);
@@ -230,7 +232,9 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
     const int uu = ri.uu0 + r * p.our, vv = ri.vv0 + r * p.ovr;
     if ((unsigned)uu < (unsigned)p.Uout && (unsigned)vv < (unsigned)p.Vout)
     {
-        float *dst = p.C + ri.outoff + ((long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.ldc + co;
+        float *dst = p.C + ri.outoff +
+                     (p.out_vu ? (long long)r * p.our + (long long)r * p.ovr * p.Uout
+                               : (long long)r * p.our * p.Vout + (long long)r * p.ovr) * p.ldc + co;
         if (p.rowadd)
         {
             const float4 ra = __ldg(reinterpret_cast<const float4 *>(p.rowadd + (size_t)ri.uo * p.rowadd_ld + co));
@@ -1170,7 +1174,7 @@ __global__ void __launch_bounds__(THREADS, 3) gemm_tc_kernel(const __grid_consta
         RowInfo ri;
         ri.uu0 = rc.uo * p.ous + p.ouo;
         ri.vv0 = rc.vo * p.ovs + p.ovo;
-        ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
+        ri.outoff = (p.out_vu ? ((long long)rc.b * p.Vout + ri.vv0) * p.Uout + ri.uu0 : ((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
         ri.uo = rc.uo;
         ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
         ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m; // per-item padding to whole 128-row tiles
@@ -1589,7 +1593,7 @@ __global__ void __launch_bounds__(p_threads(PROD), 1)
                 RowInfo ri;
                 ri.uu0 = rc.uo * p.ous + p.ouo;
                 ri.vv0 = rc.vo * p.ovs + p.ovo;
-                ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
+                ri.outoff = (p.out_vu ? ((long long)rc.b * p.Vout + ri.vv0) * p.Uout + ri.uu0 : ((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
                 ri.uo = rc.uo;
                 ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
                 ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m;
@@ -1871,7 +1875,7 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
                 }
                 ri.uu0 = rc.uo * p.ous + p.ouo;
                 ri.vv0 = rc.vo * p.ovs + p.ovo;
-                ri.outoff = (((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
+                ri.outoff = (p.out_vu ? ((long long)rc.b * p.Vout + ri.vv0) * p.Uout + ri.uu0 : ((long long)rc.b * p.Uout + ri.uu0) * p.Vout + ri.vv0) * p.ldc;
                 ri.uo = rc.uo;
                 ri.item = valid ? (p.stat_per_u ? rc.b * p.Uo + rc.uo : rc.b) : -1;
                 ri.prow = p.pack_T ? rc.b * p.pack_T + rc.uo * p.Vo + rc.vo : m;

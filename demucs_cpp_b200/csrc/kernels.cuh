@@ -57,6 +57,7 @@ struct GemmParams
     float *C = nullptr;
     int ldc = 0, Nco = 0;
     int Uout = 1, Vout = 1, ous = 1, our = 0, ouo = 0, ovs = 1, ovr = 0, ovo = 0;
+    int out_vu = 0; // output stored [b][v][u][c] instead of [b][u][v][c] (the last frequency decoder: frame-major for the iSTFT)
     // filled in by launch_gemm_tc: reciprocals for fast_div by Uo*Vo, Vo (row -> (b, u_o, v_o)) and Nco
     unsigned long long div_per = 0, div_vo = 0, div_nco = 0;
     int no_bulk = 0; // development switch: keep the transposing epilogue
@@ -113,9 +114,11 @@ int launch_gemm_tc(const GemmParams &p, const void *Wb, cudaStream_t st);
 int fft_init_device();
 int launch_stft(const float *mix, int B, const float *window, const float *tw, float *spec, double *stats,
                 cudaStream_t st);
+// xout element (b, bin k, frame t, channel c) sits at ((b * 2048 * 336) * C) + k * sk + t * st_ + c: bin-major
+// (sk = 336 * C, st_ = C) or frame-major (sk = C, st_ = 2048 * C; what the last decoder writes in production)
 int launch_istft(const float *xout, int B, int S, const float *meanstd, const float *window, const float *tw,
                  const float *wss, const float *xt_out, const float *meanstd_t, float *frames_scratch, float *out,
-                 cudaStream_t st);
+                 cudaStream_t st, int frame_major = 0);
 
 // ---------------------------------------------------------------------------------------------
 // pointwise.cu

@@ -607,6 +607,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             q.ous = 4;
             q.our = 1;
             q.ouo = -2;
+            q.out_vu = i == 3; // the spectrogram heads leave frame-major ([b][t][bin][c]): what the iSTFT reads in one piece
             q.act = i < 3 ? 1 : 0;
             if (i < 3)
                 q.addC = m->e[2 - i]; // the next decoder's skip (src/encdec.cpp:172), added once here
@@ -683,7 +684,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
         ProfScope ps(m, PC_ISTFT_FRAMES, 0.0,
                      (double)B * ((double)4 * S * NBINS * T * 4 + (double)2 * S * SEG * 4 + (double)S * 2 * SEG * 4), 2);
         if (launch_istft(m->dx[3], B, S, m->meanstd_x, m->window, m->tw, m->wss, m->dxt[3], m->meanstd_t, m->frames,
-                         d_out, st))
+                         d_out, st, 1))
             return -1;
     }
 
@@ -714,7 +715,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     const char *tn[4] = {"xt_2", "xt_1", "xt_0", "xt_out"};
     for (int i = 0; i < 4; ++i)
     {
-        set_tap(m, fn[i], m->dx[i], FREQS[3 - i], T, m->dec[i].Cout, i < 3 ? m->e[2 - i] : nullptr);
+        set_tap(m, fn[i], m->dx[i], FREQS[3 - i], T, m->dec[i].Cout, i < 3 ? m->e[2 - i] : nullptr, i == 3);
         set_tap(m, tn[i], m->dxt[i], 1, TLENS[3 - i], m->tdec[i].Cout, i < 3 ? m->te[2 - i] : nullptr);
     }
     return 0;

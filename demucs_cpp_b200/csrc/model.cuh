@@ -125,6 +125,7 @@ struct Tap
     float *ptr = nullptr;
     int64_t d1 = 0, d2 = 0, C = 0; // per batch item dims (channels-last)
     const float *minus = nullptr;   // the buffer holds value + minus (a pre-added decoder skip): the tap reports value
+    bool swapped = false;           // the buffer is stored [b][d2][d1][C] (frame-major x_out): the tap reports [b][d1][d2][C]
 };
 
 } // namespace dmx

@@ -595,11 +595,12 @@ struct Fwd
 };
 
 static void set_tap(dmx_model *m, const char *name, float *p, int64_t d1, int64_t d2, int64_t C,
-                    const float *minus = nullptr)
+                    const float *minus = nullptr, bool swapped = false)
 {
     Tap t;
     t.ptr = p;
     t.minus = minus;
+    t.swapped = swapped;
     t.d1 = d1;
     t.d2 = d2;
     t.C = C;
