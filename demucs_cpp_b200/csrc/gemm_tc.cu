@@ -99,6 +99,12 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint
 }
 
 // Instruction descriptor for kind::f16: D = F32, A = B = BF16, both K-major, M = 128, N = bn.
+// The same for kind::tf32: A = B = TF32 (fp32 words in shared memory), K = 8 per instruction.
+__device__ __forceinline__ uint32_t make_idesc_tf32(int bn)
+{
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
 __device__ __forceinline__ uint32_t make_idesc(int bn)
 {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
@@ -1762,6 +1768,21 @@ __device__ __forceinline__ void umma_lh(uint32_t tmem_d, uint32_t a_lo, uint32_t
                  : "memory");
 }
 
+__device__ __forceinline__ void umma_lh_tf32(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                             uint32_t idesc, uint32_t accum)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 ".reg .b64 da, db;\n"
+                 "mov.b64 da, {%1, %2};\n"
+                 "mov.b64 db, {%3, %4};\n"
+                 "setp.ne.b32 p, %6, 0;\n"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n"
+                 "}\n" ::"r"(tmem_d),
+                 "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accum)
+                 : "memory");
+}
+
 __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
     gemm_tc_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmC, const GemmParams p,
                        const __nv_bfloat16 *__restrict__ Wt, const int bn, const int plain_out, const int a_slots, const int b_stages,
@@ -1775,7 +1796,8 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int nkb = (p.K + BK - 1) / BK;
+    const int kblk = p.t_tf32 ? 32 : BK; // K per weight block: 128 bytes per weight row either way
+    const int nkb = (p.K + kblk - 1) / kblk;
     const int npairs = (mtiles + G - 1) / G;
     const int total_items = npairs * ntiles;
     const int ewg = ew / G; // epilogue warps per tile of a pair
@@ -2007,7 +2029,8 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
         const int g = warp - (ew + 2);
         if (lane == 0 && g < G)
         {
-            const uint32_t idesc = make_idesc(bn);
+            const bool tf32 = p.t_tf32 != 0;
+            const uint32_t idesc = tf32 ? make_idesc_tf32(bn) : make_idesc(bn);
             const uint32_t b_lbo16 = (uint32_t)bn;                                  // (bn * 16 bytes) >> 4
             // A descriptors: swizzled K-major boxes (32 bytes per K = 16 step), or the canonical no-swizzle image of tile-packed
             // activations (two 2 KB core-matrix columns per step)
@@ -2018,7 +2041,8 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
             const uint32_t b_hi = (uint32_t)(b_proto >> 32), b_lo0 = (uint32_t)b_proto;
             const uint32_t a_smem16 = smem_u32(a_smem) >> 4, box16 = (uint32_t)p.t_box_bytes >> 4, slot16 = slot_bytes >> 4;
             const uint32_t b_smem16 = smem_u32(b_smem) >> 4, bstage16 = b_stage_bytes >> 4;
-            const int spc = p.t_kw >> 4, cps = p.t_cps, tpb = p.t_tpb, nbox = p.t_nbox, ngrp = p.t_nchunk / p.t_cps;
+            const int spc = tf32 ? (p.t_kw >> 3) : (p.t_kw >> 4), cps = p.t_cps, tpb = p.t_tpb, nbox = p.t_nbox,
+                      ngrp = p.t_nchunk / p.t_cps;
             const uint32_t shift16 = (uint32_t)p.t_shift16;
             const int slots_per_item = ngrp * nbox * G;
             int itm = 0;
@@ -2113,7 +2137,10 @@ __global__ void __launch_bounds__((T_MAX_EW + 4) * 32, 1)
                                         }
                                         b_lo = b_lo0 + b_smem16 + (uint32_t)bs * bstage16;
                                     }
-                                    umma_lh(d_tmem, a_lo, a_hi, b_lo, b_hi, idesc, accum);
+                                    if (tf32)
+                                        umma_lh_tf32(d_tmem, a_lo, a_hi, b_lo, b_hi, idesc, accum);
+                                    else
+                                        umma_lh(d_tmem, a_lo, a_hi, b_lo, b_hi, idesc, accum);
                                     accum = 1;
                                     b_lo += 2 * b_lbo16;
                                     if (++bstep == 4)
@@ -2183,6 +2210,50 @@ size_t tc_packed_index(int K, int N, int k, int n)
     const int nkb = (K + tc::BK - 1) / tc::BK;
     const int nt = n / bn, nn = n % bn, kb = k / tc::BK, kr = k % tc::BK;
     return (((size_t)nt * nkb + kb) * 8 + kr / 8) * ((size_t)bn * 8) + (size_t)nn * 8 + (kr % 8);
+}
+
+// ---- tf32 variant of the plan: fp32 activations in 32-channel chunks (128-byte rows, SWIZZLE_128B) ----
+int tc_tma_plan32(int ntaps, const int *du, const int *dv, int Cin, bool share_dv, TmaPlan *pl)
+{
+    // the bf16 planner with a multiple-of-64 channel count gives the box / tap structure; the chunking is replaced
+    if (Cin % 4 || tc_tma_plan(ntaps, du, dv, 64, share_dv, pl))
+        return -1;
+    pl->cw = pl->kw = 32;
+    pl->nchunk = (Cin + 31) / 32;
+    pl->pitch = 128;
+    pl->layout = 2;
+    pl->cpitch = Cin;
+    pl->box_bytes = (pl->rows * pl->pitch + 1023) / 1024 * 1024;
+    pl->cps = 1;
+    return 0;
+}
+
+int tc_tma_k32(const TmaPlan &pl) { return pl.nchunk * 32 * pl.ntap; }
+
+int tc_tma_korig32(const TmaPlan &pl, int Cin, int kp)
+{
+    const int cc = kp % 32;
+    int r = kp / 32;
+    const int k = r % pl.tpb;
+    r /= pl.tpb;
+    const int b = r % pl.nbox, q = r / pl.nbox;
+    const int c = q * 32 + cc;
+    return c < Cin ? pl.tap_id[b * pl.tpb + k] * Cin + c : -1;
+}
+
+// fp32 weight image for kind::tf32: [n-tile][k-block of 32][kc = (k % 32) / 4][n % bn][k % 4]
+size_t tc_packed_elems32(int K, int N)
+{
+    const int bn = tc_tile_n(N);
+    return (size_t)((N + bn - 1) / bn) * ((K + 31) / 32) * bn * 32;
+}
+
+size_t tc_packed_index32(int K, int N, int k, int n)
+{
+    const int bn = tc_tile_n(N);
+    const int nkb = (K + 31) / 32;
+    const int nt = n / bn, nn = n % bn, kb = k / 32, kr = k % 32;
+    return (((size_t)nt * nkb + kb) * 8 + kr / 4) * ((size_t)bn * 4) + (size_t)nn * 4 + (kr % 4);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -2570,9 +2641,10 @@ static int tma_launch_core(const GemmParams &q, const CUtensorMap &tm, const __n
     static const int g_env = getenv("DMX_TMA_G") ? atoi(getenv("DMX_TMA_G")) : 0;
     static const bool no_res = getenv("DMX_TMA_NO_RESIDENT") != nullptr;
     static const bool no_tmast = getenv("DMX_TMA_NO_STORE") != nullptr;
-    const size_t b_stage = (size_t)bn * tc::BK * 2;
+    const size_t b_stage = (size_t)bn * tc::BK * 2; // = bn x 32 fp32 for the tf32 variant
     const size_t budget = 220 * 1024;
-    const int nkb = (q.K + tc::BK - 1) / tc::BK;
+    const int kblk = q.t_tf32 ? 32 : tc::BK;
+    const int nkb = (q.K + kblk - 1) / kblk;
     const int ntiles = (q.N + bn - 1) / bn;
     int acc_cols = 32;
     while (acc_cols < bn)
@@ -2708,7 +2780,9 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
         set_error("launch_gemm_tma: cuTensorMapEncodeTiled is not available from this driver");
         return -1;
     }
-    if (!p.Aimg || !p.Wt || p.M <= 0 || p.N <= 0 || p.K != p.ntaps * p.Cin || p.Cin % 16 || p.pro || p.A2 || p.Apk)
+    const bool tf32 = p.Wt32 != nullptr;
+    if ((!tf32 && (!p.Aimg || !p.Wt || p.Cin % 16)) || (tf32 && (!p.A || p.Cin % 4 || p.lda % 4)) || p.M <= 0 || p.N <= 0 ||
+        p.K != p.ntaps * p.Cin || p.pro || p.A2 || p.Apk || p.sv != 1)
     {
         set_error("launch_gemm_tma: unsupported problem");
         return -1;
@@ -2716,7 +2790,7 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
     static const bool share_env = getenv("DMX_TMA_NO_SHARE") == nullptr;
     const bool share = share_env && !p.t_noshare;
     TmaPlan pl;
-    if (tc_tma_plan(p.ntaps, p.du, p.dv, p.Cin, share, &pl))
+    if (tf32 ? tc_tma_plan32(p.ntaps, p.du, p.dv, p.Cin, share, &pl) : tc_tma_plan(p.ntaps, p.du, p.dv, p.Cin, share, &pl))
     {
         set_error("launch_gemm_tma: no plan for this tap set");
         return -1;
@@ -2747,6 +2821,9 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
     q.t_pitch = pl.pitch;
     q.t_box_bytes = pl.box_bytes;
     q.t_layout = pl.layout;
+    q.t_tf32 = tf32 ? 1 : 0;
+    if (tf32)
+        q.K = tc_tma_k32(pl); // K' includes the zero-filled channels of the last chunk
     const size_t slot_bytes = (size_t)pl.cps * pl.box_bytes; // one ring slot = the cps chunk boxes of a plane
     const int plain = (p.ous == 1 && p.ovs == 1 && p.our == 0 && p.ovr == 0 && p.ouo == 0 && p.ovo == 0 && p.Uout == p.Uo &&
                        p.Vout == p.Vo && p.Nco >= nout && (p.ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0 &&
@@ -2768,19 +2845,22 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
     const int items = p.M / (p.Uo * p.Vo);
     CUtensorMap tm;
     {
-        const cuuint64_t cp = (cuuint64_t)(p.Aimg_ld ? p.Aimg_ld : p.Cin);
-        if ((int)cp != pl.cpitch)
+        const cuuint64_t cp = (cuuint64_t)(tf32 ? p.lda : (p.Aimg_ld ? p.Aimg_ld : p.Cin));
+        if (!tf32 && (int)cp != pl.cpitch)
         {
             set_error("launch_gemm_tma: the image's row pitch does not match the plan");
             return -1;
         }
-        const cuuint64_t dims[4] = {cp, (cuuint64_t)p.Vi, (cuuint64_t)p.Ui, (cuuint64_t)items};
-        const cuuint64_t strides[3] = {cp * 2, (cuuint64_t)p.Vi * cp * 2, (cuuint64_t)p.Ui * p.Vi * cp * 2};
+        const cuuint64_t esz = tf32 ? 4 : 2;
+        // tf32: the channel extent is Cin, so the last 32-channel chunk of e.g. 48 channels is zero-filled past channel 47
+        const cuuint64_t dims[4] = {tf32 ? (cuuint64_t)p.Cin : cp, (cuuint64_t)p.Vi, (cuuint64_t)p.Ui, (cuuint64_t)items};
+        const cuuint64_t strides[3] = {cp * esz, (cuuint64_t)p.Vi * cp * esz, (cuuint64_t)p.Ui * p.Vi * cp * esz};
         const cuuint32_t box[4] = {(cuuint32_t)pl.cw, (cuuint32_t)pl.rows, 1, 1};
         const cuuint32_t es[4] = {1, 1, 1, 1};
-        const CUtensorMapSwizzle sw = pl.cw == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
-                                                  : (pl.cw == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-        const CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(p.Aimg), dims, strides, box, es,
+        const CUtensorMapSwizzle sw = pl.pitch == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                                      : (pl.pitch == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+        const CUresult r = enc(&tm, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                               const_cast<void *>(tf32 ? static_cast<const void *>(p.A) : p.Aimg), dims, strides, box, es,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS)
@@ -2789,7 +2869,8 @@ int launch_gemm_tma(const GemmParams &p, cudaStream_t st)
             return -1;
         }
     }
-    return tma_launch_core(q, tm, static_cast<const __nv_bfloat16 *>(p.Wt), bn, plain | vscat, nout, mtiles_of_lines(items, p.Uo, q.halo_tpr),
+    return tma_launch_core(q, tm, static_cast<const __nv_bfloat16 *>(tf32 ? p.Wt32 : p.Wt), bn, plain | vscat, nout,
+                           mtiles_of_lines(items, p.Uo, q.halo_tpr),
                            slot_bytes, pl.nbox * (pl.nchunk / pl.cps), p.Vout, (long long)items * p.Uout, st);
 }
 

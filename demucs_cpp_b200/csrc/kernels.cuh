@@ -76,6 +76,10 @@ struct GemmParams
     int t_tpb = 0, t_shift16 = 0; // taps per box; descriptor offset (16-byte units) between consecutive taps of a box
     int t_cw = 0, t_kw = 0, t_nchunk = 0, t_cps = 1, t_pitch = 0, t_box_bytes = 0, t_layout = 0;
     int Aimg_ld = 0; // channels per image row of Aimg (0: Cin)
+    // tf32 variant: A is the ordinary fp32 channels-last tensor p.A (lda channels per row), read through a tensor map in
+    // 32-channel chunks (128-byte rows) and multiplied with kind::tf32 MMAs; Wt32 = fp32 weights in that kernel's K order
+    const void *Wt32 = nullptr;
+    int t_tf32 = 0;
     int t_noshare = 0; // set by the caller: one box per tap instead of one per plane (test hook)
 };
 
@@ -95,6 +99,13 @@ struct TmaPlan
 };
 int tc_tma_plan(int ntaps, const int *du, const int *dv, int Cin, bool share_dv, TmaPlan *pl);
 int tc_tma_cpitch(int C); // image row pitch in channels for a C-channel tensor
+// the same for the tf32 variant (fp32 activations, 32-channel chunks; channels beyond Cin are zero-filled by the copy and
+// meet zero weight rows): plan, K' size, original K index of K' index kp (-1: padding), packed fp32 image size / index
+int tc_tma_plan32(int ntaps, const int *du, const int *dv, int Cin, bool share_dv, TmaPlan *pl);
+int tc_tma_k32(const TmaPlan &pl);
+int tc_tma_korig32(const TmaPlan &pl, int Cin, int kp);
+size_t tc_packed_elems32(int K, int N);
+size_t tc_packed_index32(int K, int N, int k, int n);
 // original K index (tap * Cin + c) of K' index kp
 int tc_tma_korig(const TmaPlan &pl, int Cin, int kp);
 int launch_gemm_tma(const GemmParams &p, cudaStream_t st);

@@ -145,11 +145,13 @@ int model_finalize(dmx_model *m)
         m->enc[i].C = C;
         m->tenc[i].Cin = cin_t;
         m->tenc[i].C = C;
-        if (pack_conv(m, m->enc[i].conv, e + ".conv.weight", e + ".conv.bias", C, cin_f, 8, false) ||
-            pack_conv(m, m->enc[i].rewrite, e + ".rewrite.weight", e + ".rewrite.bias", 2 * C, C, 1, true) ||
+        // tf32 ring-kernel images: the 1x1 rewrites of both branches and the strided convolutions of frequency encoders 1-3
+        const TmaPlan p_rw = enc_plan32(C, false), p_cv = enc_plan32(cin_f >= 48 ? cin_f : 48, true);
+        if (pack_conv(m, m->enc[i].conv, e + ".conv.weight", e + ".conv.bias", C, cin_f, 8, false, nullptr, i > 0 ? &p_cv : nullptr) ||
+            pack_conv(m, m->enc[i].rewrite, e + ".rewrite.weight", e + ".rewrite.bias", 2 * C, C, 1, true, nullptr, &p_rw) ||
             pack_dconv(m, m->enc[i].dc, e, C) ||
             pack_conv(m, m->tenc[i].conv, te + ".conv.weight", te + ".conv.bias", C, cin_t, 8, false) ||
-            pack_conv(m, m->tenc[i].rewrite, te + ".rewrite.weight", te + ".rewrite.bias", 2 * C, C, 1, true) ||
+            pack_conv(m, m->tenc[i].rewrite, te + ".rewrite.weight", te + ".rewrite.bias", 2 * C, C, 1, true, nullptr, &p_rw) ||
             pack_dconv(m, m->tenc[i].dc, te, C))
             return -1;
         if (dconv_mma_rw_supported(C, m->enc[i].dc.hid, LE))
@@ -395,6 +397,13 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
     };
     if (fork())
         return -1;
+    // bf16 mode: the 48- / 96-channel 1x1 rewrites of the encoders run on the ring kernel's tf32 variant, straight from the
+    // fp32 activations (per 16 segments: 212 -> 142, 114 -> 92, 217 -> 185 us).  The deeper rewrites and the strided
+    // convolutions of frequency encoders 1-3 were slower there (fp32 operands double the L2 -> SM traffic; 374 -> 440,
+    // 167 -> 231, 164 -> 204 us) and stay on the one-tile gather kernel (DMX_TF32_CONV=1 / DMX_NO_TF32_ENC=1 to switch)
+    static const bool tf32_env = getenv("DMX_NO_TF32_ENC") == nullptr;
+    static const bool tf32_conv = getenv("DMX_TF32_CONV") != nullptr;
+    const bool tf32e = tf32_env && m->use_tma && m->precision == DMX_PRECISION_BF16;
     const float *xin_f = m->spec, *xin_t = m->xt_in;
     for (int i = 0; i < 4; ++i)
     {
@@ -429,6 +438,8 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             GemmParams r = f.base(m->cA_t, C, C, te.rewrite, m->te[i], C, 1, TLENS[i + 1], 1, TLENS[i + 1]);
             r.glu = 1;
             r.Nco = C;
+            if (tf32e && C <= 96)
+                r.Wt32 = te.rewrite.Wt32;
             f.gemm(r, PC_GEMM_CONV);
         }
         // freq: conv k8 s4 p2 along frequency (+GELU), frames are independent
@@ -448,6 +459,8 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
                     p.dv[t] = 0;
                 }
                 p.act = 1;
+                if (tf32e && i > 0 && tf32_conv)
+                    p.Wt32 = fe.conv.Wt32;
                 f.gemm(p, PC_GEMM_CONV);
             }
             if (fused_rw)
@@ -474,6 +487,8 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
                     r.rowadd = m->freq_emb2;
                     r.rowadd_ld = 48;
                 }
+                else if (tf32e && C <= 96)
+                    r.Wt32 = fe.rewrite.Wt32;
                 f.gemm(r, PC_GEMM_CONV);
             }
         }

@@ -25,6 +25,7 @@ struct Packed
     float *bias = nullptr;
     void *Wb = nullptr; // bf16 tensor-core image
     void *Wt = nullptr; // the same in the K order of the TMA-fed kernel (layers that run on it)
+    void *Wt32 = nullptr; // fp32 image in the K order of that kernel's tf32 variant
     int K = 0, N = 0, ldw = 0;
 };
 

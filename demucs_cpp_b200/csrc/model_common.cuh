@@ -77,7 +77,8 @@ static inline uint16_t f32_to_bf16_bits(float f)
 // Generic packer: element (k, n) of the GEMM B operand given by f(k, n); bias by fb(n).
 // If glu: output columns are interleaved so that packed 2j = original j, packed 2j+1 = original j + N/2.
 template <typename FW, typename FB>
-static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb, const TmaPlan *tp = nullptr, int tpCin = 0)
+static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb, const TmaPlan *tp = nullptr, int tpCin = 0,
+                const TmaPlan *tp32 = nullptr)
 {
     p.K = K;
     p.N = N;
@@ -118,12 +119,29 @@ static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb, c
             return -1;
         DMX_CUDA(cudaMemcpy(p.Wt, wt.data(), wt.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
     }
+    if (tp32)
+    {
+        // fp32 image for the tf32 variant: K' covers whole 32-channel chunks, rows of channels past Cin are zero
+        const int Kp = tc_tma_k32(*tp32);
+        std::vector<float> wt(tc_packed_elems32(Kp, N), 0.f);
+        for (int kp = 0; kp < Kp; ++kp)
+        {
+            const int k = tc_tma_korig32(*tp32, tpCin, kp);
+            if (k < 0)
+                continue;
+            for (int n = 0; n < N; ++n)
+                wt[tc_packed_index32(Kp, N, kp, n)] = w[(size_t)k * p.ldw + n];
+        }
+        if (dev_alloc(m, &p.Wt32, wt.size() * sizeof(float)))
+            return -1;
+        DMX_CUDA(cudaMemcpy(p.Wt32, wt.data(), wt.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
     return 0;
 }
 
 // Conv weight (Cout, Cin, ntaps) row-major -> B[tap*Cin + c][cout]   (src/conv.hpp:97-110 equivalent)
 static int pack_conv(dmx_model *m, Packed &p, const std::string &wname, const std::string &bname, int Cout, int Cin,
-                     int ntaps, bool glu, const TmaPlan *tp = nullptr)
+                     int ntaps, bool glu, const TmaPlan *tp = nullptr, const TmaPlan *tp32 = nullptr)
 {
     const HostTensor *w = get(m, wname, (size_t)Cout * Cin * ntaps);
     const HostTensor *b = get(m, bname, Cout);
@@ -137,7 +155,20 @@ static int pack_conv(dmx_model *m, Packed &p, const std::string &wname, const st
             const int tap = k / Cin, c = k % Cin;
             return wd[((size_t)n * Cin + c) * ntaps + tap];
         },
-        [=](int n) { return bd[n]; }, tp, Cin);
+        [=](int n) { return bd[n]; }, tp, Cin, tp32);
+}
+
+// tf32 plans of the encoders: the 1x1 rewrite (one tap) and the k8 s4 convolution along frequency (eight planes
+// 4 u - 2 ... 4 u + 5, src/encdec.cpp:24-50); both read the fp32 activations as they are
+static TmaPlan enc_plan32(int C, bool conv8)
+{
+    int du[9] = {0}, dv[9] = {0};
+    const int nt = conv8 ? 8 : 1;
+    for (int t = 0; t < nt; ++t)
+        du[t] = conv8 ? t - 2 : 0;
+    TmaPlan pl;
+    tc_tma_plan32(nt, du, dv, C, true, &pl);
+    return pl;
 }
 
 // The K order of the TMA-fed kernel for the decoders' "rewrite" convolutions: 3 x 3 over (frequency, frames), tap =
@@ -367,7 +398,7 @@ struct Fwd
         if (p.gamma)
             bytes += (double)p.M * nout * 4.0;
         ProfScope ps(m, cls, 2.0 * (double)p.M * (double)p.N * (double)p.K, bytes);
-        if (m->precision == DMX_PRECISION_BF16 && p.Aimg && p.Wt)
+        if (m->precision == DMX_PRECISION_BF16 && ((p.Aimg && p.Wt) || p.Wt32))
             rc = launch_gemm_tma(p, st);
         else if (m->precision == DMX_PRECISION_BF16 && p.Wb)
             rc = launch_gemm_tc(p, p.Wb, st);
