@@ -266,7 +266,8 @@ __device__ __forceinline__ void store_group4_scatter_vec(const GemmParams &p, co
             o[2] = old.z + g.z * o[2];
             o[3] = old.w + g.w * o[3];
         }
-        *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+        if (!p.skip_c)
+            *reinterpret_cast<float4 *>(dst) = make_float4(o[0], o[1], o[2], o[3]);
         if (p.Cbf)
         {
             uint2 pk2;

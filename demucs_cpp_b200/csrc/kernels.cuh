@@ -67,6 +67,7 @@ struct GemmParams
     // optional bf16 copy of the output, same element indexing as C (identity or scatter mapping, not with bulk / packed
     // outputs): the channels-last IMAGE the next convolution's TMA loads read
     void *Cbf = nullptr;
+    int skip_c = 0; // scatter mapping with Cbf: do not store the fp32 output at all (production: only the image is read again)
     int Cbf_ld = 0; // channels per image row (>= Nco; 48-channel images are stored with a 64-channel pitch, see TmaPlan)
     // TMA-fed persistent mode (gemm_tc.cu: launch_gemm_tma): A is a bf16 channels-last image [B][Ui][Vi][Cin] read through a
     // tensor map; Wt = the weights in that kernel's K order (TmaPlan); the t_* fields are filled in by the launcher

@@ -631,6 +631,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             {
                 q.Cbf = m->dimg_f[i + 1];
                 q.Cbf_ld = tc_tma_cpitch(fd.Cout);
+                q.skip_c = !m->keep_stages && m->dec[i + 1].rewrite.Wt != nullptr; // only the image is read again
                 img_f = m->dimg_f[i + 1];
             }
             f.gemm(q, PC_GEMM_CONV);
@@ -682,6 +683,7 @@ int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             {
                 q.Cbf = m->dimg_t[i + 1];
                 q.Cbf_ld = tc_tma_cpitch(td.Cout);
+                q.skip_c = !m->keep_stages && m->tdec[i + 1].rewrite.Wt != nullptr;
                 img_t = m->dimg_t[i + 1];
             }
             f.gemm(q, PC_GEMM_CONV);

@@ -170,6 +170,7 @@ struct dmx_model
     void *cimg_f = nullptr, *cimg_t = nullptr; // ... of the DConv results that feed the transposed convolutions
     bool use_tma = false;
     // test tier (dmx_model_set_layer_taps): copies of the token streams after norm_in and after every transformer layer
+    bool keep_stages = true; // false in the track-level entry points: stage tensors nobody reads again are not written
     bool layer_taps = false;
     float *lt_f[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, *lt_t[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     float *h_f, *y2_f, *h_t, *y2_t;

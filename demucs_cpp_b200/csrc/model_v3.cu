@@ -632,6 +632,7 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             {
                 q.Cbf = m->dimg_f[i + 1];
                 q.Cbf_ld = tc_tma_cpitch(fd.Cout);
+                q.skip_c = !m->keep_stages && v->cdec[i + 1].rewrite.Wt != nullptr; // only the image is read again
                 img_f = m->dimg_f[i + 1];
             }
             f.gemm(q, PC_GEMM_CONV);
@@ -675,6 +676,7 @@ int model_v3_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
             {
                 q.Cbf = m->dimg_t[i + 1];
                 q.Cbf_ld = tc_tma_cpitch(td.Cout);
+                q.skip_c = !m->keep_stages && v->ctdec[i + 1].rewrite.Wt != nullptr;
                 img_t = m->dimg_t[i + 1];
             }
             f.gemm(q, PC_GEMM_CONV);

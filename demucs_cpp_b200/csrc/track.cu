@@ -162,6 +162,16 @@ static int ensure(float **p, size_t *cap, size_t n)
     return 0;
 }
 
+// The forward as the track-level entry points run it: stage tensors that only dmx_debug_tap would read (the fp32 outputs of
+// the decoders' transposed convolutions, whose bf16 images are what the next layer consumes) are not written.
+static int track_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
+{
+    m->keep_stages = false;
+    const int rc = model_forward(m, d_mix, B, d_out);
+    m->keep_stages = true;
+    return rc;
+}
+
 int num_segments(int64_t L, int shift)
 {
     const int64_t Ls = L + MAX_SHIFT - shift;
@@ -242,7 +252,7 @@ int track_forward_shard(dmx_model *m, const float *d_audio, int64_t L, int shift
                 (const float2 *)d_audio, L, shift, Ls, m->track_stats, rank + j0 * world, world, (float2 *)m->mix);
         }
         DMX_LAUNCH_CHECK();
-        if (model_forward(m, m->mix, nb, d_y + (size_t)j0 * S * SEG * 2))
+        if (track_forward(m, m->mix, nb, d_y + (size_t)j0 * S * SEG * 2))
             return -1;
         if (cb)
         {
@@ -387,7 +397,7 @@ int track_forward_block(dmx_model *m, const float *d_win, int64_t L, int shift, 
                                                                               (float2 *)m->mix);
         }
         DMX_LAUNCH_CHECK();
-        if (model_forward(m, m->mix, nb, d_y + (size_t)j0 * S * SEG * 2))
+        if (track_forward(m, m->mix, nb, d_y + (size_t)j0 * S * SEG * 2))
             return -1;
     }
     DMX_CUDA(cudaEventRecord(m->ev1, st));
@@ -747,7 +757,7 @@ int track_separate_host(dmx_model *m, const float *h_audio, int64_t L, int shift
             extract_segments_kernel<<<dim3((SEG + 255) / 256, nb), 256, 0, st>>>(
                 (const float2 *)m->d_audio, L, shift, Ls, m->track_stats, j0, 1, (float2 *)m->mix);
         }
-        if (cudaGetLastError() != cudaSuccess || model_forward(m, m->mix, nb, m->d_y + (size_t)j0 * S * SEG * 2))
+        if (cudaGetLastError() != cudaSuccess || track_forward(m, m->mix, nb, m->d_y + (size_t)j0 * S * SEG * 2))
         {
             rc = -1;
             break;
