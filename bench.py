@@ -228,12 +228,33 @@ def workload_config(args, world):
 
 
 # ------------------------------------------------------------------------------------------------ this repo's arm
+def bind_near_gpu(torch, index):
+    """Run this rank's host thread on the cores of its GPU's NUMA node (sysfs local_cpulist of the PCI device, within
+    the cores the process may already use), so pinned buffers it first touches land in that node's memory and each
+    GPU's DMA stays on its own socket.  Returns the core count it bound to, or 0 if it left the affinity alone."""
+    try:
+        pr = torch.cuda.get_device_properties(index)
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/local_cpulist" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            if part:
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return 0
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:  # no sysfs entry (container), no such attribute: keep the inherited affinity
+        return 0
+
+
 class SharedHostBuffer:
     """The stems of the whole track in ONE host buffer that every rank's GPU can DMA into: rank 0 owns it (POSIX
     shared memory), the other ranks map and page-lock the same pages, so each GPU copies its own stretch of the
     output over its own PCIe link and nothing funnels through one device."""
 
-    def __init__(self, shape, rank, world, torch, dist):
+    def __init__(self, shape, rank, world, torch, dist, own=None):
         import tempfile
         self.torch = torch
         n = int(np.prod(shape))
@@ -251,6 +272,11 @@ class SharedHostBuffer:
         self.path = obj[0]
         self.mm = np.memmap(self.path, dtype=np.float32, mode="r+", shape=tuple(shape))
         self.t = torch.from_numpy(self.mm)
+        if own is not None and own[1] > own[0]:
+            # first touch of the rows this rank will write, from a thread bound near its GPU: the pages of each stretch
+            # are allocated on the NUMA node its GPU hangs off
+            self.t[own[0]:own[1]].zero_()
+        dist.barrier()
         self.registered = torch.cuda.cudart().cudaHostRegister(self.t.data_ptr(), n * 4, 0)
         self.registered = int(self.registered) == 0
         dist.barrier()
@@ -285,8 +311,12 @@ class Workload:
         self.L = L = TRACK_SECONDS * SR
         self.nseg = api.num_segments(L, SHIFT)
         self.h_audio = env["h_audio"]
-        self.h_out = SharedHostBuffer((L, 2, S), self.rank, self.world, torch, dist)
         world = self.world
+        own = None
+        if world > 1:
+            pls = [api.plan_block(L, sh, self.rank, world) for sh in self.shifts]
+            own = (min(p.out_begin for p in pls), max(p.out_end for p in pls))
+        self.h_out = SharedHostBuffer((L, 2, S), self.rank, self.world, torch, dist, own)
         if world == 1:
             self.d_audio = self.h_audio.to(dev)
             self.d_out = torch.empty((L, 2, S), dtype=torch.float32, device=dev)
@@ -433,13 +463,20 @@ class Workload:
             self.h2d, self.d2h = self.L * 2 * 4, self.L * 2 * self.S * 4
             return
         # N ranks: each copies in ONLY its window of the track and copies out ONLY its stretch of the stems
+        trace = os.environ.get("DMX_BENCH_TRACE") and self.rank in (0, self.world - 1)
+        t0 = time.perf_counter()
         self.d_win.copy_(self.h_audio[self.win_lo:self.win_hi], non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        t1 = time.perf_counter()
         self.step_device()
+        t2 = time.perf_counter()
         p0 = self.plans[0]
         if p0.out_end > p0.out_begin:
             self.h_out.t[p0.out_begin:p0.out_end].copy_(self.d_out[p0.out_begin - self.olo:p0.out_end - self.olo], non_blocking=True)
             torch.cuda.current_stream().synchronize()
+        if trace:
+            sys.stderr.write("trace rank %d: h2d %.2f ms, device step %.2f ms, d2h %.2f ms (registered=%s)\n" % (
+                self.rank, (t1 - t0) * 1e3, (t2 - t1) * 1e3, (time.perf_counter() - t2) * 1e3, getattr(self.h_out, "registered", None)))
         self.h2d = (self.win_hi - self.win_lo) * 2 * 4
         self.d2h = (p0.out_end - p0.out_begin) * 2 * self.S * 4
 
@@ -535,6 +572,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    near = bind_near_gpu(torch, local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -652,7 +690,7 @@ def main():
         "metric": "audio_seconds_per_wall_second", "value": value, "unit": "audio-s/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
-        "data": "synthetic", "config": workload_config(args, world),
+        "data": "synthetic", "config": dict(workload_config(args, world), host_affinity_cores=near),
         "ms_per_segment": ms_per_step / nseg,
         "device_ms_per_step": dev_ms / args.steps, "wall_ms_per_step": wall_ms / args.steps,
         "profiled_pass_ms_per_step": prof_dev_ms / args.steps,

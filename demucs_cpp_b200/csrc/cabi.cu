@@ -234,6 +234,9 @@ void dmx_model_free(dmx_model *m)
                 cudaStreamSynchronize(s);
         if (m->stager)
             stager_free(m->stager);
+        for (auto &g : m->graphs)
+            if (g.exec)
+                cudaGraphExecDestroy(g.exec);
         for (void *p : m->allocs)
             cudaFree(p);
         for (float *p : {m->d_audio, m->d_y, m->d_out, m->d_tail, m->d_acc})

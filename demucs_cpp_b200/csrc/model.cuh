@@ -190,6 +190,16 @@ struct dmx_model
     float *d_tail = nullptr; // [S][SEG - SEG_STRIDE][2]: the previous worker's tail (dmx_separate_multi)
     dmx::HostStager *stager = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr; // device time of the last track-level call
+    // the forward of the track-level entry points, captured once per (input, output, batch) and replayed (track.cu)
+    struct FwdGraph
+    {
+        const float *mix = nullptr;
+        float *out = nullptr;
+        int B = 0, calls = 0;
+        int64_t launches = 0;
+        cudaGraphExec_t exec = nullptr;
+    };
+    std::vector<FwdGraph> graphs;
 };
 
 namespace dmx

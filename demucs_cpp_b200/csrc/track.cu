@@ -164,12 +164,76 @@ static int ensure(float **p, size_t *cap, size_t n)
 
 // The forward as the track-level entry points run it: stage tensors that only dmx_debug_tap would read (the fp32 outputs of
 // the decoders' transposed convolutions, whose bf16 images are what the next layer consumes) are not written.
+//
+// The ~700 launches of one forward are short at small batches (4 segments per worker on 8 GPUs: ~10 us each), so the forward
+// of a given (input, output, batch) is captured into a CUDA graph on its second call and replayed from then on: the
+// buffers are the model's own, the fork / join of the time branch on stream2 becomes graph edges.  The first call runs
+// eagerly (one-time attribute setup and lazily built tables happen there); DMX_NO_GRAPH=1, profiling and the per-layer
+// taps keep the eager path.
 static int track_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
 {
-    m->keep_stages = false;
+    static const bool use_graph = getenv("DMX_NO_GRAPH") == nullptr;
+    struct Stages
+    {
+        dmx_model *m;
+        explicit Stages(dmx_model *m_) : m(m_) { m->keep_stages = false; }
+        ~Stages() { m->keep_stages = true; }
+    } stages(m);
+    if (!use_graph || m->prof.on || m->layer_taps)
+        return model_forward(m, d_mix, B, d_out);
+    dmx_model::FwdGraph *g = nullptr;
+    for (auto &e : m->graphs)
+        if (e.mix == d_mix && e.out == d_out && e.B == B)
+            g = &e;
+    if (!g)
+    {
+        if (m->graphs.size() >= 64)
+        {
+            // caller buffers keep changing: drop the oldest key
+            if (m->graphs.front().exec)
+                cudaGraphExecDestroy(m->graphs.front().exec);
+            m->graphs.erase(m->graphs.begin());
+        }
+        m->graphs.emplace_back();
+        g = &m->graphs.back();
+        g->mix = d_mix;
+        g->out = d_out;
+        g->B = B;
+    }
+    if (g->exec)
+    {
+        DMX_CUDA(cudaGraphLaunch(g->exec, m->stream));
+        m->launches += g->launches;
+        m->lastB = B;
+        return 0;
+    }
+    if (g->calls < 0 || g->calls++ == 0)
+        return model_forward(m, d_mix, B, d_out);
+    const int64_t before = m->launches;
+    if (cudaStreamBeginCapture(m->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess)
+    {
+        cudaGetLastError();
+        g->calls = -1;
+        return model_forward(m, d_mix, B, d_out);
+    }
     const int rc = model_forward(m, d_mix, B, d_out);
-    m->keep_stages = true;
-    return rc;
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(m->stream, &graph);
+    if (rc || ce != cudaSuccess || !graph || cudaGraphInstantiate(&g->exec, graph, 0) != cudaSuccess)
+    {
+        // not capturable on this build / driver: stay eager for this key
+        cudaGetLastError();
+        if (graph)
+            cudaGraphDestroy(graph);
+        g->exec = nullptr;
+        g->calls = -1;
+        m->launches = before;
+        return model_forward(m, d_mix, B, d_out);
+    }
+    cudaGraphDestroy(graph);
+    g->launches = m->launches - before;
+    DMX_CUDA(cudaGraphLaunch(g->exec, m->stream));
+    return 0;
 }
 
 int num_segments(int64_t L, int shift)
