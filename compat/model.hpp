@@ -3,7 +3,8 @@
 // compat/model_b200.cpp on top of the C ABI of include/demucs_b200.h.  The model structs carry only
 // `is_4sources` (read by cli-apps/demucs.cpp:145) and a shared handle to the device-resident model; they
 // stay default-constructible, movable and usable as `const&` from several host threads
-// (cli-apps/threaded_inference.hpp:110-117): every call serialises on the model's own mutex inside the library.
+// (cli-apps/threaded_inference.hpp:110-117): calls on one device-side model serialise on its mutex inside the library;
+// with DEMUCS_NGPU replicas concurrent callers are spread over the GPUs (compat/model_b200.cpp, Handle).
 //
 // Replaces: demucscpp::load_demucs_model        src/model.hpp:649-650
 //           demucscpp::demucs_inference         src/model.hpp:658-660

@@ -6,8 +6,12 @@
 #include "demucs_b200.h"
 
 #include <algorithm>
+#include <chrono>
+#include <condition_variable>
 #include <cstdlib>
 #include <iostream>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 namespace
@@ -19,14 +23,54 @@ int env_int(const char *name, int dflt)
 }
 
 // The device-side state behind a demucs_model: the model on GPU DEMUCS_DEVICE and, with DEMUCS_NGPU = n > 1, replicas on the
-// next n - 1 GPUs; demucs_inference then splits every track over them (dmx_separate_multi).
+// next n - 1 GPUs, handed out to the host threads that call demucs_inference on the one shared model:
+//   * a lone caller (demucs.cpp / demucs_ft.cpp / demucs_v3.cpp) gets every replica and its track is split over them
+//     (dmx_separate_multi);
+//   * the chunk threads of the *_mt drivers (cli-apps/threaded_inference.hpp:110-123) arrive together: each takes ONE
+//     free replica and runs its whole chunk there, so n chunks are in flight on n GPUs instead of queueing on one
+//     context; with more threads than replicas the rest wait for the next free one.
 struct Handle
 {
     std::vector<dmx_model *> reps;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<char> busy;
+    int callers = 0;
     ~Handle()
     {
         for (dmx_model *h : reps)
             dmx_model_free(h);
+    }
+    std::vector<int> acquire()
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        ++callers;
+        if (reps.size() > 1)
+        {
+            // sibling chunk threads start microseconds apart: let them register before deciding who gets what
+            lk.unlock();
+            std::this_thread::sleep_for(std::chrono::milliseconds(2));
+            lk.lock();
+        }
+        cv.wait(lk, [&] { return std::find(busy.begin(), busy.end(), 0) != busy.end(); });
+        std::vector<int> mine;
+        const bool all_free = std::find(busy.begin(), busy.end(), 1) == busy.end();
+        for (int r = 0; r < (int)reps.size(); ++r)
+            if (!busy[r] && (mine.empty() || (callers == 1 && all_free)))
+                mine.push_back(r);
+        for (int r : mine)
+            busy[r] = 1;
+        return mine;
+    }
+    void release(const std::vector<int> &mine)
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (int r : mine)
+                busy[r] = 0;
+            --callers;
+        }
+        cv.notify_all();
     }
 };
 
@@ -69,6 +113,7 @@ std::shared_ptr<void> load(const std::string &path, int want_v3, bool *is4)
             dmx_model_set_precision(rep, DMX_PRECISION_BF16);
         hd->reps.push_back(rep);
     }
+    hd->busy.assign(hd->reps.size(), 0);
     return std::shared_ptr<void>(hd, [](void *p) { delete static_cast<Handle *>(p); });
 }
 
@@ -90,11 +135,24 @@ Eigen::Tensor3dXf separate(void *handle, const Eigen::MatrixXf &audio, demucscpp
     Eigen::Tensor3dXf out(S, 2, audio.cols());
     const int offset = rand() % 22050; // src/model_apply.cpp:114 (unseeded glibc rand, like the reference)
     std::cout << "1., apply model w/ shift, offset: " << offset << std::endl;
-    if (dmx_separate_multi(hd->reps.data(), (int)hd->reps.size(), audio.data(), (int64_t)audio.cols(), offset, out.data(),
-                           cb ? trampoline : nullptr, &cb) != 0)
+    const std::vector<int> mine = hd->acquire();
+    std::vector<dmx_model *> reps;
+    for (int r : mine)
+        reps.push_back(hd->reps[r]);
+    const int rc = dmx_separate_multi(reps.data(), (int)reps.size(), audio.data(), (int64_t)audio.cols(), offset, out.data(),
+                                      cb ? trampoline : nullptr, &cb);
+    hd->release(mine);
+    if (rc != 0)
     {
         std::cerr << "demucs_inference: " << dmx_last_error() << std::endl;
         std::exit(1);
+    }
+    if (std::getenv("DEMUCS_VERBOSE_DEVICES"))
+    {
+        std::string ids;
+        for (int r : mine)
+            ids += (ids.empty() ? "" : ",") + std::to_string(r);
+        std::cerr << "demucs_inference: " << audio.cols() << " frames on replica(s) " << ids << std::endl;
     }
     return out;
 }

@@ -26,12 +26,12 @@ def cli(name):
     return p
 
 
-def run(args, env=None, timeout=600):
+def run(args, env=None, timeout=600, with_stderr=False):
     e = dict(os.environ)
     e.update(env or {})
     r = subprocess.run(args, capture_output=True, text=True, env=e, timeout=timeout)
     assert r.returncode == 0, "%s failed:\n%s\n%s" % (args[0], r.stdout[-1500:], r.stderr[-1500:])
-    return r.stdout
+    return (r.stdout, r.stderr) if with_stderr else r.stdout
 
 
 def write_wav(path, audio):
@@ -103,3 +103,24 @@ def test_demucs_mt_and_v3_and_ft_mains_run(tmp_path):
     for mm in members:
         mm.close()
     assert util.snr_db(read_stems(out, 4), ref) >= 80.0
+
+
+def test_replicas_split_a_lone_track_and_spread_the_chunk_threads(tmp_path):
+    """DEMUCS_NGPU=2 (needs two GPUs): the single-threaded driver splits its track over both replicas and writes the same
+    stems as one GPU; the chunk threads of demucs_mt (cli-apps/threaded_inference.hpp:110-123) each get a replica of
+    their own instead of queueing on one context."""
+    if api.lib().dmx_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    audio = util.synth_audio(40 * 44100, seed=43)
+    wav = str(tmp_path / "in.wav")
+    write_wav(wav, audio)
+    env = {"DEMUCS_PRECISION": "fp32", "DEMUCS_MAX_BATCH": "4", "DEMUCS_VERBOSE_DEVICES": "1"}
+    w = weights.cached_weights("htdemucs_4s", 0)
+    run([cli("demucs"), w, wav, str(tmp_path / "one")], env)
+    _, err = run([cli("demucs"), w, wav, str(tmp_path / "two")], dict(env, DEMUCS_NGPU="2"), with_stderr=True)
+    assert "replica(s) 0,1" in err
+    assert util.snr_db(read_stems(str(tmp_path / "two"), 4), read_stems(str(tmp_path / "one"), 4)) >= 80.0
+    _, err = run([cli("demucs_mt"), w, wav, str(tmp_path / "mt"), "2"], dict(env, DEMUCS_NGPU="2"), with_stderr=True)
+    used = sorted(l.split("replica(s) ")[1].strip() for l in err.splitlines() if "replica(s) " in l)
+    assert used == ["0", "1"], err[-800:]
+    assert np.isfinite(read_stems(str(tmp_path / "mt"), 4)).all()

@@ -38,4 +38,7 @@ import json
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 with open(os.path.join(ROOT, "gpurun_out", "profile_step_classes.json"), "w") as f:
     json.dump({"sequence": seq, "classes": prof}, f)
+for name, c in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]):
+    if c["launches"]:
+        print("  %-18s %8.3f ms  %5d launches" % (name, c["ms"], c["launches"]))
 print("device ms for %d segments: %.2f" % (args.batch, m.last_device_ms))
