@@ -271,3 +271,35 @@ def test_pageable_and_pinned_host_buffers_agree():
     assert rc == 0, api.last_error()
     got = h_out.numpy().transpose(2, 1, 0)
     assert util.max_rel_err(got, ref) <= 1e-6 and np.isfinite(got).all()
+
+
+@pytest.mark.parametrize("arch,precision", [("htdemucs_4s", api.PRECISION_BF16), ("hdemucs_mmi", api.PRECISION_FP32)])
+def test_replayed_forward_graph_equals_the_eager_forward(arch, precision):
+    """The track-level entry points run their first forward of a (buffers, batch) key eagerly, capture the second into a
+    CUDA graph and replay it afterwards (csrc/track.cu track_forward).  Same model, same device buffers: call 1 (eager)
+    on track A, call 2 (captured) on track B, calls 3 / 4 (replays) on A and B again -- replays must reproduce the eager
+    results and follow the CONTENT of the buffers, and DMX_NO_GRAPH-style eager runs of another model object
+    are the cross-check for B."""
+    L = 5 * 257985 + 1000                                             # 6 segments: launches of 4 and 2 at max_batch 4
+    a = torch.from_numpy(np.ascontiguousarray(util.synth_audio(L, seed=51).T)).cuda()
+    b = torch.from_numpy(np.ascontiguousarray(util.synth_audio(L, seed=52).T)).cuda()
+    d_in = torch.empty_like(a)
+    m = model(arch, max_batch=4, precision=precision, tag=77)
+    d_out = torch.empty((L, 2, m.nb_sources), dtype=torch.float32, device="cuda")
+    outs = []
+    for src in (a, b, a, b, a):
+        d_in.copy_(src)
+        torch.cuda.synchronize()
+        m.demucs_inference_device(d_in.data_ptr(), L, d_out.data_ptr(), 4033)
+        torch.cuda.synchronize()
+        outs.append(d_out.cpu().numpy().copy())
+    assert np.isfinite(outs[0]).all() and np.abs(outs[0] - outs[1]).max() > 1e-3
+    same = lambda x, y: util.max_rel_err(x, y) <= 1e-5    # statistics are summed with atomics: last-bit differences only
+    assert same(outs[0], outs[2]) and same(outs[0], outs[4])                           # eager A == replayed A
+    assert same(outs[1], outs[3])                                                      # captured-call B == replayed B
+    m2 = model(arch, max_batch=4, precision=precision, tag=78)                         # fresh model: its first call is eager
+    d_in.copy_(b)
+    torch.cuda.synchronize()
+    m2.demucs_inference_device(d_in.data_ptr(), L, d_out.data_ptr(), 4033)
+    torch.cuda.synchronize()
+    assert same(outs[1], d_out.cpu().numpy())
