@@ -61,7 +61,7 @@ struct GemmParams
     // filled in by launch_gemm_tc: reciprocals for fast_div by Uo*Vo, Vo (row -> (b, u_o, v_o)) and Nco
     unsigned long long div_per = 0, div_vo = 0, div_nco = 0;
     int no_bulk = 0; // development switch: keep the transposing epilogue
-    int dbg_epi = 0; // development switch (DMX_DBG_EPI): 1 = epilogue_tile stops after the TMEM loads, 2 = no GELU, 3 = no scatter stores
+    int dbg_epi = 0; // development switch (DMX_DBG_EPI): 4 = transposed convolutions keep the generic transposing epilogue
     // halo mode of the tensor-core kernel (stride-1 multi-tap convolutions; see gemm_tc.cu), also set by the launcher
     int halo_nu = 0, halo_dumin = 0, halo_dvmin = 0, halo_rows = 0, halo_tpr = 0; // planes, first du / dv, patch rows, tiles per (b,u)
     unsigned long long div_tpr = 0, div_uo = 0, div_c8 = 0, div_rows = 0;
