@@ -25,7 +25,11 @@ extern "C"
     typedef struct dmx_model dmx_model;
 
     /* Progress callback, same meaning as demucscpp::ProgressCallback (src/model.hpp:17):
-     * fraction in [0,1] and a message.  Invoked on the calling thread only. */
+     * fraction in [0,1] and a message.  Invoked on the calling thread only.
+     * Only the reference's numbered stage milestones are reproduced ("Time encoder 0" ... "Time: decoder 3": 26 per segment
+     * for htdemucs, 22 for hdemucs_mmi, src/model_inference.cpp), with the reference's progress values, and they are
+     * fired after the launch that contains the segment has finished -- the reference's other per-segment messages (shape
+     * strings, "Freq branch: normalized", "Crosstransformer finished", "Mask + istft", ...) are not emitted. */
     typedef void (*dmx_progress_fn)(float progress, const char *message, void *user);
 
     /* Precision modes (BASELINE.json north_star: "bf16 mode" and "fp32 mode"). */

@@ -148,7 +148,8 @@ def test_separate_matches_reference_golden(golden_dir):
     assert out.shape == tuple(g["shape"])
     check_summary("stems", out, g["sub"], g["stat"], TOL_FP32)
     assert util.snr_db(out.reshape(-1)[sub_idx(out.size)], g["sub"]) >= SNR_FP32
-    # progress callback: the reference's 26 stage messages per segment, monotone progress ending at 1
+    # progress callback: the reference's 26 NUMBERED stage milestones per segment (its other free-text messages are not
+    # reproduced, include/demucs_b200.h), monotone progress ending at 1
     assert len(calls) == 26 * 2 and calls[0][1] == "Time encoder 0" and calls[-1][1] == "Time: decoder 3"
     ps = [p for p, _ in calls]
     assert all(b >= a for a, b in zip(ps, ps[1:])) and abs(ps[-1] - 1.0) < 1e-6
