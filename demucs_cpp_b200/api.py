@@ -33,7 +33,7 @@ EXPORTS = [
     "dmx_overlap_add_device", "dmx_last_device_ms", "dmx_stft_segments_noalloc",
     "dmx_debug_linear", "dmx_profile_sequence", "dmx_plan_block", "dmx_track_stats_device", "dmx_forward_block_device",
     "dmx_overlap_add_block_device", "dmx_model_sync", "dmx_separate_multi", "dmx_separate_bag", "dmx_debug_conv",
-    "dmx_separate_shifts", "dmx_model_set_layer_taps",
+    "dmx_separate_shifts", "dmx_model_set_layer_taps", "dmx_segment_progress",
 ]
 
 

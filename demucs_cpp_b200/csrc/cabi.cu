@@ -257,6 +257,17 @@ void dmx_model_free(dmx_model *m)
     delete m;
 }
 
+int dmx_segment_progress(const dmx_model *m, float current_progress, float segment_progress, dmx_progress_fn cb, void *user)
+{
+    if (!m || !m->finalized)
+    {
+        set_error("dmx_segment_progress: model not loaded");
+        return -1;
+    }
+    track_fire_segment_progress(m, current_progress, segment_progress, cb, user);
+    return 0;
+}
+
 int dmx_model_arch(const dmx_model *m) { return m ? m->arch : -1; }
 int dmx_model_sources(const dmx_model *m) { return m ? (m->arch == DMX_ARCH_HTDEMUCS_6S ? 6 : 4) : -1; }
 int dmx_model_max_batch(const dmx_model *m) { return m ? m->maxB : -1; }

@@ -228,6 +228,7 @@ int track_overlap_add(dmx_model *m, const float *d_audio, int64_t L, int shift, 
                       float *d_out);
 int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
                    void *user);
+void track_fire_segment_progress(const dmx_model *m, float current, float segment, dmx_progress_fn cb, void *user);
 int plan_block(int64_t L, int shift, int rank, int world, dmx_block_plan *pl);
 int track_stats_partial(dmx_model *m, const float *d_audio, int64_t n, double *d_sums);
 int track_forward_block(dmx_model *m, const float *d_win, int64_t L, int shift, const dmx_block_plan &pl, const double *d_sums,

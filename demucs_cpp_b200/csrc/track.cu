@@ -558,6 +558,16 @@ void track_fire_progress(dmx_model *m, int nseg, dmx_progress_fn cb, void *user)
             cb(((float)j + (float)(sidx + 1) / (float)nmsg) / (float)nseg, v3 ? kStageMsgsV3[sidx] : kStageMsgs[sidx], user);
 }
 
+void track_fire_segment_progress(const dmx_model *m, float current, float segment, dmx_progress_fn cb, void *user)
+{
+    if (!cb)
+        return;
+    const bool v3 = m->arch == DMX_ARCH_HDEMUCS_V3;
+    const int nmsg = v3 ? 22 : 26;
+    for (int sidx = 0; sidx < nmsg; ++sidx)
+        cb(current + segment * (float)(sidx + 1) / (float)nmsg, v3 ? kStageMsgsV3[sidx] : kStageMsgs[sidx], user);
+}
+
 int track_separate(dmx_model *m, const float *d_audio, int64_t L, int shift, float *d_out, dmx_progress_fn cb,
                    void *user)
 {

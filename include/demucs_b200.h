@@ -167,6 +167,12 @@ extern "C"
      *      segs: host (B, 343980, 2) interleaved; out: host (B, S, 343980, 2). ---- */
     int dmx_forward_segments(dmx_model *m, const float *segs, int n_segments, float *out);
 
+    /* The numbered stage milestones of ONE segment as the reference's model_inference reports them (progress =
+     * current_progress + segment_progress * k / 26, or k / 22 for hdemucs_mmi; src/model_inference.cpp:156-470,584-734),
+     * fired on the calling thread.  For callers of dmx_forward_segments that keep the reference's ProgressCallback
+     * contract at segment level (compat/model_b200.cpp: demucscpp::model_inference). */
+    int dmx_segment_progress(const dmx_model *m, float current_progress, float segment_progress, dmx_progress_fn cb, void *user);
+
     /* Test hook standing in for the reference's public per-segment scratch struct
      * (demucs_segment_buffers, src/model.hpp:569-647): copies a named activation left by the last
      * dmx_forward_segments call to the host.  dims[4] receives (B, d1, d2, C) of the channels-last

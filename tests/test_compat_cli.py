@@ -43,3 +43,22 @@ def test_reference_clis_compile_and_resolve_against_the_shim(tmp_path):
                          capture_output=True, text=True).stdout
     for s in dmx:
         assert (" T " + s) in lib, "libdemucs_b200.so does not export " + s
+
+
+def test_segment_tier_of_the_reference_api_compiles_and_resolves(tmp_path):
+    """demucs_segment_buffers / model_inference and the v3 twins (src/model.hpp:569-647,662-666,1213-1415): the driver that
+    uses them like the reference's tests do compiles against compat/model.hpp, and the shim defines what it needs."""
+    inc = ["-I", os.path.join(util.ROOT, "compat"), "-I", os.path.join(util.ROOT, "include"),
+           "-I", os.path.join(REF, "vendor", "eigen")]
+    shim = str(tmp_path / "model_b200.o")
+    assert cxx(inc + ["-fPIC", "-c", os.path.join(util.ROOT, "compat", "model_b200.cpp"), "-o", shim]).returncode == 0
+    obj = str(tmp_path / "segment_tier.o")
+    r = cxx(inc + ["-c", os.path.join(util.ROOT, "compat", "segment_tier_main.cpp"), "-o", obj])
+    assert r.returncode == 0, r.stderr[-2000:]
+    provided = subprocess.run(["nm", "-C", "--defined-only", shim], capture_output=True, text=True).stdout
+    und = subprocess.run(["nm", "-C", "--undefined-only", obj], capture_output=True, text=True).stdout
+    wanted = [ln.split(" U ", 1)[1].strip() for ln in und.splitlines() if " U demucscpp" in ln]
+    assert any("model_inference" in w for w in wanted) and any("demucs_segment_buffers" in w for w in wanted)
+    assert any("model_v3_inference" in w for w in wanted)
+    for sym in wanted:
+        assert sym in provided, "segment_tier_main.cpp needs %s, which the shim does not define" % sym

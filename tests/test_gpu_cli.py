@@ -124,3 +124,61 @@ def test_replicas_split_a_lone_track_and_spread_the_chunk_threads(tmp_path):
     used = sorted(l.split("replica(s) ")[1].strip() for l in err.splitlines() if "replica(s) " in l)
     assert used == ["0", "1"], err[-800:]
     assert np.isfinite(read_stems(str(tmp_path / "mt"), 4)).all()
+
+
+@pytest.mark.parametrize("arch,v3", [("htdemucs_4s", 0), ("htdemucs_6s", 0), ("hdemucs_mmi", 1)])
+def test_segment_tier_buffers_and_model_inference(tmp_path, arch, v3):
+    """The reference's public per-segment tier (SURVEY.md 8a a34): `demucs_segment_buffers buffers(2, 343980, S);
+    stft_buffers stft_buf(...); model_inference(model, buffers, stft_buf, cb, current, segment)` as its own tests use it,
+    provided by compat/model.hpp over the C ABI.  compat/segment_tier_main.cpp fills `mix`, calls it and dumps every
+    public tensor; here each one must equal the library's stage activation of the same segment, in the REFERENCE's
+    layout (frequency branch Tensor3dXf(C, F, T) column-major, time branch (1, C, T), targets_out (S, 2, L)), and the
+    progress callback must deliver the numbered milestones scaled into [current, current + segment]."""
+    exe = os.path.join(BUILD, "segment_tier.main")
+    if not os.path.exists(exe):
+        pytest.skip("compat/_build/segment_tier.main not built (needs the reference tree; run __graft_entry__.build())")
+    seg = util.synth_audio(api.SEG, seed=61)
+    (tmp_path / "seg.f32").write_bytes(np.ascontiguousarray(seg.T.astype(np.float32)).tobytes())
+    out = tmp_path / "out"
+    out.mkdir()
+    run([exe, weights.cached_weights(arch, 0), str(v3), str(tmp_path / "seg.f32"), str(out)], {"DEMUCS_PRECISION": "fp32"})
+    lines = (out / "shapes.txt").read_text().splitlines()
+    shapes = {l.split()[0]: tuple(int(v) for v in l.split()[1:4]) for l in lines if not l.startswith("#")}
+    dims = [l for l in lines if l.startswith("# dims")][0].split()[2:]
+    assert [int(v) for v in dims] == [336, 1536, 1620, 347136, 336, 2049]          # src/model.hpp:622-628 on 343980 samples
+    prog = [l for l in lines if l.startswith("# progress")][0]
+    nmsg = 22 if v3 else 26
+    assert prog.split()[2] == str(nmsg) and abs(float(prog.split()[3]) - 0.75) < 1e-6
+    assert "Time encoder 0" in prog or v3
+
+    def load(name):
+        d0, d1, d2 = shapes[name]
+        return np.fromfile(str(out / (name + ".f32")), dtype=np.float32).reshape(d2, d1, d0)      # column-major (d0, d1, d2)
+
+    m = api.DemucsModel(weights.cached_weights(arch, 0), max_batch=1)
+    ref_out = m.model_inference(seg)[0]                                                            # (S, 2, L)
+    S = m.nb_sources
+    assert shapes["targets_out"] == (S, 2, api.SEG)
+    assert util.max_rel_err(load("targets_out").transpose(2, 1, 0), ref_out) <= 1e-5
+    names = [n for n in shapes if n != "targets_out"]
+    assert len(names) >= 22
+    upsampled = {"x_3_channel_upsampled": "x_3_up", "xt_3_channel_upsampled": "xt_3_up"}
+    checked = 0
+    for n in names:
+        tapname = upsampled.get(n, n)
+        if arch == "htdemucs_6s" and n in upsampled:
+            continue                                                                               # 4-source models only
+        if arch == "htdemucs_6s" and n in ("x_3", "xt_3"):
+            tapname = tapname + "_up"                                                              # no down-sampler: the transformer's output
+        t = m.tap(tapname)[0]                                                                      # (d1, d2, C) channels-last
+        got = load(n)                                                                              # (d2, d1, d0)
+        if n.startswith("xt") or n.startswith("savedt") or n == "x_shared_5":
+            assert shapes[n] == (1, t.shape[2], t.shape[1]), n                                     # (1, C, T)
+            got = got[:, :, 0][None]                                                               # (1, T, C)
+        else:
+            assert shapes[n] == (t.shape[2], t.shape[0], t.shape[1]), n                            # (C, F, T)
+            got = got.transpose(1, 0, 2)                                                           # (F, T, C)
+        assert util.max_rel_err(got, t) <= 1e-5, n
+        checked += 1
+    assert checked >= 20
+    m.close()
