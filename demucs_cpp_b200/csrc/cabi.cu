@@ -1,6 +1,7 @@
 // extern "C" surface of libdemucs_b200.so (declared in include/demucs_b200.h).
 #include "model.cuh"
 
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <atomic>
@@ -162,6 +163,7 @@ dmx_model *dmx_model_load_file(const char *path, int device, int max_batch)
         set_error("dmx_model_load_file: invalid model data (bad magic)");
         return nullptr;
     }
+    const auto t_begin = std::chrono::steady_clock::now();
     dmx_model *m = dmx_model_create(arch, device, max_batch);
     if (!m)
     {
@@ -207,10 +209,21 @@ dmx_model *dmx_model_load_file(const char *path, int device, int max_batch)
     }
     fclose(f);
     f = nullptr;
-    if (dmx_model_finalize(m))
     {
-        dmx_model_free(m);
-        return nullptr;
+        const auto t_parsed = std::chrono::steady_clock::now();
+        const double pack0 = load_pack_seconds();
+        if (dmx_model_finalize(m))
+        {
+            dmx_model_free(m);
+            return nullptr;
+        }
+        if (getenv("DMX_LOAD_TRACE"))
+        {
+            const auto t_end = std::chrono::steady_clock::now();
+            fprintf(stderr, "dmx_model_load_file: read + widen %.3f s, finalize %.3f s (of which repacking incl. its uploads %.3f s)\n",
+                    std::chrono::duration<double>(t_parsed - t_begin).count(), std::chrono::duration<double>(t_end - t_parsed).count(),
+                    load_pack_seconds() - pack0);
+        }
     }
     return m;
 fail:

@@ -330,6 +330,8 @@ int model_zero_attention_pads(dmx_model *m)
     return 0;
 }
 
+double load_pack_seconds() { return LoadTimer::total(); }
+
 int model_forward(dmx_model *m, const float *d_mix, int B, float *d_out)
 {
     if (m->arch == DMX_ARCH_HDEMUCS_V3)

@@ -204,6 +204,7 @@ struct dmx_model
 
 namespace dmx
 {
+double load_pack_seconds(); // host time spent repacking weights so far (DMX_LOAD_TRACE)
 int model_finalize(dmx_model *m);
 int model_v3_finalize(dmx_model *m);
 int model_zero_attention_pads(dmx_model *m);

@@ -3,9 +3,11 @@
 #pragma once
 #include "model.cuh"
 
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 namespace dmx
 {
@@ -64,6 +66,40 @@ static int upload_vec(dmx_model *m, float **dst, const std::string &name, size_t
 
 static inline int round_up(int x, int k) { return (x + k - 1) / k * k; }
 
+// Host-side repacking at load time runs over ~40 M weights several times with strided index arithmetic: split the column
+// range over a few threads when the layer is big enough to pay for them (load time).
+template <typename F> static void par_for(int n, size_t work, F fn)
+{
+    static const int maxt = [] {
+        const char *e = getenv("DMX_LOAD_THREADS");
+        const int hw = (int)std::thread::hardware_concurrency();
+        const int t = e ? atoi(e) : (hw > 0 ? (hw < 8 ? hw : 8) : 4);
+        return t < 1 ? 1 : t;
+    }();
+    const int nt = work < (size_t)1 << 18 ? 1 : (n < maxt ? n : maxt);
+    if (nt <= 1)
+    {
+        fn(0, n);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; ++t)
+        th.emplace_back([=] { fn((int)((long long)n * t / nt), (int)((long long)n * (t + 1) / nt)); });
+    for (auto &x : th)
+        x.join();
+}
+
+struct LoadTimer
+{
+    static double &total()
+    {
+        static double t = 0.0;
+        return t;
+    }
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    ~LoadTimer() { total() += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+};
+
 static inline uint16_t f32_to_bf16_bits(float f)
 {
     uint32_t u;
@@ -84,22 +120,29 @@ static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb, c
     p.N = N;
     p.ldw = round_up(N, 128);
     const int Kpad = round_up(K, 16);
+    LoadTimer load_timer;
+    const size_t work = (size_t)K * N;
     std::vector<float> w((size_t)Kpad * p.ldw, 0.f), b(p.ldw, 0.f);
-    for (int n = 0; n < N; ++n)
-    {
-        const int src = glu ? ((n & 1) ? (n >> 1) + N / 2 : (n >> 1)) : n;
-        for (int k = 0; k < K; ++k)
-            w[(size_t)k * p.ldw + n] = fw(k, src);
-        b[n] = fb(src);
-    }
+    const int ldw = p.ldw;
+    par_for(N, work, [&, ldw](int n0, int n1) {
+        for (int n = n0; n < n1; ++n)
+        {
+            const int src = glu ? ((n & 1) ? (n >> 1) + N / 2 : (n >> 1)) : n;
+            for (int k = 0; k < K; ++k)
+                w[(size_t)k * ldw + n] = fw(k, src);
+            b[n] = fb(src);
+        }
+    });
     if (upload(m, &p.W, w) || upload(m, &p.bias, b))
         return -1;
     // bf16 image for the tcgen05 kernel: same (k, n) contents, round-to-nearest-even, zero padded
     {
         std::vector<uint16_t> wb(tc_packed_elems(K, N), 0);
-        for (int n = 0; n < N; ++n)
-            for (int k = 0; k < K; ++k)
-                wb[tc_packed_index(K, N, k, n)] = f32_to_bf16_bits(w[(size_t)k * p.ldw + n]);
+        par_for(N, work, [&, ldw](int n0, int n1) {
+            for (int n = n0; n < n1; ++n)
+                for (int k = 0; k < K; ++k)
+                    wb[tc_packed_index(K, N, k, n)] = f32_to_bf16_bits(w[(size_t)k * ldw + n]);
+        });
         if (dev_alloc(m, &p.Wb, wb.size() * sizeof(uint16_t)))
             return -1;
         DMX_CUDA(cudaMemcpy(p.Wb, wb.data(), wb.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
@@ -109,12 +152,14 @@ static int pack(dmx_model *m, Packed &p, int K, int N, bool glu, FW fw, FB fb, c
         // the same weights in the K order of the TMA-fed kernel (chunk, box, tap, channel): row k' of that image is
         // row tc_tma_korig(k') of this one
         std::vector<uint16_t> wt(tc_packed_elems(K, N), 0);
-        for (int kp = 0; kp < K; ++kp)
-        {
-            const int k = tc_tma_korig(*tp, tpCin, kp);
-            for (int n = 0; n < N; ++n)
-                wt[tc_packed_index(K, N, kp, n)] = f32_to_bf16_bits(w[(size_t)k * p.ldw + n]);
-        }
+        par_for(K, work, [&, ldw](int k0, int k1) {
+            for (int kp = k0; kp < k1; ++kp)
+            {
+                const int k = tc_tma_korig(*tp, tpCin, kp);
+                for (int n = 0; n < N; ++n)
+                    wt[tc_packed_index(K, N, kp, n)] = f32_to_bf16_bits(w[(size_t)k * ldw + n]);
+            }
+        });
         if (dev_alloc(m, &p.Wt, wt.size() * sizeof(uint16_t)))
             return -1;
         DMX_CUDA(cudaMemcpy(p.Wt, wt.data(), wt.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
