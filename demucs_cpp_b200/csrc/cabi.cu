@@ -367,6 +367,21 @@ int dmx_model_set_precision(dmx_model *m, int precision)
         return -1;
     }
     std::lock_guard<std::mutex> lk(m->mtx);
+    if (m->precision != precision && !m->graphs.empty())
+    {
+        // captured forwards hold the other mode's kernels
+        int prev = -1;
+        cudaGetDevice(&prev);
+        cudaSetDevice(m->device);
+        if (m->stream)
+            cudaStreamSynchronize(m->stream);
+        for (auto &g : m->graphs)
+            if (g.exec)
+                cudaGraphExecDestroy(g.exec);
+        m->graphs.clear();
+        if (prev >= 0)
+            cudaSetDevice(prev);
+    }
     m->precision = precision;
     return model_zero_attention_pads(m);
 }

@@ -303,3 +303,16 @@ def test_replayed_forward_graph_equals_the_eager_forward(arch, precision):
     m2.demucs_inference_device(d_in.data_ptr(), L, d_out.data_ptr(), 4033)
     torch.cuda.synchronize()
     assert same(outs[1], d_out.cpu().numpy())
+    if precision == api.PRECISION_BF16:
+        # a captured forward holds the kernels of the mode it was captured in: switching the mode must drop it
+        m.set_precision(api.PRECISION_FP32)
+        d_in.copy_(a)
+        torch.cuda.synchronize()
+        m.demucs_inference_device(d_in.data_ptr(), L, d_out.data_ptr(), 4033)
+        torch.cuda.synchronize()
+        got = d_out.cpu().numpy().copy()
+        m3 = model(arch, max_batch=4, precision=api.PRECISION_FP32, tag=79)
+        m3.demucs_inference_device(d_in.data_ptr(), L, d_out.data_ptr(), 4033)
+        torch.cuda.synchronize()
+        assert same(got, d_out.cpu().numpy()) and util.snr_db(got, outs[0]) < 75.0      # fp32 result, not the bf16 replay
+        m.set_precision(api.PRECISION_BF16)
