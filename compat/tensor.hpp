@@ -9,11 +9,13 @@
 
 namespace Eigen
 {
-typedef Tensor<float, 4> Tensor4dXf;
-typedef Tensor<float, 3> Tensor3dXf;
-typedef Tensor<float, 2> Tensor2dXf;
-typedef Tensor<float, 1> Tensor1dXf;
-typedef Tensor<std::complex<float>, 3> Tensor3dXcf;
+// alias templates by rank, then the names the API spells out
+template <int Rank> using TensorXf = Tensor<float, Rank>;
+using Tensor1dXf = TensorXf<1>;
+using Tensor2dXf = TensorXf<2>;
+using Tensor3dXf = TensorXf<3>;
+using Tensor4dXf = TensorXf<4>;
+using Tensor3dXcf = Tensor<std::complex<float>, 3>;
 } // namespace Eigen
 
 #endif
