@@ -249,6 +249,38 @@ def bind_near_gpu(torch, index):
         return 0
 
 
+def bag_fixup(torch, dist, rank, world, plans, d_out, olo, dev):
+    """htdemucs_ft over several ranks: the members' shifts differ, so member i's natural stretch on this rank
+    (plans[i].out_begin .. out_end) is member 0's moved by (shift_0 - shift_i) frames.  Final ownership follows member 0;
+    the sliver of stem i that the neighbour computed (at most 0.5 s) crosses by one small send/recv per member.
+    d_out: (frames from `olo`, 2, S) on `dev`, stem i valid on member i's stretch on entry and on member 0's on exit.
+    (Pure torch.distributed: tests/test_multi_rank_gloo.py runs it over gloo on CPU tensors.)"""
+    p0 = plans[0]
+    for i in range(1, len(plans)):
+        pi = plans[i]
+        ops, recv = [], []
+        # right edge: I own up to p0.out_end; stem i is mine only up to pi.out_end
+        if rank + 1 < world and p0.out_end > p0.out_begin:
+            if pi.out_end < p0.out_end:                                   # the next rank holds [pi.out_end, p0.out_end)
+                buf = torch.empty((p0.out_end - pi.out_end, 2), dtype=torch.float32, device=dev)
+                ops.append(dist.P2POp(dist.irecv, buf, rank + 1))
+                recv.append((buf, pi.out_end, p0.out_end))
+            elif pi.out_end > p0.out_end:                                 # I hold a sliver the next rank owns
+                ops.append(dist.P2POp(dist.isend, d_out[p0.out_end - olo:pi.out_end - olo, :, i].contiguous(), rank + 1))
+        if rank > 0 and p0.out_end > p0.out_begin:
+            if pi.out_begin > p0.out_begin:                               # the previous rank holds [p0.out_begin, pi.out_begin)
+                buf = torch.empty((pi.out_begin - p0.out_begin, 2), dtype=torch.float32, device=dev)
+                ops.append(dist.P2POp(dist.irecv, buf, rank - 1))
+                recv.append((buf, p0.out_begin, pi.out_begin))
+            elif pi.out_begin < p0.out_begin:
+                ops.append(dist.P2POp(dist.isend, d_out[pi.out_begin - olo:p0.out_begin - olo, :, i].contiguous(), rank - 1))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        for buf, a, b in recv:
+            d_out[a - olo:b - olo, :, i] = buf
+
+
 class SharedHostBuffer:
     """The stems of the whole track in ONE host buffer that every rank's GPU can DMA into: rank 0 owns it (POSIX
     shared memory), the other ranks map and page-lock the same pages, so each GPU copies its own stretch of the
@@ -411,37 +443,8 @@ class Workload:
         return ms
 
     def _bag_fixup(self):
-        """htdemucs_ft over several ranks: the members' shifts differ, so member i's natural stretch on this rank is
-        member 0's moved by (shift_0 - shift_i) frames.  Final ownership follows member 0; the sliver of stem i that
-        the neighbour computed (at most 0.5 s) crosses by one small send/recv per member."""
-        torch, dist = self.env["torch"], self.env["dist"]
-        p0 = self.plans[0]
-        for i in range(1, len(self.models)):
-            pi = self.plans[i]
-            ops, recv = [], []
-            # right edge: I own up to p0.out_end; stem i is mine only up to pi.out_end
-            if self.rank + 1 < self.world and p0.out_end > p0.out_begin:
-                if pi.out_end < p0.out_end:                                   # the next rank holds [pi.out_end, p0.out_end)
-                    buf = torch.empty((p0.out_end - pi.out_end, 2), dtype=torch.float32, device=self.env["dev"])
-                    ops.append(dist.P2POp(dist.irecv, buf, self.rank + 1))
-                    recv.append((buf, pi.out_end, p0.out_end))
-                elif pi.out_end > p0.out_end:                                 # I hold a sliver the next rank owns
-                    ops.append(dist.P2POp(dist.isend, self.d_out[p0.out_end - self.olo:pi.out_end - self.olo, :, i].contiguous(),
-                                          self.rank + 1))
-            if self.rank > 0 and p0.out_end > p0.out_begin:
-                if pi.out_begin > p0.out_begin:                               # the previous rank holds [p0.out_begin, pi.out_begin)
-                    buf = torch.empty((pi.out_begin - p0.out_begin, 2), dtype=torch.float32, device=self.env["dev"])
-                    ops.append(dist.P2POp(dist.irecv, buf, self.rank - 1))
-                    recv.append((buf, p0.out_begin, pi.out_begin))
-                elif pi.out_begin < p0.out_begin:
-                    ops.append(dist.P2POp(dist.isend, self.d_out[pi.out_begin - self.olo:p0.out_begin - self.olo, :, i].contiguous(),
-                                          self.rank - 1))
-            if ops:
-                for w in dist.batch_isend_irecv(ops):
-                    w.wait()
-            for buf, a, b in recv:
-                self.d_out[a - self.olo:b - self.olo, :, i] = buf
-        torch.cuda.current_stream().synchronize()
+        bag_fixup(self.env["torch"], self.env["dist"], self.rank, self.world, self.plans, self.d_out, self.olo, self.env["dev"])
+        self.env["torch"].cuda.current_stream().synchronize()
 
     # ---- the same through host buffers: pinned host audio -> device, stems -> (shared) pinned host ----
     def step_e2e(self):

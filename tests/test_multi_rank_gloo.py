@@ -204,3 +204,57 @@ def test_block_plans_partition_the_track():
             for r, p in enumerate(plans):
                 assert (p.tail_frames == api.TAIL_FRAMES) == (r > 0 and p.seg_end > p.seg_begin)
                 assert p.in_begin <= p.out_begin and p.in_end >= p.out_end
+
+
+# ------------------------------------------------------------------------------------------------ htdemucs_ft bag
+BAG_SHIFTS = [4033, 12436, 5427, 6865]          # the four successive rand() % 22050 draws of a fresh process
+
+
+def bag_value(i, lo, hi):
+    """What stem i holds on frames [lo, hi): depends on (stem, frame, channel) only, whoever computed it."""
+    fr = torch.arange(lo, hi, dtype=torch.float64)[:, None]
+    return (fr * 1e-3 + 0.25 * i + torch.tensor([[0.0, 0.125]], dtype=torch.float64)).float()
+
+
+def bag_worker(rank, world, port, L, ret):
+    import sys
+    sys.path.insert(0, util.ROOT)
+    import bench
+    from demucs_cpp_b200 import api
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    plans = [api.plan_block(L, sh, rank, world) for sh in BAG_SHIFTS]
+    olo, ohi = min(p.out_begin for p in plans), max(p.out_end for p in plans)
+    d_out = torch.full((max(ohi - olo, 1), 2, 4), float("nan"))
+    for i, p in enumerate(plans):                               # member i's forward + overlap-add: its own stretch of stem i
+        d_out[p.out_begin - olo:p.out_end - olo, :, i] = bag_value(i, p.out_begin, p.out_end)
+    bench.bag_fixup(torch, dist, rank, world, plans, d_out, olo, torch.device("cpu"))
+    p0 = plans[0]
+    own = d_out[p0.out_begin - olo:p0.out_end - olo]            # final ownership follows member 0
+    ok = all(torch.equal(own[:, :, i], bag_value(i, p0.out_begin, p0.out_end)) for i in range(4))
+    moved = sum(abs(p.out_begin - p0.out_begin) + abs(p.out_end - p0.out_end) for p in plans[1:])
+    ret.put((rank, p0.out_begin, p0.out_end, bool(ok), moved))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_bag_slivers_cross_to_the_owning_rank_world3():
+    """bench.py's htdemucs_ft path on N ranks (BASELINE.json configs[3]): every rank runs its block of each of the four
+    members; the members' shifts differ, so their block boundaries differ by up to 0.5 s and those slivers of stem i are
+    handed to the rank that owns the frames (bench.bag_fixup, the code the NCCL run uses, here over gloo)."""
+    L, world = 40 * 44100, 3
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=bag_worker, args=(r, world, port, L, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    parts = sorted(ret.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert parts[0][1] == 0 and parts[-1][2] == L
+    assert all(parts[r][2] == parts[r + 1][1] for r in range(world - 1))
+    assert all(ok for _, _, _, ok, _ in parts)
+    assert sum(m for *_, m in parts) > 0, "the members' boundaries coincide: the test exercised nothing"
