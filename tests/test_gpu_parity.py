@@ -260,3 +260,47 @@ def test_v3_separate_matches_oracle_pipeline():
     assert out.shape == (4, 2, 441000)
     assert util.snr_db(out, ref) >= SNR_FP32 and util.max_rel_err(out, ref) <= TOL_FP32
     assert len(calls) == 22 * 2 and calls[8][1] == "Time encoder 4" and calls[-1][1] == "Time decoder 5"
+
+
+T3X3 = [(a, b) for a in (-1, 0, 1) for b in (-1, 0, 1)]
+#               B  U  V      Cin  N    taps                          act glu share
+RING_CASES = [(1, 2, 336, 64, 64, [(0, 0)], 0, 0, 1),                       # 1x1
+              (2, 3, 336, 64, 96, T3X3, 0, 0, 0),                           # 3x3, one box per tap
+              (2, 4, 336, 48, 96, T3X3, 0, 1, 1),                           # 48 channels at the 64-channel pitch, GLU, shared boxes
+              (1, 4, 336, 192, 384, T3X3, 0, 1, 1),                         # decoder 1's rewrite
+              (1, 8, 336, 384, 768, T3X3, 1, 1, 1),                         # decoder 0's rewrite (+ GELU)
+              (2, 1, 1344, 384, 768, [(0, -1), (0, 0), (0, 1)], 0, 1, 1),   # k3 along time
+              (1, 1, 5375, 96, 24, [(0, -2), (0, 0), (0, 2)], 0, 0, 1),     # dilated k3, ragged line
+              (1, 5, 336, 96, 192, [(-1, 0), (0, 0)], 1, 0, 1),             # the two taps of a transposed convolution
+              (1, 1, 85995, 48, 96, [(0, -1), (0, 0), (0, 1)], 0, 1, 1)]    # the longest line of the time branch
+
+
+@pytest.mark.parametrize("case", range(len(RING_CASES)))
+def test_ring_kernel_convolutions_in_isolation(case):
+    """The TMA-fed ring kernel alone (dmx_debug_conv): bf16 channels-last image in through tensor-map boxes (zero fill =
+    padding, taps sharing a box through row-shifted descriptors, all three swizzle widths), bias / GELU / GLU, tensor-map
+    store out -- against the same convolution in float64 numpy on bf16-rounded operands (src/conv.hpp:97-204 is the
+    reference's im2col form of it).  Exact operand layouts and descriptors give <= 2e-4 of the tensor's maximum."""
+    from scipy.special import erf
+    B, U, V, C, N, taps, act, glu, share = RING_CASES[case]
+    rng = np.random.default_rng(100 + case)
+    img = rng.standard_normal((B, U, V, C)).astype(np.float32)
+    W = (rng.standard_normal((N, len(taps) * C)) / np.sqrt(len(taps) * C)).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    out = api.debug_conv(img, W, taps, bias, act, glu, share)
+    a = bf16_round(img).astype(np.float64)
+    w = bf16_round(W).astype(np.float64).reshape(N, len(taps), C)
+    ref = np.zeros((B, U, V, N))
+    for j, (du, dv) in enumerate(taps):
+        sh = np.zeros_like(a)
+        u0, u1, v0, v1 = max(0, -du), min(U, U - du), max(0, -dv), min(V, V - dv)
+        if u1 > u0 and v1 > v0:
+            sh[:, u0:u1, v0:v1] = a[:, u0 + du:u1 + du, v0 + dv:v1 + dv]
+        ref += sh @ w[:, j, :].T
+    ref += bias
+    if act:
+        ref = 0.5 * ref * (1.0 + erf(ref / np.sqrt(2.0)))
+    if glu:
+        ref = ref[..., :N // 2] / (1.0 + np.exp(-ref[..., N // 2:]))
+    assert out.shape == ref.shape and np.isfinite(out).all()
+    assert util.max_rel_err(out, ref) <= 2e-4
