@@ -97,7 +97,12 @@ struct LoadTimer
         return t;
     }
     std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
-    ~LoadTimer() { total() += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+    ~LoadTimer()
+    {
+        static std::mutex mu; // replicas may be loaded from several host threads at once
+        std::lock_guard<std::mutex> lk(mu);
+        total() += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
 };
 
 static inline uint16_t f32_to_bf16_bits(float f)
