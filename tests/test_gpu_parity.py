@@ -125,9 +125,17 @@ def test_forward_matches_oracle_full_batched(arch, stress):
         ot = {}
         with torch.no_grad():
             ref = fwd(W, torch.from_numpy(segs[b]), ot).numpy()
+        worst = (1e9, "")
         for n in names:
-            err = util.max_rel_err(taps[n][b], util.oracle_tap_to_cfirst(n, ot[n].numpy()))
+            o = util.oracle_tap_to_cfirst(n, ot[n].numpy())
+            err = util.max_rel_err(taps[n][b], o)
             assert err <= TOL_FP32, "b=%d %s max rel err %.3e" % (b, n, err)
+            # the tensor-normalised maximum above is the per-layer metric of BASELINE.md 4; the energy ratio over ALL elements
+            # is the stricter reading: every stage, not only the stems, must clear the 80 dB bar
+            snr = util.snr_db(taps[n][b], o)
+            worst = min(worst, (snr, n))
+            assert snr >= SNR_FP32, "b=%d %s SNR %.1f dB" % (b, n, snr)
+        print("%s b=%d: lowest stage SNR %.1f dB (%s)" % (arch, b, worst[0], worst[1]))
         assert util.snr_db(out[b], ref) >= SNR_FP32
         assert util.max_rel_err(out[b], ref) <= TOL_FP32
 
